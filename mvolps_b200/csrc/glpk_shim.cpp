@@ -1,0 +1,443 @@
+// glpk_shim.cpp -- the 34-function GLPK subset MVOLPS links against
+// (SURVEY.md section 8b), implemented over the engine C ABI
+// (include/mvolps_engine.h).  Host-only C++; every LP solve and tableau-row
+// query is forwarded to the engine (CUDA in the product library).
+//
+// Semantics follow the public GLPK API manual; the call sites served are
+// cited in include/glpk.h.
+#include "lp_model.hpp"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+static int g_term_out = GLP_ON;
+
+static void shim_abort(const char *what) {
+  std::fprintf(stderr, "glpk-shim: %s\n", what);
+  std::abort();
+}
+
+double mv_eff_lb(int type, double lb) {
+  return (type == GLP_LO || type == GLP_DB || type == GLP_FX) ? lb : -HUGE_VAL;
+}
+double mv_eff_ub(int type, double ub) {
+  return (type == GLP_UP || type == GLP_DB || type == GLP_FX) ? ub : HUGE_VAL;
+}
+double mv_snap(double x) {
+  double r = std::rint(x);
+  return std::fabs(x - r) <= MV_SNAP_TOL ? r : x;
+}
+
+static void drop_engine(glp_prob *P) {
+  if (P->eng) mvb_lp_free(P->eng);
+  P->eng = nullptr;
+  P->eng_rows = 0;
+  P->eng_stale = true;
+  P->eng_lb.clear();
+  P->eng_ub.clear();
+  P->head.clear();
+  P->nb.clear();
+  P->at.clear();
+}
+
+static MvRow &row_at(glp_prob *P, int i, const char *fn) {
+  if (i < 1 || i > (int)P->rows.size()) shim_abort(fn);
+  return P->rows[i - 1];
+}
+static MvCol &col_at(glp_prob *P, int j, const char *fn) {
+  if (j < 1 || j > (int)P->cols.size()) shim_abort(fn);
+  return P->cols[j - 1];
+}
+
+extern "C" {
+
+glp_prob *glp_create_prob(void) { return new glp_prob(); }
+
+void glp_erase_prob(glp_prob *P) {
+  drop_engine(P);
+  mvb_lp *none = nullptr;
+  (void)none;
+  glp_prob fresh;
+  P->dir = fresh.dir;
+  P->c0 = 0.0;
+  P->rows.clear();
+  P->cols.clear();
+  P->status = GLP_UNDEF;
+  P->obj_val = 0.0;
+  P->it_cnt = 0;
+  P->name.clear();
+  P->last = mvb_result{};
+}
+
+void glp_delete_prob(glp_prob *P) {
+  if (!P) return;
+  drop_engine(P);
+  delete P;
+}
+
+void glp_copy_prob(glp_prob *dest, glp_prob *src, int names) {
+  if (dest == src) shim_abort("glp_copy_prob: copying problem object to itself");
+  glp_erase_prob(dest);
+  dest->dir = src->dir;
+  dest->c0 = src->c0;
+  dest->rows = src->rows;
+  dest->cols = src->cols;
+  dest->status = src->status;
+  dest->obj_val = src->obj_val;
+  dest->it_cnt = src->it_cnt;
+  if (names) dest->name = src->name;
+  else {
+    for (auto &r : dest->rows) r.name.clear();
+    for (auto &c : dest->cols) c.name.clear();
+  }
+  if (src->eng && !src->eng_stale) {
+    dest->eng = mvb_lp_clone(src->eng);
+    if (!dest->eng) shim_abort(mvb_last_error());
+    dest->eng_rows = src->eng_rows;
+    dest->eng_stale = false;
+    dest->eng_lb = src->eng_lb;
+    dest->eng_ub = src->eng_ub;
+    dest->head = src->head;
+    dest->nb = src->nb;
+    dest->at = src->at;
+    dest->last = src->last;
+  }
+}
+
+int glp_read_lp(glp_prob *P, const void *parm, const char *fname) {
+  (void)parm;
+  glp_erase_prob(P);
+  std::string err;
+  int rc = mv_read_lp(P, fname, err);
+  if (rc) {
+    std::fprintf(stderr, "glp_read_lp: %s: %s\n", fname, err.c_str());
+    glp_erase_prob(P);
+  }
+  return rc;
+}
+
+int glp_read_mps(glp_prob *P, int fmt, const void *parm, const char *fname) {
+  (void)parm;
+  (void)fmt;
+  glp_erase_prob(P);
+  std::string err;
+  int rc = mv_read_mps(P, fname, err);
+  if (rc) {
+    std::fprintf(stderr, "glp_read_mps: %s: %s\n", fname, err.c_str());
+    glp_erase_prob(P);
+  }
+  return rc;
+}
+
+const char *glp_version(void) {
+  static char buf[64];
+  std::snprintf(buf, sizeof buf, "%d.%d (mvolps-b200 %s)", GLP_MAJOR_VERSION,
+                GLP_MINOR_VERSION, mvb_backend());
+  return buf;
+}
+
+int glp_term_out(int flag) {
+  int old = g_term_out;
+  if (flag != GLP_ON && flag != GLP_OFF) shim_abort("glp_term_out: bad flag");
+  g_term_out = flag;
+  return old;
+}
+
+int glp_get_num_rows(glp_prob *P) { return (int)P->rows.size(); }
+int glp_get_num_cols(glp_prob *P) { return (int)P->cols.size(); }
+int glp_get_num_int(glp_prob *P) {
+  int c = 0;
+  for (auto &col : P->cols) c += col.kind == GLP_IV;
+  return c;
+}
+
+int glp_get_obj_dir(glp_prob *P) { return P->dir; }
+void glp_set_obj_dir(glp_prob *P, int dir) {
+  if (dir != GLP_MIN && dir != GLP_MAX) shim_abort("glp_set_obj_dir: bad dir");
+  if (P->dir != dir) P->eng_stale = true;
+  P->dir = dir;
+}
+double glp_get_obj_coef(glp_prob *P, int j) {
+  if (j == 0) return P->c0;
+  return col_at(P, j, "glp_get_obj_coef: column out of range").coef;
+}
+void glp_set_obj_coef(glp_prob *P, int j, double coef) {
+  if (j == 0) { P->c0 = coef; return; }
+  MvCol &c = col_at(P, j, "glp_set_obj_coef: column out of range");
+  if (c.coef != coef) P->eng_stale = true;
+  c.coef = coef;
+}
+double glp_get_obj_val(glp_prob *P) { return P->obj_val; }
+
+int glp_add_rows(glp_prob *P, int nrs) {
+  if (nrs < 1) shim_abort("glp_add_rows: invalid number of rows");
+  int first = (int)P->rows.size() + 1;
+  P->rows.resize(P->rows.size() + nrs);
+  return first;
+}
+
+int glp_add_cols(glp_prob *P, int ncs) {
+  if (ncs < 1) shim_abort("glp_add_cols: invalid number of columns");
+  int first = (int)P->cols.size() + 1;
+  P->cols.resize(P->cols.size() + ncs);
+  P->eng_stale = true;
+  return first;
+}
+
+int glp_get_row_type(glp_prob *P, int i) { return row_at(P, i, "glp_get_row_type").type; }
+double glp_get_row_lb(glp_prob *P, int i) {
+  MvRow &r = row_at(P, i, "glp_get_row_lb");
+  return (r.type == GLP_FR || r.type == GLP_UP) ? -DBL_MAX : r.lb;
+}
+double glp_get_row_ub(glp_prob *P, int i) {
+  MvRow &r = row_at(P, i, "glp_get_row_ub");
+  return (r.type == GLP_FR || r.type == GLP_LO) ? +DBL_MAX : r.ub;
+}
+
+static void store_bnds(int type, double lb, double ub, int &t, double &l,
+                       double &u, int &stat) {
+  switch (type) {
+    case GLP_FR: l = u = 0.0; if (stat != GLP_BS) stat = GLP_NF; break;
+    case GLP_LO: l = lb; u = 0.0; if (stat != GLP_BS) stat = GLP_NL; break;
+    case GLP_UP: l = 0.0; u = ub; if (stat != GLP_BS) stat = GLP_NU; break;
+    case GLP_DB:
+      l = lb; u = ub;
+      if (!(stat == GLP_BS || stat == GLP_NL || stat == GLP_NU))
+        stat = std::fabs(lb) <= std::fabs(ub) ? GLP_NL : GLP_NU;
+      break;
+    case GLP_FX: l = u = lb; if (stat != GLP_BS) stat = GLP_NS; break;
+    default: shim_abort("set bounds: invalid type");
+  }
+  t = type;
+}
+
+void glp_set_row_bnds(glp_prob *P, int i, int type, double lb, double ub) {
+  MvRow &r = row_at(P, i, "glp_set_row_bnds: row out of range");
+  store_bnds(type, lb, ub, r.type, r.lb, r.ub, r.stat);
+}
+
+int glp_get_mat_row(glp_prob *P, int i, int ind[], double val[]) {
+  MvRow &r = row_at(P, i, "glp_get_mat_row: row out of range");
+  int len = (int)r.ind.size();
+  for (int t = 0; t < len; t++) {
+    if (ind) ind[t + 1] = r.ind[t];
+    if (val) val[t + 1] = r.val[t];
+  }
+  return len;
+}
+
+void glp_set_mat_row(glp_prob *P, int i, int len, const int ind[],
+                     const double val[]) {
+  MvRow &r = row_at(P, i, "glp_set_mat_row: row out of range");
+  int n = (int)P->cols.size();
+  if (len < 0 || len > n) shim_abort("glp_set_mat_row: invalid row length");
+  std::vector<std::pair<int, double>> e;
+  e.reserve(len);
+  for (int t = 1; t <= len; t++) {
+    if (ind[t] < 1 || ind[t] > n) shim_abort("glp_set_mat_row: column index out of range");
+    if (val[t] != 0.0) e.emplace_back(ind[t], val[t]);
+  }
+  std::sort(e.begin(), e.end(), [](auto &a, auto &b) { return a.first < b.first; });
+  for (size_t t = 1; t < e.size(); t++)
+    if (e[t].first == e[t - 1].first) shim_abort("glp_set_mat_row: duplicate column indices");
+  r.ind.clear();
+  r.val.clear();
+  for (auto &p : e) { r.ind.push_back(p.first); r.val.push_back(p.second); }
+  if (i <= P->eng_rows) P->eng_stale = true;  // a row the tableau already holds
+}
+
+int glp_get_row_stat(glp_prob *P, int i) { return row_at(P, i, "glp_get_row_stat").stat; }
+double glp_get_row_prim(glp_prob *P, int i) { return row_at(P, i, "glp_get_row_prim").prim; }
+
+int glp_get_col_type(glp_prob *P, int j) { return col_at(P, j, "glp_get_col_type").type; }
+double glp_get_col_lb(glp_prob *P, int j) {
+  MvCol &c = col_at(P, j, "glp_get_col_lb");
+  return (c.type == GLP_FR || c.type == GLP_UP) ? -DBL_MAX : c.lb;
+}
+double glp_get_col_ub(glp_prob *P, int j) {
+  MvCol &c = col_at(P, j, "glp_get_col_ub");
+  return (c.type == GLP_FR || c.type == GLP_LO) ? +DBL_MAX : c.ub;
+}
+void glp_set_col_bnds(glp_prob *P, int j, int type, double lb, double ub) {
+  MvCol &c = col_at(P, j, "glp_set_col_bnds: column out of range");
+  store_bnds(type, lb, ub, c.type, c.lb, c.ub, c.stat);
+}
+int glp_get_col_kind(glp_prob *P, int j) {
+  MvCol &c = col_at(P, j, "glp_get_col_kind");
+  if (c.kind == GLP_IV && c.type == GLP_DB && c.lb == 0.0 && c.ub == 1.0) return GLP_BV;
+  return c.kind;
+}
+void glp_set_col_kind(glp_prob *P, int j, int kind) {
+  MvCol &c = col_at(P, j, "glp_set_col_kind");
+  if (kind == GLP_BV) {
+    c.kind = GLP_IV;
+    store_bnds(GLP_DB, 0.0, 1.0, c.type, c.lb, c.ub, c.stat);
+  } else if (kind == GLP_CV || kind == GLP_IV) {
+    c.kind = kind;
+  } else shim_abort("glp_set_col_kind: invalid kind");
+}
+double glp_get_col_prim(glp_prob *P, int j) { return col_at(P, j, "glp_get_col_prim").prim; }
+int glp_get_col_stat(glp_prob *P, int j) { return col_at(P, j, "glp_get_col_stat").stat; }
+int glp_get_status(glp_prob *P) { return P->status; }
+int glp_get_it_cnt(glp_prob *P) { return P->it_cnt; }
+
+}  // extern "C"
+
+/* bring the engine's LP in line with the problem object: cold build when the
+ * matrix/objective changed, otherwise append the new rows (cut.cpp:23-43) and
+ * forward changed bounds (bs.cpp:274,282) */
+static int sync_engine(glp_prob *P) {
+  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  if (P->eng && !P->eng_stale && P->eng_rows > m) P->eng_stale = true;
+  std::vector<double> lb(n + m), ub(n + m);
+  for (int j = 0; j < n; j++) {
+    lb[j] = mv_eff_lb(P->cols[j].type, P->cols[j].lb);
+    ub[j] = mv_eff_ub(P->cols[j].type, P->cols[j].ub);
+  }
+  for (int i = 0; i < m; i++) {
+    lb[n + i] = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
+    ub[n + i] = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
+  }
+  if (!P->eng || P->eng_stale) {
+    if (P->eng) mvb_lp_free(P->eng);
+    P->eng = mvb_lp_create(m, n, m + 32 + m / 8);
+    if (!P->eng) return -1;
+    std::vector<double> A((size_t)m * n, 0.0), cost(n);
+    for (int i = 0; i < m; i++)
+      for (size_t t = 0; t < P->rows[i].ind.size(); t++)
+        A[(size_t)i * n + P->rows[i].ind[t] - 1] = P->rows[i].val[t];
+    for (int j = 0; j < n; j++)
+      cost[j] = P->dir == GLP_MAX ? -P->cols[j].coef : P->cols[j].coef;
+    if (mvb_lp_load(P->eng, A.data(), cost.data(), lb.data(), ub.data())) return -1;
+    P->eng_rows = m;
+    P->eng_stale = false;
+    P->eng_lb = lb;
+    P->eng_ub = ub;
+    return 0;
+  }
+  std::vector<double> a(n);
+  for (int i = P->eng_rows; i < m; i++) {
+    std::fill(a.begin(), a.end(), 0.0);
+    for (size_t t = 0; t < P->rows[i].ind.size(); t++)
+      a[P->rows[i].ind[t] - 1] = P->rows[i].val[t];
+    if (mvb_lp_append_row(P->eng, a.data(), lb[n + i], ub[n + i])) return -1;
+    P->eng_lb.push_back(lb[n + i]);
+    P->eng_ub.push_back(ub[n + i]);
+  }
+  P->eng_rows = m;
+  for (int k = 0; k < n + m; k++) {
+    if (lb[k] != P->eng_lb[k] || ub[k] != P->eng_ub[k]) {
+      if (mvb_lp_set_bounds(P->eng, k, lb[k], ub[k])) return -1;
+      P->eng_lb[k] = lb[k];
+      P->eng_ub[k] = ub[k];
+    }
+  }
+  return 0;
+}
+
+static int stat_of(int at) {
+  switch (at) {
+    case MVB_AT_LB: return GLP_NL;
+    case MVB_AT_UB: return GLP_NU;
+    case MVB_AT_FR: return GLP_NF;
+    default: return GLP_NS;
+  }
+}
+
+/* copy status, primal values and basis back from the engine */
+int mv_pull_solution(glp_prob *P, const mvb_result &res) {
+  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  std::vector<double> x(n + m);
+  P->head.resize(m);
+  P->nb.resize(n);
+  P->at.resize(n);
+  if (mvb_lp_get_primal(P->eng, x.data())) return -1;
+  if (mvb_lp_get_basis(P->eng, P->head.data(), P->nb.data(), P->at.data())) return -1;
+  for (int i = 0; i < m; i++) {
+    int k = P->head[i];
+    if (k < n) P->cols[k].stat = GLP_BS; else P->rows[k - n].stat = GLP_BS;
+  }
+  for (int j = 0; j < n; j++) {
+    int k = P->nb[j], st = stat_of(P->at[j]);
+    if (k < n) P->cols[k].stat = st; else P->rows[k - n].stat = st;
+  }
+  double z = P->c0;
+  for (int j = 0; j < n; j++) {
+    P->cols[j].prim = mv_snap(x[j]);
+    z = std::fma(P->cols[j].coef, P->cols[j].prim, z);
+  }
+  for (int i = 0; i < m; i++) P->rows[i].prim = mv_snap(x[n + i]);
+  P->obj_val = z;
+  P->it_cnt = res.iters;
+  P->last = res;
+  switch (res.status) {
+    case MVB_OPT: P->status = GLP_OPT; break;
+    case MVB_NOFEAS: P->status = GLP_NOFEAS; break;
+    case MVB_UNBND: P->status = GLP_UNBND; break;
+    default: P->status = res.primal_feasible ? GLP_FEAS : GLP_INFEAS; break;
+  }
+  return 0;
+}
+
+int mv_sync_engine(glp_prob *P) { return sync_engine(P); }
+
+extern "C" {
+
+int glp_simplex(glp_prob *P, const glp_smcp *parm) {
+  (void)parm;
+  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  if (m == 0 || n == 0) {
+    /* GLPK reports "problem has no rows/columns"; MVOLPS never gets here */
+    P->status = GLP_UNDEF;
+    return GLP_EFAIL;
+  }
+  if (sync_engine(P)) {
+    std::fprintf(stderr, "glp_simplex: engine error: %s\n", mvb_last_error());
+    return GLP_EFAIL;
+  }
+  mvb_result res;
+  mvb_opts opts{};
+  if (mvb_solve_batch(&P->eng, 1, &opts, &res)) {
+    std::fprintf(stderr, "glp_simplex: engine error: %s\n", mvb_last_error());
+    return GLP_EFAIL;
+  }
+  if (mv_pull_solution(P, res)) return GLP_EFAIL;
+  if (g_term_out == GLP_ON)
+    std::printf("mvolps-b200[%s]: %d rows, %d cols: status %d, %d iterations "
+                "(%d pivots, %d flips), obj = %.12g\n",
+                mvb_backend(), m, n, res.status, res.iters, res.pivots,
+                res.flips, P->obj_val);
+  return res.status == MVB_ITLIM ? GLP_EITLIM : 0;
+}
+
+int glp_eval_tab_row(glp_prob *P, int k, int ind[], double val[]) {
+  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  if (!P->eng || P->eng_stale || P->eng_rows != m || (int)P->head.size() != m)
+    shim_abort("glp_eval_tab_row: basis factorization does not exist");
+  if (k < 1 || k > m + n) shim_abort("glp_eval_tab_row: variable number out of range");
+  int id = k <= m ? n + (k - 1) : k - m - 1;
+  int row = -1;
+  for (int i = 0; i < m; i++)
+    if (P->head[i] == id) { row = i + 1; break; }
+  if (row < 0) shim_abort("glp_eval_tab_row: variable must be basic");
+  std::vector<double> t(n);
+  if (mvb_lp_get_tab_rows(P->eng, &row, 1, t.data())) shim_abort(mvb_last_error());
+  std::vector<std::pair<int, double>> e;
+  for (int p = 0; p < n; p++) {
+    if (t[p] == 0.0) continue;
+    int v = P->nb[p];
+    e.emplace_back(v < n ? m + v + 1 : v - n + 1, t[p]);
+  }
+  std::sort(e.begin(), e.end(), [](auto &a, auto &b) { return a.first < b.first; });
+  for (size_t s = 0; s < e.size(); s++) {
+    ind[s + 1] = e[s].first;
+    val[s + 1] = e[s].second;
+  }
+  return (int)e.size();
+}
+
+}  // extern "C"

@@ -1,0 +1,70 @@
+// lp_model.hpp -- host-side problem object behind the glpk-subset C ABI.
+//
+// The reference keeps one glp_prob per open B&B node (util.cpp:25-42) and
+// mutates it through the GLPK API; this struct is what those calls act on.
+// The dense simplex tableau itself lives in the engine (mvb_lp, on the GPU in
+// the product build); this object owns the sparse rows, typed bounds, kinds,
+// basis statuses and the last solution, and remembers what the engine has
+// already seen so that a re-solve ships only bound deltas and new cut rows.
+#pragma once
+
+#include <string>
+#include <vector>
+
+#include "../../include/glpk.h"
+#include "../../include/mvolps_engine.h"
+
+struct MvRow {
+  int type = GLP_FR;
+  double lb = 0.0, ub = 0.0;
+  std::vector<int> ind;     // 1-based column numbers, ascending
+  std::vector<double> val;
+  int stat = GLP_BS;
+  double prim = 0.0;
+  std::string name;
+};
+
+struct MvCol {
+  int type = GLP_FX;
+  double lb = 0.0, ub = 0.0;
+  int kind = GLP_CV;
+  double coef = 0.0;
+  int stat = GLP_NS;
+  double prim = 0.0;
+  std::string name;
+};
+
+struct glp_prob {
+  int dir = GLP_MIN;
+  double c0 = 0.0;
+  std::vector<MvRow> rows;  // rows[i-1]
+  std::vector<MvCol> cols;  // cols[j-1]
+  int status = GLP_UNDEF;
+  double obj_val = 0.0;
+  int it_cnt = 0;
+  std::string name;
+
+  // ---- engine mirror ----
+  mvb_lp *eng = nullptr;
+  int eng_rows = 0;            // rows the engine tableau already contains
+  bool eng_stale = true;       // matrix/objective changed: rebuild from scratch
+  std::vector<double> eng_lb, eng_ub;  // bounds last sent, by engine id
+  std::vector<int> head, nb, at;       // basis after the last solve
+  mvb_result last{};
+};
+
+// bound of a typed variable as the engine sees it (+-HUGE_VAL when absent)
+double mv_eff_lb(int type, double lb);
+double mv_eff_ub(int type, double ub);
+
+// LP-format / MPS readers (lp_reader.cpp). 0 = ok, non-zero = error
+int mv_read_lp(glp_prob *P, const char *fname, std::string &err);
+int mv_read_mps(glp_prob *P, const char *fname, std::string &err);
+
+// values closer than this to an integer are reported as that integer
+constexpr double MV_SNAP_TOL = 1e-9;
+double mv_snap(double x);
+
+// glpk_shim.cpp helpers shared with the batched B&B driver
+int mv_sync_engine(glp_prob *P);                            // push deltas to the engine
+int mv_pull_solution(glp_prob *P, const mvb_result &res);   // read result back
