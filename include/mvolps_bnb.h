@@ -1,0 +1,72 @@
+/* mvolps_bnb.h -- batched branch-and-bound driver, C ABI.
+ *
+ * Restates the reference driver `int branchAndBound(glp_prob*, ParameterObj&)`
+ * (bs.h:7, bs.cpp:54-348) with identical node order, object ids, prune tags,
+ * incumbent updates and printed tree, but solves the node LPs in device
+ * batches: with FIFO node selection the first W open nodes are all going to
+ * be popped and solved whatever the others return (bs.cpp:117 precedes the
+ * bound test at bs.cpp:210), so they are solved as one engine launch and then
+ * consumed on the host in FIFO order; the children created while consuming a
+ * batch (bs.cpp:269-288) are solved as a second launch.
+ */
+#ifndef MVOLPS_BNB_H
+#define MVOLPS_BNB_H
+
+#include "glpk.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* strategies: values follow util.h:30-33 and the CLI flags (2test.cpp:25-37) */
+#define MVB_NODE_FIFO 0 /* "-bs 0": front of the deque (util.cpp:157-167) */
+#define MVB_NODE_BEST 1 /* "-bs 1": first maximum of upperBound (util.cpp:170-187) */
+#define MVB_VAR_VO 0    /* "-vs 0": first violated (util.cpp:192-195) */
+#define MVB_VAR_VFP 1   /* "-vs 1": as the reference: evaluated on the unsolved root object */
+#define MVB_VAR_VGO 2   /* "-vs 2": largest positive objective coefficient */
+#define MVB_CUT_NONE 0  /* "-cm 0" */
+#define MVB_CUT_REF 1   /* "-cm 1": literal restatement of gmi.cpp:11-117 + cut.cpp:11-46 */
+#define MVB_CUT_GMI 2   /* textbook Gomory mixed-integer cut from the tableau row */
+
+typedef struct mvb_bnb_params {
+  int node_strategy;
+  int var_strategy;
+  int cut_mode;
+  int batch_width; /* FIFO nodes solved per launch; <=0: 256 */
+  int max_iters;   /* node budget: stop after this many loop iterations; <=0: none
+                      (the reference's own limit, bs.cpp:320, always applies) */
+  int quiet;       /* !=0: do not print the tree / solution to stdout */
+} mvb_bnb_params;
+
+typedef struct mvb_bnb_stats {
+  int iterations;        /* `count` of bs.cpp:94 */
+  int oids;              /* object ids handed out */
+  int lp_solves;         /* glp_simplex-equivalent solves (3 per branched node) */
+  int launches;          /* engine batch launches */
+  long long simplex_iters;
+  int has_incumbent;
+  int incumbent_oid;
+  double incumbent;      /* bestLower */
+  int hit_limit;         /* stopped by max_iters or the reference's 200000 cap */
+  unsigned long long event_hash; /* FNV-1a over (event, oid, pid, prune tag) */
+} mvb_bnb_stats;
+
+typedef struct mvb_bnb mvb_bnb;
+
+/* run B&B on prob (not modified, like the reference, which works on copies) */
+mvb_bnb *mvb_bnb_run(glp_prob *prob, const mvb_bnb_params *params);
+void mvb_bnb_free(mvb_bnb *h);
+const mvb_bnb_stats *mvb_bnb_get_stats(const mvb_bnb *h);
+/* tree exactly as PrettyPrintTree prints it (tree_print.h:12-22, bs.cpp:331-341) */
+const char *mvb_bnb_tree_text(const mvb_bnb *h);
+/* the "[oid] Solution is: ..." string of bs.cpp:179-190 ("" when none) */
+const char *mvb_bnb_solution_text(const mvb_bnb *h);
+/* one line per event, GrUMPy-like: "type oid pid dir [fields]" (message.h:141-226) */
+const char *mvb_bnb_event_text(const mvb_bnb *h);
+/* incumbent x[1..n] (x[0] unused); returns n or 0 when there is no incumbent */
+int mvb_bnb_get_incumbent(const mvb_bnb *h, double *x, int cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

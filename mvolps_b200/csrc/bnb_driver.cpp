@@ -1,0 +1,532 @@
+// bnb_driver.cpp -- batched branch-and-bound over the engine C ABI.
+//
+// Restates bs.cpp:54-348 (loop), util.cpp:154-230 (node / variable choice),
+// util.cpp:414-473 (status + violated list), util.cpp:11-23 (getFract),
+// gmi.cpp:11-117 and cut.cpp:6-46 (cuts), util.cpp:25-42 (object ids).  The
+// node order, ids, prune tags and incumbent updates are those of the serial
+// reference; only the LP solves are grouped into engine launches (see
+// include/mvolps_bnb.h).  Host-only C++; no LP arithmetic happens here.
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <deque>
+#include <limits>
+#include <map>
+#include <memory>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#include "../../include/mvolps_bnb.h"
+#include "../../include/mvolps_spec.h"
+#include "lp_model.hpp"
+
+namespace {
+
+template <typename... Args>
+std::string sstr(Args &&...args) {  // same formatting as util.h:124-128
+  std::ostringstream s;
+  (s << std::dec << ... << args);
+  return s.str();
+}
+
+double get_fract(double x) {  // util.cpp:11-23
+  double ip;
+  double f = std::modf(x, &ip);
+  if (f < 0.0) f += 1;
+  return f;
+}
+
+enum Prune { P_INTG, P_FEAS, P_BNDS, P_NONE };  // util.h:27
+
+struct Node {  // NodeData, util.h:35-54
+  glp_prob *prob = nullptr;
+  double upperBound = std::numeric_limits<double>::infinity();
+  bool initial = false;
+  int oid = 0;
+  ~Node() { if (prob) glp_delete_prob(prob); }
+};
+
+struct TreeRec {
+  int oid, pid, depth;
+  Prune prune = P_NONE;
+  std::vector<int> kids;
+};
+
+struct Cut {  // CutContainer, cut.h:7-13
+  std::vector<int> inds;
+  std::vector<double> vals;
+  double lb = 0.0;
+};
+
+}  // namespace
+
+struct mvb_bnb {
+  mvb_bnb_stats st{};
+  std::string tree, solution, events;
+  std::vector<double> incumbent;  // 1-based
+};
+
+namespace {
+
+struct Driver {
+  const mvb_bnb_params &pr;
+  glp_prob *root_prob;
+  mvb_bnb *out;
+  int next_id = 1;
+  std::map<int, TreeRec> tree;
+  std::vector<Cut> pool;
+  // gmi.cpp never sets CutContainer::oid on success and bs.cpp:252 tests it
+  // (`result.oid != -1`): the test reads whatever the caller's stack slot last
+  // held.  As compiled by g++ -O2 that slot is stable across loop iterations,
+  // so once any column was rejected (oid = -1, gmi.cpp:20,25) every later cut
+  // is dropped.  MVB_CUT_REF models exactly that; MVB_CUT_GMI pools every cut.
+  int ref_oid_slot = 0;
+  std::ostringstream ev;
+  unsigned long long ehash = MVB_FNV_OFFSET;
+
+  Driver(const mvb_bnb_params &p, glp_prob *r, mvb_bnb *o) : pr(p), root_prob(r), out(o) {}
+
+  void hash_mix(unsigned long long v) { ehash = (ehash ^ v) * MVB_FNV_PRIME; }
+
+  static const char *dir_of(int oid) {  // bs.cpp:43-52
+    if (oid <= 1) return "M";
+    return oid % 2 == 0 ? "R" : "L";
+  }
+  int pid_of(int oid) { return oid == 1 ? 0 : tree[oid].pid; }  // bs.cpp:27-34
+
+  template <typename... F>
+  void event(const char *type, int oid, F &&...fields) {
+    ev << type << " " << oid << " " << pid_of(oid) << " " << dir_of(oid);
+    ((ev << " " << fields), ...);
+    ev << "\n";
+    for (const char *c = type; *c; c++) hash_mix((unsigned char)*c);
+    hash_mix((unsigned)oid);
+    hash_mix((unsigned)pid_of(oid));
+  }
+
+  std::unique_ptr<Node> make_node(glp_prob *take) {  // NodeData ctor, util.cpp:25-37
+    auto n = std::make_unique<Node>();
+    n->oid = next_id++;
+    n->prob = take;
+    return n;
+  }
+
+  bool solve_many(const std::vector<glp_prob *> &ps) {
+    if (ps.empty()) return true;
+    std::vector<mvb_lp *> engs;
+    for (auto *p : ps) {
+      if (mv_sync_engine(p)) return false;
+      engs.push_back(p->eng);
+    }
+    std::vector<mvb_result> res(ps.size());
+    mvb_opts o{};
+    if (mvb_solve_batch(engs.data(), (int)engs.size(), &o, res.data())) return false;
+    for (size_t k = 0; k < ps.size(); k++) {
+      if (mv_pull_solution(ps[k], res[k])) return false;
+      out->st.simplex_iters += res[k].iters;
+    }
+    out->st.launches++;
+    out->st.lp_solves += (int)ps.size();
+    return true;
+  }
+
+  // printInfo, util.cpp:414-473: -1 infeasible, 1 integral, 0 otherwise
+  int classify(glp_prob *a, std::vector<int> &violated) {
+    violated.clear();
+    int status = glp_get_status(a);
+    if (status == GLP_NOFEAS || status == GLP_INFEAS || status == GLP_UNBND) return -1;
+    int cols = glp_get_num_cols(a);
+    for (int i = 1; i <= cols; i++) {
+      double x = glp_get_col_prim(a, i);
+      if (x != 0 && glp_get_obj_coef(a, i) != 0)
+        if (std::trunc(x) != x && glp_get_col_kind(a, i) != GLP_CV) violated.push_back(i);
+    }
+    return violated.empty() ? 1 : 0;
+  }
+
+  int pick_var(glp_prob *a, const std::vector<int> &vars) {  // util.cpp:190-230
+    (void)a;
+    if (pr.var_strategy == MVB_VAR_VFP) {
+      // evaluated on the never-solved root object, as the reference does
+      double best = std::abs(get_fract(glp_get_col_prim(root_prob, vars.front())) - 0.5);
+      int index = vars.front();
+      for (int i : vars) {
+        double cur = std::abs(get_fract(glp_get_col_prim(root_prob, i)) - 0.5);
+        if (cur < best) { best = cur; index = i; }
+      }
+      return index;
+    }
+    if (pr.var_strategy == MVB_VAR_VGO) {
+      double bestCoef = 0.0;
+      int index = vars.front();  // the reference leaves this uninitialised
+      for (int i : vars) {
+        double cur = glp_get_obj_coef(root_prob, i);
+        if (cur > bestCoef) { bestCoef = cur; index = i; }
+      }
+      return index;
+    }
+    return vars.front();
+  }
+
+  size_t pick_node(const std::deque<std::unique_ptr<Node>> &q) {  // util.cpp:154-188
+    if (pr.node_strategy == MVB_NODE_BEST) {
+      size_t best = 0;
+      for (size_t k = 1; k < q.size(); k++)
+        if (q[best]->upperBound < q[k]->upperBound) best = k;
+      return best;
+    }
+    return 0;
+  }
+
+  void gen_cuts(glp_prob *a);
+  void gen_cut_ref(glp_prob *a, int j, const double *trow);
+  void gen_cut_gmi(glp_prob *a, int j, const double *trow);
+  int add_cut_constraint(glp_prob *a);
+
+  void print_tree(int oid, std::ostringstream &os) {  // tree_print.h:12-22
+    TreeRec &t = tree[oid];
+    for (int i = 0; i < t.depth; i++) os << " ";
+    os << "-" << oid;
+    if (t.prune == P_INTG) os << " I";
+    else if (t.prune == P_FEAS) os << " F";
+    else if (t.prune == P_BNDS) os << " B";
+    os << "\n";
+    for (int k : t.kids) print_tree(k, os);
+  }
+
+  bool run();
+};
+
+}  // namespace
+
+namespace {
+
+// CutPool::addCutConstraint, cut.cpp:11-46: the LAST pooled cut becomes a new
+// GLP_LO row of a (which is not re-solved before its children are cloned)
+int Driver::add_cut_constraint(glp_prob *a) {
+  if (pool.empty()) return -1;
+  const Cut &c = pool.back();
+  int index = glp_add_rows(a, 1);
+  glp_set_mat_row(a, index, (int)c.inds.size() - 1, c.inds.data(), c.vals.data());
+  glp_set_row_bnds(a, index, GLP_LO, c.lb, 0);
+  return (int)pool.size() - 1;
+}
+
+// literal restatement of generateCut3, gmi.cpp:11-117 (see SURVEY.md 3.4 for
+// its quirks; `temp` is zero-initialised here where the reference reads an
+// indeterminate value for GLP_BV columns)
+void Driver::gen_cut_ref(glp_prob *a, int j, const double *trow) {
+  int m = glp_get_num_rows(a), n = glp_get_num_cols(a);
+  std::vector<double> work(m + n + 1, 0.0);
+  // glp_eval_tab_row ordering: ascending variable number, zeros dropped
+  std::vector<std::pair<int, double>> e;
+  for (int p = 0; p < n; p++) {
+    if (trow[p] == 0.0) continue;
+    int v = a->nb[p];
+    e.emplace_back(v < n ? m + v + 1 : v - n + 1, trow[p]);
+  }
+  std::sort(e.begin(), e.end(), [](auto &x, auto &y) { return x.first < y.first; });
+  double rhs = glp_get_col_prim(a, j);
+  double temp = 0.0;
+  for (auto &kv : e) {
+    double val = kv.second;
+    int kind;
+    double ub;
+    if (kv.first <= m) {
+      kind = GLP_CV;
+      ub = glp_get_row_ub(a, kv.first);
+    } else {
+      kind = glp_get_col_kind(a, kv.first - m);
+      ub = glp_get_col_ub(a, kv.first - m);
+    }
+    double fRhs = get_fract(rhs), fVal = get_fract(val);
+    if (kind == GLP_IV) temp = fRhs >= fVal ? fVal : (fRhs / (1.0 - fRhs)) * (1.0 - fVal);
+    if (kind == GLP_CV) temp = val >= 0.0 ? val : (fRhs / (1.0 - fRhs)) * (-1.0 * val);
+    work[kv.first] = -1.0 * temp;
+    rhs -= temp * ub;
+  }
+  for (int i = 1; i <= m; i++) {
+    const MvRow &r = a->rows[i - 1];
+    for (size_t k = 1; k <= r.val.size(); k++)  // indexes by position, as gmi.cpp:86-88
+      work[m + k] += work[i] * r.val[k - 1];
+  }
+  Cut c;
+  c.inds.push_back(0);
+  c.vals.push_back(rhs);
+  for (int i = 1; i <= n; i++) { c.inds.push_back(i); c.vals.push_back(work[m + i]); }
+  c.lb = rhs;
+  pool.push_back(std::move(c));
+}
+
+// textbook Gomory mixed-integer cut of the row of basic integer column j:
+// with non-basics shifted to their active bounds (y >= 0),
+//   x_j + sum a_k y_k = beta,  f0 = frac(beta),
+//   integer y_k   : g = f_k/f0 if f_k <= f0 else (1-f_k)/(1-f0), f_k = frac(a_k)
+//   continuous y_k: g = a_k/f0 if a_k >= 0 else -a_k/(1-f0)
+//   sum g_k y_k >= 1, then y_k substituted back to structurals.
+void Driver::gen_cut_gmi(glp_prob *a, int j, const double *trow) {
+  int n = glp_get_num_cols(a);
+  double beta = glp_get_col_prim(a, j);
+  double f0 = get_fract(beta);
+  if (f0 < 1e-6 || f0 > 1.0 - 1e-6) return;
+  std::vector<double> g(n + 1, 0.0);  // cut over structurals, 1-based
+  double rhs = 1.0;
+  for (int p = 0; p < n; p++) {
+    double alpha = trow[p];
+    if (alpha == 0.0) continue;
+    int v = a->nb[p], at = a->at[p];
+    if (at == MVB_AT_FX) continue;
+    if (at == MVB_AT_FR) return;  // free non-basic in the row: no cut
+    bool is_int = false;
+    double bound;
+    if (v < n) {
+      const MvCol &c = a->cols[v];
+      bound = at == MVB_AT_LB ? c.lb : c.ub;
+      is_int = c.kind == GLP_IV && std::trunc(bound) == bound;
+    } else {
+      const MvRow &r = a->rows[v - n];
+      bound = at == MVB_AT_LB ? r.lb : r.ub;
+    }
+    // x_j = beta + sum alpha*(x_k - v_k): y = x_k - l (at LB) or u - x_k (at UB)
+    double ak = at == MVB_AT_LB ? -alpha : alpha;  // coefficient of y_k on the lhs
+    double gk;
+    if (is_int) {
+      double fk = get_fract(ak);
+      gk = fk <= f0 ? fk / f0 : (1.0 - fk) / (1.0 - f0);
+    } else {
+      gk = ak >= 0.0 ? ak / f0 : -ak / (1.0 - f0);
+    }
+    if (gk == 0.0) continue;
+    // gk*y_k with y_k = s*(x_k - bound), s = +1 at LB, -1 at UB
+    double s = at == MVB_AT_LB ? 1.0 : -1.0;
+    rhs += gk * s * bound;
+    if (v < n) g[v + 1] += gk * s;
+    else {
+      const MvRow &r = a->rows[v - n];
+      for (size_t t = 0; t < r.ind.size(); t++) g[r.ind[t]] += gk * s * r.val[t];
+    }
+  }
+  Cut c;
+  c.inds.push_back(0);
+  c.vals.push_back(rhs);
+  for (int i = 1; i <= n; i++) { c.inds.push_back(i); c.vals.push_back(g[i]); }
+  c.lb = rhs;
+  pool.push_back(std::move(c));
+}
+
+// bs.cpp:249-258: every basic GLP_IV column generates; rows are gathered from
+// the engine tableau in one call so only those rows cross PCIe
+void Driver::gen_cuts(glp_prob *a) {
+  int m = glp_get_num_rows(a), n = glp_get_num_cols(a);
+  std::vector<int> js, rows;
+  for (int j = 1; j <= n; j++) {
+    int kind = glp_get_col_kind(a, j);
+    bool ok = pr.cut_mode == MVB_CUT_REF ? kind == GLP_IV : kind != GLP_CV;
+    if (!ok || glp_get_col_stat(a, j) != GLP_BS) { js.push_back(-j); rows.push_back(0); continue; }
+    for (int i = 0; i < m; i++)
+      if (a->head[i] == j - 1) { js.push_back(j); rows.push_back(i + 1); break; }
+  }
+  if (!js.empty()) {
+    std::vector<double> t((size_t)js.size() * n);
+    if (mvb_lp_get_tab_rows(a->eng, rows.data(), (int)rows.size(), t.data())) return;
+    for (size_t k = 0; k < js.size(); k++) {
+      if (js[k] < 0) { ref_oid_slot = -1; continue; }  // rejected column
+      if (pr.cut_mode == MVB_CUT_GMI) gen_cut_gmi(a, js[k], t.data() + k * n);
+      else if (ref_oid_slot != -1) gen_cut_ref(a, js[k], t.data() + k * n);
+    }
+  }
+  add_cut_constraint(a);
+}
+
+}  // namespace
+
+namespace {
+
+bool Driver::run() {
+  const double inf = std::numeric_limits<double>::infinity();
+  std::deque<std::unique_ptr<Node>> open;  // leafContainer, bs.cpp:79
+  std::vector<std::string> evs;            // event lines (candidates filled late)
+  auto ev_line = [&](const char *type, int oid, const std::string &fields) {
+    evs.push_back(sstr(type, " ", oid, " ", pid_of(oid), " ", dir_of(oid), fields));
+    return evs.size() - 1;
+  };
+
+  {  // S1, bs.cpp:80-87
+    glp_prob *c = glp_create_prob();
+    glp_copy_prob(c, root_prob, GLP_ON);
+    auto s1 = make_node(c);
+    s1->initial = true;
+    tree[s1->oid] = TreeRec{s1->oid, 0, 0, P_NONE, {}};
+    open.push_back(std::move(s1));
+  }
+  double bestLower = -inf;
+  std::string solution;
+  int count = 0;
+  bool stop = false;
+  int width = pr.batch_width > 0 ? pr.batch_width : 256;
+
+  struct Pending {  // children awaiting their LP solve (bs.cpp:279,287)
+    std::unique_ptr<Node> node;
+    size_t ev_slot;
+  };
+
+  while (!open.empty() && !stop) {
+    // ---- the nodes this round pops, in pop order ----
+    std::vector<std::unique_ptr<Node>> batch;
+    if (pr.node_strategy == MVB_NODE_BEST) {
+      size_t idx = pick_node(open);
+      batch.push_back(std::move(open[idx]));
+      open.erase(open.begin() + idx);
+    } else {
+      size_t w = std::min<size_t>(width, open.size());
+      if (pr.max_iters > 0) w = std::min<size_t>(w, (size_t)std::max(1, pr.max_iters - count));
+      for (size_t k = 0; k < w; k++) { batch.push_back(std::move(open.front())); open.pop_front(); }
+    }
+    // ---- LP solve #1 of every popped node (bs.cpp:114-117), one launch ----
+    {
+      std::vector<glp_prob *> ps;
+      for (auto &nd : batch) ps.push_back(nd->prob);
+      if (!solve_many(ps)) return false;
+    }
+    std::vector<Pending> kids;
+    size_t consumed = 0;
+    for (auto &nd : batch) {
+      consumed++;
+      Node *node = nd.get();
+      glp_prob *a = node->prob;
+      TreeRec &rec = tree[node->oid];
+      ev_line("pregnant", node->oid, sstr(" ", glp_get_obj_val(a), " 1 2"));
+      std::vector<int> vars;
+      int status = classify(a, vars);
+      if (node->initial) {  // bs.cpp:134-149
+        if (status == -1) { rec.prune = P_FEAS; stop = true; break; }
+        if (status == 1) { node->upperBound = glp_get_obj_val(a); rec.prune = P_INTG; stop = true; break; }
+      }
+      node->upperBound = glp_get_obj_val(a);
+      if (status == 1) {  // bs.cpp:158-193
+        rec.prune = P_INTG;
+        ev_line("integer", node->oid, sstr(" ", node->upperBound));
+        if (node->upperBound > bestLower) {
+          bestLower = node->upperBound;
+          solution = sstr("[", node->oid, "] Solution is: ");
+          int n = glp_get_num_cols(a);
+          out->incumbent.assign(n + 1, 0.0);
+          for (int i = 1; i <= n; i++) {
+            out->incumbent[i] = glp_get_col_prim(a, i);
+            if (glp_get_col_prim(a, i) != 0 && glp_get_obj_coef(a, i) != 0)
+              solution += sstr(glp_get_obj_coef(a, i), "*(x[", i, "] = ", glp_get_col_prim(a, i), ") + ");
+          }
+          solution += sstr(glp_get_obj_coef(a, 0), " = ", glp_get_obj_val(a), "\n");
+          out->st.has_incumbent = 1;
+          out->st.incumbent_oid = node->oid;
+          out->st.incumbent = bestLower;
+        }
+      } else if (status == -1) {  // bs.cpp:194-209
+        rec.prune = P_FEAS;
+        ev_line("infeasible", node->oid, " 1 2");
+      } else if (glp_get_obj_val(a) <= bestLower) {  // bs.cpp:210-223
+        rec.prune = P_BNDS;
+        ev_line("fathomed", node->oid, "");
+      } else {  // branch, bs.cpp:224-324
+        double acc = 0;
+        for (int i : vars) acc += get_fract(glp_get_col_prim(a, i));
+        ev_line("branched", node->oid, sstr(" ", node->upperBound, " ", acc, " ", vars.size(), " 1 2"));
+        if (pr.cut_mode != MVB_CUT_NONE) gen_cuts(a);
+        int pick = pick_var(a, vars);
+        double bound = glp_get_col_prim(a, pick);
+        // S2/S3 are copies of a (util.cpp:34); a itself is dead afterwards, so
+        // S3 takes it over instead of copying a third time
+        glp_prob *c2 = glp_create_prob();
+        glp_copy_prob(c2, a, GLP_ON);
+        auto s2 = make_node(c2);
+        node->prob = nullptr;
+        auto s3 = make_node(a);
+        glp_set_col_bnds(s2->prob, pick, GLP_UP, 0, std::floor(bound));  // bs.cpp:274
+        glp_set_col_bnds(s3->prob, pick, GLP_LO, std::ceil(bound), 0);   // bs.cpp:282
+        for (Node *s : {s2.get(), s3.get()}) {
+          tree[s->oid] = TreeRec{s->oid, node->oid, tree[node->oid].depth + 1, P_NONE, {}};
+          tree[node->oid].kids.push_back(s->oid);
+        }
+        size_t e2 = ev_line("candidate", s2->oid, "");
+        size_t e3 = ev_line("candidate", s3->oid, "");
+        kids.push_back(Pending{std::move(s2), e2});
+        kids.push_back(Pending{std::move(s3), e3});
+        if (count > 200000) { out->st.hit_limit = 1; stop = true; }  // bs.cpp:320-323 (exit(-1) there)
+      }
+      count++;
+      if (pr.max_iters > 0 && count >= pr.max_iters) { out->st.hit_limit = 1; stop = true; }
+      if (stop) break;
+    }
+    // nodes of the batch not consumed because the loop stopped go back unopened
+    for (size_t k = batch.size(); k-- > consumed;)
+      if (batch[k] && batch[k]->prob) open.push_front(std::move(batch[k]));
+    // ---- LP solves #2/#3 of the new children (bs.cpp:279,287), one launch ----
+    {
+      std::vector<glp_prob *> ps;
+      for (auto &k : kids) ps.push_back(k.node->prob);
+      if (!solve_many(ps)) return false;
+      for (auto &k : kids) {
+        k.node->upperBound = glp_get_obj_val(k.node->prob);
+        evs[k.ev_slot] += sstr(" ", k.node->upperBound);
+        open.push_back(std::move(k.node));
+      }
+    }
+  }
+
+  std::ostringstream ts;
+  print_tree(1, ts);
+  out->tree = ts.str();
+  out->solution = solution;
+  for (auto &l : evs) {
+    out->events += l + "\n";
+    // hash type, oid, pid (the leading three fields), not the fp fields
+    int sp = 0;
+    for (char ch : l) {
+      if (ch == ' ' && ++sp == 3) break;
+      hash_mix((unsigned char)ch);
+    }
+  }
+  for (auto &kv : tree) { hash_mix((unsigned)kv.first); hash_mix((unsigned)kv.second.prune); }
+  out->st.iterations = count;
+  out->st.oids = next_id - 1;
+  out->st.event_hash = ehash;
+  return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+mvb_bnb *mvb_bnb_run(glp_prob *prob, const mvb_bnb_params *params) {
+  mvb_bnb_params p{};
+  if (params) p = *params;
+  auto *h = new mvb_bnb();
+  Driver d(p, prob, h);
+  if (!d.run()) {
+    std::fprintf(stderr, "mvb_bnb_run: engine error: %s\n", mvb_last_error());
+    delete h;
+    return nullptr;
+  }
+  if (!p.quiet) {  // bs.cpp:329-343
+    std::printf("[I = Integral node, F = Infeasible node, B = Worse bound node]\n%s\n%s\n",
+                h->tree.c_str(), h->solution.c_str());
+    std::printf("Solution found after %d iterations\n", h->st.iterations);
+  }
+  return h;
+}
+
+void mvb_bnb_free(mvb_bnb *h) { delete h; }
+const mvb_bnb_stats *mvb_bnb_get_stats(const mvb_bnb *h) { return &h->st; }
+const char *mvb_bnb_tree_text(const mvb_bnb *h) { return h->tree.c_str(); }
+const char *mvb_bnb_solution_text(const mvb_bnb *h) { return h->solution.c_str(); }
+const char *mvb_bnb_event_text(const mvb_bnb *h) { return h->events.c_str(); }
+int mvb_bnb_get_incumbent(const mvb_bnb *h, double *x, int cap) {
+  if (!h->st.has_incumbent) return 0;
+  int n = (int)h->incumbent.size() - 1;
+  for (int i = 0; i <= n && i < cap; i++) x[i] = h->incumbent[i];
+  return n;
+}
+
+}  // extern "C"
