@@ -46,6 +46,7 @@ struct LPDev {
   double *lb, *ub;  // n+mcap by variable id
   double *cost;     // n
   double *p1part;   // phase-1 partial sums: ceil(mcap/32) x ld
+  double *vnb;      // n: values of the non-basic variables (beta rebuild)
   // outbox: one contiguous block copied back after the solve
   DevResult *res;
   double *xval;     // n+mcap
@@ -308,3 +309,797 @@ __device__ __forceinline__ double p1_cost(const LPDev &L, int j) {
 }
 
 }  // namespace
+
+namespace {
+
+// per-solve bookkeeping replicated in every thread (identical everywhere)
+struct Tally {
+  int iters = 0, pivots = 0, flips = 0, it1 = 0, it2 = 0, itd = 0, bland = 0;
+  unsigned long long hash = MVB_FNV_OFFSET;
+};
+
+__device__ __forceinline__ void tally_iter(Tally &t, const LPDev &L, int g, int mode, int r,
+                                           int q, bool bland) {
+  unsigned long long h = t.hash;
+  h = (h ^ (unsigned long long)mode) * MVB_FNV_PRIME;
+  h = (h ^ (unsigned long long)r) * MVB_FNV_PRIME;
+  h = (h ^ (unsigned long long)q) * MVB_FNV_PRIME;
+  t.hash = h;
+  if (g == 0 && threadIdx.x == 0 && L.pivlog && t.iters < L.pivlog_cap) {
+    L.pivlog[2 * t.iters] = r;
+    L.pivlog[2 * t.iters + 1] = q;
+  }
+  t.iters++;
+  if (r) t.pivots++; else t.flips++;
+  if (mode == MVB_MODE_PRIMAL1) t.it1++;
+  else if (mode == MVB_MODE_PRIMAL2) t.it2++;
+  else t.itd++;
+  if (bland) t.bland++;
+}
+
+// beta_i = det_dot(T_i, v): one warp per row, lane-strided fma chains and a
+// halving tree (the order fixed by the specification)
+__device__ void compute_beta(const LPDev &L, int cT, int cS, int g, int G) {
+  const double *T = L.T[cT];
+  double *beta = L.beta[cS];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int i = 1 + g * nw + w; i <= L.m; i += G * nw) {
+    const double *row = T + (size_t)i * L.ld;
+    double p = 0.0;
+    for (int j = lane; j < L.n; j += 32) p = fma(ldcg(row + j), ldcg(L.vnb + j), p);
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) p = p + __shfl_down_sync(0xffffffffu, p, off);
+    if (lane == 0) beta[i] = p;
+  }
+}
+
+}  // namespace
+
+namespace {
+
+// one row of the primal ratio test (phase 2: s == 0; phase 1: an infeasible
+// basic variable blocks only when it reaches its violated bound).  Returns
+// whether the row blocks, its step t >= 0 and the flag the leaving variable takes
+__device__ __forceinline__ bool primal_ratio_row(double alpha, int dir, int s, double b, double l,
+                                                 double u, double &t, int &fl) {
+  const double a = dir > 0 ? alpha : -alpha;
+  if (a < -MVB_TOL_PIV) {  // basic variable decreases
+    if (s < 0) return false;
+    const double bound = s > 0 ? u : l;
+    if (!(bound > -HUGE_VAL)) return false;
+    t = (b - bound) / (-a);
+    fl = s > 0 ? MVB_AT_UB : MVB_AT_LB;
+  } else if (a > MVB_TOL_PIV) {  // basic variable increases
+    if (s > 0) return false;
+    const double bound = s < 0 ? l : u;
+    if (!(bound < HUGE_VAL)) return false;
+    t = (bound - b) / a;
+    fl = s < 0 ? MVB_AT_LB : MVB_AT_UB;
+  } else {
+    return false;
+  }
+  if (!(t > 0.0)) t = 0.0;
+  return true;
+}
+
+// One whole LP solve by a group of G CTAs (this CTA is number g of it).
+__device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &gen, int tcl,
+                         Smem &sm) {
+  const int m = L.m, n = L.n, ld = L.ld, tid = threadIdx.x, NT = blockDim.x;
+  int cT = L.curT, cS = L.curS;
+  Tally ty;
+  int status = MVB_ITLIM, degen = 0;
+
+  // values of the non-basic variables, then beta = T v
+  for (int j = g * NT + tid; j < n; j += G * NT) {
+    const int k = ldcg(L.nb[cS] + j);
+    L.vnb[j] = nb_value(ldcg(L.at[cS] + j), ldcg(L.lb + k), ldcg(L.ub + k));
+  }
+  group_sync(ctr, G, gen);
+  compute_beta(L, cT, cS, g, G);
+  group_sync(ctr, G, gen);
+
+  int mode;
+  if (count_primal_infeas(L, cS, sm) == 0) mode = MVB_MODE_PRIMAL2;
+  else if (count_dual_infeas(L, cT, cS, sm) == 0) mode = MVB_MODE_DUAL;
+  else mode = MVB_MODE_PRIMAL1;
+
+  while (true) {
+    const bool bland = degen >= MVB_BLAND_AFTER;
+    const double *T = L.T[cT];
+    const double *beta = L.beta[cS];
+    const int *head = L.head[cS], *nb = L.nb[cS], *at = L.at[cS];
+    int r = 0, q = -1, newat = MVB_AT_LB;
+    double delta = 0.0, newbr = 0.0;
+
+    if (mode == MVB_MODE_DUAL) {
+      // K5a leaving row: largest bound violation, lowest variable id on ties
+      Key best = key_none();
+      for (int i = 1 + tid; i <= m; i += NT) {
+        const int var = ldcg(head + i);
+        const double b = ldcg(beta + i), l = ldcg(L.lb + var), u = ldcg(L.ub + var);
+        const int s = row_infeas(b, l, u);
+        if (!s) continue;
+        const double viol = s < 0 ? l - b : b - u;
+        const Key k{bland ? 0ULL : ~dbits(viol), var, i};
+        if (key_less(k, best)) best = k;
+      }
+      best = block_argmin(best, sm.redK);
+      if (best.idx < 0) { status = MVB_OPT; break; }
+      if (ty.iters >= L.max_iters) break;
+      r = best.idx;
+      const int rvar = best.var;
+      const double br = ldcg(beta + r), lr = ldcg(L.lb + rvar), ur = ldcg(L.ub + rvar);
+      const int rs = row_infeas(br, lr, ur);
+      // K5b entering column: min |d_j| / |T_rj| over columns that move x_r
+      // toward its violated bound, lowest variable id on ties
+      const double *row = T + (size_t)r * ld;
+      Key bq = key_none();
+      for (int j = tid; j < n; j += NT) {
+        const int f = ldcg(at + j);
+        if (f == MVB_AT_FX) continue;
+        const double alpha = ldcg(row + j);
+        const double a = rs < 0 ? alpha : -alpha;
+        const bool ok = (f == MVB_AT_LB && a > MVB_TOL_PIV) || (f == MVB_AT_UB && a < -MVB_TOL_PIV) ||
+                        (f == MVB_AT_FR && (a > MVB_TOL_PIV || a < -MVB_TOL_PIV));
+        if (!ok) continue;
+        const double ratio = fabs(ldcg(T + j)) / fabs(alpha);
+        const Key k{dbits(ratio), ldcg(nb + j), j};
+        if (key_less(k, bq)) bq = k;
+      }
+      bq = block_argmin(bq, sm.redK);
+      if (bq.idx < 0) { status = MVB_NOFEAS; break; }
+      q = bq.idx;
+      const double qratio = __longlong_as_double((long long)bq.k);
+      const double target = rs < 0 ? lr : ur;
+      delta = (target - br) / ldcg(row + q);
+      const int kq = ldcg(nb + q);
+      newbr = nb_value(ldcg(at + q), ldcg(L.lb + kq), ldcg(L.ub + kq)) + delta;
+      newat = rs < 0 ? MVB_AT_LB : MVB_AT_UB;
+      degen = qratio == 0.0 ? degen + 1 : 0;
+    } else {
+      const bool phase1 = mode == MVB_MODE_PRIMAL1;
+      if (phase1) {
+        if (count_primal_infeas(L, cS, sm) == 0) { mode = MVB_MODE_PRIMAL2; degen = 0; continue; }
+        p1_partials(L, cT, cS, g, G);
+        group_sync(ctr, G, gen);
+      }
+      // K1 pricing: largest |d_j| among eligible columns, lowest variable id on
+      // ties (Bland: lowest eligible id)
+      Key bq = key_none();
+      for (int j = tid; j < n; j += NT) {
+        const int f = ldcg(at + j);
+        if (f == MVB_AT_FX) continue;
+        const double dj = phase1 ? p1_cost(L, j) : ldcg(T + j);
+        if (!dj_eligible(f, dj)) continue;
+        const Key k{bland ? 0ULL : ~dbits(fabs(dj)), ldcg(nb + j), j};
+        if (key_less(k, bq)) bq = k;
+      }
+      bq = block_argmin(bq, sm.redK);
+      if (bq.idx < 0) { status = phase1 ? MVB_NOFEAS : MVB_OPT; break; }
+      if (ty.iters >= L.max_iters) break;
+      q = bq.idx;
+      const double dq = phase1 ? p1_cost(L, q) : ldcg(T + q);
+      const int dir = dq < 0.0 ? 1 : -1;
+      // K2 ratio test over the pivot column, lowest variable id on ties
+      Key bi = key_none();
+      for (int i = 1 + tid; i <= m; i += NT) {
+        const double alpha = ldcg(T + (size_t)i * ld + q);
+        const int var = ldcg(head + i);
+        const double b = ldcg(beta + i), l = ldcg(L.lb + var), u = ldcg(L.ub + var);
+        const int s = phase1 ? row_infeas(b, l, u) : 0;
+        double t;
+        int fl;
+        if (!primal_ratio_row(alpha, dir, s, b, l, u, t, fl)) continue;
+        const Key k{dbits(t), var, i};
+        if (key_less(k, bi)) bi = k;
+      }
+      bi = block_argmin(bi, sm.redK);
+      const int kq = ldcg(nb + q);
+      const double lq = ldcg(L.lb + kq), uq = ldcg(L.ub + kq);
+      const int fq = ldcg(at + q);
+      const double tflip = uq - lq;
+      const double tmin = bi.idx >= 0 ? __longlong_as_double((long long)bi.k) : HUGE_VAL;
+      if (tflip <= tmin) {
+        if (!(tflip < HUGE_VAL)) { status = phase1 ? MVB_NOFEAS : MVB_UNBND; break; }
+        r = 0;  // bound flip, no basis change
+        delta = dir > 0 ? tflip : -tflip;
+        newat = fq == MVB_AT_LB ? MVB_AT_UB : MVB_AT_LB;
+        degen = 0;
+      } else {
+        r = bi.idx;
+        const double alpha = ldcg(T + (size_t)r * ld + q);
+        const double b = ldcg(beta + r), l = ldcg(L.lb + bi.var), u = ldcg(L.ub + bi.var);
+        double t;
+        primal_ratio_row(alpha, dir, phase1 ? row_infeas(b, l, u) : 0, b, l, u, t, newat);
+        delta = dir > 0 ? tmin : -tmin;
+        newbr = nb_value(fq, lq, uq) + delta;
+        degen = tmin == 0.0 ? degen + 1 : 0;
+      }
+    }
+
+    // ---- apply the iteration: next small state, then the rank-1 update ----
+    const int kin = ldcg(nb + q);
+    int kout = kin;
+    if (r) {
+      kout = ldcg(head + r);
+      if (ldcg(L.lb + kout) == ldcg(L.ub + kout)) newat = MVB_AT_FX;
+    }
+    tally_iter(ty, L, g, mode, r, q, bland);
+    state_update(L, cT, cS, r, q, delta, newbr, kin, kout, newat, g, G);
+    if (r) {
+      const double inv = 1.0 / ldcg(T + (size_t)r * ld + q);
+      tile_update(L, T, L.T[cT ^ 1], r, q, inv, g, G, tcl, sm);
+      cT ^= 1;
+    }
+    cS ^= 1;
+    group_sync(ctr, G, gen);
+  }
+
+  // ---- finish: primal values by variable id, basis copy, objective ----
+  const double *beta = L.beta[cS];
+  const int *head = L.head[cS], *nb = L.nb[cS], *at = L.at[cS];
+  for (int j = g * NT + tid; j < n; j += G * NT) {
+    const int k = ldcg(nb + j), f = ldcg(at + j);
+    L.xval[k] = nb_value(f, ldcg(L.lb + k), ldcg(L.ub + k));
+    L.onb[j] = k;
+    L.oat[j] = f;
+  }
+  for (int i = 1 + g * NT + tid; i <= m; i += G * NT) {
+    const int k = ldcg(head + i);
+    L.xval[k] = ldcg(beta + i);
+    L.ohead[i - 1] = k;
+  }
+  group_sync(ctr, G, gen);
+  if (g == 0) {
+    const int ninf = count_primal_infeas(L, cS, sm);
+    if (tid < 32) {
+      double p = 0.0;
+      for (int j = tid; j < n; j += 32) p = fma(ldcg(L.cost + j), ldcg(L.xval + j), p);
+#pragma unroll
+      for (int off = 16; off >= 1; off >>= 1) p = p + __shfl_down_sync(0xffffffffu, p, off);
+      if (tid == 0) {
+        mvb_result &o = L.res->r;
+        o.status = status;
+        o.iters = ty.iters;
+        o.pivots = ty.pivots;
+        o.flips = ty.flips;
+        o.iters_primal1 = ty.it1;
+        o.iters_primal2 = ty.it2;
+        o.iters_dual = ty.itd;
+        o.bland_iters = ty.bland;
+        o.pivot_hash = ty.hash;
+        o.obj = p;
+        o.primal_feasible = ninf == 0;
+        o.reserved = 0;
+        L.res->curT = cT;
+        L.res->curS = cS;
+      }
+    }
+  }
+}
+
+// grid = ngroups * G CTAs (all co-resident: cooperative launch); group k owns
+// LPs k, k + ngroups, ...
+__global__ void __launch_bounds__(512, 1)
+simplex_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
+  __shared__ Smem sm;
+  const int group = blockIdx.x / G, g = blockIdx.x - group * G, ngroups = gridDim.x / G;
+  unsigned gen = 0;
+  for (int k = group; k < nlp; k += ngroups) {
+    const LPDev L = lps[k];
+    int t = tcl;
+    if (t < 0) {  // per-LP thread shape: columns = pow2 >= ld/2, capped at the block
+      t = 0;
+      while ((1 << t) < (L.ld + 1) / 2 && (2 << t) <= (int)blockDim.x) t++;
+    }
+    solve_lp(L, g, G, ctrs + group, gen, t, sm);
+    __syncthreads();
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host
+namespace {
+
+thread_local std::string g_err;
+std::atomic<unsigned long long> g_launches{0};
+
+struct DeviceCtx {
+  bool ready = false;
+  int device = -1, sms = 0;
+  cudaStream_t stream = nullptr;
+  int max_ctas = 0;        // co-resident CTAs of simplex_kernel at NT threads
+  int nt = 512;            // threads per CTA
+  unsigned *ctrs = nullptr; int ctrs_cap = 0;
+  LPDev *dlps = nullptr; int dlps_cap = 0;
+  char *stage = nullptr; size_t stage_cap = 0;   // device staging (row gathers, new rows)
+};
+DeviceCtx g_ctx;
+
+bool fail(const std::string &m) { g_err = m; return false; }
+#define CK(call)                                                                     \
+  do {                                                                               \
+    cudaError_t e_ = (call);                                                         \
+    if (e_ != cudaSuccess) {                                                         \
+      g_err = std::string(#call) + ": " + cudaGetErrorString(e_);                    \
+      return false;                                                                  \
+    }                                                                                \
+  } while (0)
+
+bool ctx_init(int device) {
+  if (g_ctx.ready && (device < 0 || device == g_ctx.device)) return true;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+    return fail("no CUDA device: the mvolps_b200 engine has no CPU fallback");
+  if (device < 0) device = 0;
+  CK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) return fail("mvolps_b200 is built for sm_100a (B200) only");
+  g_ctx.device = device;
+  g_ctx.sms = prop.multiProcessorCount;
+  CK(cudaStreamCreateWithFlags(&g_ctx.stream, cudaStreamNonBlocking));
+  cudaMemPool_t pool;
+  CK(cudaDeviceGetDefaultMemPool(&pool, device));
+  unsigned long long keep = ~0ULL;  // keep freed slabs cached for reuse
+  CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+  int per_sm = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_kernel, g_ctx.nt, 0));
+  if (per_sm < 1) return fail("simplex_kernel does not fit an SM");
+  g_ctx.max_ctas = per_sm * g_ctx.sms;
+  g_ctx.ready = true;
+  return true;
+}
+
+bool ensure_stage(size_t bytes) {
+  if (bytes <= g_ctx.stage_cap) return true;
+  if (g_ctx.stage) CK(cudaFreeAsync(g_ctx.stage, g_ctx.stream));
+  g_ctx.stage = nullptr;
+  g_ctx.stage_cap = 0;
+  size_t cap = std::max<size_t>(bytes, 1 << 20);
+  CK(cudaMallocAsync((void **)&g_ctx.stage, cap, g_ctx.stream));
+  g_ctx.stage_cap = cap;
+  return true;
+}
+
+size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+// Host handle: device slab + host mirror of the small state.
+struct mvb_lp {
+  int m = 0, n = 0, ld = 0, mcap = 0;
+  char *slab = nullptr;
+  size_t slab_bytes = 0, t_bytes = 0, small_off = 0, small_bytes = 0, out_off = 0, out_bytes = 0;
+  LPDev dev{};
+  int curT = 0, curS = 0;
+  std::vector<double> lb, ub;       // by variable id (n + m)
+  std::vector<int> head, nb, at;    // basis mirror (valid: mirror_ok)
+  std::vector<double> x;            // primal by id after the last solve
+  bool bounds_dirty = false, at_dirty = false;
+  mvb_result res{};
+  int *pivlog = nullptr; int pivlog_cap = 0, pivlog_n = 0;
+  std::vector<char> outbox;         // host copy of the outbox
+};
+
+namespace {
+
+// carve the slab; every sub-array 256-byte aligned
+bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
+  if (mcap < m) mcap = m;
+  lp->m = m; lp->n = n; lp->mcap = mcap;
+  lp->ld = (int)align_up((size_t)std::max(n, 1), MVB_LD_ALIGN);
+  const size_t A = 256;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, A); return o; };
+  lp->t_bytes = align_up((size_t)(mcap + 1) * lp->ld * sizeof(double), A);
+  size_t oT0 = take(lp->t_bytes), oT1 = take(lp->t_bytes);
+  lp->small_off = off;
+  size_t ob0 = take((mcap + 1) * sizeof(double)), ob1 = take((mcap + 1) * sizeof(double));
+  size_t olb = take((size_t)(n + mcap) * sizeof(double)), oub = take((size_t)(n + mcap) * sizeof(double));
+  size_t ocost = take((size_t)std::max(n, 1) * sizeof(double));
+  size_t oh0 = take((mcap + 1) * sizeof(int)), oh1 = take((mcap + 1) * sizeof(int));
+  size_t on0 = take((size_t)std::max(n, 1) * sizeof(int)), on1 = take((size_t)std::max(n, 1) * sizeof(int));
+  size_t oa0 = take((size_t)std::max(n, 1) * sizeof(int)), oa1 = take((size_t)std::max(n, 1) * sizeof(int));
+  lp->small_bytes = off - lp->small_off;
+  size_t ovnb = take((size_t)std::max(n, 1) * sizeof(double));
+  size_t nchunks = (mcap + MVB_P1_CHUNK - 1) / MVB_P1_CHUNK + 1;
+  size_t op1 = take(nchunks * lp->ld * sizeof(double));
+  lp->out_off = off;
+  size_t ores = take(sizeof(DevResult));
+  size_t ox = take((size_t)(n + mcap) * sizeof(double));
+  size_t ooh = take((size_t)std::max(mcap, 1) * sizeof(int));
+  size_t oon = take((size_t)std::max(n, 1) * sizeof(int)), ooa = take((size_t)std::max(n, 1) * sizeof(int));
+  lp->out_bytes = off - lp->out_off;
+  lp->slab_bytes = off;
+  CK(cudaMallocAsync((void **)&lp->slab, lp->slab_bytes, g_ctx.stream));
+  char *s = lp->slab;
+  LPDev &d = lp->dev;
+  d.m = m; d.n = n; d.ld = lp->ld; d.mcap = mcap;
+  d.T[0] = (double *)(s + oT0); d.T[1] = (double *)(s + oT1);
+  d.beta[0] = (double *)(s + ob0); d.beta[1] = (double *)(s + ob1);
+  d.lb = (double *)(s + olb); d.ub = (double *)(s + oub); d.cost = (double *)(s + ocost);
+  d.head[0] = (int *)(s + oh0); d.head[1] = (int *)(s + oh1);
+  d.nb[0] = (int *)(s + on0); d.nb[1] = (int *)(s + on1);
+  d.at[0] = (int *)(s + oa0); d.at[1] = (int *)(s + oa1);
+  d.vnb = (double *)(s + ovnb); d.p1part = (double *)(s + op1);
+  d.res = (DevResult *)(s + ores); d.xval = (double *)(s + ox);
+  d.ohead = (int *)(s + ooh); d.onb = (int *)(s + oon); d.oat = (int *)(s + ooa);
+  d.pivlog = nullptr; d.pivlog_cap = 0;
+  lp->curT = lp->curS = 0;
+  lp->outbox.resize(lp->out_bytes);
+  return true;
+}
+
+void lp_release(mvb_lp *lp) {
+  if (lp->slab) cudaFreeAsync(lp->slab, g_ctx.stream);
+  if (lp->pivlog) cudaFreeAsync(lp->pivlog, g_ctx.stream);
+  lp->slab = nullptr;
+  lp->pivlog = nullptr;
+  lp->pivlog_cap = 0;
+}
+
+int nb_flag_for(double l, double u, int keep) {
+  const bool hasl = l > -HUGE_VAL, hasu = u < HUGE_VAL;
+  if (hasl && hasu && l == u) return MVB_AT_FX;
+  if (keep == MVB_AT_UB && hasu) return MVB_AT_UB;
+  if (keep == MVB_AT_LB && hasl) return MVB_AT_LB;
+  if (hasl) return MVB_AT_LB;
+  if (hasu) return MVB_AT_UB;
+  return MVB_AT_FR;
+}
+
+// push host bounds / flags that changed since the last solve
+bool lp_push_small(mvb_lp *lp) {
+  const int n = lp->n, m = lp->m;
+  if (lp->bounds_dirty) {
+    CK(cudaMemcpyAsync(lp->dev.lb, lp->lb.data(), (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, g_ctx.stream));
+    CK(cudaMemcpyAsync(lp->dev.ub, lp->ub.data(), (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, g_ctx.stream));
+    lp->bounds_dirty = false;
+  }
+  if (lp->at_dirty) {
+    CK(cudaMemcpyAsync(lp->dev.at[lp->curS], lp->at.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, g_ctx.stream));
+    lp->at_dirty = false;
+  }
+  return true;
+}
+
+}  // namespace
+
+#define CKI(call)                                                                    \
+  do {                                                                               \
+    cudaError_t e_ = (call);                                                         \
+    if (e_ != cudaSuccess) {                                                         \
+      g_err = std::string(#call) + ": " + cudaGetErrorString(e_);                    \
+      return -1;                                                                     \
+    }                                                                                \
+  } while (0)
+
+extern "C" {
+
+const char *mvb_backend(void) { return "cuda-sm100a"; }
+const char *mvb_last_error(void) { return g_err.c_str(); }
+int mvb_device_init(int device) { return ctx_init(device) ? 0 : -1; }
+unsigned long long mvb_kernel_launches(void) { return g_launches.load(); }
+
+mvb_lp *mvb_lp_create(int m, int n, int row_cap) {
+  if (m < 0 || n < 1) { g_err = "mvb_lp_create: bad dimensions"; return nullptr; }
+  if (!ctx_init(-1)) return nullptr;
+  mvb_lp *lp = new mvb_lp();
+  if (!lp_alloc(lp, m, n, row_cap)) { delete lp; return nullptr; }
+  return lp;
+}
+
+void mvb_lp_free(mvb_lp *lp) {
+  if (!lp) return;
+  lp_release(lp);
+  delete lp;
+}
+
+int mvb_lp_dims(const mvb_lp *lp, int *m, int *n) {
+  if (m) *m = lp->m;
+  if (n) *n = lp->n;
+  return 0;
+}
+
+int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost, const double *lb,
+                const double *ub) {
+  const int m = lp->m, n = lp->n, ld = lp->ld;
+  cudaStream_t st = g_ctx.stream;
+  LPDev &d = lp->dev;
+  lp->curT = lp->curS = 0;
+  CKI(cudaMemsetAsync(d.T[0], 0, lp->t_bytes, st));
+  CKI(cudaMemcpyAsync(d.T[0], cost, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
+  if (m > 0)
+    CKI(cudaMemcpy2DAsync(d.T[0] + ld, (size_t)ld * sizeof(double), A, (size_t)n * sizeof(double),
+                          (size_t)n * sizeof(double), m, cudaMemcpyHostToDevice, st));
+  CKI(cudaMemcpyAsync(d.cost, cost, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
+  lp->lb.assign(lb, lb + n + m);
+  lp->ub.assign(ub, ub + n + m);
+  lp->head.resize(m);
+  lp->nb.resize(n);
+  lp->at.resize(n);
+  for (int i = 0; i < m; i++) lp->head[i] = n + i;
+  for (int j = 0; j < n; j++) { lp->nb[j] = j; lp->at[j] = nb_flag_for(lb[j], ub[j], MVB_AT_LB); }
+  if (m > 0)
+    CKI(cudaMemcpyAsync(d.head[0] + 1, lp->head.data(), (size_t)m * sizeof(int), cudaMemcpyHostToDevice, st));
+  CKI(cudaMemcpyAsync(d.nb[0], lp->nb.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, st));
+  lp->bounds_dirty = lp->at_dirty = true;
+  if (!lp_push_small(lp)) return -1;
+  lp->x.assign(n + m, 0.0);
+  lp->res = mvb_result{};
+  lp->res.status = MVB_UNSOLVED;
+  CKI(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int mvb_lp_assign(mvb_lp *dst, const mvb_lp *src) {
+  if (dst->n != src->n || dst->mcap != src->mcap) { g_err = "mvb_lp_assign: shape mismatch"; return -1; }
+  cudaStream_t st = g_ctx.stream;
+  dst->m = src->m;
+  dst->dev.m = src->m;
+  dst->curT = src->curT;
+  dst->curS = src->curS;
+  // the current tableau buffer and the whole small-state region, device to device
+  CKI(cudaMemcpyAsync(dst->dev.T[src->curT], src->dev.T[src->curT],
+                      (size_t)(src->m + 1) * src->ld * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  CKI(cudaMemcpyAsync(dst->slab + dst->small_off, src->slab + src->small_off, src->small_bytes,
+                      cudaMemcpyDeviceToDevice, st));
+  dst->lb = src->lb; dst->ub = src->ub;
+  dst->head = src->head; dst->nb = src->nb; dst->at = src->at; dst->x = src->x;
+  dst->bounds_dirty = src->bounds_dirty;
+  dst->at_dirty = src->at_dirty;
+  dst->res = src->res;
+  dst->pivlog_n = 0;
+  return 0;
+}
+
+mvb_lp *mvb_lp_clone(const mvb_lp *src) {
+  mvb_lp *lp = mvb_lp_create(src->m, src->n, src->mcap);
+  if (!lp) return nullptr;
+  if (mvb_lp_assign(lp, src)) { mvb_lp_free(lp); return nullptr; }
+  return lp;
+}
+
+int mvb_lp_set_bounds(mvb_lp *lp, int k, double lb, double ub) {
+  if (k < 0 || k >= lp->n + lp->m) { g_err = "mvb_lp_set_bounds: variable id"; return -1; }
+  lp->lb[k] = lb;
+  lp->ub[k] = ub;
+  lp->bounds_dirty = true;
+  for (int j = 0; j < lp->n; j++)
+    if (lp->nb[j] == k) {
+      int f = nb_flag_for(lb, ub, lp->at[j]);
+      if (f != lp->at[j]) { lp->at[j] = f; lp->at_dirty = true; }
+      break;
+    }
+  return 0;
+}
+
+}  // extern "C"
+
+namespace {
+
+// tableau row of a new constraint a.x: a_N + sum_i a_{head[i]} T[i,:], terms in
+// row order, one fma each (specification: oracle mvb_lp_append_row)
+__global__ void append_row_kernel(LPDev L, int cT, int cS, const double *a) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int m = L.m, n = L.n, ld = L.ld;
+  if (p >= ld) return;
+  const double *T = L.T[cT];
+  double acc = 0.0;
+  if (p < n) {
+    const int k = L.nb[cS][p];
+    acc = k < n ? a[k] : 0.0;
+    for (int i = 1; i <= m; i++) {
+      const int h = L.head[cS][i];
+      if (h < n && a[h] != 0.0) acc = fma(a[h], T[(size_t)i * ld + p], acc);
+    }
+  }
+  L.T[cT][(size_t)(m + 1) * ld + p] = acc;
+  if (p == 0) {
+    L.head[cS][m + 1] = n + m;
+    L.beta[cS][m + 1] = 0.0;
+  }
+}
+
+// K7: gather tableau rows into a contiguous staging buffer
+__global__ void gather_rows_kernel(const double *T, int ld, int n, const int *rows, int nrows,
+                                   double *out) {
+  const int t = blockIdx.y;
+  if (t >= nrows) return;
+  const double *src = T + (size_t)rows[t] * ld;
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
+    out[(size_t)t * n + j] = src[j];
+}
+
+bool lp_grow(mvb_lp *lp, int mcap) {
+  mvb_lp nl;
+  if (!lp_alloc(&nl, lp->m, lp->n, mcap)) return false;
+  cudaStream_t st = g_ctx.stream;
+  const int m = lp->m, n = lp->n;
+  const LPDev &s = lp->dev;
+  LPDev &d = nl.dev;
+  CK(cudaMemcpyAsync(d.T[0], s.T[lp->curT], (size_t)(m + 1) * lp->ld * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(d.beta[0], s.beta[lp->curS], (size_t)(m + 1) * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(d.head[0], s.head[lp->curS], (size_t)(m + 1) * sizeof(int), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(d.nb[0], s.nb[lp->curS], (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(d.at[0], s.at[lp->curS], (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(d.cost, s.cost, (size_t)n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  lp_release(lp);
+  lp->slab = nl.slab; nl.slab = nullptr;
+  lp->slab_bytes = nl.slab_bytes; lp->t_bytes = nl.t_bytes;
+  lp->small_off = nl.small_off; lp->small_bytes = nl.small_bytes;
+  lp->out_off = nl.out_off; lp->out_bytes = nl.out_bytes;
+  lp->mcap = nl.mcap;
+  lp->dev = nl.dev;
+  lp->curT = lp->curS = 0;
+  lp->outbox.resize(lp->out_bytes);
+  lp->bounds_dirty = true;  // lb/ub are re-sent from the host mirror
+  return true;
+}
+
+}  // namespace
+
+extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double ub) {
+  if (lp->m + 1 > lp->mcap && !lp_grow(lp, lp->mcap + 16 + lp->mcap / 4)) return -1;
+  const int n = lp->n, m = lp->m;
+  cudaStream_t st = g_ctx.stream;
+  if (!lp_push_small(lp)) return -1;  // flags of the current state must be on the device
+  if (!ensure_stage((size_t)n * sizeof(double))) return -1;
+  CKI(cudaMemcpyAsync(g_ctx.stage, a, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
+  lp->dev.m = m;
+  append_row_kernel<<<(lp->ld + 127) / 128, 128, 0, st>>>(lp->dev, lp->curT, lp->curS,
+                                                          (const double *)g_ctx.stage);
+  CKI(cudaGetLastError());
+  g_launches++;
+  lp->m = m + 1;
+  lp->dev.m = m + 1;
+  lp->lb.push_back(lb);
+  lp->ub.push_back(ub);
+  lp->head.push_back(n + m);
+  lp->x.push_back(0.0);
+  lp->bounds_dirty = true;
+  CKI(cudaStreamSynchronize(st));  // `a` and the staging buffer are free again
+  return 0;
+}
+
+extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *opts,
+                               mvb_result *out) {
+  if (count <= 0) return 0;
+  if (!ctx_init(-1)) return -1;
+  cudaStream_t st = g_ctx.stream;
+  std::vector<LPDev> h(count);
+  size_t max_bytes = 0;
+  for (int k = 0; k < count; k++) {
+    mvb_lp *lp = lps[k];
+    if (!lp_push_small(lp)) return -1;
+    int mi = (opts && opts->max_iters > 0) ? opts->max_iters : 50 * (lp->m + lp->n) + 10000;
+    if (opts && opts->log_pivots) {
+      int want = std::min(mi, 1 << 22);
+      if (lp->pivlog_cap < want) {
+        if (lp->pivlog) CKI(cudaFreeAsync(lp->pivlog, st));
+        CKI(cudaMallocAsync((void **)&lp->pivlog, (size_t)want * 2 * sizeof(int), st));
+        lp->pivlog_cap = want;
+      }
+    }
+    lp->dev.m = lp->m;
+    lp->dev.curT = lp->curT;
+    lp->dev.curS = lp->curS;
+    lp->dev.max_iters = mi;
+    lp->dev.pivlog = (opts && opts->log_pivots) ? lp->pivlog : nullptr;
+    lp->dev.pivlog_cap = lp->dev.pivlog ? lp->pivlog_cap : 0;
+    h[k] = lp->dev;
+    max_bytes = std::max(max_bytes, (size_t)(lp->m + 1) * lp->ld * sizeof(double));
+  }
+  // CTAs per LP: by tableau size, bounded by what is co-resident
+  int G = (opts && opts->ctas_per_lp > 0) ? opts->ctas_per_lp
+                                          : (int)std::min<size_t>((max_bytes + (128 << 10) - 1) / (128 << 10), (size_t)g_ctx.max_ctas);
+  if (!(opts && opts->ctas_per_lp > 0) && count > 1) G = std::max(1, std::min(G, g_ctx.max_ctas / count));
+  G = std::max(1, std::min(G, g_ctx.max_ctas));
+  int ngroups = std::max(1, std::min(count, g_ctx.max_ctas / G));
+  if (g_ctx.ctrs_cap < ngroups) {
+    if (g_ctx.ctrs) CKI(cudaFreeAsync(g_ctx.ctrs, st));
+    CKI(cudaMallocAsync((void **)&g_ctx.ctrs, (size_t)ngroups * sizeof(unsigned), st));
+    g_ctx.ctrs_cap = ngroups;
+  }
+  if (g_ctx.dlps_cap < count) {
+    if (g_ctx.dlps) CKI(cudaFreeAsync(g_ctx.dlps, st));
+    CKI(cudaMallocAsync((void **)&g_ctx.dlps, (size_t)count * sizeof(LPDev), st));
+    g_ctx.dlps_cap = count;
+  }
+  CKI(cudaMemsetAsync(g_ctx.ctrs, 0, (size_t)ngroups * sizeof(unsigned), st));
+  CKI(cudaMemcpyAsync(g_ctx.dlps, h.data(), (size_t)count * sizeof(LPDev), cudaMemcpyHostToDevice, st));
+  const LPDev *dl = g_ctx.dlps;
+  unsigned *ctrs = g_ctx.ctrs;
+  int tcl = -1;
+  void *args[] = {(void *)&dl, (void *)&count, (void *)&G, (void *)&ctrs, (void *)&tcl};
+  CKI(cudaLaunchCooperativeKernel((const void *)simplex_kernel, dim3(ngroups * G), dim3(g_ctx.nt),
+                                  args, 0, st));
+  g_launches++;
+  for (int k = 0; k < count; k++)
+    CKI(cudaMemcpyAsync(lps[k]->outbox.data(), lps[k]->slab + lps[k]->out_off, lps[k]->out_bytes,
+                        cudaMemcpyDeviceToHost, st));
+  CKI(cudaStreamSynchronize(st));
+  for (int k = 0; k < count; k++) {
+    mvb_lp *lp = lps[k];
+    const char *ob = lp->outbox.data();
+    const char *base = lp->slab + lp->out_off;
+    const DevResult *dr = (const DevResult *)(ob + ((const char *)lp->dev.res - base));
+    const double *x = (const double *)(ob + ((const char *)lp->dev.xval - base));
+    const int *oh = (const int *)(ob + ((const char *)lp->dev.ohead - base));
+    const int *on = (const int *)(ob + ((const char *)lp->dev.onb - base));
+    const int *oa = (const int *)(ob + ((const char *)lp->dev.oat - base));
+    lp->res = dr->r;
+    lp->curT = dr->curT;
+    lp->curS = dr->curS;
+    lp->x.assign(x, x + lp->n + lp->m);
+    lp->head.assign(oh, oh + lp->m);
+    lp->nb.assign(on, on + lp->n);
+    lp->at.assign(oa, oa + lp->n);
+    lp->pivlog_n = lp->dev.pivlog ? std::min(dr->r.iters, lp->pivlog_cap) : 0;
+    out[k] = dr->r;
+  }
+  return 0;
+}
+
+extern "C" {
+
+int mvb_lp_get_primal(mvb_lp *lp, double *x) {
+  if ((int)lp->x.size() != lp->n + lp->m) { g_err = "mvb_lp_get_primal: no solution"; return -1; }
+  std::memcpy(x, lp->x.data(), lp->x.size() * sizeof(double));
+  return 0;
+}
+
+int mvb_lp_get_basis(mvb_lp *lp, int *head, int *nb, int *at) {
+  std::memcpy(head, lp->head.data(), (size_t)lp->m * sizeof(int));
+  std::memcpy(nb, lp->nb.data(), (size_t)lp->n * sizeof(int));
+  std::memcpy(at, lp->at.data(), (size_t)lp->n * sizeof(int));
+  return 0;
+}
+
+int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
+  if (nrows <= 0) return 0;
+  for (int t = 0; t < nrows; t++)
+    if (rows[t] < 0 || rows[t] > lp->m) { g_err = "mvb_lp_get_tab_rows: row out of range"; return -1; }
+  cudaStream_t st = g_ctx.stream;
+  const size_t rb = align_up((size_t)nrows * sizeof(int), 256);
+  const size_t ob = (size_t)nrows * lp->n * sizeof(double);
+  if (!ensure_stage(rb + ob)) return -1;
+  int *drows = (int *)g_ctx.stage;
+  double *dout = (double *)(g_ctx.stage + rb);
+  CKI(cudaMemcpyAsync(drows, rows, (size_t)nrows * sizeof(int), cudaMemcpyHostToDevice, st));
+  dim3 grid((lp->n + 255) / 256, nrows);
+  grid.x = std::min<unsigned>(grid.x, 64);
+  gather_rows_kernel<<<grid, 256, 0, st>>>(lp->dev.T[lp->curT], lp->ld, lp->n, drows, nrows, dout);
+  CKI(cudaGetLastError());
+  g_launches++;
+  CKI(cudaMemcpyAsync(out, dout, ob, cudaMemcpyDeviceToHost, st));
+  CKI(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int mvb_lp_get_tableau(mvb_lp *lp, double *T, double *beta) {
+  cudaStream_t st = g_ctx.stream;
+  CKI(cudaMemcpy2DAsync(T, (size_t)lp->n * sizeof(double), lp->dev.T[lp->curT],
+                        (size_t)lp->ld * sizeof(double), (size_t)lp->n * sizeof(double), lp->m + 1,
+                        cudaMemcpyDeviceToHost, st));
+  if (beta)
+    CKI(cudaMemcpyAsync(beta, lp->dev.beta[lp->curS], (size_t)(lp->m + 1) * sizeof(double),
+                        cudaMemcpyDeviceToHost, st));
+  CKI(cudaStreamSynchronize(st));
+  if (beta) beta[0] = 0.0;
+  return 0;
+}
+
+int mvb_lp_get_pivot_log(mvb_lp *lp, int *rowcol, int cap) {
+  int c = std::min(lp->pivlog_n, cap);
+  if (c > 0) {
+    CKI(cudaMemcpyAsync(rowcol, lp->pivlog, (size_t)c * 2 * sizeof(int), cudaMemcpyDeviceToHost, g_ctx.stream));
+    CKI(cudaStreamSynchronize(g_ctx.stream));
+  }
+  return lp->pivlog_n;
+}
+
+}  // extern "C"
