@@ -1,0 +1,248 @@
+#!/usr/bin/env python
+"""bench.py -- simplex pivots/s of the LP-relaxation hot path on B200.
+
+Workload at every N: BASELINE.json configs[1] -- one dense feasible LP
+relaxation m=1024 n=2048 fp64 per GPU (seed 1234 + rank), solved from the slack
+basis to optimality by the persistent cooperative kernel.  One step = one full
+solve.  `value`: inputs resident in HBM (a pristine device tableau is cloned
+device-to-device inside the timed region), CUDA events on the engine's launch
+stream, L2 flushed between steps.  `e2e`: the same solve through the
+reference-facing call glp_simplex() on a host glp_prob (dense build, H2D,
+solve, D2H inside the timed region).  N > 1: independent LPs per rank (the
+north_star's "open nodes sharded across GPUs"), no data-path collective.
+
+--impl reference: the CPU restatement (oracle) on all host threads, bounded
+sample (the reference's own LP engine, GLPK, is absent from this image; see
+DESIGN.md).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from mvolps_b200 import capi, instances  # noqa: E402
+from mvolps_b200.lp import EngineLP, GlpProb  # noqa: E402
+
+M, N_COLS, SEED = 1024, 2048, 1234
+ORACLE_LIB = os.path.join(ROOT, "oracle", "_build", "libglpk_oracle.so")
+METRIC = "simplex_pivots_per_sec"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+
+    def __init__(self, index):
+        self.rows, self.stop = [], False
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        self.cmd = ["nvidia-smi", f"--id={index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"]
+        self.t = threading.Thread(target=self.run, daemon=True)
+
+    def run(self):
+        while not self.stop:
+            try:
+                out = subprocess.run(self.cmd, capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop = True
+        self.t.join(timeout=6)
+
+    def summary(self):
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def cpu_sample(threads, max_iters):
+    """Oracle on the same workload, first `max_iters` pivots of the solve."""
+    orc = capi.load_library(ORACLE_LIB)
+    lp = EngineLP.from_instance(orc, instances.dense_lp(M, N_COLS, SEED))
+    t0 = time.perf_counter()
+    r = lp.solve(max_iters=max_iters, threads=threads)
+    dt = time.perf_counter() - t0
+    return r["pivots"] / dt, r["pivots"], dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sample_iters = 400
+    for _ in range(args.warmup):
+        cpu_sample(cores, 50)
+    tot_p, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        _, p, dt = cpu_sample(cores, sample_iters)
+        tot_p += p
+        tot_t += dt
+    v = tot_p / tot_t
+    sample = f"first {sample_iters} pivots of the m={M} n={N_COLS} solve per step, OpenMP over tableau rows"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "pivots/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": {"workload": f"dense LP m={M} n={N_COLS} seed={SEED} (BASELINE configs[1])"},
+        "cpu_baseline": {"value": v, "unit": "pivots/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "pivots/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--ctas-per-lp", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    L = capi.load_product()  # no fallback: raises when the CUDA library is missing
+    if L.mvb_device_init(local) != 0:
+        raise RuntimeError("CUDA engine unavailable: " + L.mvb_last_error().decode())
+    L.glp_term_out(capi.GLP_OFF)
+    inst = instances.dense_lp(M, N_COLS, SEED + rank)
+    template = EngineLP.from_instance(L, inst)      # pristine tableau, resident in HBM
+    work = template.clone()
+    host_prob = GlpProb.from_instance(L, inst)      # what a GLPK client holds on the host
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def device_step():
+        L.mvb_timer_record(0)
+        work.assign(template)                       # device-to-device, part of the step
+        r = work.solve(ctas_per_lp=args.ctas_per_lp)
+        L.mvb_timer_record(1)
+        ms = L.mvb_timer_elapsed_ms(0, 1)
+        return r, ms, L.mvb_last_kernel_ms()
+
+    def e2e_step():
+        t0 = time.perf_counter()
+        p = host_prob.copy()                        # host copy: no engine state yet
+        p.simplex()                                 # dense build + H2D + solve + D2H
+        obj = p.obj_val()
+        its = L.glp_get_it_cnt(p.h)
+        dt = time.perf_counter() - t0
+        p.free()
+        return its, obj, dt
+
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+        L.mvb_flush_l2()
+    e2e_step()
+
+    barrier()
+    launches0 = L.mvb_kernel_launches()
+    piv = 0
+    step_ms = kern_ms = 0.0
+    with ClockSampler(local) as clk:
+        for _ in range(args.steps):
+            L.mvb_flush_l2()
+            r, ms, kms = device_step()
+            assert r["status"] == 0, r
+            piv += r["pivots"]
+            step_ms += ms
+            kern_ms += kms
+        launches = int(L.mvb_kernel_launches() - launches0)
+        barrier()
+        e_piv, e_t = 0, 0.0
+        for _ in range(args.steps):
+            its, obj, dt = e2e_step()
+            e_piv += its
+            e_t += dt
+    barrier()
+    tot_piv, max_ms, e_tot_piv, e_max_t = piv, step_ms, e_piv, e_t
+    if dist is not None:
+        import torch
+        t = torch.tensor([piv, e_piv], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        tm = torch.tensor([step_ms, e_t], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+        tot_piv, e_tot_piv = t[0].item(), t[1].item()
+        max_ms, e_max_t = tm[0].item(), tm[1].item()
+    if rank != 0:
+        return
+    G, groups, nt = C.c_int(), C.c_int(), C.c_int()
+    L.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
+    peak, peak_src = peaks()
+    alg_bytes = 16.0 * (M + 1) * (N_COLS + 1) * (piv / args.steps)   # per launch (= per solve)
+    achieved = alg_bytes / (kern_ms / args.steps * 1e-3) / 1e9
+    m, n = M, N_COLS
+    h2d = 8 * (m * n + 2 * n + 2 * (n + m)) + 4 * (m + 2 * n)
+    d2h = 8 * (n + m) + 4 * (m + 2 * n) + 96
+    line = {
+        "metric": METRIC, "value": tot_piv / (max_ms * 1e-3), "unit": "pivots/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": max_ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": f"dense LP m={M} n={N_COLS} seed={SEED}+rank (BASELINE configs[1]), one LP per GPU, "
+                               "full solve from the slack basis per step",
+                   "pivots_per_step": piv / args.steps, "l2": "flushed between steps (256 MiB memset); "
+                   "within a step the 2x16.8 MB ping-pong tableau is L2-resident",
+                   "ctas_per_lp": G.value, "threads_per_cta": nt.value},
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "kernel": "simplex_kernel (one launch = whole solve)",
+                     "algorithmic_bytes_per_pivot": 16 * (M + 1) * (N_COLS + 1),
+                     "kernel_ms_per_launch": kern_ms / args.steps,
+                     "frac_of_8TBs": achieved / 8000.0},
+        "e2e": {"value": e_tot_piv / e_max_t, "unit": "pivots/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "api": "glp_simplex on a host glp_prob (dense build + H2D + solve + D2H)"},
+        "gpu_launches": launches,
+        "clocks": clk.summary(),
+    }
+    if not args.no_cpu_baseline and world == 1:
+        v, p, dt = cpu_sample(1, 1500)
+        line["cpu_baseline"] = {"value": v, "unit": "pivots/s", "cores": 1, "kind": "port",
+                                "sample": f"oracle (oracle/simplex_oracle.c), first {p} pivots of the same LP, "
+                                          f"{dt:.1f} s, 1 thread; host has {os.cpu_count()} cores"}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

@@ -79,6 +79,18 @@ int mvb_device_init(int device);
 /* CUDA: number of kernels this library launched since load (bench evidence) */
 unsigned long long mvb_kernel_launches(void);
 
+/* measurement hooks (bench.py): CUDA events on the engine's launch stream
+ * (oracle: host clock).  slot in [0,16) */
+int mvb_timer_record(int slot);
+/* waits for slot b; milliseconds between the two records */
+double mvb_timer_elapsed_ms(int a, int b);
+/* CUDA: overwrite a buffer larger than L2 so the next step starts cold */
+int mvb_flush_l2(void);
+/* device time of the last solve kernel alone (CUDA events around the launch) */
+double mvb_last_kernel_ms(void);
+/* shape of the last launch: CTAs per LP, groups, threads per CTA */
+int mvb_last_launch(int *ctas_per_lp, int *groups, int *threads);
+
 /* ---- LP objects ---- */
 /* new empty LP with room for row_cap rows (grown on demand) */
 mvb_lp *mvb_lp_create(int m, int n, int row_cap);

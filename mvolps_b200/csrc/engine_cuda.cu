@@ -615,6 +615,10 @@ struct DeviceCtx {
   unsigned *ctrs = nullptr; int ctrs_cap = 0;
   LPDev *dlps = nullptr; int dlps_cap = 0;
   char *stage = nullptr; size_t stage_cap = 0;   // device staging (row gathers, new rows)
+  cudaEvent_t ev[16] = {};
+  cudaEvent_t kev[2] = {};
+  char *flush = nullptr; size_t flush_bytes = 0;
+  int last_G = 0, last_groups = 0;
 };
 DeviceCtx g_ctx;
 
@@ -1015,9 +1019,14 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
   unsigned *ctrs = g_ctx.ctrs;
   int tcl = -1;
   void *args[] = {(void *)&dl, (void *)&count, (void *)&G, (void *)&ctrs, (void *)&tcl};
+  if (!g_ctx.kev[0]) { CKI(cudaEventCreate(&g_ctx.kev[0])); CKI(cudaEventCreate(&g_ctx.kev[1])); }
+  CKI(cudaEventRecord(g_ctx.kev[0], st));
   CKI(cudaLaunchCooperativeKernel((const void *)simplex_kernel, dim3(ngroups * G), dim3(g_ctx.nt),
                                   args, 0, st));
+  CKI(cudaEventRecord(g_ctx.kev[1], st));
   g_launches++;
+  g_ctx.last_G = G;
+  g_ctx.last_groups = ngroups;
   for (int k = 0; k < count; k++)
     CKI(cudaMemcpyAsync(lps[k]->outbox.data(), lps[k]->slab + lps[k]->out_off, lps[k]->out_bytes,
                         cudaMemcpyDeviceToHost, st));
@@ -1100,6 +1109,50 @@ int mvb_lp_get_pivot_log(mvb_lp *lp, int *rowcol, int cap) {
     CKI(cudaStreamSynchronize(g_ctx.stream));
   }
   return lp->pivlog_n;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int mvb_timer_record(int slot) {
+  if (!ctx_init(-1)) return -1;
+  slot &= 15;
+  if (!g_ctx.ev[slot]) CKI(cudaEventCreate(&g_ctx.ev[slot]));
+  CKI(cudaEventRecord(g_ctx.ev[slot], g_ctx.stream));
+  return 0;
+}
+
+double mvb_timer_elapsed_ms(int a, int b) {
+  float ms = -1.0f;
+  if (cudaEventSynchronize(g_ctx.ev[b & 15]) != cudaSuccess) return -1.0;
+  if (cudaEventElapsedTime(&ms, g_ctx.ev[a & 15], g_ctx.ev[b & 15]) != cudaSuccess) return -1.0;
+  return ms;
+}
+
+double mvb_last_kernel_ms(void) {
+  float ms = -1.0f;
+  if (!g_ctx.kev[1] || cudaEventSynchronize(g_ctx.kev[1]) != cudaSuccess) return -1.0;
+  if (cudaEventElapsedTime(&ms, g_ctx.kev[0], g_ctx.kev[1]) != cudaSuccess) return -1.0;
+  return ms;
+}
+
+int mvb_flush_l2(void) {
+  if (!ctx_init(-1)) return -1;
+  if (!g_ctx.flush) {
+    g_ctx.flush_bytes = (size_t)256 << 20;  // > 126 MB L2
+    CKI(cudaMalloc((void **)&g_ctx.flush, g_ctx.flush_bytes));
+  }
+  static int v = 0;
+  CKI(cudaMemsetAsync(g_ctx.flush, ++v & 0xff, g_ctx.flush_bytes, g_ctx.stream));
+  return 0;
+}
+
+int mvb_last_launch(int *c, int *g, int *t) {
+  if (c) *c = g_ctx.last_G;
+  if (g) *g = g_ctx.last_groups;
+  if (t) *t = g_ctx.nt;
+  return 0;
 }
 
 }  // extern "C"

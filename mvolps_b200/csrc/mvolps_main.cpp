@@ -1,0 +1,76 @@
+// mvolps_main.cpp -- command line of the B200 build; same flags and file-type
+// rule as the reference's main (2test.cpp:13-157, InputParser.h:8-35), running
+// the batched driver (bnb_driver.cpp) instead of the serial one.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "../../include/glpk.h"
+#include "../../include/mvolps_bnb.h"
+#include "../../include/mvolps_engine.h"
+
+namespace {
+// presence + next-token lookup, as InputParser.h:16-31
+struct Args {
+  std::vector<std::string> tokens;
+  Args(int argc, char **argv) { for (int i = 1; i < argc; i++) tokens.emplace_back(argv[i]); }
+  bool has(const std::string &o) const { return std::find(tokens.begin(), tokens.end(), o) != tokens.end(); }
+  std::string get(const std::string &o) const {
+    auto it = std::find(tokens.begin(), tokens.end(), o);
+    if (it != tokens.end() && ++it != tokens.end()) return *it;
+    return "";
+  }
+};
+}  // namespace
+
+int main(int argc, char **argv) {
+  Args in(argc, argv);
+  if (in.has("-h") || in.has("--help")) {
+    std::cout << "Usage: mvolps_b200 [OPTION]\n"
+              << "  -f [FILENAME.{mps|lp}]\n"
+              << "  -s/--silent  -v/--verbose  -d/--debug  -so/--solver-output\n"
+              << "  -vs [{0|1|2}]  variable choice: order | fractional part | objective impact\n"
+              << "  -bs [{0|1}]    node choice: FIFO | best bound\n"
+              << "  -cm [{0|1|2}]  cuts: off | reference gmi.cpp formula | textbook GMI\n"
+              << "  -bw N          FIFO nodes solved per device launch (default 256)\n"
+              << "  -nl N          node budget\n";
+    return 0;
+  }
+  glp_term_out(GLP_OFF);
+  if (in.has("-d") || in.has("--debug") || in.has("-so") || in.has("--solver-output")) glp_term_out(GLP_ON);
+  if (!in.has("-f")) { std::cout << "see ./mvolps_b200 -h for usage\n"; return 0; }
+  std::string fn = in.get("-f");
+  std::string ext = fn.substr(fn.find_last_of('.') == std::string::npos ? 0 : fn.find_last_of('.'));
+  glp_prob *prob = glp_create_prob();
+  int rc;
+  if (ext == ".lp") rc = glp_read_lp(prob, nullptr, fn.c_str());
+  else if (ext == ".mps") rc = glp_read_mps(prob, GLP_MPS_FILE, nullptr, fn.c_str());
+  else { std::cout << "Unrecognized filetype\n"; return -1; }
+  if (rc) std::exit(-1);  // util.cpp:284-292
+  mvb_bnb_params p{};
+  auto ival = [&](const char *flag, int lo, int hi, int &dst) {
+    if (!in.has(flag)) return true;
+    int v = std::atoi(in.get(flag).c_str());
+    if (v < lo || v > hi) { std::fprintf(stderr, "Unknown parameter value for %s\n", flag); return false; }
+    dst = v;
+    return true;
+  };
+  if (!ival("-bs", 0, 1, p.node_strategy) || !ival("-vs", 0, 2, p.var_strategy) ||
+      !ival("-cm", 0, 2, p.cut_mode) || !ival("-bw", 1, 1 << 20, p.batch_width) ||
+      !ival("-nl", 1, 1 << 30, p.max_iters))
+    return -1;
+  if (mvb_device_init(0)) { std::fprintf(stderr, "%s\n", mvb_last_error()); return 2; }
+  mvb_bnb *h = mvb_bnb_run(prob, &p);
+  if (!h) return 2;
+  if (!in.has("-s") && !in.has("--silent")) {
+    const mvb_bnb_stats *st = mvb_bnb_get_stats(h);
+    std::printf("[%s] %d iterations, %d LP solves in %d launches, %lld simplex iterations\n",
+                mvb_backend(), st->iterations, st->lp_solves, st->launches, st->simplex_iters);
+  }
+  mvb_bnb_free(h);
+  glp_delete_prob(prob);
+  return 0;
+}

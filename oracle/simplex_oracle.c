@@ -54,6 +54,19 @@ const char *mvb_last_error(void) { return g_err; }
 int mvb_device_init(int device) { (void)device; return 0; }
 unsigned long long mvb_kernel_launches(void) { return 0ULL; }
 
+#include <time.h>
+static double g_slots[16];
+int mvb_timer_record(int slot) {
+  struct timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  g_slots[slot & 15] = ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+  return 0;
+}
+double mvb_timer_elapsed_ms(int a, int b) { return g_slots[b & 15] - g_slots[a & 15]; }
+int mvb_flush_l2(void) { return 0; }
+double mvb_last_kernel_ms(void) { return 0.0; }
+int mvb_last_launch(int *c, int *g, int *t) { if (c) *c = 0; if (g) *g = 0; if (t) *t = 0; return 0; }
+
 static int round_up(int x, int a) { return (x + a - 1) / a * a; }
 
 static void lp_release(mvb_lp *lp) {
