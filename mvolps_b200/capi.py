@@ -3,7 +3,7 @@
 `load_product()` opens mvolps_b200/lib/libglpk_b200.so (CUDA engine) and fails
 loudly when it is missing -- there is no CPU fallback in the product.
 `load_library(path)` binds the same symbols of any library exporting them; the
-tests use it to open the oracle build (oracle/_build/libglpk_oracle.so).
+tests use it to open the test-only CPU oracle build.
 """
 import ctypes as C
 import os

@@ -62,14 +62,14 @@ def write_lp(inst, path):
         t = []
         for j, v in enumerate(row):
             if v != 0:
-                t.append(f"{'+' if v >= 0 else '-'} {abs(v)!r} x{j + 1}")
+                t.append(f"{'+' if v >= 0 else '-'} {float(abs(v))!r} x{j + 1}")
         return " ".join(t) if t else "0 x1"
 
     with open(path, "w") as f:
         f.write("Maximize\n" if inst["sense"] == "max" else "Minimize\n")
         f.write(" obj: " + expr(c) + "\nSubject To\n")
         for i in range(m):
-            lo, hi = inst["row_lb"][i], inst["row_ub"][i]
+            lo, hi = float(inst["row_lb"][i]), float(inst["row_ub"][i])
             if lo == hi:
                 f.write(f" c{i + 1}: {expr(A[i])} = {lo!r}\n")
             elif np.isfinite(hi):

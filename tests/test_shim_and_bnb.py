@@ -1,0 +1,215 @@
+"""CPU tests of the host side: the glpk-subset shim (include/glpk.h), the LP/MPS
+readers, and the batched B&B driver (include/mvolps_bnb.h) against (i) the
+reference's own unmodified driver, recorded in tests/golden/bnb_golden.json,
+(ii) that driver run live where oracle/_ref exists, (iii) SciPy/HiGHS MILP."""
+import hashlib
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from mvolps_b200 import capi, instances
+from mvolps_b200.lp import GlpProb
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+SMALL3 = os.path.join(ROOT, "examples", "small3.lp")
+FLAGS = {"-bs": "node_strategy", "-vs": "var_strategy", "-cm": "cut_mode"}
+
+
+def _gold():
+    with open(os.path.join(GOLDEN, "bnb_golden.json")) as f:
+        return json.load(f)["cases"]
+
+
+def _kwargs(flags):
+    return {FLAGS[flags[i]]: int(flags[i + 1]) for i in range(0, len(flags), 2)}
+
+
+def _prob(lib, case, tmp_path):
+    if case["gen"] is None:
+        return GlpProb.from_file(lib, SMALL3)
+    inst = getattr(instances, case["gen"])(*case["args"])
+    path = str(tmp_path / (case["name"] + ".lp"))
+    instances.write_lp(inst, path)
+    return GlpProb.from_file(lib, path)
+
+
+# ---------------------------------------------------------------- shim
+def test_read_lp_small3(oracle):
+    p = GlpProb.from_file(oracle, SMALL3)
+    L, h = oracle, p.h
+    assert (p.nrows, p.ncols, L.glp_get_num_int(h)) == (4, 3, 3)
+    assert L.glp_get_obj_dir(h) == capi.GLP_MAX
+    assert [L.glp_get_obj_coef(h, j) for j in range(4)] == [0.0, 1.0, 1.0, 1.0]
+    assert [L.glp_get_row_type(h, i) for i in range(1, 5)] == [capi.GLP_UP] * 4
+    assert [L.glp_get_row_ub(h, i) for i in range(1, 5)] == [4877.0, 6750.0, 4587.0, 6911.0]
+    assert [L.glp_get_col_type(h, j) for j in range(1, 4)] == [capi.GLP_DB] * 3
+    assert [L.glp_get_col_kind(h, j) for j in range(1, 4)] == [capi.GLP_IV] * 3
+    ind = np.zeros(4, np.int32)
+    val = np.zeros(4)
+    assert L.glp_get_mat_row(h, 3, capi.iptr(ind), capi.dptr(val)) == 3
+    assert dict(zip(ind[1:].tolist(), val[1:].tolist())) == {1: 2.0, 2: 9.0, 3: 4.0}
+
+
+def test_simplex_status_and_accessors(oracle):
+    p = GlpProb.from_file(oracle, SMALL3)
+    assert p.status() == capi.GLP_UNDEF
+    assert p.simplex() == 0 and p.status() == capi.GLP_OPT
+    x = p.col_prim()
+    assert abs(p.obj_val() - x.sum()) < 1e-9 and p.obj_val() > 1202.0
+    L, h = oracle, p.h
+    stats = [L.glp_get_col_stat(h, j) for j in range(1, 4)] + [L.glp_get_row_stat(h, i) for i in range(1, 5)]
+    assert stats.count(capi.GLP_BS) == 4  # m basic variables
+    # glp_eval_tab_row: x_B = sum alpha_k xN_k reproduces the basic variable's value
+    for j in range(1, 4):
+        if L.glp_get_col_stat(h, j) != capi.GLP_BS:
+            continue
+        ind, val = p.eval_tab_row(4 + j)
+        tot = 0.0
+        for k, a in zip(ind, val):
+            assert L.glp_get_row_stat(h, k) != capi.GLP_BS if k <= 4 else L.glp_get_col_stat(h, k - 4) != capi.GLP_BS
+            tot += a * (L.glp_get_row_prim(h, k) if k <= 4 else L.glp_get_col_prim(h, k - 4))
+        assert abs(tot - x[j - 1]) <= 1e-9 * max(1.0, abs(x[j - 1]))
+        assert list(ind) == sorted(ind)  # documented ordering: ascending variable index
+
+
+def test_copy_prob_carries_basis_and_bound_replacement(oracle):
+    """bs.cpp:114-117 (copy, re-solve: 0 iterations) and bs.cpp:274/282 (type replaced)."""
+    L = oracle
+    p = GlpProb.from_file(L, SMALL3)
+    p.simplex()
+    q = p.copy()
+    assert q.simplex() == 0 and L.glp_get_it_cnt(q.h) == 0 and q.obj_val() == p.obj_val()
+    x = p.col_prim()
+    j = int(np.argmax(x != np.floor(x))) + 1
+    L.glp_set_col_bnds(q.h, j, capi.GLP_UP, 0.0, float(np.floor(x[j - 1])))
+    assert L.glp_get_col_type(q.h, j) == capi.GLP_UP
+    assert L.glp_get_col_lb(q.h, j) == -np.finfo(np.float64).max  # lower bound dropped
+    q.simplex()
+    assert q.status() == capi.GLP_OPT and q.obj_val() <= p.obj_val()
+    assert L.glp_get_col_prim(q.h, j) <= np.floor(x[j - 1]) + 1e-9
+    L.glp_erase_prob(q.h)
+    assert q.nrows == 0 and q.ncols == 0
+
+
+def test_add_cut_row_like_cutpool(oracle):
+    """cut.cpp:23,40-43: glp_add_rows(1) + glp_set_row_bnds(GLP_LO) + glp_set_mat_row with ind[0] junk."""
+    L = oracle
+    p = GlpProb.from_file(L, SMALL3)
+    p.simplex()
+    z0 = p.obj_val()
+    r = L.glp_add_rows(p.h, 1)
+    assert r == 5
+    ind = np.array([0, 1, 2, 3], np.int32)
+    val = np.array([123.0, -1.0, -1.0, -1.0])
+    L.glp_set_mat_row(p.h, r, 3, capi.iptr(ind), capi.dptr(val))
+    L.glp_set_row_bnds(p.h, r, capi.GLP_LO, -1200.0, 0.0)  # x1+x2+x3 <= 1200
+    p.simplex()
+    assert p.status() == capi.GLP_OPT and abs(p.obj_val() - 1200.0) < 1e-9 < z0 - 1200.0
+
+
+def test_read_mps_roundtrip(oracle, tmp_path):
+    mps = tmp_path / "t.mps"
+    mps.write_text(
+        "NAME          T\nROWS\n N  COST\n L  C1\n G  C2\n E  C3\nCOLUMNS\n"
+        "    MARKER    'MARKER'  'INTORG'\n"
+        "    X  COST  1.0  C1  1.0\n    X  C2  1.0\n"
+        "    MARKER    'MARKER'  'INTEND'\n"
+        "    Y  COST  2.0  C1  1.0\n    Y  C3  1.0\n"
+        "RHS\n    RHS  C1  4.0  C2  1.0\n    RHS  C3  1.5\n"
+        "BOUNDS\n UP BND  X  3.0\nENDATA\n")
+    p = GlpProb.from_file(oracle, str(mps))
+    L, h = oracle, p.h
+    assert (p.nrows, p.ncols) == (3, 2)
+    assert [L.glp_get_row_type(h, i) for i in (1, 2, 3)] == [capi.GLP_UP, capi.GLP_LO, capi.GLP_FX]
+    assert L.glp_get_col_kind(h, 1) == capi.GLP_IV and L.glp_get_col_kind(h, 2) == capi.GLP_CV
+    assert L.glp_get_obj_dir(h) == capi.GLP_MIN
+    p.simplex()
+    assert p.status() == capi.GLP_OPT and abs(p.obj_val() - 4.0) < 1e-12  # x=1, y=1.5
+
+
+def test_read_errors(oracle, tmp_path):
+    bad = tmp_path / "bad.lp"
+    bad.write_text("Maximize\n obj: x +\nSubject To\n c1: x <= \nEnd\n")
+    with pytest.raises(ValueError):
+        GlpProb.from_file(oracle, str(bad))
+    with pytest.raises(ValueError):
+        GlpProb.from_file(oracle, str(tmp_path / "missing.lp"))
+
+
+def test_bv_kind_reported_for_01_integer(oracle, tmp_path):
+    lp = tmp_path / "b.lp"
+    lp.write_text("Maximize\n obj: x + y\nSubject To\n c: x + y <= 1.5\nBinary\n x\nGeneral\n y\nEnd\n")
+    p = GlpProb.from_file(oracle, str(lp))
+    assert oracle.glp_get_col_kind(p.h, 1) == capi.GLP_BV and oracle.glp_get_col_kind(p.h, 2) == capi.GLP_IV
+
+
+# ---------------------------------------------------------------- B&B driver
+@pytest.mark.parametrize("case", _gold(), ids=lambda c: c["name"])
+def test_bnb_matches_recorded_reference_driver(oracle, case, tmp_path):
+    """Batched driver == the reference's bs.cpp run (recorded): tree, solution string, count."""
+    out = _prob(oracle, case, tmp_path).bnb(**_kwargs(case["flags"]))
+    tree = [ln for ln in out["tree"].splitlines() if ln.strip()]
+    assert len(tree) == case["tree_lines"]
+    assert tree[: len(case["tree"])] == case["tree"]
+    assert hashlib.sha256("\n".join(tree).encode()).hexdigest() == case["tree_sha256"]
+    assert out["solution"].strip() == case["solution"]
+    assert out["iterations"] == case["iterations"]
+
+
+@pytest.mark.parametrize("width", [1, 2, 7, 64])
+def test_bnb_batch_width_invariance(oracle, width, tmp_path):
+    """FIFO batches of any width give the serial run's oids/prunes/incumbents."""
+    case = [c for c in _gold() if c["name"] == "mdkp_12x4_s1"][0]
+    base = _prob(oracle, case, tmp_path).bnb(batch_width=1)
+    out = _prob(oracle, case, tmp_path).bnb(batch_width=width)
+    for k in ("tree", "solution", "events", "event_hash", "iterations", "oids", "incumbent"):
+        assert out[k] == base[k], k
+    if width > 1:
+        assert out["launches"] < base["launches"]
+
+
+@pytest.mark.parametrize("name", ["small3", "mdkp_12x4_s1", "mdkp_12x4_s4_cm1"])
+def test_bnb_optimum_vs_highs(oracle, name, tmp_path):
+    case = [c for c in _gold() if c["name"] == name][0]
+    out = _prob(oracle, case, tmp_path).bnb(**_kwargs(case["flags"]))
+    assert out["has_incumbent"]
+    assert abs(out["incumbent"] - case["highs_ilp"]) <= 1e-9 * abs(case["highs_ilp"])
+    assert np.array_equal(out["x"], np.round(out["x"]))
+
+
+def test_bnb_textbook_gmi_is_valid(oracle, tmp_path):
+    """cut_mode 2 (textbook GMI off the tableau row) never cuts off the ILP optimum."""
+    for name in ("small3", "mdkp_12x4_s1", "mdkp_12x4_s4_cm1"):
+        case = [c for c in _gold() if c["name"] == name][0]
+        out = _prob(oracle, case, tmp_path).bnb(cut_mode=2)
+        assert out["has_incumbent"], name
+        assert abs(out["incumbent"] - case["highs_ilp"]) <= 1e-9 * abs(case["highs_ilp"]), name
+
+
+def test_bnb_node_budget_and_events(oracle, tmp_path):
+    case = [c for c in _gold() if c["name"] == "mdkp_15x5_s2"][0]
+    out = _prob(oracle, case, tmp_path).bnb(max_iters=50)
+    assert out["hit_limit"] == 1 and out["iterations"] == 50
+    full = _prob(oracle, case, tmp_path).bnb()
+    ev, evf = out["events"].splitlines(), full["events"].splitlines()
+    assert ev and evf[: len(ev)] == ev  # the budgeted run is a prefix of the full run
+    assert re.match(r"^\w+ \d+ -?\d+ ", ev[0])
+
+
+def test_bnb_live_reference_driver(oracle, ref_bin, tmp_path):
+    """Where /root/reference was compiled (oracle/_ref): run it now and compare stdout."""
+    inst = instances.mdkp(11, 4, 9)
+    path = str(tmp_path / "live.lp")
+    instances.write_lp(inst, path)
+    p = subprocess.run([ref_bin, "-f", path], capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0
+    tree = [ln for ln in p.stdout.splitlines() if re.fullmatch(r"\s*-\d+( [IFB])?\s*", ln)]
+    sol = [ln.strip() for ln in p.stdout.splitlines() if "Solution is:" in ln]
+    out = GlpProb.from_file(oracle, path).bnb()
+    assert [ln for ln in out["tree"].splitlines() if ln.strip()] == tree
+    assert out["solution"].strip() == (sol[-1] if sol else "")
