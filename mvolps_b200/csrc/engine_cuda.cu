@@ -23,6 +23,7 @@
 #include <atomic>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -382,9 +383,18 @@ __device__ __forceinline__ bool primal_ratio_row(double alpha, int dir, int s, d
   return true;
 }
 
+}  // namespace
+
+#include "engine_ps.cuh"
+
+namespace {
+
 // One whole LP solve by a group of G CTAs (this CTA is number g of it).
+// dyn != nullptr: the launch carries enough dynamic shared memory for the
+// private-state loop (engine_ps.cuh), used unless the LP needs phase 1.
+template <bool PSK>
 __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &gen, int tcl,
-                         Smem &sm) {
+                         Smem &sm, unsigned char *dyn) {
   const int m = L.m, n = L.n, ld = L.ld, tid = threadIdx.x, NT = blockDim.x;
   int cT = L.curT, cS = L.curS;
   Tally ty;
@@ -404,7 +414,15 @@ __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &
   else if (count_dual_infeas(L, cT, cS, sm) == 0) mode = MVB_MODE_DUAL;
   else mode = MVB_MODE_PRIMAL1;
 
-  while (true) {
+  if (PSK) {
+    if (mode == MVB_MODE_PRIMAL1) {  // needs the general kernel: nothing has been changed yet
+      if (g == 0 && tid == 0) L.res->r.status = MVB_PS_FALLBACK;
+      return;
+    }
+    status = ps_loop(L, g, G, ctr, gen, tcl, dyn, mode, cT, cS, ty);
+  }
+
+  while (!PSK) {
     const bool bland = degen >= MVB_BLAND_AFTER;
     const double *T = L.T[cT];
     const double *beta = L.beta[cS];
@@ -581,21 +599,40 @@ __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &
 
 // grid = ngroups * G CTAs (all co-resident: cooperative launch); group k owns
 // LPs k, k + ngroups, ...
-__global__ void __launch_bounds__(512, 1)
-simplex_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
+template <bool PSK>
+__device__ __forceinline__ void kernel_body(const LPDev *lps, int nlp, int G, unsigned *ctrs,
+                                            int tcl, unsigned char *dyn) {
   __shared__ Smem sm;
+  __shared__ LPDev L;
   const int group = blockIdx.x / G, g = blockIdx.x - group * G, ngroups = gridDim.x / G;
   unsigned gen = 0;
   for (int k = group; k < nlp; k += ngroups) {
-    const LPDev L = lps[k];
+    __syncthreads();
+    if (threadIdx.x == 0) L = lps[k];
+    __syncthreads();
     int t = tcl;
     if (t < 0) {  // per-LP thread shape: columns = pow2 >= ld/2, capped at the block
       t = 0;
       while ((1 << t) < (L.ld + 1) / 2 && (2 << t) <= (int)blockDim.x) t++;
     }
-    solve_lp(L, g, G, ctrs + group, gen, t, sm);
-    __syncthreads();
+    solve_lp<PSK>(L, g, G, ctrs + group, gen, t, sm, dyn);
   }
+}
+
+// grid = ngroups * G CTAs (all co-resident: cooperative launch); group k owns
+// LPs k, k + ngroups, ...
+__global__ void __launch_bounds__(512, 1)
+simplex_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
+  kernel_body<false>(lps, nlp, G, ctrs, tcl, nullptr);
+}
+
+// private-state variant (engine_ps.cuh): every LP of the launch fits the
+// dynamic shared memory; LPs that turn out to need phase 1 come back with
+// status MVB_PS_FALLBACK and are re-run by simplex_kernel.
+__global__ void __launch_bounds__(512, 1)
+simplex_ps_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
+  extern __shared__ __align__(128) unsigned char dyn_smem[];
+  kernel_body<true>(lps, nlp, G, ctrs, tcl, dyn_smem);
 }
 
 }  // namespace
@@ -619,6 +656,10 @@ struct DeviceCtx {
   cudaEvent_t kev[2] = {};
   char *flush = nullptr; size_t flush_bytes = 0;
   int last_G = 0, last_groups = 0;
+  bool last_ps = false;
+  int max_ctas_ps = 0;     // co-resident CTAs of simplex_ps_kernel with max_dyn
+  size_t max_dyn = 0;      // dynamic shared memory simplex_kernel may ask for
+  bool no_ps = false;      // MVOLPS_NO_PS=1: general loop only (debugging / A-B timing)
 };
 DeviceCtx g_ctx;
 
@@ -649,10 +690,21 @@ bool ctx_init(int device) {
   CK(cudaDeviceGetDefaultMemPool(&pool, device));
   unsigned long long keep = ~0ULL;  // keep freed slabs cached for reuse
   CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+  int optin = 0;
+  CK(cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+  cudaFuncAttributes fa;
+  CK(cudaFuncGetAttributes(&fa, simplex_ps_kernel));
+  g_ctx.max_dyn = (size_t)optin > fa.sharedSizeBytes + 1024 ? (size_t)optin - fa.sharedSizeBytes - 1024 : 0;
+  CK(cudaFuncSetAttribute(simplex_ps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_ctx.max_dyn));
+  const char *nops = getenv("MVOLPS_NO_PS");
+  g_ctx.no_ps = nops && nops[0] == '1';
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_kernel, g_ctx.nt, 0));
   if (per_sm < 1) return fail("simplex_kernel does not fit an SM");
   g_ctx.max_ctas = per_sm * g_ctx.sms;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_ps_kernel, g_ctx.nt, g_ctx.max_dyn));
+  if (per_sm < 1) return fail("simplex_ps_kernel does not fit an SM");
+  g_ctx.max_ctas_ps = per_sm * g_ctx.sms;
   g_ctx.ready = true;
   return true;
 }
@@ -969,13 +1021,70 @@ extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double 
   return 0;
 }
 
+namespace {
+
+// one cooperative launch over the LPs `idx` (indices into lps), results into the outboxes
+bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opts *opts, bool psk) {
+  const int count = (int)idx.size();
+  if (!count) return true;
+  cudaStream_t st = g_ctx.stream;
+  std::vector<LPDev> h(count);
+  size_t max_bytes = 0, dyn = 0;
+  for (int k = 0; k < count; k++) {
+    mvb_lp *lp = lps[idx[k]];
+    h[k] = lp->dev;
+    max_bytes = std::max(max_bytes, (size_t)(lp->m + 1) * lp->ld * sizeof(double));
+    if (psk) dyn = std::max(dyn, ps_smem_bytes(lp->m, lp->ld));
+  }
+  const int max_ctas = psk ? g_ctx.max_ctas_ps : g_ctx.max_ctas;
+  // CTAs per LP: by tableau size, bounded by what is co-resident
+  const size_t per_cta = psk ? (96 << 10) : (128 << 10);
+  int G = (opts && opts->ctas_per_lp > 0) ? opts->ctas_per_lp
+                                          : (int)std::min<size_t>((max_bytes + per_cta - 1) / per_cta, (size_t)max_ctas);
+  if (!(opts && opts->ctas_per_lp > 0) && count > 1) G = std::max(1, std::min(G, max_ctas / count));
+  G = std::max(1, std::min(G, max_ctas));
+  int ngroups = std::max(1, std::min(count, max_ctas / G));
+  if (g_ctx.ctrs_cap < ngroups) {
+    if (g_ctx.ctrs) CK(cudaFreeAsync(g_ctx.ctrs, st));
+    CK(cudaMallocAsync((void **)&g_ctx.ctrs, (size_t)ngroups * sizeof(unsigned), st));
+    g_ctx.ctrs_cap = ngroups;
+  }
+  if (g_ctx.dlps_cap < count) {
+    if (g_ctx.dlps) CK(cudaFreeAsync(g_ctx.dlps, st));
+    CK(cudaMallocAsync((void **)&g_ctx.dlps, (size_t)count * sizeof(LPDev), st));
+    g_ctx.dlps_cap = count;
+  }
+  CK(cudaMemsetAsync(g_ctx.ctrs, 0, (size_t)ngroups * sizeof(unsigned), st));
+  CK(cudaMemcpyAsync(g_ctx.dlps, h.data(), (size_t)count * sizeof(LPDev), cudaMemcpyHostToDevice, st));
+  const LPDev *dl = g_ctx.dlps;
+  unsigned *ctrs = g_ctx.ctrs;
+  int tcl = -1, cnt = count;
+  void *args[] = {(void *)&dl, (void *)&cnt, (void *)&G, (void *)&ctrs, (void *)&tcl};
+  if (!g_ctx.kev[0]) { CK(cudaEventCreate(&g_ctx.kev[0])); CK(cudaEventCreate(&g_ctx.kev[1])); }
+  CK(cudaEventRecord(g_ctx.kev[0], st));
+  CK(cudaLaunchCooperativeKernel(psk ? (const void *)simplex_ps_kernel : (const void *)simplex_kernel,
+                                 dim3(ngroups * G), dim3(g_ctx.nt), args, dyn, st));
+  CK(cudaEventRecord(g_ctx.kev[1], st));
+  g_launches++;
+  g_ctx.last_G = G;
+  g_ctx.last_groups = ngroups;
+  g_ctx.last_ps = psk;
+  for (int k = 0; k < count; k++) {
+    mvb_lp *lp = lps[idx[k]];
+    CK(cudaMemcpyAsync(lp->outbox.data(), lp->slab + lp->out_off, lp->out_bytes, cudaMemcpyDeviceToHost, st));
+  }
+  CK(cudaStreamSynchronize(st));
+  return true;
+}
+
+}  // namespace
+
 extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *opts,
                                mvb_result *out) {
   if (count <= 0) return 0;
   if (!ctx_init(-1)) return -1;
   cudaStream_t st = g_ctx.stream;
-  std::vector<LPDev> h(count);
-  size_t max_bytes = 0;
+  std::vector<int> ps_idx, gen_idx;
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[k];
     if (!lp_push_small(lp)) return -1;
@@ -994,43 +1103,19 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     lp->dev.max_iters = mi;
     lp->dev.pivlog = (opts && opts->log_pivots) ? lp->pivlog : nullptr;
     lp->dev.pivlog_cap = lp->dev.pivlog ? lp->pivlog_cap : 0;
-    h[k] = lp->dev;
-    max_bytes = std::max(max_bytes, (size_t)(lp->m + 1) * lp->ld * sizeof(double));
+    const bool fits = !g_ctx.no_ps && lp->m >= 1 && ps_smem_bytes(lp->m, lp->ld) <= g_ctx.max_dyn &&
+                      lp->m + 1 <= PS_CREG * g_ctx.nt;
+    (fits ? ps_idx : gen_idx).push_back(k);
   }
-  // CTAs per LP: by tableau size, bounded by what is co-resident
-  int G = (opts && opts->ctas_per_lp > 0) ? opts->ctas_per_lp
-                                          : (int)std::min<size_t>((max_bytes + (128 << 10) - 1) / (128 << 10), (size_t)g_ctx.max_ctas);
-  if (!(opts && opts->ctas_per_lp > 0) && count > 1) G = std::max(1, std::min(G, g_ctx.max_ctas / count));
-  G = std::max(1, std::min(G, g_ctx.max_ctas));
-  int ngroups = std::max(1, std::min(count, g_ctx.max_ctas / G));
-  if (g_ctx.ctrs_cap < ngroups) {
-    if (g_ctx.ctrs) CKI(cudaFreeAsync(g_ctx.ctrs, st));
-    CKI(cudaMallocAsync((void **)&g_ctx.ctrs, (size_t)ngroups * sizeof(unsigned), st));
-    g_ctx.ctrs_cap = ngroups;
+  // private-state kernel first; what needs phase 1 (or does not fit) goes to the general one
+  if (!launch_solve(lps, ps_idx, opts, true)) return -1;
+  for (int k : ps_idx) {
+    mvb_lp *lp = lps[k];
+    const DevResult *dr = (const DevResult *)(lp->outbox.data() + ((const char *)lp->dev.res - (lp->slab + lp->out_off)));
+    if (dr->r.status == MVB_PS_FALLBACK) gen_idx.push_back(k);
   }
-  if (g_ctx.dlps_cap < count) {
-    if (g_ctx.dlps) CKI(cudaFreeAsync(g_ctx.dlps, st));
-    CKI(cudaMallocAsync((void **)&g_ctx.dlps, (size_t)count * sizeof(LPDev), st));
-    g_ctx.dlps_cap = count;
-  }
-  CKI(cudaMemsetAsync(g_ctx.ctrs, 0, (size_t)ngroups * sizeof(unsigned), st));
-  CKI(cudaMemcpyAsync(g_ctx.dlps, h.data(), (size_t)count * sizeof(LPDev), cudaMemcpyHostToDevice, st));
-  const LPDev *dl = g_ctx.dlps;
-  unsigned *ctrs = g_ctx.ctrs;
-  int tcl = -1;
-  void *args[] = {(void *)&dl, (void *)&count, (void *)&G, (void *)&ctrs, (void *)&tcl};
-  if (!g_ctx.kev[0]) { CKI(cudaEventCreate(&g_ctx.kev[0])); CKI(cudaEventCreate(&g_ctx.kev[1])); }
-  CKI(cudaEventRecord(g_ctx.kev[0], st));
-  CKI(cudaLaunchCooperativeKernel((const void *)simplex_kernel, dim3(ngroups * G), dim3(g_ctx.nt),
-                                  args, 0, st));
-  CKI(cudaEventRecord(g_ctx.kev[1], st));
-  g_launches++;
-  g_ctx.last_G = G;
-  g_ctx.last_groups = ngroups;
-  for (int k = 0; k < count; k++)
-    CKI(cudaMemcpyAsync(lps[k]->outbox.data(), lps[k]->slab + lps[k]->out_off, lps[k]->out_bytes,
-                        cudaMemcpyDeviceToHost, st));
-  CKI(cudaStreamSynchronize(st));
+  std::sort(gen_idx.begin(), gen_idx.end());
+  if (!launch_solve(lps, gen_idx, opts, false)) return -1;
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[k];
     const char *ob = lp->outbox.data();

@@ -116,8 +116,6 @@ struct PS {
   Key (*slot)[32];
   unsigned long long *mbar;
   double *scal;                            // broadcast scratch (8 doubles)
-  int par;
-  unsigned mphase;
 };
 
 __host__ __device__ inline size_t ps_smem_bytes(int m, int ld) {
@@ -145,8 +143,6 @@ __device__ inline void ps_carve(PS &S, unsigned char *base, int m, int ld) {
   S.nbv = (int *)take((size_t)ld * 4);
   S.atv = (int *)take((size_t)ld * 4);
   S.head = (int *)take((size_t)(m + 2) * 4);
-  S.par = 0;
-  S.mphase = 0;
 }
 
 }  // namespace
@@ -233,6 +229,8 @@ struct PSCtx {
   unsigned *ctr;
   unsigned gen;
   int cT;  // tableau buffer that holds T_k (read side of the pending update)
+  int par;          // block_argmin_fast slot parity (per thread, identical everywhere)
+  unsigned mphase;  // mbarrier phase of the next row load
 };
 
 // run the pending rank-1 update (if any) and signal the group
@@ -254,8 +252,8 @@ __device__ __forceinline__ void fetch_row(PSCtx &X, const Prev &pv, int r, int p
 }
 __device__ __forceinline__ void finish_row(PSCtx &X, const Prev &pv, int r, int pn) {
   PS &S = *X.S;
-  mbar_wait(S.mbar, S.mphase);
-  S.mphase ^= 1;
+  mbar_wait(S.mbar, X.mphase);
+  X.mphase ^= 1;
   if (pv.piv) {
     const double *rho = S.rho[pv.p];
     const double cr = S.col[pv.p][r];
@@ -311,7 +309,7 @@ __device__ Dec decide_primal(PSCtx &X, const Prev &pv, bool bland, int iters) {
     const Key k{bland ? 0ULL : ~dbits(fabs(dj)), S.nbv[j], j};
     if (key_less(k, bq)) bq = k;
   }
-  bq = block_argmin_fast(bq, S.slot, S.par);
+  bq = block_argmin_fast(bq, S.slot, X.par);
   int q = bq.idx;
   if (q < 0) dc.status = MVB_OPT;
   else if (iters >= L.max_iters) { dc.status = MVB_ITLIM; q = -1; }
@@ -332,7 +330,7 @@ __device__ Dec decide_primal(PSCtx &X, const Prev &pv, bool bland, int iters) {
       const Key k{dbits(t), S.head[i], i};
       if (key_less(k, bi)) bi = k;
     }
-    bi = block_argmin_fast(bi, S.slot, S.par);
+    bi = block_argmin_fast(bi, S.slot, X.par);
     const double lq = S.lbN[q], uq = S.ubN[q];
     const int fq = S.atv[q];
     const double tflip = uq - lq;
@@ -382,7 +380,7 @@ __device__ Dec decide_dual(PSCtx &X, const Prev &pv, bool bland, int iters) {
     const Key k{bland ? 0ULL : ~dbits(viol), S.head[i], i};
     if (key_less(k, best)) best = k;
   }
-  best = block_argmin_fast(best, S.slot, S.par);
+  best = block_argmin_fast(best, S.slot, X.par);
   int r = best.idx;
   if (r < 0) dc.status = MVB_OPT;
   else if (iters >= L.max_iters) { dc.status = MVB_ITLIM; r = -1; }
@@ -407,7 +405,7 @@ __device__ Dec decide_dual(PSCtx &X, const Prev &pv, bool bland, int iters) {
       const Key k{dbits(ratio), S.nbv[j], j};
       if (key_less(k, bq)) bq = k;
     }
-    bq = block_argmin_fast(bq, S.slot, S.par);
+    bq = block_argmin_fast(bq, S.slot, X.par);
     const int q = bq.idx;
     if (q < 0) {
       dc.status = MVB_NOFEAS;
@@ -462,6 +460,90 @@ __device__ void apply_state(PSCtx &X, const Dec &dc, int p) {
     }
   }
   __syncthreads();
+}
+
+}  // namespace
+
+namespace {
+
+// The private-state iteration loop of one LP (mode PRIMAL2 or DUAL; neither
+// changes mode).  Entered after the common prologue (beta[cS] valid in global
+// memory); leaves the final small state in the global arrays of parity cS and
+// the final tableau in buffer cT, as the general loop does.  Returns the status.
+__device__ int ps_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &gen, int tcl,
+                       unsigned char *dyn, int mode, int &cT, int cS, Tally &ty) {
+  const int m = L.m, n = L.n, ld = L.ld, tid = threadIdx.x, NT = blockDim.x;
+  __shared__ PS S;  // pointers into the carved dynamic shared memory
+  if (tid == 0) {
+    ps_carve(S, dyn, m, ld);
+    mbar_init(S.mbar, 1);
+  }
+  __syncthreads();
+  {
+    const double *d0 = L.T[cT];
+    const int *nb = L.nb[cS], *at = L.at[cS], *head = L.head[cS];
+    const double *beta = L.beta[cS];
+    for (int j = tid; j < ld; j += NT) {
+      if (j < n) {
+        const int k = ldcg(nb + j);
+        S.d[j] = ldcg(d0 + j);
+        S.nbv[j] = k;
+        S.atv[j] = ldcg(at + j);
+        S.lbN[j] = ldcg(L.lb + k);
+        S.ubN[j] = ldcg(L.ub + k);
+      } else {  // padding columns never price
+        S.d[j] = 0.0;
+        S.nbv[j] = 0x7fffffff;
+        S.atv[j] = MVB_AT_FX;
+        S.lbN[j] = S.ubN[j] = 0.0;
+      }
+    }
+    for (int i = tid; i <= m + 1; i += NT) {
+      if (i >= 1 && i <= m) {
+        const int k = ldcg(head + i);
+        S.beta[i] = ldcg(beta + i);
+        S.head[i] = k;
+        S.lbB[i] = ldcg(L.lb + k);
+        S.ubB[i] = ldcg(L.ub + k);
+      } else {
+        S.beta[i] = 0.0;
+        S.head[i] = 0x7fffffff;
+        S.lbB[i] = -HUGE_VAL;
+        S.ubB[i] = HUGE_VAL;
+      }
+    }
+  }
+  __syncthreads();
+
+  PSCtx X{&L, &S, g, G, tcl, ctr, gen, cT, 0, 0u};
+  Prev pv{false, 0, 0, 0};
+  int status, degen = 0;
+  while (true) {
+    const bool bland = degen >= MVB_BLAND_AFTER;
+    const Dec dc = mode == MVB_MODE_DUAL ? decide_dual(X, pv, bland, ty.iters)
+                                         : decide_primal(X, pv, bland, ty.iters);
+    if (pv.piv) X.cT ^= 1;  // the pending update has landed everywhere
+    if (dc.status >= 0) { status = dc.status; break; }
+    const int pn = pv.p ^ 1;
+    tally_iter(ty, L, g, mode, dc.r, dc.q, bland);
+    apply_state(X, dc, pn);
+    degen = dc.degenerate ? degen + 1 : 0;
+    pv.piv = dc.r != 0;
+    pv.r = dc.r;
+    pv.q = dc.q;
+    pv.p = pn;
+  }
+  gen = X.gen;
+  cT = X.cT;
+  // hand the private state back (every CTA holds the same values)
+  if (g == 0) {
+    double *beta = L.beta[cS];
+    int *head = L.head[cS], *nb = L.nb[cS], *at = L.at[cS];
+    for (int i = 1 + tid; i <= m; i += NT) { beta[i] = S.beta[i]; head[i] = S.head[i]; }
+    for (int j = tid; j < n; j += NT) { nb[j] = S.nbv[j]; at[j] = S.atv[j]; }
+  }
+  group_sync(ctr, G, gen);
+  return status;
 }
 
 }  // namespace
