@@ -57,6 +57,7 @@ struct LPDev {
   int pivlog_cap;
   int curT, curS;   // parities at entry
   int max_iters;
+  int lzK;          // pending-update depth of the lazy loop for this launch
 };
 
 namespace {
@@ -385,7 +386,7 @@ __device__ __forceinline__ bool primal_ratio_row(double alpha, int dir, int s, d
 
 }  // namespace
 
-#include "engine_ps.cuh"
+#include "engine_lz.cuh"
 
 namespace {
 
@@ -419,7 +420,7 @@ __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &
       if (g == 0 && tid == 0) L.res->r.status = MVB_PS_FALLBACK;
       return;
     }
-    status = ps_loop(L, g, G, ctr, gen, tcl, dyn, mode, cT, cS, ty);
+    status = lz_loop(L, g, G, ctr, gen, tcl, L.lzK, mode, cT, cS, ty);
   }
 
   while (!PSK) {
@@ -631,7 +632,6 @@ simplex_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
 // status MVB_PS_FALLBACK and are re-run by simplex_kernel.
 __global__ void __launch_bounds__(512, 1)
 simplex_ps_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
-  extern __shared__ __align__(128) unsigned char dyn_smem[];
   kernel_body<true>(lps, nlp, G, ctrs, tcl, dyn_smem);
 }
 
@@ -660,6 +660,7 @@ struct DeviceCtx {
   int max_ctas_ps = 0;     // co-resident CTAs of simplex_ps_kernel with max_dyn
   size_t max_dyn = 0;      // dynamic shared memory simplex_kernel may ask for
   bool no_ps = false;      // MVOLPS_NO_PS=1: general loop only (debugging / A-B timing)
+  int force_k = 0;         // MVOLPS_LZ_K=k: cap the pending-update depth (A-B timing)
 };
 DeviceCtx g_ctx;
 
@@ -698,6 +699,8 @@ bool ctx_init(int device) {
   CK(cudaFuncSetAttribute(simplex_ps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_ctx.max_dyn));
   const char *nops = getenv("MVOLPS_NO_PS");
   g_ctx.no_ps = nops && nops[0] == '1';
+  const char *fk = getenv("MVOLPS_LZ_K");
+  g_ctx.force_k = fk ? atoi(fk) : 0;
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_kernel, g_ctx.nt, 0));
   if (per_sm < 1) return fail("simplex_kernel does not fit an SM");
@@ -1034,7 +1037,12 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
     mvb_lp *lp = lps[idx[k]];
     h[k] = lp->dev;
     max_bytes = std::max(max_bytes, (size_t)(lp->m + 1) * lp->ld * sizeof(double));
-    if (psk) dyn = std::max(dyn, ps_smem_bytes(lp->m, lp->ld));
+    if (psk) {
+      int K = lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn);
+      if (g_ctx.force_k > 0) K = std::min(K, g_ctx.force_k);
+      h[k].lzK = K;
+      dyn = std::max(dyn, lz_smem_bytes(lp->m, lp->ld, K));
+    }
   }
   const int max_ctas = psk ? g_ctx.max_ctas_ps : g_ctx.max_ctas;
   // CTAs per LP: by tableau size, bounded by what is co-resident
@@ -1103,7 +1111,7 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     lp->dev.max_iters = mi;
     lp->dev.pivlog = (opts && opts->log_pivots) ? lp->pivlog : nullptr;
     lp->dev.pivlog_cap = lp->dev.pivlog ? lp->pivlog_cap : 0;
-    const bool fits = !g_ctx.no_ps && lp->m >= 1 && ps_smem_bytes(lp->m, lp->ld) <= g_ctx.max_dyn &&
+    const bool fits = !g_ctx.no_ps && lp->m >= 1 && lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn) >= 1 &&
                       lp->m + 1 <= PS_CREG * g_ctx.nt;
     (fits ? ps_idx : gen_idx).push_back(k);
   }
@@ -1241,3 +1249,15 @@ int mvb_last_launch(int *c, int *g, int *t) {
 }
 
 }  // extern "C"
+
+#ifdef MVB_PROF
+// profiling builds only (make PROF=1): per-CTA phase clocks of the private-state loop
+extern "C" int mvb_debug_prof(long long *out, int reset) {
+  if (out) cudaMemcpyFromSymbol(out, g_prof, sizeof(long long) * 256 * 16);
+  if (reset) {
+    static long long z[256 * 16];
+    cudaMemcpyToSymbol(g_prof, z, sizeof(z));
+  }
+  return 0;
+}
+#endif
