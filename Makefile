@@ -14,7 +14,7 @@ HOST := glpk_shim lp_reader bnb_driver
 
 all: $(LIB) $(BIN)
 
-$(OBJ)/engine_cuda.o: $(CSRC)/engine_cuda.cu $(ROOT)/include/mvolps_engine.h $(ROOT)/include/mvolps_spec.h
+$(OBJ)/engine_cuda.o: $(CSRC)/engine_cuda.cu $(wildcard $(CSRC)/*.cuh) $(ROOT)/include/mvolps_engine.h $(ROOT)/include/mvolps_spec.h
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 

@@ -24,7 +24,7 @@
 
 namespace {
 
-constexpr int PS_CREG = 4;            // pivot-column values a thread can hold in flight
+constexpr int PS_CREG = 8;            // pivot-column values a thread can hold in flight
 constexpr int LZ_KMAX = 8;            // most pending pivots between two flush passes
 constexpr int MVB_PS_FALLBACK = 100;  // DevResult status: needs the general kernel
 
@@ -51,13 +51,12 @@ struct FastRed {
   Key slot[2][32];
   int par;
 };
-__device__ __forceinline__ Key block_argmin_fast(Key v, Key (*slot)[32], int &par) {
+__device__ __forceinline__ Key block_argmin_fast(Key v, Key (*slot)[32], int par) {
   v = warp_argmin(v);
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
   if (lane == 0) slot[par][w] = v;
   __syncthreads();
   v = lane < nw ? slot[par][lane] : key_none();
-  par ^= 1;
   return warp_argmin(v);
 }
 
@@ -117,13 +116,13 @@ __device__ __forceinline__ void group_wait(unsigned *ctr, int G, unsigned gen) {
 #ifdef MVB_PROF
 // per-CTA phase clocks (thread 0): built only with -DMVB_PROF, read by mvb_debug_prof
 __device__ long long g_prof[256 * 16];
-#define PROF(i)                                                     \
-  do {                                                              \
-    if (threadIdx.x == 0) {                                         \
-      const long long t_ = clock64();                               \
-      g_prof[blockIdx.x * 16 + (i)] += t_ - Z.prof_last;            \
-      Z.prof_last = t_;                                             \
-    }                                                               \
+#define PROF(i)                                             \
+  do {                                                      \
+    if (threadIdx.x == 0) {                                 \
+      const long long t_ = clock64();                       \
+      S->prof[(i)] += t_ - S->prof_last;                    \
+      S->prof_last = t_;                                    \
+    }                                                       \
   } while (0)
 #else
 #define PROF(i) do {} while (0)
@@ -193,20 +192,25 @@ __device__ __forceinline__ int *zPend(const Lay &l, int m) {
   return reinterpret_cast<int *>(zTail(l, m) + sizeof(Key) * 64 + 16);
 }
 
-// per-thread context of the lazy loop (identical values in every thread)
-struct LZ {
-  Lay lay;
-  int m, n, ld;
-  int g, G, tcl;
+// Context of one solve, in static shared memory.  The first block is written
+// once; the evolving fields are written by thread 0 between barriers and read
+// by everyone after the next barrier.  The phases below are separate
+// (noinline) functions so that each gets its own register allocation.
+struct LZS {
+  const double *lb, *ub;  // bounds by variable id (global)
+  double *T[2];           // ping-pong tableau buffers (global)
+  int *pivlog;
   unsigned *ctr;
-  unsigned gen;
-  int cT;            // tableau buffer the pending updates apply to (the stale one)
-  int np;            // pending pivots (their rows / columns: zPend)
-  int par;           // block_argmin_fast slot parity
-  unsigned mphase;   // mbarrier phase of the next row load
-  bool must_wait;    // a flush barrier has been arrived at but not yet waited for
+  Lay lay;
+  int m, n, ld, g, G, tcl, mode, max_iters, pivlog_cap;
+  // evolving
+  unsigned gen, mphase;
+  int cT, np, must_wait;
+  int r, q, newat, degenerate, degen;
+  double delta, newbr, lq, uq, inv, alpha;
+  Tally ty;
 #ifdef MVB_PROF
-  long long prof_last;
+  long long prof_last, prof[16];
 #endif
 };
 
@@ -220,30 +224,56 @@ __device__ __forceinline__ double lz_step(double v, bool is_r, bool is_q, double
   return is_r ? rhoj : t;
 }
 
-// FLUSH: stream this CTA's share of the tableau Ts -> Td applying the np
+// FLUSH: stream this CTA's share of the tableau Ts -> Td applying the KC
 // pending updates in order.  Work unit = (row, column chunk of 2*tcols
 // doubles) as in tile_update; each thread owns two adjacent columns, keeps the
-// rho pairs of all pending pivots in registers and UNROLL rows in flight.
+// rho pairs of all pending pivots in registers and UN rows in flight.
+// one (row, double2) element through the KC pending updates
+template <int KC, bool SPECIAL>
+__device__ __forceinline__ double2 lz_chain(double2 o, const unsigned char *cb, unsigned mv,
+                                            const double2 (&rh)[KC], const int (&pr)[KC],
+                                            unsigned qmask, int ii) {
+#pragma unroll
+  for (int p = 0; p < KC; p++) {
+    const double c = *reinterpret_cast<const double *>(cb + p * mv);
+    if (SPECIAL) {
+      const bool isr = ii == pr[p];
+      o.x = lz_step(o.x, isr, (qmask >> (2 * p)) & 1u, c, rh[p].x);
+      o.y = lz_step(o.y, isr, (qmask >> (2 * p + 1)) & 1u, c, rh[p].y);
+    } else {
+      o.x = fma(c, rh[p].x, o.x);
+      o.y = fma(c, rh[p].y, o.y);
+    }
+  }
+  return o;
+}
+
 template <int KC>
-__device__ __noinline__ void lz_flush_k(const Lay l, const int m, const int ld, const int tcl,
-                                       const int g, const int G, const double *__restrict__ Ts,
-                                       double *__restrict__ Td) {
+__device__ __noinline__ void lz_flush_k(const LZS *S) {
+  const Lay l = S->lay;
+  const int m = S->m, ld = S->ld, tcl = S->tcl, g = S->g, G = S->G;
+  const double *__restrict__ Ts = S->T[S->cT];
+  double *__restrict__ Td = S->T[S->cT ^ 1];
   const int R = m + 1;
   const int tcols = 1 << tcl, trows = blockDim.x >> tcl;
   const int tx = threadIdx.x & (tcols - 1), ty = threadIdx.x >> tcl;
   const int CW = 2 * tcols, nch = (ld + CW - 1) / CW;
   const int *pend = zPend(l, m);
+  const unsigned mv = l.mv;
+  const unsigned char *colbase = zM(l);
   int pr[KC];
 #pragma unroll
   for (int p = 0; p < KC; p++) pr[p] = pend[2 * p];
-  const long long nunits = (long long)nch * R;
-  long long u0 = nunits * g / G;
-  const long long u1 = nunits * (g + 1) / G;
-  constexpr int UN = KC <= 2 ? 8 : 4;
+  // units = (column chunk, row), chunk-major; the group's units are split evenly
+  const unsigned nunits = (unsigned)nch * (unsigned)R;  // < 2^31 (checked on the host)
+  unsigned u0 = (unsigned)((unsigned long long)nunits * (unsigned)g / (unsigned)G);
+  const unsigned u1 = (unsigned)((unsigned long long)nunits * (unsigned)(g + 1) / (unsigned)G);
+  constexpr int UN = KC <= 4 ? 8 : 4;
   while (u0 < u1) {
-    const int ch = (int)(u0 / R);
-    const int ia = (int)(u0 - (long long)ch * R);
-    const long long segend = u1 < (long long)(ch + 1) * R ? u1 : (long long)(ch + 1) * R;
+    const int ch = (int)(u0 / (unsigned)R);
+    const int ia = (int)(u0 - (unsigned)ch * (unsigned)R);
+    const unsigned chend = (unsigned)(ch + 1) * (unsigned)R;
+    const unsigned segend = u1 < chend ? u1 : chend;
     const int ib = ia + (int)(segend - u0);
     const int col = ch * CW + 2 * tx;
     if (col < ld) {
@@ -255,31 +285,34 @@ __device__ __noinline__ void lz_flush_k(const Lay l, const int m, const int ld, 
         const int qp = pend[2 * p + 1];
         qmask |= (col == qp ? 1u : 0u) << (2 * p) | (col + 1 == qp ? 1u : 0u) << (2 * p + 1);
       }
-      const double *src = Ts + col;
-      double *dst = Td + col;
-      for (int i = ia + ty; i < ib; i += trows * UN) {
+      const size_t rs = (size_t)trows * ld;  // row step of this thread, in doubles
+      const double *src = Ts + (size_t)(ia + ty) * ld + col;
+      double *dst = Td + (size_t)(ia + ty) * ld + col;
+      const unsigned span = (unsigned)(trows * UN);
+      int i = ia + ty;
+      for (; i + (UN - 1) * trows < ib; i += trows * UN, src += rs * UN, dst += rs * UN) {
         double2 t[UN];
 #pragma unroll
-        for (int u = 0; u < UN; u++) {
-          const int ii = i + u * trows;
-          if (ii < ib) t[u] = ldcg2(src + (size_t)ii * ld);
-        }
+        for (int u = 0; u < UN; u++) t[u] = ldcg2(src + rs * u);
+        // pivot rows / columns of the pending updates need the special cases
+        // of lz_step; everything else is a plain fma chain
+        bool special = qmask != 0;
 #pragma unroll
-        for (int u = 0; u < UN; u++) {
-          const int ii = i + u * trows;
-          if (ii < ib) {
-            double2 o = t[u];
+        for (int p = 0; p < KC; p++) special |= (unsigned)(pr[p] - i) < span;
+        const unsigned char *cb = colbase + (size_t)i * 8;
+        if (!special) {
 #pragma unroll
-            for (int p = 0; p < KC; p++) {
-              const double c = zCol(l, p)[ii];
-              const bool isr = ii == pr[p];
-              o.x = lz_step(o.x, isr, (qmask >> (2 * p)) & 1u, c, rh[p].x);
-              o.y = lz_step(o.y, isr, (qmask >> (2 * p + 1)) & 1u, c, rh[p].y);
-            }
-            stcg2(dst + (size_t)ii * ld, o);
-          }
+          for (int u = 0; u < UN; u++)
+            stcg2(dst + rs * u, lz_chain<KC, false>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, 0));
+        } else {
+#pragma unroll
+          for (int u = 0; u < UN; u++)
+            stcg2(dst + rs * u,
+                  lz_chain<KC, true>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, i + u * trows));
         }
       }
+      for (; i < ib; i += trows, src += rs, dst += rs)
+        stcg2(dst, lz_chain<KC, true>(ldcg2(src), colbase + (size_t)i * 8, mv, rh, pr, qmask, i));
     }
     u0 = segend;
   }
@@ -287,29 +320,45 @@ __device__ __noinline__ void lz_flush_k(const Lay l, const int m, const int ld, 
 
 // flush + arrive at the group barrier; the wait is deferred to the next read
 // of the tableau (lz_need_tableau)
-__device__ __forceinline__ void lz_flush(LZ &Z, const LPDev &L) {
-  if (Z.np == 0) return;
-  const double *Ts = L.T[Z.cT];
-  double *Td = L.T[Z.cT ^ 1];
-  switch (Z.np) {
-    case 1: lz_flush_k<1>(Z.lay, Z.m, Z.ld, Z.tcl, Z.g, Z.G, Ts, Td); break;
-    case 2: lz_flush_k<2>(Z.lay, Z.m, Z.ld, Z.tcl, Z.g, Z.G, Ts, Td); break;
-    case 3: lz_flush_k<3>(Z.lay, Z.m, Z.ld, Z.tcl, Z.g, Z.G, Ts, Td); break;
-    case 4: lz_flush_k<4>(Z.lay, Z.m, Z.ld, Z.tcl, Z.g, Z.G, Ts, Td); break;
-    case 5: lz_flush_k<5>(Z.lay, Z.m, Z.ld, Z.tcl, Z.g, Z.G, Ts, Td); break;
-    case 6: lz_flush_k<6>(Z.lay, Z.m, Z.ld, Z.tcl, Z.g, Z.G, Ts, Td); break;
-    case 7: lz_flush_k<7>(Z.lay, Z.m, Z.ld, Z.tcl, Z.g, Z.G, Ts, Td); break;
-    default: lz_flush_k<8>(Z.lay, Z.m, Z.ld, Z.tcl, Z.g, Z.G, Ts, Td); break;
+__device__ __forceinline__ void lz_flush(LZS *S) {
+  const int np = S->np;
+  if (np == 0) return;
+  switch (np) {
+    case 1: lz_flush_k<1>(S); break;
+    case 2: lz_flush_k<2>(S); break;
+    case 3: lz_flush_k<3>(S); break;
+    case 4: lz_flush_k<4>(S); break;
+    case 5: lz_flush_k<5>(S); break;
+    case 6: lz_flush_k<6>(S); break;
+    case 7: lz_flush_k<7>(S); break;
+    default: lz_flush_k<8>(S); break;
   }
-  group_arrive(Z.ctr, Z.G, Z.gen);
-  Z.cT ^= 1;
-  Z.np = 0;
-  Z.must_wait = true;
+  __syncthreads();  // all stores of this CTA issued
+  if (threadIdx.x == 0) {
+    if (S->G > 1) {
+      __threadfence();
+      atomicAdd(S->ctr, 1u);
+    }
+    S->gen++;
+    S->cT ^= 1;
+    S->np = 0;
+    S->must_wait = 1;
+  }
+  __syncthreads();
+  PROF(6);
 }
-__device__ __forceinline__ void lz_need_tableau(LZ &Z) {
-  if (Z.must_wait) {
-    group_wait(Z.ctr, Z.G, Z.gen);
-    Z.must_wait = false;
+// before the first tableau read after a flush: wait for the whole group
+__device__ __forceinline__ void lz_need_tableau(LZS *S) {
+  if (S->must_wait) {
+    if (threadIdx.x == 0 && S->G > 1) {
+      const unsigned target = S->gen * (unsigned)S->G;
+      unsigned seen;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(S->ctr) : "memory");
+      } while (seen < target);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) S->must_wait = 0;
   }
 }
 
@@ -318,82 +367,321 @@ __device__ __forceinline__ void lz_need_tableau(LZ &Z) {
 namespace {
 
 // column q of the CURRENT tableau (rows 0..m) into col slot np: strided gather
-// from the stale buffer, then the pending updates in order
-__device__ __forceinline__ void lz_issue_col(const LZ &Z, const double *T, int q,
-                                             double (&raw)[PS_CREG]) {
+// from the stale buffer, then the pending updates in order.  Also fetches the
+// bounds of the variable at position q (S->lq, S->uq).
+__device__ __noinline__ void lz_col(LZS *S, int q) {
+  const Lay l = S->lay;
+  const int m = S->m, np = S->np, tid = threadIdx.x, NT = blockDim.x;
+  lz_need_tableau(S);
+  PROF(12);
+  const double *T = S->T[S->cT] + q;
+  const size_t ld = (size_t)S->ld;
+  double v[PS_CREG];
 #pragma unroll
   for (int u = 0; u < PS_CREG; u++) {
-    const int i = threadIdx.x + u * blockDim.x;
-    if (i <= Z.m) raw[u] = ldcg(T + (size_t)i * Z.ld + q);
+    const int i = tid + u * NT;
+    if (i <= m) v[u] = ldcg(T + (size_t)i * ld);
   }
-}
-__device__ __forceinline__ void lz_finish_col(const LZ &Z, int q, double (&v)[PS_CREG]) {
-  const Lay &l = Z.lay;
-  const int *pend = zPend(l, Z.m);
-  for (int p = 0; p < Z.np; p++) {
+  double lq = 0.0, uq = 0.0;
+  if (tid == 0) {
+    const int kq = zNbv(l)[q];
+    lq = ldcg(S->lb + kq);
+    uq = ldcg(S->ub + kq);
+  }
+  const int *pend = zPend(l, m);
+  for (int p = 0; p < np; p++) {
     const double rq = zRho(l, p)[q];
     const int prp = pend[2 * p];
     const bool isq = pend[2 * p + 1] == q;
     const double *cp = zCol(l, p);
 #pragma unroll
     for (int u = 0; u < PS_CREG; u++) {
-      const int i = threadIdx.x + u * blockDim.x;
-      if (i <= Z.m) v[u] = lz_step(v[u], i == prp, isq, cp[i], rq);
+      const int i = tid + u * NT;
+      if (i <= m) v[u] = lz_step(v[u], i == prp, isq, cp[i], rq);
     }
   }
-  double *dst = zCol(l, Z.np);
+  double *dst = zCol(l, np);
 #pragma unroll
   for (int u = 0; u < PS_CREG; u++) {
-    const int i = threadIdx.x + u * blockDim.x;
-    if (i <= Z.m) dst[i] = v[u];
+    const int i = tid + u * NT;
+    if (i <= m) dst[i] = v[u];
+  }
+  if (tid == 0) {
+    S->lq = lq;
+    S->uq = uq;
   }
   __syncthreads();
 }
 
-// row r of the CURRENT tableau into rho slot np.  The raw row lands by TMA;
-// `finish` applies the pending updates in place and, when scale is set,
-// turns it into the scaled pivot row rho_q = inv, rho_j = -(v_j * inv).
-__device__ __forceinline__ void lz_issue_row(LZ &Z, const double *T, int r) {
-  if (threadIdx.x == 0)
-    bulk_row_load(zRho(Z.lay, Z.np), T + (size_t)r * Z.ld, (unsigned)(Z.ld * sizeof(double)),
-                  zMbar(Z.lay, Z.m));
+// TMA fetch of row r of the stale tableau into rho slot np (thread 0)
+__device__ __forceinline__ void lz_issue_row(LZS *S, int r) {
+  bulk_row_load(zRho(S->lay, S->np), S->T[S->cT] + (size_t)r * S->ld,
+                (unsigned)(S->ld * sizeof(double)), zMbar(S->lay, S->m));
 }
-__device__ __forceinline__ void lz_finish_row(LZ &Z, int r, bool scale, int q, double inv) {
-  const Lay &l = Z.lay;
-  const int *pend = zPend(l, Z.m);
-  mbar_wait(zMbar(l, Z.m), Z.mphase);
-  Z.mphase ^= 1;
+
+// wait for the raw row, apply the pending updates in place and, when scale is
+// set, turn it into the scaled pivot row rho_q = inv, rho_j = -(v_j * inv)
+__device__ __noinline__ void lz_row(LZS *S, int r, int q, int scale) {
+  const Lay l = S->lay;
+  const int m = S->m, ld = S->ld, np = S->np, tid = threadIdx.x, NT = blockDim.x;
+  const double inv = S->inv;
+  const int *pend = zPend(l, m);
+  mbar_wait(zMbar(l, m), S->mphase);
   constexpr int JU = 4;
-  double *buf = zRho(l, Z.np);
-  for (int j0 = threadIdx.x; j0 < Z.ld; j0 += JU * blockDim.x) {
+  double *buf = zRho(l, np);
+  for (int j0 = tid; j0 < ld; j0 += JU * NT) {
     double v[JU];
 #pragma unroll
     for (int u = 0; u < JU; u++) {
-      const int j = j0 + u * blockDim.x;
-      if (j < Z.ld) v[u] = buf[j];
+      const int j = j0 + u * NT;
+      if (j < ld) v[u] = buf[j];
     }
-    for (int p = 0; p < Z.np; p++) {
+    for (int p = 0; p < np; p++) {
       const double cr = zCol(l, p)[r];
       const bool isr = pend[2 * p] == r;
       const int pqp = pend[2 * p + 1];
       const double *rp = zRho(l, p);
 #pragma unroll
       for (int u = 0; u < JU; u++) {
-        const int j = j0 + u * blockDim.x;
-        if (j < Z.ld) v[u] = lz_step(v[u], isr, j == pqp, cr, rp[j]);
+        const int j = j0 + u * NT;
+        if (j < ld) v[u] = lz_step(v[u], isr, j == pqp, cr, rp[j]);
       }
     }
 #pragma unroll
     for (int u = 0; u < JU; u++) {
-      const int j = j0 + u * blockDim.x;
-      if (j < Z.ld) buf[j] = scale ? (j == q ? inv : -(v[u] * inv)) : v[u];
+      const int j = j0 + u * NT;
+      if (j < ld) buf[j] = scale ? (j == q ? inv : -(v[u] * inv)) : v[u];
     }
   }
   __syncthreads();
+  if (tid == 0) S->mphase ^= 1;
 }
-__device__ __forceinline__ void lz_scale_row(LZ &Z, int q, double inv) {
-  double *buf = zRho(Z.lay, Z.np);
-  for (int j = threadIdx.x; j < Z.ld; j += blockDim.x) buf[j] = j == q ? inv : -(buf[j] * inv);
+
+// K1 pricing: largest |d_j| among eligible columns, lowest variable id on
+// ties (Bland: lowest eligible id).  Returns q or -1.
+__device__ __noinline__ int lz_price(LZS *S) {
+  const Lay l = S->lay;
+  const int n = S->n, tid = threadIdx.x, NT = blockDim.x;
+  const bool bland = S->degen >= MVB_BLAND_AFTER;
+  const double *d = zD(l);
+  const int *atv = zAtv(l), *nbv = zNbv(l);
+  Key bq = key_none();
+  for (int j = tid; j < n; j += NT) {  // branch-free form of dj_eligible + key build
+    const double dj = d[j];
+    const int f = atv[j];
+    const bool neg = dj < -MVB_TOL_DJ, pos = dj > MVB_TOL_DJ;
+    const bool e = (f == MVB_AT_LB && neg) || (f == MVB_AT_UB && pos) || (f == MVB_AT_FR && (neg || pos));
+    const Key k{e ? (bland ? 0ULL : ~dbits(fabs(dj))) : ~0ULL, e ? nbv[j] : 0x7fffffff, e ? j : -1};
+    if (key_less(k, bq)) bq = k;
+  }
+  PROF(8);
+#ifdef MVB_PROF
+  {
+    Key v = warp_argmin(bq);
+    PROF(9);
+    Key(*slot)[32] = zSlot(l, S->m);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    if (lane == 0) slot[0][w] = v;
+    __syncthreads();
+    PROF(10);
+    v = lane < nw ? slot[0][lane] : key_none();
+    v = warp_argmin(v);
+    PROF(11);
+    return v.idx;
+  }
+#endif
+  bq = block_argmin_fast(bq, zSlot(l, S->m), 0);
+  return bq.idx;
+}
+
+// K2 ratio test over the pivot column (col slot np), lowest variable id on
+// ties.  Returns r > 0 (pivot; its row load is issued), 0 (bound flip) or -1
+// (unbounded); thread 0 records the step in S.
+__device__ __noinline__ int lz_ratio_primal(LZS *S, int q) {
+  const Lay l = S->lay;
+  const int m = S->m, tid = threadIdx.x, NT = blockDim.x;
+  const double *colN = zCol(l, S->np), *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l);
+  const int *head = zHead(l);
+  const int dir = zD(l)[q] < 0.0 ? 1 : -1;
+  Key bi = key_none();
+  for (int i = 1 + tid; i <= m; i += NT) {
+    double t;
+    int fl;
+    if (!primal_ratio_row(colN[i], dir, 0, beta[i], lbB[i], ubB[i], t, fl)) continue;
+    const Key k{dbits(t), head[i], i};
+    if (key_less(k, bi)) bi = k;
+  }
+  bi = block_argmin_fast(bi, zSlot(l, m), 1);
+  const double lq = S->lq, uq = S->uq;
+  const int fq = zAtv(l)[q];
+  const double tflip = uq - lq;
+  const double tmin = bi.idx >= 0 ? __longlong_as_double((long long)bi.k) : HUGE_VAL;
+  int r;
+  if (tflip <= tmin) {
+    if (!(tflip < HUGE_VAL)) return -1;
+    r = 0;  // bound flip, no basis change
+    if (tid == 0) {
+      S->delta = dir > 0 ? tflip : -tflip;
+      S->newat = fq == MVB_AT_LB ? MVB_AT_UB : MVB_AT_LB;
+      S->degenerate = 0;
+    }
+  } else {
+    r = bi.idx;
+    if (tid == 0) {
+      lz_issue_row(S, r);
+      double t;
+      int newat;
+      primal_ratio_row(colN[r], dir, 0, beta[r], lbB[r], ubB[r], t, newat);
+      const double delta = dir > 0 ? tmin : -tmin;
+      S->newat = newat;
+      S->delta = delta;
+      S->newbr = nb_value(fq, lq, uq) + delta;
+      S->degenerate = tmin == 0.0;
+      S->inv = 1.0 / colN[r];
+    }
+  }
+  if (tid == 0) { S->r = r; S->q = q; }
+  __syncthreads();
+  return r;
+}
+
+}  // namespace
+
+namespace {
+
+// K5a leaving row of the dual simplex: largest bound violation, lowest
+// variable id on ties.  Returns r >= 1 (its row load is issued), -1 when the
+// basis is primal feasible (optimal), -2 at the iteration limit.
+__device__ __noinline__ int lz_dual_select(LZS *S) {
+  const Lay l = S->lay;
+  const int m = S->m, tid = threadIdx.x, NT = blockDim.x;
+  const bool bland = S->degen >= MVB_BLAND_AFTER;
+  const double *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l);
+  const int *head = zHead(l);
+  Key best = key_none();
+  for (int i = 1 + tid; i <= m; i += NT) {
+    const double b = beta[i], lo = lbB[i], up = ubB[i];
+    const int s = row_infeas(b, lo, up);
+    if (!s) continue;
+    const double viol = s < 0 ? lo - b : b - up;
+    const Key k{bland ? 0ULL : ~dbits(viol), head[i], i};
+    if (key_less(k, best)) best = k;
+  }
+  best = block_argmin_fast(best, zSlot(l, m), 0);
+  const int r = best.idx;
+  if (r < 0) return -1;
+  if (S->ty.iters >= S->max_iters) return -2;
+  lz_need_tableau(S);
+  if (tid == 0) lz_issue_row(S, r);
+  return r;
+}
+
+// K5b entering column: min |d_j| / |T_rj| over columns that move x_r toward
+// its violated bound, lowest variable id on ties; the row is in rho slot np.
+// Returns q or -1 (primal infeasible).
+__device__ __noinline__ int lz_dual_ratio(LZS *S, int r) {
+  const Lay l = S->lay;
+  const int n = S->n, tid = threadIdx.x, NT = blockDim.x;
+  const double *row = zRho(l, S->np), *d = zD(l);
+  const int *atv = zAtv(l), *nbv = zNbv(l);
+  const int rs = row_infeas(zBeta(l)[r], zLbB(l)[r], zUbB(l)[r]);
+  Key bq = key_none();
+  for (int j = tid; j < n; j += NT) {
+    const int f = atv[j];
+    if (f == MVB_AT_FX) continue;
+    const double alpha = row[j];
+    const double a = rs < 0 ? alpha : -alpha;
+    const bool ok = (f == MVB_AT_LB && a > MVB_TOL_PIV) || (f == MVB_AT_UB && a < -MVB_TOL_PIV) ||
+                    (f == MVB_AT_FR && (a > MVB_TOL_PIV || a < -MVB_TOL_PIV));
+    if (!ok) continue;
+    const double ratio = fabs(d[j]) / fabs(alpha);
+    const Key k{dbits(ratio), nbv[j], j};
+    if (key_less(k, bq)) bq = k;
+  }
+  bq = block_argmin_fast(bq, zSlot(l, S->m), 1);
+  const int q = bq.idx;
+  if (q < 0) return -1;
+  if (tid == 0) {
+    const double alpha_rq = row[q];
+    S->r = r;
+    S->q = q;
+    S->alpha = alpha_rq;
+    S->inv = 1.0 / alpha_rq;
+    S->degenerate = __longlong_as_double((long long)bq.k) == 0.0;
+  }
+  return q;  // S is read after the barrier inside lz_col
+}
+
+// after lz_col: the step of the dual iteration, then the row is scaled in place
+__device__ __noinline__ void lz_dual_finish(LZS *S, int r, int q) {
+  const Lay l = S->lay;
+  const int ld = S->ld, tid = threadIdx.x, NT = blockDim.x;
+  if (tid == 0) {
+    const double br = zBeta(l)[r], lr = zLbB(l)[r], ur = zUbB(l)[r];
+    const int rs = row_infeas(br, lr, ur);
+    const double target = rs < 0 ? lr : ur;
+    const double delta = (target - br) / S->alpha;
+    S->delta = delta;
+    S->newbr = nb_value(zAtv(l)[q], S->lq, S->uq) + delta;
+    S->newat = rs < 0 ? MVB_AT_LB : MVB_AT_UB;
+  }
+  const double inv = S->inv;
+  double *buf = zRho(l, S->np);
+  for (int j = tid; j < ld; j += NT) buf[j] = j == q ? inv : -(buf[j] * inv);
+  __syncthreads();
+}
+
+// apply the iteration to the private state; the tableau update stays pending
+//   beta'_i = i == r ? newbr : fma(T_iq, delta, beta_i)
+//   d'_j    = fma(d_q, rho_j, j == q ? 0 : d_j)           (row 0 of the update)
+//   basis swap incl. the per-row bounds and the non-basic flag
+__device__ __noinline__ void lz_apply(LZS *S) {
+  const Lay l = S->lay;
+  const int m = S->m, ld = S->ld, np = S->np, r = S->r, q = S->q, tid = threadIdx.x, NT = blockDim.x;
+  const double delta = S->delta, newbr = S->newbr;
+  const double *colN = zCol(l, np), *rhoN = zRho(l, np);
+  double *beta = zBeta(l), *d = zD(l);
+  for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
+  if (r) {
+    const double dq = colN[0];
+    for (int j = tid; j < ld; j += NT) d[j] = fma(dq, rhoN[j], j == q ? 0.0 : d[j]);
+  }
+  __syncthreads();  // everyone has read the step out of S
+  if (tid == 0) {
+    int *nbv = zNbv(l), *atv = zAtv(l), *head = zHead(l), *pend = zPend(l, m);
+    double *lbB = zLbB(l), *ubB = zUbB(l);
+    const bool bland = S->degen >= MVB_BLAND_AFTER;
+    // tally (as tally_iter): hash, log, counters
+    Tally &t = S->ty;
+    unsigned long long h = t.hash;
+    h = (h ^ (unsigned long long)S->mode) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)r) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)q) * MVB_FNV_PRIME;
+    t.hash = h;
+    if (S->g == 0 && S->pivlog && t.iters < S->pivlog_cap) {
+      S->pivlog[2 * t.iters] = r;
+      S->pivlog[2 * t.iters + 1] = q;
+    }
+    t.iters++;
+    if (r) t.pivots++; else t.flips++;
+    if (S->mode == MVB_MODE_PRIMAL2) t.it2++; else t.itd++;
+    if (bland) t.bland++;
+    S->degen = S->degenerate ? S->degen + 1 : 0;
+    if (r) {
+      const int kin = nbv[q], kout = head[r];
+      const double lo = lbB[r], uo = ubB[r];
+      head[r] = kin;
+      lbB[r] = S->lq;
+      ubB[r] = S->uq;
+      nbv[q] = kout;
+      atv[q] = lo == uo ? MVB_AT_FX : S->newat;
+      pend[2 * np] = r;
+      pend[2 * np + 1] = q;
+      S->np = np + 1;
+    } else {
+      atv[q] = S->newat;
+    }
+  }
   __syncthreads();
 }
 
@@ -408,16 +696,26 @@ namespace {
 __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &gen, int tcl,
                        int K, int mode, int &cT, int cS, Tally &ty) {
   const int m = L.m, n = L.n, ld = L.ld, tid = threadIdx.x, NT = blockDim.x;
-  LZ Z;
-  Z.lay = Lay{lz_nv(ld), lz_mv(m), K};
-  Z.m = m; Z.n = n; Z.ld = ld; Z.g = g; Z.G = G; Z.tcl = tcl;
-  Z.ctr = ctr; Z.gen = gen; Z.cT = cT; Z.np = 0; Z.par = 0; Z.mphase = 0; Z.must_wait = false;
-  const Lay &l = Z.lay;
-  double *d = zD(l), *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l);
-  int *nbv = zNbv(l), *atv = zAtv(l), *head = zHead(l), *pend = zPend(l, m);
-  Key(*slot)[32] = zSlot(l, m);
-  if (tid == 0) mbar_init(zMbar(l, m), 1);
+  __shared__ LZS ctx;
+  LZS *S = &ctx;
+  const Lay l{lz_nv(ld), lz_mv(m), K};
+  if (tid == 0) {
+    S->lb = L.lb; S->ub = L.ub; S->T[0] = L.T[0]; S->T[1] = L.T[1];
+    S->pivlog = L.pivlog; S->pivlog_cap = L.pivlog_cap; S->ctr = ctr; S->lay = l;
+    S->m = m; S->n = n; S->ld = ld; S->g = g; S->G = G; S->tcl = tcl; S->mode = mode;
+    S->max_iters = L.max_iters;
+    S->gen = gen; S->mphase = 0; S->cT = cT; S->np = 0; S->must_wait = 0;
+    S->r = 0; S->q = 0; S->newat = 0; S->degenerate = 0; S->degen = 0;
+    S->ty = ty;
+    mbar_init(zMbar(l, m), 1);
+#ifdef MVB_PROF
+    for (int i = 0; i < 16; i++) S->prof[i] = 0;
+    S->prof_last = clock64();
+#endif
+  }
   {
+    double *d = zD(l), *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l);
+    int *nbv = zNbv(l), *atv = zAtv(l), *head = zHead(l);
     const double *d0 = L.T[cT];
     const int *gnb = L.nb[cS], *gat = L.at[cS], *ghead = L.head[cS];
     const double *gbeta = L.beta[cS];
@@ -429,175 +727,62 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
     }
     for (int i = tid; i <= m + 1; i += NT) {
       const bool in = i >= 1 && i <= m;
-      const int k = in ? ldcg(ghead + i) : 0x7fffffff;
+      const int k = in ? ldcg(ghead + i) : 0;
       beta[i] = in ? ldcg(gbeta + i) : 0.0;
-      head[i] = k;
+      head[i] = in ? k : 0x7fffffff;
       lbB[i] = in ? ldcg(L.lb + k) : -HUGE_VAL;
       ubB[i] = in ? ldcg(L.ub + k) : HUGE_VAL;
     }
   }
   __syncthreads();
-#ifdef MVB_PROF
-  Z.prof_last = clock64();
-#endif
 
-  int status, degen = 0;
+  int status;
   while (true) {
-    const bool bland = degen >= MVB_BLAND_AFTER;
-    const double *T = L.T[Z.cT];
-    double *colN = zCol(l, Z.np), *rhoN = zRho(l, Z.np);
-    int r = 0, q = -1, newat = MVB_AT_LB;
-    double delta = 0.0, newbr = 0.0, lq = 0.0, uq = 0.0;
-    bool degenerate = false;
-    double raw[PS_CREG];
-
     if (mode == MVB_MODE_DUAL) {
-      // K5a leaving row: largest bound violation, lowest variable id on ties
-      Key best = key_none();
-      for (int i = 1 + tid; i <= m; i += NT) {
-        const double b = beta[i], lo = lbB[i], up = ubB[i];
-        const int s = row_infeas(b, lo, up);
-        if (!s) continue;
-        const double viol = s < 0 ? lo - b : b - up;
-        const Key k{bland ? 0ULL : ~dbits(viol), head[i], i};
-        if (key_less(k, best)) best = k;
-      }
-      best = block_argmin_fast(best, slot, Z.par);
-      r = best.idx;
-      if (r < 0) { status = MVB_OPT; break; }
-      if (ty.iters >= L.max_iters) { status = MVB_ITLIM; break; }
+      const int r = lz_dual_select(S);
+      if (r < 0) { status = r == -1 ? MVB_OPT : MVB_ITLIM; break; }
       PROF(0);
-      lz_need_tableau(Z);
-      lz_issue_row(Z, T, r);
-      lz_finish_row(Z, r, false, 0, 0.0);
+      lz_row(S, r, 0, 0);
       PROF(1);
-      const double br = beta[r], lr = lbB[r], ur = ubB[r];
-      const int rs = row_infeas(br, lr, ur);
-      // K5b entering column: min |d_j| / |T_rj| over columns that move x_r
-      // toward its violated bound, lowest variable id on ties
-      Key bq = key_none();
-      for (int j = tid; j < n; j += NT) {
-        const int f = atv[j];
-        if (f == MVB_AT_FX) continue;
-        const double alpha = rhoN[j];
-        const double a = rs < 0 ? alpha : -alpha;
-        const bool ok = (f == MVB_AT_LB && a > MVB_TOL_PIV) || (f == MVB_AT_UB && a < -MVB_TOL_PIV) ||
-                        (f == MVB_AT_FR && (a > MVB_TOL_PIV || a < -MVB_TOL_PIV));
-        if (!ok) continue;
-        const double ratio = fabs(d[j]) / fabs(alpha);
-        const Key k{dbits(ratio), nbv[j], j};
-        if (key_less(k, bq)) bq = k;
-      }
-      bq = block_argmin_fast(bq, slot, Z.par);
-      q = bq.idx;
+      const int q = lz_dual_ratio(S, r);
       if (q < 0) { status = MVB_NOFEAS; break; }
       PROF(2);
-      const double alpha_rq = rhoN[q];
-      lz_issue_col(Z, T, q, raw);
-      const int kq = nbv[q];
-      lq = ldcg(L.lb + kq);
-      uq = ldcg(L.ub + kq);
-      lz_finish_col(Z, q, raw);
+      lz_col(S, q);
       PROF(3);
-      const double target = rs < 0 ? lr : ur;
-      delta = (target - br) / alpha_rq;
-      newbr = nb_value(atv[q], lq, uq) + delta;
-      newat = rs < 0 ? MVB_AT_LB : MVB_AT_UB;
-      degenerate = __longlong_as_double((long long)bq.k) == 0.0;
-      lz_scale_row(Z, q, 1.0 / alpha_rq);
+      lz_dual_finish(S, r, q);
       PROF(4);
     } else {
-      // K1 pricing: largest |d_j| among eligible columns, lowest variable id on
-      // ties (Bland: lowest eligible id)
-      Key bq = key_none();
-      for (int j = tid; j < n; j += NT) {
-        const double dj = d[j];
-        if (!dj_eligible(atv[j], dj)) continue;
-        const Key k{bland ? 0ULL : ~dbits(fabs(dj)), nbv[j], j};
-        if (key_less(k, bq)) bq = k;
-      }
-      bq = block_argmin_fast(bq, slot, Z.par);
-      q = bq.idx;
+      const int q = lz_price(S);
       if (q < 0) { status = MVB_OPT; break; }
-      if (ty.iters >= L.max_iters) { status = MVB_ITLIM; break; }
+      if (S->ty.iters >= S->max_iters) { status = MVB_ITLIM; break; }
       PROF(0);
-      lz_need_tableau(Z);
-      lz_issue_col(Z, T, q, raw);
-      const int kq = nbv[q];
-      lq = ldcg(L.lb + kq);
-      uq = ldcg(L.ub + kq);
-      lz_finish_col(Z, q, raw);
+      lz_col(S, q);
       PROF(1);
-      const int dir = d[q] < 0.0 ? 1 : -1;
-      // K2 ratio test over the pivot column, lowest variable id on ties
-      Key bi = key_none();
-      for (int i = 1 + tid; i <= m; i += NT) {
-        double t;
-        int fl;
-        if (!primal_ratio_row(colN[i], dir, 0, beta[i], lbB[i], ubB[i], t, fl)) continue;
-        const Key k{dbits(t), head[i], i};
-        if (key_less(k, bi)) bi = k;
-      }
-      bi = block_argmin_fast(bi, slot, Z.par);
+      const int r = lz_ratio_primal(S, q);
+      if (r < 0) { status = MVB_UNBND; break; }
       PROF(2);
-      const int fq = atv[q];
-      const double tflip = uq - lq;
-      const double tmin = bi.idx >= 0 ? __longlong_as_double((long long)bi.k) : HUGE_VAL;
-      if (tflip <= tmin) {
-        if (!(tflip < HUGE_VAL)) { status = MVB_UNBND; break; }
-        r = 0;  // bound flip, no basis change
-        delta = dir > 0 ? tflip : -tflip;
-        newat = fq == MVB_AT_LB ? MVB_AT_UB : MVB_AT_LB;
-      } else {
-        r = bi.idx;
-        lz_issue_row(Z, T, r);
-        double t;
-        primal_ratio_row(colN[r], dir, 0, beta[r], lbB[r], ubB[r], t, newat);
-        delta = dir > 0 ? tmin : -tmin;
-        newbr = nb_value(fq, lq, uq) + delta;
-        degenerate = tmin == 0.0;
-        lz_finish_row(Z, r, true, q, 1.0 / colN[r]);
-      }
+      if (r > 0) lz_row(S, r, q, 1);
       PROF(3);
     }
-
-    // ---- apply the iteration to the private state; the tableau update stays pending ----
-    tally_iter(ty, L, g, mode, r, q, bland);
-    for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
-    if (r) {
-      const double dq = colN[0];
-      for (int j = tid; j < ld; j += NT) d[j] = fma(dq, rhoN[j], j == q ? 0.0 : d[j]);
-    }
-    if (tid == 0) {
-      if (r) {
-        const int kin = nbv[q], kout = head[r];
-        const double lo = lbB[r], uo = ubB[r];
-        head[r] = kin;
-        lbB[r] = lq;
-        ubB[r] = uq;
-        nbv[q] = kout;
-        atv[q] = lo == uo ? MVB_AT_FX : newat;
-        pend[2 * Z.np] = r;
-        pend[2 * Z.np + 1] = q;
-      } else {
-        atv[q] = newat;
-      }
-    }
-    __syncthreads();
-    if (r) Z.np++;
-    degen = degenerate ? degen + 1 : 0;
+    lz_apply(S);
     PROF(5);
-    if (Z.np == K) {
-      lz_flush(Z, L);
-      PROF(6);
-    }
+    if (S->np == K) lz_flush(S);
   }
-  lz_flush(Z, L);
-  lz_need_tableau(Z);
-  gen = Z.gen;
-  cT = Z.cT;
+  __syncthreads();
+  lz_flush(S);
+  lz_need_tableau(S);
+  __syncthreads();
+  gen = S->gen;
+  cT = S->cT;
+  ty = S->ty;
+#ifdef MVB_PROF
+  if (tid == 0)
+    for (int i = 0; i < 16; i++) g_prof[blockIdx.x * 16 + i] += S->prof[i];
+#endif
   // hand the private state back (every CTA holds the same values)
   if (g == 0) {
+    const double *beta = zBeta(l);
+    const int *head = zHead(l), *nbv = zNbv(l), *atv = zAtv(l);
     double *gbeta = L.beta[cS];
     int *ghead = L.head[cS], *gnb = L.nb[cS], *gat = L.at[cS];
     for (int i = 1 + tid; i <= m; i += NT) { gbeta[i] = beta[i]; ghead[i] = head[i]; }

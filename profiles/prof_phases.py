@@ -23,6 +23,7 @@ names = ["price(+wait)", "col fetch+derive", "ratio", "row fetch+derive", "-", "
 print(f"m={m} n={n} pivots={r['pivots']} kernel {ms:.3f} ms -> {1e3*ms/r['iters']:.2f} us/iter")
 used = p[:, 0] > 0
 print("ctas", used.sum())
+names += ["price:loop", "price:warp1", "price:sync", "price:warp2", "col:barrier wait"]
 for i, nm in enumerate(names):
     c = p[used, i] / r["iters"]
     print(f"{nm:12s} mean {c.mean():8.0f} clk  min {c.min():8.0f}  max {c.max():8.0f}   ({c.mean()/1965:.2f} us)")
