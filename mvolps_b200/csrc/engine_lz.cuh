@@ -376,35 +376,34 @@ __device__ __noinline__ void lz_col(LZS *S, int q) {
   PROF(12);
   const double *T = S->T[S->cT] + q;
   const size_t ld = (size_t)S->ld;
-  double v[PS_CREG];
-#pragma unroll
-  for (int u = 0; u < PS_CREG; u++) {
-    const int i = tid + u * NT;
-    if (i <= m) v[u] = ldcg(T + (size_t)i * ld);
-  }
+  const int *pend = zPend(l, m);
+  double *dst = zCol(l, np);
+  constexpr int NU = 4;  // rows per thread and pass, all computed unconditionally
   double lq = 0.0, uq = 0.0;
   if (tid == 0) {
     const int kq = zNbv(l)[q];
     lq = ldcg(S->lb + kq);
     uq = ldcg(S->ub + kq);
   }
-  const int *pend = zPend(l, m);
-  for (int p = 0; p < np; p++) {
-    const double rq = zRho(l, p)[q];
-    const int prp = pend[2 * p];
-    const bool isq = pend[2 * p + 1] == q;
-    const double *cp = zCol(l, p);
+  for (int i0 = tid; i0 <= m; i0 += NU * NT) {
+    int ii[NU];
+    double v[NU];
 #pragma unroll
-    for (int u = 0; u < PS_CREG; u++) {
-      const int i = tid + u * NT;
-      if (i <= m) v[u] = lz_step(v[u], i == prp, isq, cp[i], rq);
+    for (int u = 0; u < NU; u++) {
+      ii[u] = min(i0 + u * NT, m);  // clamped: out-of-range lanes redo row m, never stored
+      v[u] = ldcg(T + (size_t)ii[u] * ld);
     }
-  }
-  double *dst = zCol(l, np);
+    for (int p = 0; p < np; p++) {
+      const double rq = zRho(l, p)[q];
+      const int prp = pend[2 * p];
+      const bool isq = pend[2 * p + 1] == q;
+      const double *cp = zCol(l, p);
 #pragma unroll
-  for (int u = 0; u < PS_CREG; u++) {
-    const int i = tid + u * NT;
-    if (i <= m) dst[i] = v[u];
+      for (int u = 0; u < NU; u++) v[u] = lz_step(v[u], ii[u] == prp, isq, cp[ii[u]], rq);
+    }
+#pragma unroll
+    for (int u = 0; u < NU; u++)
+      if (i0 + u * NT <= m) dst[ii[u]] = v[u];
   }
   if (tid == 0) {
     S->lq = lq;
@@ -427,14 +426,15 @@ __device__ __noinline__ void lz_row(LZS *S, int r, int q, int scale) {
   const double inv = S->inv;
   const int *pend = zPend(l, m);
   mbar_wait(zMbar(l, m), S->mphase);
-  constexpr int JU = 4;
+  constexpr int JU = 4;  // columns per thread and pass, all computed unconditionally
   double *buf = zRho(l, np);
   for (int j0 = tid; j0 < ld; j0 += JU * NT) {
+    int jj[JU];
     double v[JU];
 #pragma unroll
     for (int u = 0; u < JU; u++) {
-      const int j = j0 + u * NT;
-      if (j < ld) v[u] = buf[j];
+      jj[u] = min(j0 + u * NT, ld - 1);
+      v[u] = buf[jj[u]];
     }
     for (int p = 0; p < np; p++) {
       const double cr = zCol(l, p)[r];
@@ -442,16 +442,15 @@ __device__ __noinline__ void lz_row(LZS *S, int r, int q, int scale) {
       const int pqp = pend[2 * p + 1];
       const double *rp = zRho(l, p);
 #pragma unroll
-      for (int u = 0; u < JU; u++) {
-        const int j = j0 + u * NT;
-        if (j < ld) v[u] = lz_step(v[u], isr, j == pqp, cr, rp[j]);
-      }
+      for (int u = 0; u < JU; u++) v[u] = lz_step(v[u], isr, jj[u] == pqp, cr, rp[jj[u]]);
+    }
+    if (scale) {
+#pragma unroll
+      for (int u = 0; u < JU; u++) v[u] = jj[u] == q ? inv : -(v[u] * inv);
     }
 #pragma unroll
-    for (int u = 0; u < JU; u++) {
-      const int j = j0 + u * NT;
-      if (j < ld) buf[j] = scale ? (j == q ? inv : -(v[u] * inv)) : v[u];
-    }
+    for (int u = 0; u < JU; u++)
+      if (j0 + u * NT < ld) buf[jj[u]] = v[u];
   }
   __syncthreads();
   if (tid == 0) S->mphase ^= 1;
@@ -504,12 +503,24 @@ __device__ __noinline__ int lz_ratio_primal(LZS *S, int q) {
   const int *head = zHead(l);
   const int dir = zD(l)[q] < 0.0 ? 1 : -1;
   Key bi = key_none();
-  for (int i = 1 + tid; i <= m; i += NT) {
-    double t;
-    int fl;
-    if (!primal_ratio_row(colN[i], dir, 0, beta[i], lbB[i], ubB[i], t, fl)) continue;
-    const Key k{dbits(t), head[i], i};
-    if (key_less(k, bi)) bi = k;
+  constexpr int NU = 2;  // branch-free form of primal_ratio_row (phase 2), NU rows in flight
+  for (int i0 = 1 + tid; i0 <= m; i0 += NU * NT) {
+#pragma unroll
+    for (int u = 0; u < NU; u++) {
+      const int i = min(i0 + u * NT, m);
+      const double alpha = colN[i], b = beta[i], lo = lbB[i], up = ubB[i];
+      const double a = dir > 0 ? alpha : -alpha;
+      const bool dec = a < -MVB_TOL_PIV, inc = a > MVB_TOL_PIV;
+      const double bound = dec ? lo : up;
+      const bool ok = (dec && bound > -HUGE_VAL) || (inc && bound < HUGE_VAL);
+      double t = 0.0;
+      if (ok) {
+        t = dec ? (b - bound) / (-a) : (bound - b) / a;
+        if (!(t > 0.0)) t = 0.0;
+      }
+      const Key k{ok ? dbits(t) : ~0ULL, ok ? head[i] : 0x7fffffff, ok ? i : -1};
+      if (key_less(k, bi)) bi = k;
+    }
   }
   bi = block_argmin_fast(bi, zSlot(l, m), 1);
   const double lq = S->lq, uq = S->uq;
@@ -647,11 +658,25 @@ __device__ __noinline__ void lz_apply(LZS *S) {
     for (int j = tid; j < ld; j += NT) d[j] = fma(dq, rhoN[j], j == q ? 0.0 : d[j]);
   }
   __syncthreads();  // everyone has read the step out of S
-  if (tid == 0) {
+  if (tid == 32) {  // basis swap (one warp) ...
     int *nbv = zNbv(l), *atv = zAtv(l), *head = zHead(l), *pend = zPend(l, m);
     double *lbB = zLbB(l), *ubB = zUbB(l);
+    if (r) {
+      const int kin = nbv[q], kout = head[r];
+      const double lo = lbB[r], uo = ubB[r];
+      head[r] = kin;
+      lbB[r] = S->lq;
+      ubB[r] = S->uq;
+      nbv[q] = kout;
+      atv[q] = lo == uo ? MVB_AT_FX : S->newat;
+      pend[2 * np] = r;
+      pend[2 * np + 1] = q;
+    } else {
+      atv[q] = S->newat;
+    }
+  }
+  if (tid == 0) {  // ... while another does the bookkeeping (as tally_iter)
     const bool bland = S->degen >= MVB_BLAND_AFTER;
-    // tally (as tally_iter): hash, log, counters
     Tally &t = S->ty;
     unsigned long long h = t.hash;
     h = (h ^ (unsigned long long)S->mode) * MVB_FNV_PRIME;
@@ -667,20 +692,7 @@ __device__ __noinline__ void lz_apply(LZS *S) {
     if (S->mode == MVB_MODE_PRIMAL2) t.it2++; else t.itd++;
     if (bland) t.bland++;
     S->degen = S->degenerate ? S->degen + 1 : 0;
-    if (r) {
-      const int kin = nbv[q], kout = head[r];
-      const double lo = lbB[r], uo = ubB[r];
-      head[r] = kin;
-      lbB[r] = S->lq;
-      ubB[r] = S->uq;
-      nbv[q] = kout;
-      atv[q] = lo == uo ? MVB_AT_FX : S->newat;
-      pend[2 * np] = r;
-      pend[2 * np + 1] = q;
-      S->np = np + 1;
-    } else {
-      atv[q] = S->newat;
-    }
+    if (r) S->np = np + 1;
   }
   __syncthreads();
 }
