@@ -14,7 +14,7 @@ HOST := glpk_shim lp_reader bnb_driver
 
 all: $(LIB) $(BIN)
 
-$(OBJ)/engine_cuda.o: $(CSRC)/engine_cuda.cu $(wildcard $(CSRC)/*.cuh) $(ROOT)/include/mvolps_engine.h $(ROOT)/include/mvolps_spec.h
+$(OBJ)/engine_cuda.o: $(CSRC)/engine_cuda.cu $(wildcard $(CSRC)/*.cuh) $(ROOT)/include/mvolps_engine.h $(ROOT)/include/mvolps_spec.h $(ROOT)/include/mvolps_dist.h
 	@mkdir -p $(OBJ)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 
@@ -24,7 +24,7 @@ $(OBJ)/%.o: $(CSRC)/%.cpp $(CSRC)/lp_model.hpp $(ROOT)/include/glpk.h $(ROOT)/in
 
 $(LIB): $(OBJ)/engine_cuda.o $(addprefix $(OBJ)/,$(addsuffix .o,$(HOST)))
 	@mkdir -p $(dir $@)
-	$(NVCC) $(ARCH) -shared -o $@ $^ -Xlinker -Bsymbolic
+	$(NVCC) $(ARCH) -shared -o $@ $^ -Xlinker -Bsymbolic -ldl
 
 $(BIN): $(OBJ)/mvolps_main.o $(LIB)
 	@mkdir -p $(dir $@)

@@ -1,0 +1,97 @@
+/* mvolps_dist.h -- multi-GPU layer of the LP-relaxation engine, C ABI.
+ *
+ * (1) One very large tableau, COLUMN-SHARDED across the GPUs of one box
+ *     (north_star: "one very large tableau is column-sharded with an NCCL
+ *     argmin allreduce per pivot"; BASELINE configs[4], m=16384 n=32768).
+ *     Rank k owns the global non-basic positions [col0, col0+ncols) of every
+ *     tableau row; beta, basis heads and bounds are replicated.  Per pivot:
+ *       local pricing (K1) -> candidate (key, variable id, its column, m+1
+ *       doubles) -> ONE all-gather -> every rank picks the same global
+ *       entering column by the total order (value bits, variable id), runs the
+ *       ratio test (K2) on it redundantly, and applies the rank-1 update (K3,
+ *       K4) to its own columns; the pivot row is local to every shard.
+ *     Pivot sequence, tableau and objective are bit-identical to the
+ *     single-GPU engine (mvolps_engine.h) and therefore to the oracle.
+ *     It stands behind the same reference call as the single-GPU path:
+ *     glp_simplex (bs.cpp:117,279,287).
+ *     Restrictions of this path: primal phase 2 from the slack basis (every
+ *     non-basic variable at value 0 and the slack basis primal feasible, as in
+ *     configs[1]/[4]); anything else is rejected with an error.
+ *
+ * (2) Open B&B nodes SHARDED across GPUs: node LPs are independent, so each
+ *     rank solves its own nodes with mvb_solve_batch; the only exchange is
+ *     the incumbent / bound (a max-reduction of one double per round) for
+ *     which `mvb_comm::allreduce_max` is provided.
+ *
+ * The communicator is a small vtable so that the same host code runs over
+ * NCCL (product; libnccl.so.2 is dlopen'ed, preferring the copy already loaded
+ * by the process), over a single-process loop-back of several shards on one
+ * GPU (tests), or over callbacks supplied by the caller (gloo in CPU tests).
+ */
+#ifndef MVOLPS_DIST_H
+#define MVOLPS_DIST_H
+
+#include <stddef.h>
+
+#include "mvolps_engine.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct mvb_comm {
+  void *ctx;
+  int rank, world;
+  /* all-gather of `bytes` bytes per rank, DEVICE buffers, enqueued on `stream`
+   * (a cudaStream_t); recv holds world*bytes.  0 = ok */
+  int (*allgather_dev)(void *ctx, const void *send, void *recv, size_t bytes, void *stream);
+  /* max-reduction of count doubles in place, HOST buffer (incumbent / bound broadcast) */
+  int (*allreduce_max)(void *ctx, double *vals, int count);
+  /* release ctx */
+  void (*destroy)(void *ctx);
+} mvb_comm;
+
+/* ---- NCCL communicator (one process per GPU) ---- */
+#define MVB_NCCL_ID_BYTES 128
+/* rank 0: fill id[128] (ncclGetUniqueId); the caller ships it to the other ranks
+ * (bench.py: torch.distributed broadcast) */
+int mvb_nccl_unique_id(void *id);
+/* every rank, after mvb_device_init(local_rank) */
+mvb_comm *mvb_comm_nccl(const void *id, int rank, int world);
+/* member `rank` of a single-process group of `world` shards on ONE GPU (tests,
+ * emulation of the ranks on one device): allgather_dev is NULL and
+ * mvb_shard_solve is called once with all shards */
+mvb_comm *mvb_comm_local(int rank, int world);
+void mvb_comm_free(mvb_comm *c);
+
+/* contiguous split of n positions over `world` ranks, multiples of 16 columns
+ * (row stride alignment) except for the last rank */
+void mvb_shard_partition(int n, int world, int rank, int *col0, int *ncols);
+
+/* ---- column-sharded LP ---- */
+typedef struct mvb_shard mvb_shard;
+
+/* shard of an LP with m rows and n_global structural columns holding the
+ * columns [col0, col0+ncols) = mvb_shard_partition(n_global, comm->world, comm->rank) */
+mvb_shard *mvb_shard_create(int m, int n_global, int col0, int ncols, const mvb_comm *comm);
+void mvb_shard_free(mvb_shard *s);
+/* A_local: m x ncols row-major (the shard's columns of A); cost_local: ncols
+ * (internal min form); lb/ub: n_global + m by variable id (replicated) */
+int mvb_shard_load(mvb_shard *s, const double *A_local, const double *cost_local,
+                   const double *lb, const double *ub);
+/* Collective.  NCCL: every rank calls it with its one shard (nlocal = 1).
+ * Single-process group: one call with all shards of the LP in rank order; the
+ * all-gather is emulated with device-to-device copies.  out: one result,
+ * identical on every rank. */
+int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_opts *opts, mvb_result *out);
+/* x[n_global + m] by variable id of the last solve (replicated) */
+int mvb_shard_get_primal(mvb_shard *s, double *x);
+/* copies up to cap (row, global position) pairs of the last solve; returns total logged */
+int mvb_shard_get_pivot_log(mvb_shard *s, int *rowcol, int cap);
+/* device time of the last solve's kernels + exchanges (CUDA events), ms */
+double mvb_shard_last_ms(mvb_shard *s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

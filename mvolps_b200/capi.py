@@ -48,6 +48,11 @@ BNB_SYMBOLS = [
     "mvb_bnb_run", "mvb_bnb_free", "mvb_bnb_get_stats", "mvb_bnb_tree_text",
     "mvb_bnb_solution_text", "mvb_bnb_event_text", "mvb_bnb_get_incumbent",
 ]
+DIST_SYMBOLS = [  # include/mvolps_dist.h: exported by the product only
+    "mvb_nccl_unique_id", "mvb_comm_nccl", "mvb_comm_local", "mvb_comm_free", "mvb_shard_partition",
+    "mvb_shard_create", "mvb_shard_free", "mvb_shard_load", "mvb_shard_solve",
+    "mvb_shard_get_primal", "mvb_shard_get_pivot_log", "mvb_shard_last_ms",
+]
 ALL_SYMBOLS = GLPK_SYMBOLS + GLPK_EXTRA_SYMBOLS + ENGINE_SYMBOLS + BNB_SYMBOLS
 
 
@@ -158,6 +163,25 @@ def _bind(lib):
         fn = getattr(lib, name)  # AttributeError = missing export
         fn.restype = res
         fn.argtypes = args
+    dist = {
+        "mvb_nccl_unique_id": (C.c_int, [C.c_void_p]),
+        "mvb_comm_nccl": (_P, [C.c_void_p, C.c_int, C.c_int]),
+        "mvb_comm_local": (_P, [C.c_int, C.c_int]),
+        "mvb_comm_free": (None, [_P]),
+        "mvb_shard_partition": (None, [C.c_int, C.c_int, C.c_int, _ip, _ip]),
+        "mvb_shard_create": (_P, [C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+        "mvb_shard_free": (None, [_P]),
+        "mvb_shard_load": (C.c_int, [_P, _dp, _dp, _dp, _dp]),
+        "mvb_shard_solve": (C.c_int, [C.POINTER(_P), C.c_int, C.POINTER(Opts), C.POINTER(Result)]),
+        "mvb_shard_get_primal": (C.c_int, [_P, _dp]),
+        "mvb_shard_get_pivot_log": (C.c_int, [_P, _ip, C.c_int]),
+        "mvb_shard_last_ms": (C.c_double, [_P]),
+    }
+    if hasattr(lib, "mvb_shard_create"):  # the oracle build has no multi-GPU layer
+        for name, (res, args) in dist.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
     return lib
 
 

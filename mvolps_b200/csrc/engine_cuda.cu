@@ -1261,3 +1261,4 @@ extern "C" int mvb_debug_prof(long long *out, int reset) {
   return 0;
 }
 #endif
+#include "engine_shard.cuh"

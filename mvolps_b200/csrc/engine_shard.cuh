@@ -1,0 +1,685 @@
+// engine_shard.cuh -- column-sharded tableau simplex across the GPUs of one
+// box (include/mvolps_dist.h).  Included at the end of engine_cuda.cu: it uses
+// that file's device helpers (Key order, block_argmin, primal_ratio_row) so
+// that the sharded path takes bit-for-bit the decisions of solve_lp / the oracle.
+//
+// Per pivot and rank:  shard_price_kernel  (K1 over the local columns + pack
+// of the candidate column)  ->  ONE all-gather of (key, id, bounds, column)
+// ->  shard_pivot_kernel  (same global winner everywhere by the (value bits,
+// variable id) order, replicated K2 ratio test, K3/K4 on the local columns,
+// tableau A -> B).  The kernel boundary is the only synchronisation; the
+// control block ping-pongs by iteration parity so a finished solve turns the
+// remaining launches of a chunk into no-ops.
+#pragma once
+#include <dlfcn.h>
+
+#include "../../include/mvolps_dist.h"
+
+namespace {
+
+struct ShardCtl {
+  int status;  // -1 while running, then MVB_*
+  int iters, pivots, flips, bland_iters, degen;
+  int cT, cS;
+  unsigned long long hash;
+};
+
+struct Cand {  // header of one exchange record; the column (m+1 doubles) follows at byte 64
+  unsigned long long key;  // ~bits(|d_q|), 0 under Bland's rule, ~0: no eligible column
+  int var, pos, flag, pad;
+  double lq, uq;
+};
+constexpr size_t SHARD_HDR = 64;
+
+struct ShardDev {
+  int m, nloc, ld, col0, world, max_iters;
+  double *T[2];
+  double *beta[2];
+  int *head[2];
+  int *nb[2];
+  int *at[2];
+  double *lb, *ub;  // by variable id, n_global + m (replicated)
+  ShardCtl *ctl;    // [2]
+  unsigned char *send, *recv;
+  size_t rec_bytes;
+  int *pivlog;
+  int pivlog_cap;
+};
+
+// K1 over the local columns (one CTA: n/G columns, a few per thread) + gather
+// of the winning column into the send record
+__global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int par) {
+  __shared__ Key red[32];
+  __shared__ int s_q;
+  const ShardCtl c = D.ctl[par];
+  Cand *out = reinterpret_cast<Cand *>(D.send);
+  if (c.status != -1) return;
+  const bool bland = c.degen >= MVB_BLAND_AFTER;
+  const double *d = D.T[c.cT];
+  const int *at = D.at[c.cS], *nb = D.nb[c.cS];
+  Key best = key_none();
+  for (int j = threadIdx.x; j < D.nloc; j += blockDim.x) {
+    const int f = at[j];
+    if (f == MVB_AT_FX) continue;
+    const double dj = d[j];
+    if (!dj_eligible(f, dj)) continue;
+    const Key k{bland ? 0ULL : ~dbits(fabs(dj)), nb[j], j};
+    if (key_less(k, best)) best = k;
+  }
+  best = block_argmin(best, red);
+  if (threadIdx.x == 0) {
+    s_q = best.idx;
+    Cand h{};
+    h.key = best.idx >= 0 ? best.k : ~0ULL;
+    h.var = best.idx >= 0 ? best.var : 0x7fffffff;
+    h.pos = best.idx >= 0 ? D.col0 + best.idx : -1;
+    h.flag = best.idx >= 0 ? at[best.idx] : 0;
+    h.lq = best.idx >= 0 ? D.lb[best.var] : 0.0;
+    h.uq = best.idx >= 0 ? D.ub[best.var] : 0.0;
+    *out = h;
+  }
+  __syncthreads();
+  const int q = s_q;
+  if (q < 0) return;
+  double *col = reinterpret_cast<double *>(D.send + SHARD_HDR);
+  const double *T = D.T[c.cT] + q;
+  for (int i = threadIdx.x; i <= D.m; i += blockDim.x) col[i] = T[(size_t)i * D.ld];
+}
+
+// rank-1 update of this CTA's share of the local columns, pivot column taken
+// from `colg` (m+1 doubles in global memory), same unit split and arithmetic
+// as tile_update
+__device__ void shard_tile_update(const ShardDev &D, const double *__restrict__ Ts,
+                                  double *__restrict__ Td, int r, int qloc, double inv,
+                                  const double *__restrict__ colg, Smem &sm) {
+  const int R = D.m + 1, ld = D.ld, g = blockIdx.x, G = gridDim.x;
+  int tcl = 0;
+  while ((1 << tcl) < (ld + 1) / 2 && (2 << tcl) <= (int)blockDim.x) tcl++;
+  const int tcols = 1 << tcl, trows = blockDim.x >> tcl;
+  const int tx = threadIdx.x & (tcols - 1), ty = threadIdx.x >> tcl;
+  const int CW = 2 * tcols, nch = (ld + CW - 1) / CW;
+  const long long nunits = (long long)nch * R;
+  long long u0 = nunits * g / G;
+  const long long u1 = nunits * (g + 1) / G;
+  while (u0 < u1) {
+    const int ch = (int)(u0 / R);
+    const int ia = (int)(u0 - (long long)ch * R);
+    const long long segend = u1 < (long long)(ch + 1) * R ? u1 : (long long)(ch + 1) * R;
+    const int ib = ia + (int)(segend - u0);
+    const int col = ch * CW + 2 * tx;
+    const bool act = col < ld;
+    const bool qx = col == qloc, qy = col + 1 == qloc;
+    double2 rho = make_double2(0.0, 0.0);
+    if (act) {
+      const double2 t = ldcg2(Ts + (size_t)r * ld + col);
+      rho.x = qx ? inv : -(t.x * inv);
+      rho.y = qy ? inv : -(t.y * inv);
+    }
+    for (int s0 = ia; s0 < ib; s0 += STAGE_ROWS) {
+      const int s1 = ib < s0 + STAGE_ROWS ? ib : s0 + STAGE_ROWS;
+      __syncthreads();
+      for (int k = threadIdx.x; k < s1 - s0; k += blockDim.x) sm.colS[k] = colg[s0 + k];
+      __syncthreads();
+      if (!act) continue;
+      for (int i = s0 + ty; i < s1; i += trows * UNROLL) {
+        double2 t[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+          const int ii = i + u * trows;
+          if (ii < s1) t[u] = ldcg2(Ts + (size_t)ii * ld + col);
+        }
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+          const int ii = i + u * trows;
+          if (ii < s1) {
+            const double c = sm.colS[ii - s0];
+            double2 o;
+            o.x = fma(c, rho.x, qx ? 0.0 : t[u].x);
+            o.y = fma(c, rho.y, qy ? 0.0 : t[u].y);
+            if (ii == r) o = rho;
+            stcg2(Td + (size_t)ii * ld + col, o);
+          }
+        }
+      }
+    }
+    u0 = segend;
+  }
+}
+
+}  // namespace
+
+namespace {
+
+// one iteration on every rank: global winner, replicated ratio test, local update
+__global__ void __launch_bounds__(512, 1) shard_pivot_kernel(ShardDev D, int par) {
+  __shared__ Smem sm;
+  const ShardCtl c = D.ctl[par];
+  ShardCtl *next = &D.ctl[par ^ 1];
+  const bool lead = blockIdx.x == 0 && threadIdx.x == 0;
+  if (c.status != -1) {
+    if (lead) *next = c;
+    return;
+  }
+  const int m = D.m, tid = threadIdx.x, NT = blockDim.x;
+  // same winner everywhere: minimum (key, variable id) over the ranks' candidates
+  int wk = -1;
+  unsigned long long bk = ~0ULL;
+  int bvar = 0x7fffffff;
+  for (int k = 0; k < D.world; k++) {
+    const Cand *h = reinterpret_cast<const Cand *>(D.recv + (size_t)k * D.rec_bytes);
+    if (h->pos < 0) continue;
+    if (h->key < bk || (h->key == bk && h->var < bvar)) { bk = h->key; bvar = h->var; wk = k; }
+  }
+  ShardCtl n = c;
+  if (wk < 0) {
+    n.status = MVB_OPT;
+    if (lead) *next = n;
+    return;
+  }
+  if (c.iters >= D.max_iters) {
+    n.status = MVB_ITLIM;
+    if (lead) *next = n;
+    return;
+  }
+  const Cand cand = *reinterpret_cast<const Cand *>(D.recv + (size_t)wk * D.rec_bytes);
+  const double *col = reinterpret_cast<const double *>(D.recv + (size_t)wk * D.rec_bytes + SHARD_HDR);
+  const bool bland = c.degen >= MVB_BLAND_AFTER;
+  const double *beta = D.beta[c.cS];
+  const int *head = D.head[c.cS];
+  const int dir = col[0] < 0.0 ? 1 : -1;
+  // K2 ratio test over the gathered pivot column, lowest variable id on ties
+  Key bi = key_none();
+  for (int i = 1 + tid; i <= m; i += NT) {
+    const int var = head[i];
+    double t;
+    int fl;
+    if (!primal_ratio_row(col[i], dir, 0, beta[i], D.lb[var], D.ub[var], t, fl)) continue;
+    const Key k{dbits(t), var, i};
+    if (key_less(k, bi)) bi = k;
+  }
+  bi = block_argmin(bi, sm.redK);
+  const double lq = cand.lq, uq = cand.uq;
+  const int fq = cand.flag;
+  const double tflip = uq - lq;
+  const double tmin = bi.idx >= 0 ? __longlong_as_double((long long)bi.k) : HUGE_VAL;
+  int r = 0, newat = MVB_AT_LB;
+  double delta, newbr = 0.0;
+  if (tflip <= tmin) {
+    if (!(tflip < HUGE_VAL)) {
+      n.status = MVB_UNBND;
+      if (lead) *next = n;
+      return;
+    }
+    delta = dir > 0 ? tflip : -tflip;
+    newat = fq == MVB_AT_LB ? MVB_AT_UB : MVB_AT_LB;
+    n.degen = 0;
+  } else {
+    r = bi.idx;
+    double t;
+    primal_ratio_row(col[r], dir, 0, beta[r], D.lb[bi.var], D.ub[bi.var], t, newat);
+    delta = dir > 0 ? tmin : -tmin;
+    newbr = nb_value(fq, lq, uq) + delta;
+    n.degen = tmin == 0.0 ? c.degen + 1 : 0;
+  }
+  const int kin = cand.var;
+  int kout = kin;
+  if (r) {
+    kout = bi.var;
+    if (D.lb[kout] == D.ub[kout]) newat = MVB_AT_FX;
+  }
+  const int qloc = cand.pos - D.col0;  // local position of the entering column, if it is ours
+  // next small state (ping-pong), split over the whole grid
+  {
+    double *bd = D.beta[c.cS ^ 1];
+    int *hd = D.head[c.cS ^ 1], *nd = D.nb[c.cS ^ 1], *ad = D.at[c.cS ^ 1];
+    const int *ns = D.nb[c.cS], *as = D.at[c.cS];
+    const int gt = blockIdx.x * NT + tid, stride = gridDim.x * NT;
+    for (int i = 1 + gt; i <= m; i += stride) {
+      bd[i] = i == r ? newbr : fma(col[i], delta, beta[i]);
+      hd[i] = i == r ? kin : head[i];
+    }
+    for (int j = gt; j < D.nloc; j += stride) {
+      nd[j] = j == qloc ? kout : ns[j];
+      ad[j] = j == qloc ? newat : as[j];
+    }
+  }
+  if (r) {
+    const double inv = 1.0 / col[r];
+    shard_tile_update(D, D.T[c.cT], D.T[c.cT ^ 1], r, qloc, inv, col, sm);
+    n.cT = c.cT ^ 1;
+  }
+  n.cS = c.cS ^ 1;
+  if (lead) {
+    unsigned long long h = c.hash;
+    h = (h ^ (unsigned long long)MVB_MODE_PRIMAL2) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)r) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)cand.pos) * MVB_FNV_PRIME;
+    n.hash = h;
+    if (D.pivlog && c.iters < D.pivlog_cap) {
+      D.pivlog[2 * c.iters] = r;
+      D.pivlog[2 * c.iters + 1] = cand.pos;
+    }
+    n.iters = c.iters + 1;
+    if (r) n.pivots++; else n.flips++;
+    if (bland) n.bland_iters++;
+    *next = n;
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host
+namespace {
+
+// NCCL through dlopen: prefer the copy the process has already loaded (torch's),
+// then $MVOLPS_NCCL_LIB, then the system library
+struct NcclId { char internal[MVB_NCCL_ID_BYTES]; };
+struct NcclApi {
+  void *lib = nullptr;
+  int (*GetUniqueId)(void *) = nullptr;
+  int (*CommInitRank)(void **, int, NcclId /* ncclUniqueId, by value */, int) = nullptr;
+  int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
+  int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void *) = nullptr;
+  const char *(*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+
+bool nccl_load() {
+  if (g_nccl.lib) return true;
+  void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+  if (!h && getenv("MVOLPS_NCCL_LIB")) h = dlopen(getenv("MVOLPS_NCCL_LIB"), RTLD_NOW);
+  if (!h) h = dlopen("libnccl.so.2", RTLD_NOW);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW);
+  if (!h) return fail(std::string("cannot load NCCL: ") + dlerror());
+  g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))dlsym(h, "ncclCommInitRank");
+  g_nccl.AllGather = (decltype(g_nccl.AllGather))dlsym(h, "ncclAllGather");
+  g_nccl.AllReduce = (decltype(g_nccl.AllReduce))dlsym(h, "ncclAllReduce");
+  g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(h, "ncclCommDestroy");
+  g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(h, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.AllReduce ||
+      !g_nccl.CommDestroy)
+    return fail("NCCL library lacks a required symbol");
+  g_nccl.lib = h;
+  return true;
+}
+
+struct NcclCtx {
+  void *comm = nullptr;
+  double *dbuf = nullptr;  // device scratch for the small host reductions
+};
+
+int nccl_allgather(void *ctx, const void *send, void *recv, size_t bytes, void *stream) {
+  NcclCtx *c = (NcclCtx *)ctx;
+  const int rc = g_nccl.AllGather(send, recv, bytes, /*ncclChar*/ 0, c->comm, (cudaStream_t)stream);
+  if (rc) { g_err = std::string("ncclAllGather: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "error"); return -1; }
+  return 0;
+}
+int nccl_allreduce_max(void *ctx, double *vals, int count) {
+  NcclCtx *c = (NcclCtx *)ctx;
+  if (count > 64) { g_err = "allreduce_max: at most 64 values"; return -1; }
+  cudaStream_t st = g_ctx.stream;
+  if (cudaMemcpyAsync(c->dbuf, vals, count * sizeof(double), cudaMemcpyHostToDevice, st) != cudaSuccess) return -1;
+  const int rc = g_nccl.AllReduce(c->dbuf, c->dbuf, count, /*ncclDouble*/ 8, /*ncclMax*/ 2, c->comm, st);
+  if (rc) { g_err = "ncclAllReduce failed"; return -1; }
+  if (cudaMemcpyAsync(vals, c->dbuf, count * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
+  return cudaStreamSynchronize(st) == cudaSuccess ? 0 : -1;
+}
+void nccl_destroy(void *ctx) {
+  NcclCtx *c = (NcclCtx *)ctx;
+  if (c->comm) g_nccl.CommDestroy(c->comm);
+  if (c->dbuf) cudaFree(c->dbuf);
+  delete c;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mvb_nccl_unique_id(void *id) {
+  if (!nccl_load()) return -1;
+  return g_nccl.GetUniqueId(id) ? (g_err = "ncclGetUniqueId failed", -1) : 0;
+}
+
+mvb_comm *mvb_comm_nccl(const void *id, int rank, int world) {
+  if (!ctx_init(-1) || !nccl_load()) return nullptr;
+  NcclId nid;
+  std::memcpy(nid.internal, id, MVB_NCCL_ID_BYTES);
+  NcclCtx *c = new NcclCtx();
+  const int rc = g_nccl.CommInitRank(&c->comm, world, nid, rank);
+  if (rc || cudaMalloc((void **)&c->dbuf, 64 * sizeof(double)) != cudaSuccess) {
+    g_err = "ncclCommInitRank failed";
+    delete c;
+    return nullptr;
+  }
+  mvb_comm *m = new mvb_comm();
+  m->ctx = c;
+  m->rank = rank;
+  m->world = world;
+  m->allgather_dev = nccl_allgather;
+  m->allreduce_max = nccl_allreduce_max;
+  m->destroy = nccl_destroy;
+  return m;
+}
+
+// member of a single-process group of `world` shards on one GPU (tests, emulation):
+// mvb_shard_solve then takes all shards in one call and copies device-to-device
+mvb_comm *mvb_comm_local(int rank, int world) {
+  mvb_comm *m = new mvb_comm();
+  m->ctx = nullptr;
+  m->rank = rank;
+  m->world = world;
+  m->allgather_dev = nullptr;
+  m->allreduce_max = nullptr;
+  m->destroy = nullptr;
+  return m;
+}
+
+void mvb_comm_free(mvb_comm *c) {
+  if (!c) return;
+  if (c->destroy) c->destroy(c->ctx);
+  delete c;
+}
+
+void mvb_shard_partition(int n, int world, int rank, int *col0, int *ncols) {
+  int per = (n + world - 1) / world;
+  per = (per + MVB_LD_ALIGN - 1) / MVB_LD_ALIGN * MVB_LD_ALIGN;
+  int a = std::min(n, rank * per), b = std::min(n, (rank + 1) * per);
+  if (col0) *col0 = a;
+  if (ncols) *ncols = b - a;
+}
+
+}  // extern "C"
+
+struct mvb_shard {
+  int m = 0, nglob = 0, col0 = 0, nloc = 0, ld = 0, maxloc = 0;
+  const mvb_comm *comm = nullptr;
+  int world = 1, rank = 0;
+  char *slab = nullptr;
+  ShardDev dev{};
+  size_t fin_bytes = 0;            // per-rank record of the final gather (nb | at | cost)
+  unsigned char *fin_send = nullptr, *fin_recv = nullptr;
+  double *cost = nullptr;          // local costs (device)
+  std::vector<double> lb, ub;      // replicated bounds (host)
+  std::vector<double> x;           // primal by id after the last solve
+  int *pivlog = nullptr; int pivlog_cap = 0, pivlog_n = 0;
+  cudaEvent_t ev[2] = {};
+  float last_ms = 0.f;
+};
+
+namespace {
+
+bool shard_alloc(mvb_shard *s) {
+  const int m = s->m, nloc = s->nloc;
+  s->ld = (int)align_up((size_t)std::max(nloc, 1), MVB_LD_ALIGN);
+  int per = (s->nglob + s->world - 1) / s->world;
+  s->maxloc = (per + MVB_LD_ALIGN - 1) / MVB_LD_ALIGN * MVB_LD_ALIGN;
+  const size_t A = 256;
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, A); return o; };
+  const size_t tb = (size_t)(m + 1) * s->ld * sizeof(double);
+  const size_t rec = align_up(SHARD_HDR + (size_t)(m + 1) * sizeof(double), 16);
+  s->fin_bytes = align_up((size_t)s->maxloc * (2 * sizeof(int) + sizeof(double)), 16);
+  size_t oT0 = take(tb), oT1 = take(tb);
+  size_t ob0 = take((m + 1) * sizeof(double)), ob1 = take((m + 1) * sizeof(double));
+  size_t oh0 = take((m + 1) * sizeof(int)), oh1 = take((m + 1) * sizeof(int));
+  size_t on0 = take((size_t)s->ld * sizeof(int)), on1 = take((size_t)s->ld * sizeof(int));
+  size_t oa0 = take((size_t)s->ld * sizeof(int)), oa1 = take((size_t)s->ld * sizeof(int));
+  size_t olb = take((size_t)(s->nglob + m) * sizeof(double)), oub = take((size_t)(s->nglob + m) * sizeof(double));
+  size_t oc = take((size_t)s->ld * sizeof(double));
+  size_t octl = take(2 * sizeof(ShardCtl));
+  size_t osend = take(rec), orecv = take(rec * s->world);
+  size_t ofs = take(s->fin_bytes), ofr = take(s->fin_bytes * s->world);
+  CK(cudaMallocAsync((void **)&s->slab, off, g_ctx.stream));
+  CK(cudaMemsetAsync(s->slab, 0, off, g_ctx.stream));
+  char *b = s->slab;
+  ShardDev &d = s->dev;
+  d.m = m; d.nloc = nloc; d.ld = s->ld; d.col0 = s->col0; d.world = s->world;
+  d.T[0] = (double *)(b + oT0); d.T[1] = (double *)(b + oT1);
+  d.beta[0] = (double *)(b + ob0); d.beta[1] = (double *)(b + ob1);
+  d.head[0] = (int *)(b + oh0); d.head[1] = (int *)(b + oh1);
+  d.nb[0] = (int *)(b + on0); d.nb[1] = (int *)(b + on1);
+  d.at[0] = (int *)(b + oa0); d.at[1] = (int *)(b + oa1);
+  d.lb = (double *)(b + olb); d.ub = (double *)(b + oub);
+  s->cost = (double *)(b + oc);
+  d.ctl = (ShardCtl *)(b + octl);
+  d.send = (unsigned char *)(b + osend); d.recv = (unsigned char *)(b + orecv);
+  d.rec_bytes = rec;
+  s->fin_send = (unsigned char *)(b + ofs); s->fin_recv = (unsigned char *)(b + ofr);
+  return true;
+}
+
+// final gather record: nb[maxloc] | at[maxloc] | cost[maxloc]
+__global__ void shard_pack_final(ShardDev D, int par, const double *cost, int maxloc, unsigned char *out) {
+  const ShardCtl c = D.ctl[par];
+  int *nb = (int *)out, *at = nb + maxloc;
+  double *co = (double *)(at + maxloc);
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < maxloc; j += gridDim.x * blockDim.x) {
+    const bool in = j < D.nloc;
+    nb[j] = in ? D.nb[c.cS][j] : -1;
+    at[j] = in ? D.at[c.cS][j] : 0;
+    co[j] = in ? cost[j] : 0.0;
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+mvb_shard *mvb_shard_create(int m, int n_global, int col0, int ncols, const mvb_comm *comm) {
+  if (m < 1 || n_global < 1 || col0 < 0 || ncols < 0 || col0 + ncols > n_global) {
+    g_err = "mvb_shard_create: bad dimensions";
+    return nullptr;
+  }
+  if (!ctx_init(-1)) return nullptr;
+  mvb_shard *s = new mvb_shard();
+  if (!comm) { g_err = "mvb_shard_create: a communicator is required (mvb_comm_nccl / mvb_comm_local)"; delete s; return nullptr; }
+  s->m = m; s->nglob = n_global; s->col0 = col0; s->nloc = ncols; s->comm = comm;
+  s->world = comm->world; s->rank = comm->rank;
+  return s;  // device memory is allocated at load
+}
+
+void mvb_shard_free(mvb_shard *s) {
+  if (!s) return;
+  if (s->slab) cudaFreeAsync(s->slab, g_ctx.stream);
+  if (s->pivlog) cudaFreeAsync(s->pivlog, g_ctx.stream);
+  if (s->ev[0]) { cudaEventDestroy(s->ev[0]); cudaEventDestroy(s->ev[1]); }
+  delete s;
+}
+
+int mvb_shard_load(mvb_shard *s, const double *A_local, const double *cost_local, const double *lb,
+                   const double *ub) {
+  const int m = s->m, nloc = s->nloc, ng = s->nglob;
+  cudaStream_t st = g_ctx.stream;
+  // this path starts primal phase 2 from the slack basis with every non-basic at value 0
+  for (int j = 0; j < nloc; j++) {
+    const double l = lb[s->col0 + j], u = ub[s->col0 + j];
+    const bool zero_ok = (l == 0.0) || (!(l > -HUGE_VAL) && (u == 0.0 || !(u < HUGE_VAL)));
+    if (!zero_ok) { g_err = "mvb_shard_load: sharded path needs non-basic values 0 (lb = 0 or free)"; return -1; }
+  }
+  for (int i = 0; i < m; i++)
+    if (lb[ng + i] > 0.0 || ub[ng + i] < 0.0) {
+      g_err = "mvb_shard_load: slack basis is not primal feasible (phase 1 is not sharded)";
+      return -1;
+    }
+  if (s->slab) { CKI(cudaFreeAsync(s->slab, st)); s->slab = nullptr; }
+  if (!shard_alloc(s)) return -1;
+  ShardDev &d = s->dev;
+  if (nloc > 0) {
+    CKI(cudaMemcpyAsync(d.T[0], cost_local, (size_t)nloc * sizeof(double), cudaMemcpyHostToDevice, st));
+    CKI(cudaMemcpy2DAsync(d.T[0] + s->ld, (size_t)s->ld * sizeof(double), A_local, (size_t)nloc * sizeof(double),
+                          (size_t)nloc * sizeof(double), m, cudaMemcpyHostToDevice, st));
+    CKI(cudaMemcpyAsync(s->cost, cost_local, (size_t)nloc * sizeof(double), cudaMemcpyHostToDevice, st));
+  }
+  CKI(cudaMemcpyAsync(d.lb, lb, (size_t)(ng + m) * sizeof(double), cudaMemcpyHostToDevice, st));
+  CKI(cudaMemcpyAsync(d.ub, ub, (size_t)(ng + m) * sizeof(double), cudaMemcpyHostToDevice, st));
+  s->lb.assign(lb, lb + ng + m);
+  s->ub.assign(ub, ub + ng + m);
+  std::vector<int> head(m + 1, 0), nb(std::max(nloc, 1)), at(std::max(nloc, 1));
+  for (int i = 1; i <= m; i++) head[i] = ng + i - 1;
+  for (int j = 0; j < nloc; j++) {
+    nb[j] = s->col0 + j;
+    at[j] = nb_flag_for(lb[s->col0 + j], ub[s->col0 + j], MVB_AT_LB);
+  }
+  CKI(cudaMemcpyAsync(d.head[0], head.data(), (size_t)(m + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
+  if (nloc > 0) {
+    CKI(cudaMemcpyAsync(d.nb[0], nb.data(), (size_t)nloc * sizeof(int), cudaMemcpyHostToDevice, st));
+    CKI(cudaMemcpyAsync(d.at[0], at.data(), (size_t)nloc * sizeof(int), cudaMemcpyHostToDevice, st));
+  }
+  // beta = T v with v = 0: exactly +0.0 in every row (slab is zero-filled)
+  CKI(cudaStreamSynchronize(st));
+  s->x.assign(ng + m, 0.0);
+  return 0;
+}
+
+int mvb_shard_get_primal(mvb_shard *s, double *x) {
+  if ((int)s->x.size() != s->nglob + s->m) { g_err = "mvb_shard_get_primal: no solution"; return -1; }
+  std::memcpy(x, s->x.data(), s->x.size() * sizeof(double));
+  return 0;
+}
+
+int mvb_shard_get_pivot_log(mvb_shard *s, int *rowcol, int cap) {
+  int c = std::min(s->pivlog_n, cap);
+  if (c > 0) {
+    CKI(cudaMemcpyAsync(rowcol, s->pivlog, (size_t)c * 2 * sizeof(int), cudaMemcpyDeviceToHost, g_ctx.stream));
+    CKI(cudaStreamSynchronize(g_ctx.stream));
+  }
+  return s->pivlog_n;
+}
+
+double mvb_shard_last_ms(mvb_shard *s) { return s->last_ms; }
+
+}  // extern "C"
+
+extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_opts *opts,
+                               mvb_result *out) {
+  if (nlocal < 1) return 0;
+  if (!ctx_init(-1)) return -1;
+  cudaStream_t st = g_ctx.stream;
+  mvb_shard *s0 = shards[0];
+  const bool local = s0->comm->allgather_dev == nullptr;
+  if (local && nlocal != s0->world) { g_err = "mvb_shard_solve: a local group needs all its shards"; return -1; }
+  if (!local && nlocal != 1) { g_err = "mvb_shard_solve: one shard per process over NCCL"; return -1; }
+  const int m = s0->m, ng = s0->nglob;
+  const int mi = (opts && opts->max_iters > 0) ? opts->max_iters : 50 * (m + ng) + 10000;
+  ShardCtl init{};
+  init.status = -1;
+  init.hash = MVB_FNV_OFFSET;
+  for (int k = 0; k < nlocal; k++) {
+    mvb_shard *s = shards[k];
+    if (!s->slab) { g_err = "mvb_shard_solve: shard not loaded"; return -1; }
+    if (opts && opts->log_pivots) {
+      const int want = std::min(mi, 1 << 22);
+      if (s->pivlog_cap < want) {
+        if (s->pivlog) CKI(cudaFreeAsync(s->pivlog, st));
+        CKI(cudaMallocAsync((void **)&s->pivlog, (size_t)want * 2 * sizeof(int), st));
+        s->pivlog_cap = want;
+      }
+    }
+    s->dev.max_iters = mi;
+    s->dev.pivlog = (opts && opts->log_pivots) ? s->pivlog : nullptr;
+    s->dev.pivlog_cap = s->dev.pivlog ? s->pivlog_cap : 0;
+    CKI(cudaMemcpyAsync(&s->dev.ctl[0], &init, sizeof(init), cudaMemcpyHostToDevice, st));
+    if (!s->ev[0]) { CKI(cudaEventCreate(&s->ev[0])); CKI(cudaEventCreate(&s->ev[1])); }
+  }
+  auto exchange = [&](bool fin) -> bool {
+    for (int k = 0; k < nlocal; k++) {
+      mvb_shard *s = shards[k];
+      const unsigned char *snd = fin ? s->fin_send : s->dev.send;
+      const size_t bytes = fin ? s->fin_bytes : s->dev.rec_bytes;
+      if (!local) {
+        unsigned char *rcv = fin ? s->fin_recv : s->dev.recv;
+        if (s->comm->allgather_dev(s->comm->ctx, snd, rcv, bytes, st)) return false;
+      } else {
+        for (int t = 0; t < nlocal; t++) {
+          unsigned char *rcv = (fin ? shards[t]->fin_recv : shards[t]->dev.recv) + (size_t)s->rank * bytes;
+          CK(cudaMemcpyAsync(rcv, snd, bytes, cudaMemcpyDeviceToDevice, st));
+        }
+      }
+    }
+    return true;
+  };
+  const int grid = std::max(1, g_ctx.max_ctas);
+  const int CHUNK = 32;  // iterations enqueued between two looks at the control block
+  int par = 0;
+  ShardCtl h{};
+  CKI(cudaEventRecord(s0->ev[0], st));
+  while (true) {
+    for (int it = 0; it < CHUNK; it++) {
+      for (int k = 0; k < nlocal; k++) shard_price_kernel<<<1, 1024, 0, st>>>(shards[k]->dev, par);
+      if (!exchange(false)) return -1;
+      for (int k = 0; k < nlocal; k++) shard_pivot_kernel<<<grid, 512, 0, st>>>(shards[k]->dev, par);
+      g_launches += 2 * nlocal;
+      par ^= 1;
+    }
+    CKI(cudaGetLastError());
+    CKI(cudaMemcpyAsync(&h, &s0->dev.ctl[par], sizeof(h), cudaMemcpyDeviceToHost, st));
+    CKI(cudaStreamSynchronize(st));
+    if (h.status != -1) break;
+  }
+  // final gather: positions / flags / costs of every rank, then x and the objective on the host
+  for (int k = 0; k < nlocal; k++)
+    shard_pack_final<<<32, 256, 0, st>>>(shards[k]->dev, par, shards[k]->cost, shards[k]->maxloc,
+                                         shards[k]->fin_send);
+  g_launches += nlocal;
+  if (!exchange(true)) return -1;
+  CKI(cudaEventRecord(s0->ev[1], st));
+  for (int k = 0; k < nlocal; k++) {
+    mvb_shard *s = shards[k];
+    const int W = s->world, ML = s->maxloc;
+    std::vector<unsigned char> fin(s->fin_bytes * W);
+    std::vector<double> beta(m + 1);
+    std::vector<int> head(m + 1);
+    CKI(cudaMemcpyAsync(fin.data(), s->fin_recv, fin.size(), cudaMemcpyDeviceToHost, st));
+    CKI(cudaMemcpyAsync(beta.data(), s->dev.beta[h.cS], (size_t)(m + 1) * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CKI(cudaMemcpyAsync(head.data(), s->dev.head[h.cS], (size_t)(m + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CKI(cudaStreamSynchronize(st));
+    std::vector<double> cost(ng, 0.0);
+    s->x.assign(ng + m, 0.0);
+    for (int r = 0; r < W; r++) {
+      int c0, nc;
+      mvb_shard_partition(ng, W, r, &c0, &nc);
+      const int *nb = (const int *)(fin.data() + (size_t)r * s->fin_bytes), *at = nb + ML;
+      const double *co = (const double *)(at + ML);
+      for (int j = 0; j < nc; j++) {
+        cost[c0 + j] = co[j];
+        const int id = nb[j], f = at[j];
+        s->x[id] = (f == MVB_AT_LB || f == MVB_AT_FX) ? s->lb[id] : f == MVB_AT_UB ? s->ub[id] : 0.0;
+      }
+    }
+    int ninf = 0;
+    for (int i = 1; i <= m; i++) {
+      const int id = head[i];
+      s->x[id] = beta[i];
+      const double l = s->lb[id], u = s->ub[id], b = beta[i];
+      if (l - b > MVB_TOL_BND * (1.0 + std::fabs(l)) || b - u > MVB_TOL_BND * (1.0 + std::fabs(u))) ninf++;
+    }
+    // objective: the engine's 32-lane fma chains + halving tree (solve_lp epilogue)
+    double lane[32];
+    for (int l = 0; l < 32; l++) {
+      double p = 0.0;
+      for (int j = l; j < ng; j += 32) p = std::fma(cost[j], s->x[j], p);
+      lane[l] = p;
+    }
+    for (int off = 16; off >= 1; off >>= 1)
+      for (int l = 0; l < off; l++) lane[l] = lane[l] + lane[l + off];
+    s->pivlog_n = s->dev.pivlog ? std::min(h.iters, s->pivlog_cap) : 0;
+    if (k == 0) {
+      mvb_result r{};
+      r.status = h.status;
+      r.iters = h.iters;
+      r.pivots = h.pivots;
+      r.flips = h.flips;
+      r.iters_primal2 = h.iters;
+      r.bland_iters = h.bland_iters;
+      r.pivot_hash = h.hash;
+      r.obj = lane[0];
+      r.primal_feasible = ninf == 0;
+      *out = r;
+    }
+  }
+  CKI(cudaEventElapsedTime(&s0->last_ms, s0->ev[0], s0->ev[1]));
+  for (int k = 1; k < nlocal; k++) shards[k]->last_ms = s0->last_ms;
+  return 0;
+}
