@@ -126,6 +126,17 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--ctas-per-lp", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="dense", choices=["dense", "batch", "shard", "bnb"],
+                    help="dense: configs[1], one LP per GPU (default, the driver's line); batch: configs[3], "
+                         "node LPs m=256 n=512 dealt over the ranks; shard: configs[4], one tableau column-sharded")
+    ap.add_argument("--lps", type=int, default=4096, help="batch: LPs in total")
+    ap.add_argument("--distinct", type=int, default=128, help="batch: distinct seeds (the rest are clones)")
+    ap.add_argument("--m", type=int, default=0)
+    ap.add_argument("--n", type=int, default=0)
+    ap.add_argument("--pivots", type=int, default=300, help="shard: pivot budget per step")
+    ap.add_argument("--nodes", type=int, default=2000, help="bnb: node budget per step")
+    ap.add_argument("--cut-mode", type=int, default=0, help="bnb: 0 none, 1 reference gmi.cpp, 2 textbook GMI")
+    ap.add_argument("--batch-width", type=int, default=256, help="bnb: FIFO nodes per engine launch")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -144,6 +155,10 @@ def main():
     if L.mvb_device_init(local) != 0:
         raise RuntimeError("CUDA engine unavailable: " + L.mvb_last_error().decode())
     L.glp_term_out(capi.GLP_OFF)
+    if args.workload != "dense":
+        from bench_extra import run_batch, run_bnb, run_shard
+        fn = {"batch": run_batch, "shard": run_shard, "bnb": run_bnb}[args.workload]
+        return fn(args, L, rank, world, local, dist, ClockSampler, peaks)
     inst = instances.dense_lp(M, N_COLS, SEED + rank)
     template = EngineLP.from_instance(L, inst)      # pristine tableau, resident in HBM
     work = template.clone()
@@ -247,4 +262,12 @@ def main():
 
 
 if __name__ == "__main__":
-    main()
+    try:
+        main()
+    finally:
+        try:
+            import torch.distributed as _d
+            if _d.is_available() and _d.is_initialized():
+                _d.destroy_process_group()
+        except Exception:
+            pass

@@ -1,0 +1,172 @@
+"""bench.py --workload batch|shard: the multi-LP and the column-sharded configs
+(BASELINE.json configs[3] and configs[4]).  Same timing rules as bench.py: CUDA
+events on the engine stream, L2 flushed between steps, max over ranks."""
+import ctypes as C
+import json
+import time
+
+import numpy as np
+
+from mvolps_b200 import capi, instances
+from mvolps_b200.dist import ShardGroup, nccl_comm
+from mvolps_b200.lp import EngineLP, solve_batch
+
+
+def _reduce(dist, vals_sum, vals_max):
+    if dist is None:
+        return vals_sum, vals_max
+    import torch
+    a = torch.tensor(vals_sum, dtype=torch.float64, device="cuda")
+    b = torch.tensor(vals_max, dtype=torch.float64, device="cuda")
+    dist.all_reduce(a)
+    dist.all_reduce(b, op=dist.ReduceOp.MAX)
+    return a.tolist(), b.tolist()
+
+
+def run_batch(args, L, rank, world, local, dist, ClockSampler, peaks):
+    """configs[3]: `--lps` node LPs (m=256 n=512, cfg-2 distribution) dealt round-robin over the
+    ranks, each rank one mvb_solve_batch launch per step; no data-path collective."""
+    m, n = args.m or 256, args.n or 512
+    mine = [k for k in range(args.lps) if k % world == rank]
+    seeds = sorted({k % args.distinct for k in mine})
+    tmpl = {sd: EngineLP.from_instance(L, instances.dense_lp(m, n, sd)) for sd in seeds}
+    work = [tmpl[k % args.distinct].clone() for k in mine]
+
+    def step():
+        for w, k in zip(work, mine):
+            w.assign(tmpl[k % args.distinct])
+        L.mvb_flush_l2()
+        L.mvb_timer_record(0)
+        res = solve_batch(L, work, ctas_per_lp=args.ctas_per_lp)
+        L.mvb_timer_record(1)
+        return res, L.mvb_timer_elapsed_ms(0, 1)
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    if dist is not None:
+        dist.barrier()
+    l0 = L.mvb_kernel_launches()
+    piv, ms = 0, 0.0
+    with ClockSampler(local) as clk:
+        for _ in range(args.steps):
+            res, t = step()
+            assert all(r["status"] == 0 for r in res)
+            piv += sum(r["pivots"] for r in res)
+            ms += t
+    launches = int(L.mvb_kernel_launches() - l0)
+    (tot_piv,), (max_ms,) = _reduce(dist, [piv], [ms])
+    if rank != 0:
+        return
+    G, groups, nt = C.c_int(), C.c_int(), C.c_int()
+    L.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
+    peak, src = peaks()
+    alg = 16.0 * (m + 1) * (n + 1) * tot_piv
+    ach = alg / (max_ms * 1e-3) / 1e9
+    print(json.dumps({
+        "metric": "lp_pivots_per_sec", "value": tot_piv / (max_ms * 1e-3), "unit": "pivots/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": max_ms / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{args.lps} node LPs m={m} n={n} ({args.distinct} distinct seeds, cloned on the device), "
+                               "full solves, dealt round-robin over the ranks (BASELINE configs[3])",
+                   "lps_per_sec": args.lps * args.steps / (max_ms * 1e-3), "ctas_per_lp": G.value,
+                   "groups": groups.value, "l2": "flushed between steps"},
+        "roofline": {"bound": "hbm", "achieved": ach, "peak": peak * world, "unit": "GB/s", "frac": ach / (peak * world),
+                     "traffic": None, "peak_source": src, "kernel": "simplex_ps_kernel (batched, G CTAs per LP)"},
+        "gpu_launches": launches, "clocks": clk.summary(),
+    }))
+
+
+def run_shard(args, L, rank, world, local, dist, ClockSampler, peaks):
+    """configs[4]: one dense LP, tableau column-sharded over the ranks, `--pivots` iterations per step."""
+    m, n = args.m or 16384, args.n or 32768
+    inst = instances.dense_lp(m, n, 5)
+    comm = nccl_comm(L, rank, world, dist) if dist is not None else None
+
+    def fresh():
+        return ShardGroup(L, inst, world, comm=comm, rank=rank)
+
+    tot_ms, tot_piv, r = 0.0, 0, None
+    l0 = None
+    with ClockSampler(local) as clk:
+        for k in range(max(args.warmup, 1) + args.steps):
+            g = fresh()  # reload: a step starts from the slack basis
+            L.mvb_flush_l2()
+            if dist is not None:
+                dist.barrier()
+            if k == max(args.warmup, 1):
+                l0 = L.mvb_kernel_launches()
+            r = g.solve(max_iters=args.pivots)
+            if k >= max(args.warmup, 1):
+                tot_ms += g.last_ms()
+                tot_piv += r["pivots"]
+            g.free()
+    launches = int(L.mvb_kernel_launches() - l0)
+    _, (max_ms,) = _reduce(dist, [0.0], [tot_ms])
+    if rank != 0:
+        return
+    peak, src = peaks()
+    ach = 16.0 * (m + 1) * (n + 1) * tot_piv / (max_ms * 1e-3) / 1e9
+    print(json.dumps({
+        "metric": "simplex_pivots_per_sec", "value": tot_piv / (max_ms * 1e-3), "unit": "pivots/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": max_ms / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"dense LP m={m} n={n} seed=5, tableau column-sharded over {world} GPU(s), first "
+                               f"{args.pivots} pivots from the slack basis per step (BASELINE configs[4])",
+                   "exchange": "one all-gather per pivot: 64 B header + 8*(m+1) B column per rank",
+                   "pivot_hash": str(r["pivot_hash"]), "l2": "tableau shard larger than L2"},
+        "roofline": {"bound": "hbm", "achieved": ach, "peak": peak * world, "unit": "GB/s", "frac": ach / (peak * world),
+                     "traffic": None, "peak_source": src, "kernel": "shard_pivot_kernel (eager rank-1 update of the local columns)"},
+        "gpu_launches": launches, "clocks": clk.summary(),
+    }))
+
+
+def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks):
+    """configs[2]: MDKP 200 vars x 50 rows (seed 2024 + rank), FIFO B&B with a node budget through
+    mvb_bnb_run (batched node LPs on the device); the same driver on the CPU oracle is the baseline.
+    N > 1: one independent tree per rank (no exchange)."""
+    import os
+    from mvolps_b200.lp import GlpProb
+    inst = instances.mdkp(args.n or 200, args.m or 50, 2024 + rank)
+    prob = GlpProb.from_instance(L, inst)
+
+    def step(lib, p):
+        t0 = time.perf_counter()
+        out = p.bnb(cut_mode=args.cut_mode, batch_width=args.batch_width, max_iters=args.nodes)
+        return out, time.perf_counter() - t0
+
+    for _ in range(max(args.warmup, 1)):
+        step(L, prob)
+    if dist is not None:
+        dist.barrier()
+    l0 = L.mvb_kernel_launches()
+    nodes, secs, out = 0, 0.0, None
+    with ClockSampler(local) as clk:
+        for _ in range(args.steps):
+            out, dt = step(L, prob)
+            nodes += out["iterations"]
+            secs += dt
+    launches = int(L.mvb_kernel_launches() - l0)
+    (tot_nodes,), (max_s,) = _reduce(dist, [nodes], [secs])
+    if rank != 0:
+        return
+    line = {
+        "metric": "bnb_nodes_per_sec", "value": tot_nodes / max_s, "unit": "nodes/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * max_s / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"MDKP {args.n or 200} vars x {args.m or 50} rows seed 2024+rank, FIFO B&B, node budget "
+                               f"{args.nodes}, cut mode {args.cut_mode}, batch width {args.batch_width} (BASELINE configs[2]); "
+                               "host wall clock around mvb_bnb_run (host logic + H2D/D2H included)",
+                   "lp_solves": out["lp_solves"], "engine_launches": out["launches"],
+                   "simplex_iters": out["simplex_iters"], "event_hash": str(out["event_hash"])},
+        "gpu_launches": launches, "clocks": clk.summary(),
+    }
+    if not args.no_cpu_baseline and world == 1:
+        orc = capi.load_library(os.path.join(os.path.dirname(os.path.abspath(__file__)), "oracle", "_build",
+                                             "libglpk_oracle.so"))
+        orc.glp_term_out(capi.GLP_OFF)
+        po = GlpProb.from_instance(orc, inst)
+        oo, dt = step(orc, po)
+        line["cpu_baseline"] = {"value": oo["iterations"] / dt, "unit": "nodes/s", "cores": os.cpu_count(),
+                                "kind": "port", "sample": f"same driver on the oracle engine, {oo['iterations']} nodes, "
+                                f"{dt:.1f} s; event hash {'equal' if oo['event_hash'] == out['event_hash'] else 'DIFFERENT'}"}
+    print(json.dumps(line))
