@@ -64,6 +64,11 @@ mvb_comm *mvb_comm_nccl(const void *id, int rank, int world);
 mvb_comm *mvb_comm_local(int rank, int world);
 void mvb_comm_free(mvb_comm *c);
 
+/* incumbent / bound broadcast of a node-sharded tree (bs.cpp:172 keeps the first
+ * strictly better incumbent): on return *incumbent is the maximum over the ranks
+ * and *owner the lowest rank that held it.  Uses comm->allreduce_max twice. */
+int mvb_incumbent_exchange(const mvb_comm *c, double *incumbent, int *owner);
+
 /* contiguous split of n positions over `world` ranks, multiples of 16 columns
  * (row stride alignment) except for the last rank */
 void mvb_shard_partition(int n, int world, int rank, int *col0, int *ncols);

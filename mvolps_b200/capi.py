@@ -50,6 +50,7 @@ BNB_SYMBOLS = [
 ]
 DIST_SYMBOLS = [  # include/mvolps_dist.h: exported by the product only
     "mvb_nccl_unique_id", "mvb_comm_nccl", "mvb_comm_local", "mvb_comm_free", "mvb_shard_partition",
+    "mvb_incumbent_exchange",
     "mvb_shard_create", "mvb_shard_free", "mvb_shard_load", "mvb_shard_solve",
     "mvb_shard_get_primal", "mvb_shard_get_pivot_log", "mvb_shard_last_ms",
 ]
@@ -168,6 +169,7 @@ def _bind(lib):
         "mvb_comm_nccl": (_P, [C.c_void_p, C.c_int, C.c_int]),
         "mvb_comm_local": (_P, [C.c_int, C.c_int]),
         "mvb_comm_free": (None, [_P]),
+        "mvb_incumbent_exchange": (C.c_int, [_P, _dp, _ip]),
         "mvb_shard_partition": (None, [C.c_int, C.c_int, C.c_int, _ip, _ip]),
         "mvb_shard_create": (_P, [C.c_int, C.c_int, C.c_int, C.c_int, _P]),
         "mvb_shard_free": (None, [_P]),
@@ -183,6 +185,17 @@ def _bind(lib):
             fn.restype = res
             fn.argtypes = args
     return lib
+
+
+ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
+ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, _dp, C.c_int)
+DESTROY_FN = C.CFUNCTYPE(None, C.c_void_p)
+
+
+class Comm(C.Structure):
+    """struct mvb_comm (include/mvolps_dist.h): a caller-supplied communicator."""
+    _fields_ = [("ctx", C.c_void_p), ("rank", C.c_int), ("world", C.c_int),
+                ("allgather_dev", ALLGATHER_FN), ("allreduce_max", ALLREDUCE_FN), ("destroy", DESTROY_FN)]
 
 
 def load_library(path):

@@ -382,6 +382,19 @@ void mvb_comm_free(mvb_comm *c) {
   delete c;
 }
 
+// incumbent / bound broadcast of a sharded tree: two max-reductions of one double
+int mvb_incumbent_exchange(const mvb_comm *c, double *incumbent, int *owner) {
+  if (!c || !c->allreduce_max) { g_err = "mvb_incumbent_exchange: communicator has no allreduce_max"; return -1; }
+  const double mine = *incumbent;
+  double v = mine;
+  if (c->allreduce_max(c->ctx, &v, 1)) return -1;
+  double who = (mine == v) ? -(double)c->rank : -HUGE_VAL;  // lowest rank holding the maximum
+  if (c->allreduce_max(c->ctx, &who, 1)) return -1;
+  *incumbent = v;
+  if (owner) *owner = (int)(-who);
+  return 0;
+}
+
 void mvb_shard_partition(int n, int world, int rank, int *col0, int *ncols) {
   int per = (n + world - 1) / world;
   per = (per + MVB_LD_ALIGN - 1) / MVB_LD_ALIGN * MVB_LD_ALIGN;

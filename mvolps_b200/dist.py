@@ -99,3 +99,21 @@ class ShardGroup:
         for c in self.comms:
             self.lib.mvb_comm_free(c)
         self.shards, self.comms = [], []
+
+
+def torch_comm(dist):
+    """mvb_comm whose host reductions run over an initialised torch.distributed group
+    (gloo on CPU in the tests).  Keep the returned object alive while C code uses it."""
+    import torch
+
+    def allreduce_max(ctx, vals, count):
+        t = torch.tensor([vals[i] for i in range(count)], dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        for i in range(count):
+            vals[i] = float(t[i])
+        return 0
+
+    cb = capi.ALLREDUCE_FN(allreduce_max)
+    comm = capi.Comm(None, dist.get_rank(), dist.get_world_size(), capi.ALLGATHER_FN(), cb, capi.DESTROY_FN())
+    comm._keep = cb
+    return comm

@@ -1,0 +1,102 @@
+"""Host logic of the multi-GPU layer (include/mvolps_dist.h) on CPU: world size 2
+over gloo for the exchange steps, plus the partition / slicing rules.  The
+device kernels of the sharded path are covered by tests/test_gpu_shard.py."""
+import ctypes as C
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from mvolps_b200 import capi, instances
+from mvolps_b200.dist import partition, slice_instance, torch_comm
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return capi.load_library(capi.PRODUCT_LIB)
+
+
+def test_partition_matches_c(lib):
+    for n in (1, 15, 16, 17, 100, 513, 2048, 32768, 32769):
+        for world in (1, 2, 3, 4, 8):
+            cover = []
+            for r in range(world):
+                c0, nc = C.c_int(), C.c_int()
+                lib.mvb_shard_partition(n, world, r, C.byref(c0), C.byref(nc))
+                assert (c0.value, nc.value) == partition(n, world, r)
+                assert nc.value >= 0 and (nc.value == 0 or c0.value % 16 == 0)
+                cover += list(range(c0.value, c0.value + nc.value))
+            assert cover == list(range(n))  # contiguous, disjoint, complete
+
+
+def test_slices_reassemble_instance():
+    inst = instances.dense_lp(20, 70, 3)
+    parts = [slice_instance(inst, 3, r) for r in range(3)]
+    assert np.array_equal(np.hstack([p["A"] for p in parts]), inst["A"])
+    assert np.array_equal(np.concatenate([p["cost"] for p in parts]), -inst["c"])  # max -> internal min
+    for p in parts:
+        assert p["lb"].shape == (70 + 20,) and np.array_equal(p["ub"][70:], inst["row_ub"])
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        lib = capi.load_library(capi.PRODUCT_LIB)
+        comm = torch_comm(dist)
+        out = []
+        # rounds of a node-sharded tree: each rank reports the best integral node of its batch
+        rounds = [(-np.inf, 1196.0), (1201.0, 1199.0), (1202.0, 1202.0), (1150.0, -np.inf)]
+        best, best_owner = -np.inf, -1
+        for mine in rounds:
+            inc, owner = C.c_double(mine[rank]), C.c_int(-1)
+            assert lib.mvb_incumbent_exchange(C.byref(comm), C.byref(inc), C.byref(owner)) == 0
+            if inc.value > best:  # strict, first found kept (bs.cpp:172)
+                best, best_owner = inc.value, owner.value
+            out.append((inc.value, owner.value, best, best_owner))
+        # the NCCL-id plumbing (dist.nccl_comm) is a 128-byte broadcast from rank 0: same call over gloo
+        import torch
+        t = torch.arange(128, dtype=torch.uint8) if rank == 0 else torch.zeros(128, dtype=torch.uint8)
+        dist.broadcast(t, 0)
+        out.append(t.tolist() == list(range(128)))
+        # dealing of a FIFO batch over the ranks: round-robin, disjoint, complete
+        batch = list(range(37))
+        mine_lps = [k for k in batch if k % world == rank]
+        counts = [None] * world
+        dist.all_gather_object(counts, mine_lps)
+        out.append(sorted(sum(counts, [])) == batch)
+        q.put((rank, out))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_incumbent_exchange_world2_gloo(lib):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[0] == res[1]  # replicated decisions
+    rounds = res[0][:4]
+    assert rounds[0][:2] == (1196.0, 1)
+    assert rounds[1][:2] == (1201.0, 0)
+    assert rounds[2][:2] == (1202.0, 0)      # tie: lowest rank owns it
+    assert rounds[3] == (1150.0, 0, 1202.0, 0)  # a worse round does not replace the incumbent
+    assert res[0][4] is True and res[0][5] is True
