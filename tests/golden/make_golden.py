@@ -38,6 +38,8 @@ LP_CASES = [
     ("dense_lp", [257, 300, 7]), ("general_lp", [6, 8, 11]), ("general_lp", [20, 30, 12]),
     ("general_lp", [50, 80, 13]), ("general_lp", [100, 150, 14]), ("general_lp", [40, 200, 15]),
     ("mdkp", [40, 10, 21]), ("mdkp", [40, 10, 22]), ("mdkp", [200, 50, 2024]),
+    # full BASELINE sizes: configs[3] node LP and configs[1] (about 15 s on one core)
+    ("dense_lp", [256, 512, 0]), ("dense_lp", [256, 512, 1]), ("dense_lp", [1024, 2048, 1234]),
 ]
 
 BNB_CASES = [  # (name, generator, args, reference CLI flags)

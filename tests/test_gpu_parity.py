@@ -109,3 +109,46 @@ def test_status_parity(oracle, product, kind):
     a, b, ra, rb = _pair(oracle, product, inst)
     assert ra["status"] == (1 if kind == "infeasible" else 2)
     _assert_same(a, b, ra, rb)
+
+
+def test_golden_fixtures_full_sizes(product):
+    """tests/golden/lp_golden.json (cut from the oracle, HiGHS-anchored) incl. the full BASELINE
+    sizes: configs[1] m=1024 n=2048 (13403 pivots) and configs[3] m=256 n=512."""
+    import json
+    import os
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "lp_golden.json")) as f:
+        gold = json.load(f)["cases"]
+    lps = [EngineLP.from_instance(product, getattr(instances, c["gen"])(*c["args"])) for c in gold]
+    res = solve_batch(product, lps)  # one launch for all of them
+    for c, r in zip(gold, res):
+        assert r["status"] == c["status"] and r["iters"] == c["iters"], c
+        assert r["pivot_hash"] == int(c["pivot_hash"]), c
+        assert np.float64(r["obj"]).tobytes().hex() == c["obj_hex"], c
+        if c["highs_obj"] is not None:
+            assert abs(r["obj"] - c["highs_obj"]) <= 1e-9 * max(1.0, abs(c["highs_obj"])), c
+
+
+def test_full_size_dense_lp_sharded_and_properties(product):
+    """configs[1] at full size: sharded over 8 emulated ranks == golden hash; and
+    size-independent properties of the final tableau (dictionary identity, optimality)."""
+    import json
+    import os
+    from mvolps_b200.dist import ShardGroup
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "lp_golden.json")) as f:
+        c = [x for x in json.load(f)["cases"] if x["args"] == [1024, 2048, 1234]][0]
+    inst = instances.dense_lp(1024, 2048, 1234)
+    g = ShardGroup(product, inst, 8)
+    r = g.solve()
+    assert r["pivot_hash"] == int(c["pivot_hash"]) and np.float64(r["obj"]).tobytes().hex() == c["obj_hex"]
+    lp = EngineLP.from_instance(product, inst)
+    lp.solve()
+    assert np.array_equal(lp.primal(), g.primal())
+    g.free()
+    T, beta = lp.tableau()
+    head, nb, at = lp.basis()
+    x = lp.primal()
+    assert np.allclose(T[1:] @ x[nb], x[head], rtol=1e-9, atol=1e-9)      # x_B = T x_N
+    assert np.allclose(x[2048:], inst["A"] @ x[:2048], rtol=1e-9, atol=1e-7)  # auxiliaries = A x
+    d = T[0]
+    assert np.all(d[at == 0] >= -1e-9) and np.all(d[at == 1] <= 1e-9)     # dual feasible = optimal
+    assert np.all(x[:2048] >= -1e-9) and np.all(x[2048:] <= inst["row_ub"] * (1 + 1e-9))
