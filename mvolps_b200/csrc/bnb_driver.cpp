@@ -10,6 +10,9 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdio>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <deque>
 #include <limits>
 #include <map>
@@ -113,20 +116,29 @@ struct Driver {
     return n;
   }
 
+  double t_sync = 0, t_solve = 0, t_pull = 0, t_copy = 0;  // MVOLPS_BNB_TIMING=1 prints them
+  static double now() {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+  }
+
   bool solve_many(const std::vector<glp_prob *> &ps) {
     if (ps.empty()) return true;
     std::vector<mvb_lp *> engs;
+    double t0 = now();
     for (auto *p : ps) {
       if (mv_sync_engine(p)) return false;
       engs.push_back(p->eng);
     }
+    double t1 = now();
     std::vector<mvb_result> res(ps.size());
     mvb_opts o{};
     if (mvb_solve_batch(engs.data(), (int)engs.size(), &o, res.data())) return false;
+    double t2 = now();
     for (size_t k = 0; k < ps.size(); k++) {
       if (mv_pull_solution(ps[k], res[k])) return false;
       out->st.simplex_iters += res[k].iters;
     }
+    t_sync += t1 - t0; t_solve += t2 - t1; t_pull += now() - t2;
     out->st.launches++;
     out->st.lp_solves += (int)ps.size();
     return true;
@@ -438,8 +450,10 @@ bool Driver::run() {
         double bound = glp_get_col_prim(a, pick);
         // S2/S3 are copies of a (util.cpp:34); a itself is dead afterwards, so
         // S3 takes it over instead of copying a third time
+        const double tc0 = now();
         glp_prob *c2 = glp_create_prob();
         glp_copy_prob(c2, a, GLP_ON);
+        t_copy += now() - tc0;
         auto s2 = make_node(c2);
         node->prob = nullptr;
         auto s3 = make_node(a);
@@ -489,6 +503,9 @@ bool Driver::run() {
     }
   }
   for (auto &kv : tree) { hash_mix((unsigned)kv.first); hash_mix((unsigned)kv.second.prune); }
+  if (getenv("MVOLPS_BNB_TIMING"))
+    std::fprintf(stderr, "bnb timing: sync %.1f ms, solve %.1f ms, pull %.1f ms, copy_prob %.1f ms\n",
+                 1e3 * t_sync, 1e3 * t_solve, 1e3 * t_pull, 1e3 * t_copy);
   out->st.iterations = count;
   out->st.oids = next_id - 1;
   out->st.event_hash = ehash;

@@ -31,10 +31,21 @@
 #include "../../include/mvolps_engine.h"
 #include "../../include/mvolps_spec.h"
 
+#ifndef MVB_PS_NT
+#define MVB_PS_NT 512  // threads per CTA of the private-state kernel
+#endif
+
 // ------------------------------------------------------------------ device
 struct DevResult {
   mvb_result r;
   int curT, curS;  // which ping-pong buffers hold the final state
+};
+
+// a bound change made on the host since the last solve (branching, bs.cpp:274,282),
+// applied by the solve kernel itself so that it costs no transfer of its own
+struct BoundPatch {
+  int var, pos, flag, pad;  // pos >= 0: non-basic position whose flag becomes `flag`
+  double lb, ub;
 };
 
 struct LPDev {
@@ -58,6 +69,8 @@ struct LPDev {
   int curT, curS;   // parities at entry
   int max_iters;
   int lzK;          // pending-update depth of the lazy loop for this launch
+  int npatch;       // bound patches to apply before the solve
+  const BoundPatch *patch;
 };
 
 namespace {
@@ -616,6 +629,16 @@ __device__ __forceinline__ void kernel_body(const LPDev *lps, int nlp, int G, un
       t = 0;
       while ((1 << t) < (L.ld + 1) / 2 && (2 << t) <= (int)blockDim.x) t++;
     }
+    if (L.npatch) {  // host-side bound changes since the last solve
+      if (g == 0)
+        for (int k = threadIdx.x; k < L.npatch; k += blockDim.x) {
+          const BoundPatch p = L.patch[k];
+          L.lb[p.var] = p.lb;
+          L.ub[p.var] = p.ub;
+          if (p.pos >= 0) L.at[L.curS][p.pos] = p.flag;
+        }
+      group_sync(ctrs + group, G, gen);
+    }
     solve_lp<PSK>(L, g, G, ctrs + group, gen, t, sm, dyn);
   }
 }
@@ -630,7 +653,7 @@ simplex_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
 // private-state variant (engine_ps.cuh): every LP of the launch fits the
 // dynamic shared memory; LPs that turn out to need phase 1 come back with
 // status MVB_PS_FALLBACK and are re-run by simplex_kernel.
-__global__ void __launch_bounds__(512, 1)
+__global__ void __launch_bounds__(MVB_PS_NT, 1)
 simplex_ps_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
   kernel_body<true>(lps, nlp, G, ctrs, tcl, dyn_smem);
 }
@@ -648,10 +671,16 @@ struct DeviceCtx {
   int device = -1, sms = 0;
   cudaStream_t stream = nullptr;
   int max_ctas = 0;        // co-resident CTAs of simplex_kernel at NT threads
-  int nt = 512;            // threads per CTA
+  int nt = 512;            // threads per CTA (general kernel)
+  int nt_ps = MVB_PS_NT;   // threads per CTA (private-state kernel)
   unsigned *ctrs = nullptr; int ctrs_cap = 0;
   LPDev *dlps = nullptr; int dlps_cap = 0;
   char *stage = nullptr; size_t stage_cap = 0;   // device staging (row gathers, new rows)
+  // per-launch arenas: bound patches go up and all outboxes come back in ONE copy each
+  char *d_out = nullptr, *h_out = nullptr; size_t out_cap = 0;
+  BoundPatch *d_patch = nullptr, *h_patch = nullptr; size_t patch_cap = 0;
+  std::vector<std::pair<size_t, char *>> free_slabs;  // recycled LP slabs (size, pointer)
+  size_t free_bytes = 0;
   cudaEvent_t ev[16] = {};
   cudaEvent_t kev[2] = {};
   char *flush = nullptr; size_t flush_bytes = 0;
@@ -705,7 +734,7 @@ bool ctx_init(int device) {
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_kernel, g_ctx.nt, 0));
   if (per_sm < 1) return fail("simplex_kernel does not fit an SM");
   g_ctx.max_ctas = per_sm * g_ctx.sms;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_ps_kernel, g_ctx.nt, g_ctx.max_dyn));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_ps_kernel, g_ctx.nt_ps, g_ctx.max_dyn));
   if (per_sm < 1) return fail("simplex_ps_kernel does not fit an SM");
   g_ctx.max_ctas_ps = per_sm * g_ctx.sms;
   g_ctx.ready = true;
@@ -738,6 +767,7 @@ struct mvb_lp {
   std::vector<int> head, nb, at;    // basis mirror (valid: mirror_ok)
   std::vector<double> x;            // primal by id after the last solve
   bool bounds_dirty = false, at_dirty = false;
+  std::vector<BoundPatch> patches;  // set_bounds calls not yet on the device
   mvb_result res{};
   int *pivlog = nullptr; int pivlog_cap = 0, pivlog_n = 0;
   std::vector<char> outbox;         // host copy of the outbox
@@ -754,7 +784,9 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, A); return o; };
   lp->t_bytes = align_up((size_t)(mcap + 1) * lp->ld * sizeof(double), A);
-  size_t oT0 = take(lp->t_bytes), oT1 = take(lp->t_bytes);
+  // T[0] | small state | T[1]: the current tableau buffer and the small state are
+  // contiguous whichever buffer is current, so a clone is ONE device-to-device copy
+  size_t oT0 = take(lp->t_bytes);
   lp->small_off = off;
   size_t ob0 = take((mcap + 1) * sizeof(double)), ob1 = take((mcap + 1) * sizeof(double));
   size_t olb = take((size_t)(n + mcap) * sizeof(double)), oub = take((size_t)(n + mcap) * sizeof(double));
@@ -763,6 +795,7 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
   size_t on0 = take((size_t)std::max(n, 1) * sizeof(int)), on1 = take((size_t)std::max(n, 1) * sizeof(int));
   size_t oa0 = take((size_t)std::max(n, 1) * sizeof(int)), oa1 = take((size_t)std::max(n, 1) * sizeof(int));
   lp->small_bytes = off - lp->small_off;
+  size_t oT1 = take(lp->t_bytes);
   size_t ovnb = take((size_t)std::max(n, 1) * sizeof(double));
   size_t nchunks = (mcap + MVB_P1_CHUNK - 1) / MVB_P1_CHUNK + 1;
   size_t op1 = take(nchunks * lp->ld * sizeof(double));
@@ -773,7 +806,16 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
   size_t oon = take((size_t)std::max(n, 1) * sizeof(int)), ooa = take((size_t)std::max(n, 1) * sizeof(int));
   lp->out_bytes = off - lp->out_off;
   lp->slab_bytes = off;
-  CK(cudaMallocAsync((void **)&lp->slab, lp->slab_bytes, g_ctx.stream));
+  lp->slab = nullptr;
+  for (size_t k = 0; k < g_ctx.free_slabs.size(); k++)
+    if (g_ctx.free_slabs[k].first == lp->slab_bytes) {  // recycle: no driver call at all
+      lp->slab = g_ctx.free_slabs[k].second;
+      g_ctx.free_bytes -= lp->slab_bytes;
+      g_ctx.free_slabs[k] = g_ctx.free_slabs.back();
+      g_ctx.free_slabs.pop_back();
+      break;
+    }
+  if (!lp->slab) CK(cudaMallocAsync((void **)&lp->slab, lp->slab_bytes, g_ctx.stream));
   char *s = lp->slab;
   LPDev &d = lp->dev;
   d.m = m; d.n = n; d.ld = lp->ld; d.mcap = mcap;
@@ -793,7 +835,16 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
 }
 
 void lp_release(mvb_lp *lp) {
-  if (lp->slab) cudaFreeAsync(lp->slab, g_ctx.stream);
+  if (lp->slab) {
+    // node LPs come and go in equal sizes (util.cpp:25-42): keep up to 1 GiB of slabs for reuse
+    if (lp->slab_bytes <= ((size_t)64 << 20) && g_ctx.free_bytes + lp->slab_bytes <= ((size_t)1 << 30) &&
+        g_ctx.free_slabs.size() < 8192) {
+      g_ctx.free_slabs.emplace_back(lp->slab_bytes, lp->slab);
+      g_ctx.free_bytes += lp->slab_bytes;
+    } else {
+      cudaFreeAsync(lp->slab, g_ctx.stream);
+    }
+  }
   if (lp->pivlog) cudaFreeAsync(lp->pivlog, g_ctx.stream);
   lp->slab = nullptr;
   lp->pivlog = nullptr;
@@ -813,6 +864,11 @@ int nb_flag_for(double l, double u, int keep) {
 // push host bounds / flags that changed since the last solve
 bool lp_push_small(mvb_lp *lp) {
   const int n = lp->n, m = lp->m;
+  if (lp->bounds_dirty && lp->at_dirty) lp->patches.clear();
+  else if (lp->bounds_dirty || lp->at_dirty) {  // mixed: keep it simple, push everything
+    lp->bounds_dirty = lp->at_dirty = true;
+    lp->patches.clear();
+  }
   if (lp->bounds_dirty) {
     CK(cudaMemcpyAsync(lp->dev.lb, lp->lb.data(), (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, g_ctx.stream));
     CK(cudaMemcpyAsync(lp->dev.ub, lp->ub.data(), (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, g_ctx.stream));
@@ -901,15 +957,16 @@ int mvb_lp_assign(mvb_lp *dst, const mvb_lp *src) {
   dst->dev.m = src->m;
   dst->curT = src->curT;
   dst->curS = src->curS;
-  // the current tableau buffer and the whole small-state region, device to device
-  CKI(cudaMemcpyAsync(dst->dev.T[src->curT], src->dev.T[src->curT],
-                      (size_t)(src->m + 1) * src->ld * sizeof(double), cudaMemcpyDeviceToDevice, st));
-  CKI(cudaMemcpyAsync(dst->slab + dst->small_off, src->slab + src->small_off, src->small_bytes,
+  // the current tableau buffer and the small state are adjacent (lp_alloc): one copy
+  if (dst->t_bytes != src->t_bytes || dst->small_bytes != src->small_bytes) { g_err = "mvb_lp_assign: layout mismatch"; return -1; }
+  const size_t from = src->curT == 0 ? 0 : src->small_off;
+  CKI(cudaMemcpyAsync(dst->slab + from, src->slab + from, src->t_bytes + src->small_bytes,
                       cudaMemcpyDeviceToDevice, st));
   dst->lb = src->lb; dst->ub = src->ub;
   dst->head = src->head; dst->nb = src->nb; dst->at = src->at; dst->x = src->x;
   dst->bounds_dirty = src->bounds_dirty;
   dst->at_dirty = src->at_dirty;
+  dst->patches = src->patches;
   dst->res = src->res;
   dst->pivlog_n = 0;
   return 0;
@@ -926,13 +983,23 @@ int mvb_lp_set_bounds(mvb_lp *lp, int k, double lb, double ub) {
   if (k < 0 || k >= lp->n + lp->m) { g_err = "mvb_lp_set_bounds: variable id"; return -1; }
   lp->lb[k] = lb;
   lp->ub[k] = ub;
-  lp->bounds_dirty = true;
+  int pos = -1, flag = 0;
   for (int j = 0; j < lp->n; j++)
     if (lp->nb[j] == k) {
-      int f = nb_flag_for(lb, ub, lp->at[j]);
-      if (f != lp->at[j]) { lp->at[j] = f; lp->at_dirty = true; }
+      pos = j;
+      flag = nb_flag_for(lb, ub, lp->at[j]);
+      lp->at[j] = flag;
       break;
     }
+  if (lp->bounds_dirty && (lp->at_dirty || pos < 0)) return 0;  // a bulk push is pending anyway
+  for (auto &p : lp->patches)
+    if (p.var == k) { p.lb = lb; p.ub = ub; p.pos = pos; p.flag = flag; return 0; }
+  if (lp->patches.size() >= 256) {  // too many: fall back to the bulk push
+    lp->bounds_dirty = lp->at_dirty = true;
+    lp->patches.clear();
+    return 0;
+  }
+  lp->patches.push_back(BoundPatch{k, pos, flag, 0, lb, ub});
   return 0;
 }
 
@@ -1062,6 +1129,44 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
     CK(cudaMallocAsync((void **)&g_ctx.dlps, (size_t)count * sizeof(LPDev), st));
     g_ctx.dlps_cap = count;
   }
+  // outbox arena: every LP's result block at its offset, one D2H for the launch
+  std::vector<size_t> ooff(count);
+  size_t otot = 0, ptot = 0;
+  for (int k = 0; k < count; k++) {
+    ooff[k] = otot;
+    otot += lps[idx[k]]->out_bytes;
+    ptot += lps[idx[k]]->patches.size();
+  }
+  if (g_ctx.out_cap < otot) {
+    if (g_ctx.d_out) CK(cudaFreeAsync(g_ctx.d_out, st));
+    if (g_ctx.h_out) CK(cudaFreeHost(g_ctx.h_out));
+    g_ctx.out_cap = std::max(otot * 2, (size_t)1 << 20);
+    CK(cudaMallocAsync((void **)&g_ctx.d_out, g_ctx.out_cap, st));
+    CK(cudaMallocHost((void **)&g_ctx.h_out, g_ctx.out_cap));
+  }
+  if (g_ctx.patch_cap < ptot) {
+    if (g_ctx.d_patch) CK(cudaFreeAsync(g_ctx.d_patch, st));
+    if (g_ctx.h_patch) CK(cudaFreeHost(g_ctx.h_patch));
+    g_ctx.patch_cap = std::max(ptot * 2, (size_t)4096);
+    CK(cudaMallocAsync((void **)&g_ctx.d_patch, g_ctx.patch_cap * sizeof(BoundPatch), st));
+    CK(cudaMallocHost((void **)&g_ctx.h_patch, g_ctx.patch_cap * sizeof(BoundPatch)));
+  }
+  size_t pat = 0;
+  for (int k = 0; k < count; k++) {
+    mvb_lp *lp = lps[idx[k]];
+    const ptrdiff_t rel = (g_ctx.d_out + ooff[k]) - (lp->slab + lp->out_off);
+    h[k].res = (DevResult *)((char *)lp->dev.res + rel);
+    h[k].xval = (double *)((char *)lp->dev.xval + rel);
+    h[k].ohead = (int *)((char *)lp->dev.ohead + rel);
+    h[k].onb = (int *)((char *)lp->dev.onb + rel);
+    h[k].oat = (int *)((char *)lp->dev.oat + rel);
+    h[k].npatch = (int)lp->patches.size();
+    h[k].patch = g_ctx.d_patch + pat;
+    for (const BoundPatch &bp : lp->patches) g_ctx.h_patch[pat++] = bp;
+    lp->patches.clear();
+  }
+  if (ptot)
+    CK(cudaMemcpyAsync(g_ctx.d_patch, g_ctx.h_patch, ptot * sizeof(BoundPatch), cudaMemcpyHostToDevice, st));
   CK(cudaMemsetAsync(g_ctx.ctrs, 0, (size_t)ngroups * sizeof(unsigned), st));
   CK(cudaMemcpyAsync(g_ctx.dlps, h.data(), (size_t)count * sizeof(LPDev), cudaMemcpyHostToDevice, st));
   const LPDev *dl = g_ctx.dlps;
@@ -1071,17 +1176,18 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   if (!g_ctx.kev[0]) { CK(cudaEventCreate(&g_ctx.kev[0])); CK(cudaEventCreate(&g_ctx.kev[1])); }
   CK(cudaEventRecord(g_ctx.kev[0], st));
   CK(cudaLaunchCooperativeKernel(psk ? (const void *)simplex_ps_kernel : (const void *)simplex_kernel,
-                                 dim3(ngroups * G), dim3(g_ctx.nt), args, dyn, st));
+                                 dim3(ngroups * G), dim3(psk ? g_ctx.nt_ps : g_ctx.nt), args, dyn, st));
   CK(cudaEventRecord(g_ctx.kev[1], st));
   g_launches++;
   g_ctx.last_G = G;
   g_ctx.last_groups = ngroups;
   g_ctx.last_ps = psk;
+  CK(cudaMemcpyAsync(g_ctx.h_out, g_ctx.d_out, otot, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[idx[k]];
-    CK(cudaMemcpyAsync(lp->outbox.data(), lp->slab + lp->out_off, lp->out_bytes, cudaMemcpyDeviceToHost, st));
+    std::memcpy(lp->outbox.data(), g_ctx.h_out + ooff[k], lp->out_bytes);
   }
-  CK(cudaStreamSynchronize(st));
   return true;
 }
 
@@ -1112,7 +1218,7 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     lp->dev.pivlog = (opts && opts->log_pivots) ? lp->pivlog : nullptr;
     lp->dev.pivlog_cap = lp->dev.pivlog ? lp->pivlog_cap : 0;
     const bool fits = !g_ctx.no_ps && lp->m >= 1 && lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn) >= 1 &&
-                      lp->m + 1 <= PS_CREG * g_ctx.nt;
+                      lp->m + 1 <= PS_CREG * g_ctx.nt_ps;
     (fits ? ps_idx : gen_idx).push_back(k);
   }
   // private-state kernel first; what needs phase 1 (or does not fit) goes to the general one
@@ -1244,7 +1350,7 @@ int mvb_flush_l2(void) {
 int mvb_last_launch(int *c, int *g, int *t) {
   if (c) *c = g_ctx.last_G;
   if (g) *g = g_ctx.last_groups;
-  if (t) *t = g_ctx.nt;
+  if (t) *t = g_ctx.last_ps ? g_ctx.nt_ps : g_ctx.nt;
   return 0;
 }
 

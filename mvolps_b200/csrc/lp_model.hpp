@@ -8,17 +8,37 @@
 // already seen so that a re-solve ships only bound deltas and new cut rows.
 #pragma once
 
+#include <memory>
 #include <string>
 #include <vector>
 
 #include "../../include/glpk.h"
 #include "../../include/mvolps_engine.h"
 
+// Copy-on-write vector: every open B&B node holds a copy of the problem
+// (util.cpp:25-42) but only cut rows ever differ, so copies share the
+// coefficient storage and glp_copy_prob costs a reference count per row.
+template <class T>
+class CowVec {
+  std::shared_ptr<std::vector<T>> p_;
+  std::vector<T> &mut() {
+    if (!p_) p_ = std::make_shared<std::vector<T>>();
+    else if (p_.use_count() > 1) p_ = std::make_shared<std::vector<T>>(*p_);
+    return *p_;
+  }
+
+ public:
+  size_t size() const { return p_ ? p_->size() : 0; }
+  const T &operator[](size_t i) const { return (*p_)[i]; }
+  void clear() { p_.reset(); }
+  void push_back(const T &v) { mut().push_back(v); }
+};
+
 struct MvRow {
   int type = GLP_FR;
   double lb = 0.0, ub = 0.0;
-  std::vector<int> ind;     // 1-based column numbers, ascending
-  std::vector<double> val;
+  CowVec<int> ind;     // 1-based column numbers, ascending
+  CowVec<double> val;
   int stat = GLP_BS;
   double prim = 0.0;
   std::string name;
