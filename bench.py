@@ -35,6 +35,9 @@ from mvolps_b200.lp import EngineLP, GlpProb  # noqa: E402
 M, N_COLS, SEED = 1024, 2048, 1234
 ORACLE_LIB = os.path.join(ROOT, "oracle", "_build", "libglpk_oracle.so")
 METRIC = "simplex_pivots_per_sec"
+# DRAM traffic of the timed launch (one full configs[1] solve), from the ncu capture of this very
+# command committed as profiles/r1c_bench_ps_summary.txt: 17.10 MB read + 3.75 MB written
+NCU_DRAM_BYTES_PER_LAUNCH = 17098240 + 3754240
 
 
 def peaks():
@@ -243,7 +246,10 @@ def main():
                    "algorithmic 16*R*C bytes per pivot",
                    "ctas_per_lp": G.value, "threads_per_cta": nt.value},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH, "peak_source": peak_src,
+                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full, "
+                                       "profiles/r1c_bench_ps_summary.txt (the tableau stays in L2; the algorithmic "
+                                       "bytes per launch are 16*R*C*pivots = 450 GB)",
                      "kernel": "simplex_ps_kernel (one cooperative launch = whole solve; lazy rank-1 updates, K pivots per tableau pass)",
                      "algorithmic_bytes_per_pivot": 16 * (M + 1) * (N_COLS + 1),
                      "kernel_ms_per_launch": kern_ms / args.steps,

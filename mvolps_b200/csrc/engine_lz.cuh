@@ -464,15 +464,26 @@ __device__ __noinline__ int lz_price(LZS *S) {
   const bool bland = S->degen >= MVB_BLAND_AFTER;
   const double *d = zD(l);
   const int *atv = zAtv(l), *nbv = zNbv(l);
-  Key bq = key_none();
-  for (int j = tid; j < n; j += NT) {  // branch-free form of dj_eligible + key build
-    const double dj = d[j];
-    const int f = atv[j];
-    const bool neg = dj < -MVB_TOL_DJ, pos = dj > MVB_TOL_DJ;
-    const bool e = (f == MVB_AT_LB && neg) || (f == MVB_AT_UB && pos) || (f == MVB_AT_FR && (neg || pos));
-    const Key k{e ? (bland ? 0ULL : ~dbits(fabs(dj))) : ~0ULL, e ? nbv[j] : 0x7fffffff, e ? j : -1};
-    if (key_less(k, bq)) bq = k;
+  // per thread: best score s = |d_j| of an eligible column (FX / ineligible: -1), ties to the
+  // lower variable id; branch-free, NJ columns in flight.  Same order as the (~bits, id) keys.
+  double best = -1.0;
+  int bj = -1, bvar = 0x7fffffff;
+  constexpr int NJ = 4;
+  for (int j0 = tid; j0 < n; j0 += NJ * NT) {
+#pragma unroll
+    for (int u = 0; u < NJ; u++) {
+      const int j = j0 + u * NT, jj = min(j, n - 1);
+      const double dj = d[jj];
+      const int f = atv[jj], v = nbv[jj];
+      const double s = f == MVB_AT_LB ? -dj : f == MVB_AT_UB ? dj : f == MVB_AT_FR ? fabs(dj) : -1.0;
+      const double sc = (j < n && s > MVB_TOL_DJ) ? (bland ? 1.0 : s) : -1.0;
+      const bool better = sc > best || (sc == best && sc > 0.0 && v < bvar);
+      best = better ? sc : best;
+      bj = better ? jj : bj;
+      bvar = better ? v : bvar;
+    }
   }
+  Key bq = best > 0.0 ? Key{bland ? 0ULL : ~dbits(best), bvar, bj} : key_none();
   PROF(8);
 #ifdef MVB_PROF
   {

@@ -46,11 +46,12 @@ struct ShardDev {
   int pivlog_cap;
 };
 
-// K1 over the local columns (one CTA: n/G columns, a few per thread) + gather
-// of the winning column into the send record
+// K1 over the local columns + gather of the winning column into the send
+// record.  Every CTA of the (small) grid repeats the cheap argmin over the
+// local reduced costs and then gathers its own slice of the column rows, so the
+// strided gather (one 32-byte sector per element) runs on many SMs.
 __global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int par) {
   __shared__ Key red[32];
-  __shared__ int s_q;
   const ShardCtl c = D.ctl[par];
   Cand *out = reinterpret_cast<Cand *>(D.send);
   if (c.status != -1) return;
@@ -66,24 +67,23 @@ __global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int pa
     const Key k{bland ? 0ULL : ~dbits(fabs(dj)), nb[j], j};
     if (key_less(k, best)) best = k;
   }
-  best = block_argmin(best, red);
-  if (threadIdx.x == 0) {
-    s_q = best.idx;
+  best = block_argmin(best, red);  // result on every thread, identical in every CTA
+  const int q = best.idx;
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
     Cand h{};
-    h.key = best.idx >= 0 ? best.k : ~0ULL;
-    h.var = best.idx >= 0 ? best.var : 0x7fffffff;
-    h.pos = best.idx >= 0 ? D.col0 + best.idx : -1;
-    h.flag = best.idx >= 0 ? at[best.idx] : 0;
-    h.lq = best.idx >= 0 ? D.lb[best.var] : 0.0;
-    h.uq = best.idx >= 0 ? D.ub[best.var] : 0.0;
+    h.key = q >= 0 ? best.k : ~0ULL;
+    h.var = q >= 0 ? best.var : 0x7fffffff;
+    h.pos = q >= 0 ? D.col0 + q : -1;
+    h.flag = q >= 0 ? at[q] : 0;
+    h.lq = q >= 0 ? D.lb[best.var] : 0.0;
+    h.uq = q >= 0 ? D.ub[best.var] : 0.0;
     *out = h;
   }
-  __syncthreads();
-  const int q = s_q;
   if (q < 0) return;
   double *col = reinterpret_cast<double *>(D.send + SHARD_HDR);
   const double *T = D.T[c.cT] + q;
-  for (int i = threadIdx.x; i <= D.m; i += blockDim.x) col[i] = T[(size_t)i * D.ld];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= D.m; i += gridDim.x * blockDim.x)
+    col[i] = T[(size_t)i * D.ld];
 }
 
 // rank-1 update of this CTA's share of the local columns, pivot column taken
@@ -614,13 +614,14 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
     return true;
   };
   const int grid = std::max(1, g_ctx.max_ctas);
+  const int price_grid = std::max(1, std::min(32, (m + 1 + 1023) / 1024));  // CTAs sharing the column gather
   const int CHUNK = 32;  // iterations enqueued between two looks at the control block
   int par = 0;
   ShardCtl h{};
   CKI(cudaEventRecord(s0->ev[0], st));
   while (true) {
     for (int it = 0; it < CHUNK; it++) {
-      for (int k = 0; k < nlocal; k++) shard_price_kernel<<<1, 1024, 0, st>>>(shards[k]->dev, par);
+      for (int k = 0; k < nlocal; k++) shard_price_kernel<<<price_grid, 1024, 0, st>>>(shards[k]->dev, par);
       if (!exchange(false)) return -1;
       for (int k = 0; k < nlocal; k++) shard_pivot_kernel<<<grid, 512, 0, st>>>(shards[k]->dev, par);
       g_launches += 2 * nlocal;
