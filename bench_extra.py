@@ -121,43 +121,49 @@ def run_shard(args, L, rank, world, local, dist, ClockSampler, peaks):
 
 
 def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks):
-    """configs[2]: MDKP 200 vars x 50 rows (seed 2024 + rank), FIFO B&B with a node budget through
+    """configs[2]: MDKP 200 vars x 50 rows (seed 2024), FIFO B&B with a node budget through
     mvb_bnb_run (batched node LPs on the device); the same driver on the CPU oracle is the baseline.
-    N > 1: one independent tree per rank (no exchange)."""
+    N > 1: ONE tree, node-sharded (mvb_bnb_run_dist): lock-step ramp-up, then every rank works on
+    its share of the open nodes with the incumbent exchanged by NCCL max-reduction every round;
+    the node budget is per rank."""
     import os
     from mvolps_b200.lp import GlpProb
-    inst = instances.mdkp(args.n or 200, args.m or 50, 2024 + rank)
+    inst = instances.mdkp(args.n or 200, args.m or 50, 2024)
     prob = GlpProb.from_instance(L, inst)
+    comm = nccl_comm(L, rank, world, dist) if dist is not None else None
 
-    def step(lib, p):
+    def step(lib, p, c=None):
         t0 = time.perf_counter()
-        out = p.bnb(cut_mode=args.cut_mode, batch_width=args.batch_width, max_iters=args.nodes)
+        out = p.bnb(cut_mode=args.cut_mode, batch_width=args.batch_width, max_iters=args.nodes, comm=c)
         return out, time.perf_counter() - t0
 
     for _ in range(max(args.warmup, 1)):
-        step(L, prob)
+        step(L, prob, comm)
     if dist is not None:
         dist.barrier()
     l0 = L.mvb_kernel_launches()
     nodes, secs, out = 0, 0.0, None
     with ClockSampler(local) as clk:
         for _ in range(args.steps):
-            out, dt = step(L, prob)
-            nodes += out["iterations"]
+            out, dt = step(L, prob, comm)
+            nodes += out["total_nodes"]
             secs += dt
     launches = int(L.mvb_kernel_launches() - l0)
-    (tot_nodes,), (max_s,) = _reduce(dist, [nodes], [secs])
+    _, (max_s,) = _reduce(dist, [0.0], [secs])
     if rank != 0:
         return
     line = {
-        "metric": "bnb_nodes_per_sec", "value": tot_nodes / max_s, "unit": "nodes/s", "n_gpus": world,
+        "metric": "bnb_nodes_per_sec", "value": nodes / max_s, "unit": "nodes/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * max_s / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"MDKP {args.n or 200} vars x {args.m or 50} rows seed 2024+rank, FIFO B&B, node budget "
-                               f"{args.nodes}, cut mode {args.cut_mode}, batch width {args.batch_width} (BASELINE configs[2]); "
-                               "host wall clock around mvb_bnb_run (host logic + H2D/D2H included)",
-                   "lp_solves": out["lp_solves"], "engine_launches": out["launches"],
-                   "simplex_iters": out["simplex_iters"], "event_hash": str(out["event_hash"])},
+        "config": {"workload": f"MDKP {args.n or 200} vars x {args.m or 50} rows seed 2024, FIFO B&B, node budget "
+                               f"{args.nodes} per rank, cut mode {args.cut_mode}, batch width {args.batch_width} "
+                               "(BASELINE configs[2]); host wall clock around mvb_bnb_run[_dist] (host logic + H2D/D2H "
+                               "included)" + ("; one tree node-sharded over the ranks, NCCL incumbent max-reduction "
+                                              "per round" if world > 1 else ""),
+                   "nodes_total": out["total_nodes"], "nodes_rank0": out["iterations"], "split_at": out["split_at"],
+                   "lp_solves_rank0": out["lp_solves"], "engine_launches_rank0": out["launches"],
+                   "event_hash_rank0": str(out["event_hash"])},
         "gpu_launches": launches, "clocks": clk.summary(),
     }
     if not args.no_cpu_baseline and world == 1:

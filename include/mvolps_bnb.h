@@ -13,6 +13,7 @@
 #define MVOLPS_BNB_H
 
 #include "glpk.h"
+#include "mvolps_comm.h"
 
 #ifdef __cplusplus
 extern "C" {
@@ -49,12 +50,30 @@ typedef struct mvb_bnb_stats {
   double incumbent;      /* bestLower */
   int hit_limit;         /* stopped by max_iters or the reference's 200000 cap */
   unsigned long long event_hash; /* FNV-1a over (event, oid, pid, prune tag) */
+  int split_at;          /* dist: iteration count at which the queue was dealt out (-1: never) */
+  int incumbent_rank;    /* dist: rank that found the incumbent (0 in serial runs) */
+  long long total_nodes; /* dist: nodes processed by all ranks (serial: = iterations) */
 } mvb_bnb_stats;
 
 typedef struct mvb_bnb mvb_bnb;
 
 /* run B&B on prob (not modified, like the reference, which works on copies) */
 mvb_bnb *mvb_bnb_run(glp_prob *prob, const mvb_bnb_params *params);
+
+/* Node-sharded B&B over comm->world ranks (one process per GPU).  Every rank
+ * calls it with the same problem and parameters.  The ranks run the serial
+ * driver in lock step (identical decisions) until the FIFO queue holds at
+ * least 4 nodes per rank; the open nodes are then dealt round-robin and each
+ * rank continues on its own share, one batch per round, exchanging only the
+ * incumbent (comm->allreduce_max: the bound test of bs.cpp:210 uses the best
+ * incumbent of ALL ranks) and the number of open nodes (termination).  There
+ * is no node hand-over after the split.  Exact search: the optimum equals the
+ * serial one; node order, oids and tree text are per rank and NOT those of
+ * the serial run (the non-sequence-identical mode).
+ * Results per rank: its own tree / events; stats.incumbent is the global
+ * optimum on every rank, mvb_bnb_get_incumbent returns the winning x on every
+ * rank, stats.iterations counts the nodes this rank processed. */
+mvb_bnb *mvb_bnb_run_dist(glp_prob *prob, const mvb_bnb_params *params, const mvb_comm *comm);
 void mvb_bnb_free(mvb_bnb *h);
 const mvb_bnb_stats *mvb_bnb_get_stats(const mvb_bnb *h);
 /* tree exactly as PrettyPrintTree prints it (tree_print.h:12-22, bs.cpp:331-341) */

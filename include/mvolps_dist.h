@@ -33,23 +33,14 @@
 
 #include <stddef.h>
 
+#include "mvolps_comm.h"
 #include "mvolps_engine.h"
 
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-typedef struct mvb_comm {
-  void *ctx;
-  int rank, world;
-  /* all-gather of `bytes` bytes per rank, DEVICE buffers, enqueued on `stream`
-   * (a cudaStream_t); recv holds world*bytes.  0 = ok */
-  int (*allgather_dev)(void *ctx, const void *send, void *recv, size_t bytes, void *stream);
-  /* max-reduction of count doubles in place, HOST buffer (incumbent / bound broadcast) */
-  int (*allreduce_max)(void *ctx, double *vals, int count);
-  /* release ctx */
-  void (*destroy)(void *ctx);
-} mvb_comm;
+/* struct mvb_comm: include/mvolps_comm.h */
 
 /* ---- NCCL communicator (one process per GPU) ---- */
 #define MVB_NCCL_ID_BYTES 128

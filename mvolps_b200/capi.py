@@ -45,7 +45,7 @@ ENGINE_SYMBOLS = [
     "mvb_lp_get_tableau", "mvb_lp_get_pivot_log",
 ]
 BNB_SYMBOLS = [
-    "mvb_bnb_run", "mvb_bnb_free", "mvb_bnb_get_stats", "mvb_bnb_tree_text",
+    "mvb_bnb_run", "mvb_bnb_run_dist", "mvb_bnb_free", "mvb_bnb_get_stats", "mvb_bnb_tree_text",
     "mvb_bnb_solution_text", "mvb_bnb_event_text", "mvb_bnb_get_incumbent",
 ]
 DIST_SYMBOLS = [  # include/mvolps_dist.h: exported by the product only
@@ -81,6 +81,7 @@ class BnbStats(C.Structure):
         ("iterations", C.c_int), ("oids", C.c_int), ("lp_solves", C.c_int), ("launches", C.c_int),
         ("simplex_iters", C.c_longlong), ("has_incumbent", C.c_int), ("incumbent_oid", C.c_int),
         ("incumbent", C.c_double), ("hit_limit", C.c_int), ("event_hash", C.c_ulonglong),
+        ("split_at", C.c_int), ("incumbent_rank", C.c_int), ("total_nodes", C.c_longlong),
     ]
 
 
@@ -153,6 +154,7 @@ def _bind(lib):
         "mvb_lp_get_tableau": (C.c_int, [_P, _dp, _dp]),
         "mvb_lp_get_pivot_log": (C.c_int, [_P, _ip, C.c_int]),
         "mvb_bnb_run": (_P, [_P, C.POINTER(BnbParams)]),
+        "mvb_bnb_run_dist": (_P, [_P, C.POINTER(BnbParams), _P]),
         "mvb_bnb_free": (None, [_P]),
         "mvb_bnb_get_stats": (C.POINTER(BnbStats), [_P]),
         "mvb_bnb_tree_text": (C.c_char_p, [_P]),

@@ -89,7 +89,16 @@ struct Driver {
   std::ostringstream ev;
   unsigned long long ehash = MVB_FNV_OFFSET;
 
+  const mvb_comm *comm = nullptr;  // node-sharded run (mvb_bnb_run_dist)
+
   Driver(const mvb_bnb_params &p, glp_prob *r, mvb_bnb *o) : pr(p), root_prob(r), out(o) {}
+
+  // max-reduction over the ranks, in chunks the communicator accepts
+  bool reduce_max(double *v, int count) {
+    for (int o = 0; o < count; o += 32)
+      if (comm->allreduce_max(comm->ctx, v + o, std::min(32, count - o))) return false;
+    return true;
+  }
 
   void hash_mix(unsigned long long v) { ehash = (ehash ^ v) * MVB_FNV_PRIME; }
 
@@ -384,7 +393,19 @@ bool Driver::run() {
     size_t ev_slot;
   };
 
-  while (!open.empty() && !stop) {
+  const bool dist = comm != nullptr && comm->world > 1;
+  bool split = false;        // dist: the queue has been dealt out, ranks now work on their own share
+  bool retired = false;      // dist: this rank hit its budget and only takes part in the exchanges
+  int inc_rank = 0;
+  out->st.split_at = -1;
+  while (true) {
+    if (dist && split) {     // termination is global: somebody still has open nodes
+      double alive = retired ? 0.0 : (double)open.size();
+      if (!reduce_max(&alive, 1)) return false;
+      if (alive == 0.0) break;
+    } else if (open.empty() || stop) {
+      break;
+    }
     // ---- the nodes this round pops, in pop order ----
     std::vector<std::unique_ptr<Node>> batch;
     if (pr.node_strategy == MVB_NODE_BEST) {
@@ -487,7 +508,53 @@ bool Driver::run() {
         open.push_back(std::move(k.node));
       }
     }
+    if (dist) {
+      if (!split && !stop && pr.node_strategy != MVB_NODE_BEST && open.size() >= (size_t)4 * comm->world) {
+        // deal the FIFO queue round-robin; from here on every rank owns its share
+        std::deque<std::unique_ptr<Node>> mine;
+        for (size_t k = 0; k < open.size(); k++)
+          if ((int)(k % comm->world) == comm->rank) mine.push_back(std::move(open[k]));
+        open.swap(mine);
+        split = true;
+        out->st.split_at = count;
+      }
+      if (split) {
+        if (stop) { retired = true; stop = false; open.clear(); }
+        // incumbent broadcast: the bound test (bs.cpp:210) sees the best incumbent of all ranks
+        double best = bestLower;
+        if (!reduce_max(&best, 1)) return false;
+        if (best > bestLower) { bestLower = best; solution.clear(); out->st.has_incumbent = 0; }
+      }
+    }
   }
+  if (dist) {
+    // final exchange: who holds the optimum (lowest rank on ties), its x, and the node counts
+    double best = out->st.has_incumbent ? bestLower : -inf;
+    double g = best;
+    if (!reduce_max(&g, 1)) return false;
+    double who = (out->st.has_incumbent && best == g) ? -(double)comm->rank : -inf;
+    if (!reduce_max(&who, 1)) return false;
+    if (g > -inf) {
+      inc_rank = (int)(-who);
+      int n = glp_get_num_cols(root_prob);
+      std::vector<double> x(n + 1, -inf);
+      if (comm->rank == inc_rank) x = out->incumbent;
+      x.resize(n + 1, -inf);
+      if (!reduce_max(x.data(), n + 1)) return false;
+      out->incumbent = x;
+      out->st.has_incumbent = 1;
+      out->st.incumbent = g;
+      bestLower = g;
+    }
+    std::vector<double> cnt(comm->world, -inf);
+    cnt[comm->rank] = (double)count;
+    if (!reduce_max(cnt.data(), comm->world)) return false;
+    out->st.total_nodes = 0;
+    for (double c : cnt) out->st.total_nodes += (long long)c;
+  } else {
+    out->st.total_nodes = count;
+  }
+  out->st.incumbent_rank = inc_rank;
 
   std::ostringstream ts;
   print_tree(1, ts);
@@ -516,11 +583,17 @@ bool Driver::run() {
 
 extern "C" {
 
-mvb_bnb *mvb_bnb_run(glp_prob *prob, const mvb_bnb_params *params) {
+static mvb_bnb *bnb_run(glp_prob *prob, const mvb_bnb_params *params, const mvb_comm *comm) {
   mvb_bnb_params p{};
   if (params) p = *params;
   auto *h = new mvb_bnb();
   Driver d(p, prob, h);
+  d.comm = comm;
+  if (comm && comm->world > 1 && !comm->allreduce_max) {
+    std::fprintf(stderr, "mvb_bnb_run_dist: communicator has no allreduce_max\n");
+    delete h;
+    return nullptr;
+  }
   if (!d.run()) {
     std::fprintf(stderr, "mvb_bnb_run: engine error: %s\n", mvb_last_error());
     delete h;
@@ -532,6 +605,11 @@ mvb_bnb *mvb_bnb_run(glp_prob *prob, const mvb_bnb_params *params) {
     std::printf("Solution found after %d iterations\n", h->st.iterations);
   }
   return h;
+}
+
+mvb_bnb *mvb_bnb_run(glp_prob *prob, const mvb_bnb_params *params) { return bnb_run(prob, params, nullptr); }
+mvb_bnb *mvb_bnb_run_dist(glp_prob *prob, const mvb_bnb_params *params, const mvb_comm *comm) {
+  return bnb_run(prob, params, comm);
 }
 
 void mvb_bnb_free(mvb_bnb *h) { delete h; }

@@ -211,10 +211,14 @@ class GlpProb:
         self.lib.glp_copy_prob(c.h, self.h, capi.GLP_ON)
         return c
 
-    def bnb(self, node_strategy=0, var_strategy=0, cut_mode=0, batch_width=0, max_iters=0):
+    def bnb(self, node_strategy=0, var_strategy=0, cut_mode=0, batch_width=0, max_iters=0, comm=None):
+        """comm: None (serial driver) or a communicator (capi.Comm / pointer) for the node-sharded run."""
         L = self.lib
         p = capi.BnbParams(node_strategy, var_strategy, cut_mode, batch_width, max_iters, 1)
-        hb = L.mvb_bnb_run(self.h, C.byref(p))
+        if comm is None:
+            hb = L.mvb_bnb_run(self.h, C.byref(p))
+        else:
+            hb = L.mvb_bnb_run_dist(self.h, C.byref(p), C.byref(comm) if isinstance(comm, capi.Comm) else comm)
         if not hb:
             raise RuntimeError("mvb_bnb_run failed: " + L.mvb_last_error().decode())
         st = L.mvb_bnb_get_stats(hb).contents

@@ -82,6 +82,61 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
+def _bnb_worker(rank, world, port, q, oracle_lib):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from mvolps_b200.lp import GlpProb
+        orc = capi.load_library(oracle_lib)  # the driver is engine-agnostic: CPU engine here
+        orc.glp_term_out(capi.GLP_OFF)
+        comm = torch_comm(dist)
+        res = {}
+        for name, args in (("mdkp_12x4_s1", (12, 4, 1)), ("mdkp_15x5_s2", (15, 5, 2))):
+            p = GlpProb.from_instance(orc, instances.mdkp(*args))
+            out = p.bnb(batch_width=16, comm=comm)
+            res[name] = dict(incumbent=out["incumbent"], x=None if out["x"] is None else out["x"].tolist(),
+                             iterations=out["iterations"], total=out["total_nodes"], split_at=out["split_at"],
+                             inc_rank=out["incumbent_rank"], has=out["has_incumbent"])
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_node_sharded_bnb_world2_gloo():
+    """mvb_bnb_run_dist on 2 ranks (gloo, CPU engine): exact search -> the serial optimum, the
+    same x on both ranks, work split between the ranks after the lock-step ramp-up."""
+    import json
+    from mvolps_b200.lp import GlpProb
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    oracle_lib = os.path.join(root, "oracle", "_build", "libglpk_oracle.so")
+    gold = {c["name"]: c for c in json.load(open(os.path.join(root, "tests", "golden", "bnb_golden.json")))["cases"]}
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_bnb_worker, args=(r, 2, port, q, oracle_lib)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    orc = capi.load_library(oracle_lib)
+    orc.glp_term_out(capi.GLP_OFF)
+    for name, args in (("mdkp_12x4_s1", (12, 4, 1)), ("mdkp_15x5_s2", (15, 5, 2))):
+        serial = GlpProb.from_instance(orc, instances.mdkp(*args)).bnb()
+        a, b = res[0][name], res[1][name]
+        assert a["has"] and b["has"]
+        assert a["incumbent"] == b["incumbent"] == serial["incumbent"]
+        assert a["x"] == b["x"] and a["inc_rank"] == b["inc_rank"] and a["total"] == b["total"]
+        assert abs(np.dot(instances.mdkp(*args)["c"], a["x"]) - a["incumbent"]) < 1e-9
+        assert a["split_at"] == b["split_at"] and a["split_at"] >= 0
+        assert a["iterations"] + b["iterations"] - a["split_at"] == a["total"] - a["split_at"]
+        assert 0 < a["iterations"] < a["total"] and 0 < b["iterations"] < b["total"]
+        if name == "mdkp_12x4_s1":
+            assert abs(a["incumbent"] - gold[name]["highs_ilp"]) < 1e-9
+
+
 def test_incumbent_exchange_world2_gloo(lib):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
