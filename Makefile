@@ -9,7 +9,7 @@ BIN  := $(ROOT)/mvolps_b200/bin/mvolps_b200
 NVCC := nvcc
 ARCH := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS := $(ARCH) -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -I$(ROOT)/include $(if $(PROF),-DMVB_PROF) $(if $(PSNT),-DMVB_PS_NT=$(PSNT))
-CXXFLAGS := -std=c++17 -O2 -fPIC -Wall -I$(ROOT)/include
+CXXFLAGS := -std=c++17 -O2 -mfma -ffp-contract=off -fPIC -Wall -I$(ROOT)/include
 HOST := glpk_shim lp_reader bnb_driver
 
 all: $(LIB) $(BIN)

@@ -666,6 +666,26 @@ namespace {
 thread_local std::string g_err;
 std::atomic<unsigned long long> g_launches{0};
 
+struct CloneJob {
+  const char *src;
+  char *dst;
+  unsigned long long bytes;  // multiple of 256
+};
+
+// every queued clone in one launch: blockIdx.y = job, blockIdx.x strides the 16-byte units
+__global__ void __launch_bounds__(256) clone_kernel(const CloneJob *jobs) {
+  const CloneJob j = jobs[blockIdx.y];
+  const uint4 *__restrict__ s = reinterpret_cast<const uint4 *>(j.src);
+  uint4 *__restrict__ d = reinterpret_cast<uint4 *>(j.dst);
+  const size_t n16 = j.bytes / 16, step = (size_t)gridDim.x * blockDim.x;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 3 * step < n16; i += 4 * step) {
+    const uint4 a = s[i], b = s[i + step], c = s[i + 2 * step], e = s[i + 3 * step];
+    d[i] = a; d[i + step] = b; d[i + 2 * step] = c; d[i + 3 * step] = e;
+  }
+  for (; i < n16; i += step) d[i] = s[i];
+}
+
 struct DeviceCtx {
   bool ready = false;
   int device = -1, sms = 0;
@@ -681,6 +701,12 @@ struct DeviceCtx {
   BoundPatch *d_patch = nullptr, *h_patch = nullptr; size_t patch_cap = 0;
   std::vector<std::pair<size_t, char *>> free_slabs;  // recycled LP slabs (size, pointer)
   size_t free_bytes = 0;
+  // deferred clones (glp_copy_prob, util.cpp:34 / bs.cpp:116): queued here and carried out
+  // by ONE clone_kernel launch in front of the next device operation
+  std::vector<CloneJob> clone_jobs;
+  std::vector<std::pair<size_t, char *>> zombies;  // slabs released while a queued clone may read them
+  CloneJob *d_jobs = nullptr; size_t jobs_cap = 0;
+  unsigned clone_epoch = 1;  // bumped by every flush: marks which handles take part in queued clones
   cudaEvent_t ev[16] = {};
   cudaEvent_t kev[2] = {};
   char *flush = nullptr; size_t flush_bytes = 0;
@@ -771,6 +797,8 @@ struct mvb_lp {
   mvb_result res{};
   int *pivlog = nullptr; int pivlog_cap = 0, pivlog_n = 0;
   std::vector<char> outbox;         // host copy of the outbox
+  unsigned clone_epoch = 0;         // == g_ctx.clone_epoch: source (1) / destination (2) of a queued clone
+  int clone_role = 0;
 };
 
 namespace {
@@ -834,21 +862,55 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
   return true;
 }
 
+void slab_recycle(size_t bytes, char *slab) {
+  // node LPs come and go in equal sizes (util.cpp:25-42): keep up to 1 GiB of slabs for reuse
+  if (bytes <= ((size_t)64 << 20) && g_ctx.free_bytes + bytes <= ((size_t)1 << 30) &&
+      g_ctx.free_slabs.size() < 8192) {
+    g_ctx.free_slabs.emplace_back(bytes, slab);
+    g_ctx.free_bytes += bytes;
+  } else {
+    cudaFreeAsync(slab, g_ctx.stream);
+  }
+}
+
 void lp_release(mvb_lp *lp) {
   if (lp->slab) {
-    // node LPs come and go in equal sizes (util.cpp:25-42): keep up to 1 GiB of slabs for reuse
-    if (lp->slab_bytes <= ((size_t)64 << 20) && g_ctx.free_bytes + lp->slab_bytes <= ((size_t)1 << 30) &&
-        g_ctx.free_slabs.size() < 8192) {
-      g_ctx.free_slabs.emplace_back(lp->slab_bytes, lp->slab);
-      g_ctx.free_bytes += lp->slab_bytes;
-    } else {
-      cudaFreeAsync(lp->slab, g_ctx.stream);
-    }
+    // a queued clone may still have to read (or write) this slab: park it until the flush
+    if (!g_ctx.clone_jobs.empty()) g_ctx.zombies.emplace_back(lp->slab_bytes, lp->slab);
+    else slab_recycle(lp->slab_bytes, lp->slab);
   }
   if (lp->pivlog) cudaFreeAsync(lp->pivlog, g_ctx.stream);
   lp->slab = nullptr;
   lp->pivlog = nullptr;
   lp->pivlog_cap = 0;
+}
+
+// carry out the queued clones: one H2D of the job list + one kernel, stream-ordered in
+// front of whatever the caller enqueues next
+bool flush_clones() {
+  if (g_ctx.clone_jobs.empty()) return true;
+  cudaStream_t st = g_ctx.stream;
+  std::vector<CloneJob> &jobs = g_ctx.clone_jobs;
+  if (g_ctx.jobs_cap < jobs.size()) {
+    if (g_ctx.d_jobs) CK(cudaFreeAsync(g_ctx.d_jobs, st));
+    g_ctx.jobs_cap = std::max(jobs.size() * 2, (size_t)1024);
+    CK(cudaMallocAsync((void **)&g_ctx.d_jobs, g_ctx.jobs_cap * sizeof(CloneJob), st));
+  }
+  // pageable source: the driver stages it before returning, so `jobs` may be reused at once
+  CK(cudaMemcpyAsync(g_ctx.d_jobs, jobs.data(), jobs.size() * sizeof(CloneJob), cudaMemcpyHostToDevice, st));
+  unsigned long long max_bytes = 0;
+  for (const CloneJob &j : jobs) max_bytes = std::max(max_bytes, j.bytes);
+  const size_t per_block = (size_t)256 * 16 * 8;  // eight 16-byte units per thread
+  size_t gx = (max_bytes + per_block - 1) / per_block;
+  gx = std::max<size_t>(1, std::min<size_t>(gx, std::max<size_t>(1, (size_t)g_ctx.sms * 32 / jobs.size())));
+  clone_kernel<<<dim3((unsigned)gx, (unsigned)jobs.size()), 256, 0, st>>>(g_ctx.d_jobs);
+  CK(cudaGetLastError());
+  g_launches++;
+  jobs.clear();
+  g_ctx.clone_epoch++;
+  for (auto &z : g_ctx.zombies) slab_recycle(z.first, z.second);
+  g_ctx.zombies.clear();
+  return true;
 }
 
 int nb_flag_for(double l, double u, int keep) {
@@ -921,6 +983,7 @@ int mvb_lp_dims(const mvb_lp *lp, int *m, int *n) {
 
 int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost, const double *lb,
                 const double *ub) {
+  if (!flush_clones()) return -1;
   const int m = lp->m, n = lp->n, ld = lp->ld;
   cudaStream_t st = g_ctx.stream;
   LPDev &d = lp->dev;
@@ -952,7 +1015,6 @@ int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost, const double *l
 
 int mvb_lp_assign(mvb_lp *dst, const mvb_lp *src) {
   if (dst->n != src->n || dst->mcap != src->mcap) { g_err = "mvb_lp_assign: shape mismatch"; return -1; }
-  cudaStream_t st = g_ctx.stream;
   dst->m = src->m;
   dst->dev.m = src->m;
   dst->curT = src->curT;
@@ -960,8 +1022,22 @@ int mvb_lp_assign(mvb_lp *dst, const mvb_lp *src) {
   // the current tableau buffer and the small state are adjacent (lp_alloc): one copy
   if (dst->t_bytes != src->t_bytes || dst->small_bytes != src->small_bytes) { g_err = "mvb_lp_assign: layout mismatch"; return -1; }
   const size_t from = src->curT == 0 ? 0 : src->small_off;
-  CKI(cudaMemcpyAsync(dst->slab + from, src->slab + from, src->t_bytes + src->small_bytes,
-                      cudaMemcpyDeviceToDevice, st));
+  // queued, not issued: all clones of a B&B round go out as one kernel (flush_clones).
+  // A handle may be read by several queued clones, but a chain (clone of a queued
+  // destination, or overwriting a queued source/destination) is flushed first.
+  const unsigned ep = g_ctx.clone_epoch;
+  const bool src_is_dst = src->clone_epoch == ep && (src->clone_role & 2);
+  const bool dst_busy = dst->clone_epoch == ep && dst->clone_role != 0;
+  if (src_is_dst || dst_busy || g_ctx.clone_jobs.size() >= 32768) {
+    if (!flush_clones()) return -1;
+  }
+  mvb_lp *msrc = const_cast<mvb_lp *>(src);
+  if (msrc->clone_epoch != g_ctx.clone_epoch) { msrc->clone_epoch = g_ctx.clone_epoch; msrc->clone_role = 0; }
+  msrc->clone_role |= 1;
+  dst->clone_epoch = g_ctx.clone_epoch;
+  dst->clone_role = 2;
+  g_ctx.clone_jobs.push_back(CloneJob{src->slab + from, dst->slab + from,
+                                      (unsigned long long)(src->t_bytes + src->small_bytes)});
   dst->lb = src->lb; dst->ub = src->ub;
   dst->head = src->head; dst->nb = src->nb; dst->at = src->at; dst->x = src->x;
   dst->bounds_dirty = src->bounds_dirty;
@@ -1069,6 +1145,7 @@ bool lp_grow(mvb_lp *lp, int mcap) {
 }  // namespace
 
 extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double ub) {
+  if (!flush_clones()) return -1;
   if (lp->m + 1 > lp->mcap && !lp_grow(lp, lp->mcap + 16 + lp->mcap / 4)) return -1;
   const int n = lp->n, m = lp->m;
   cudaStream_t st = g_ctx.stream;
@@ -1099,17 +1176,12 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   if (!count) return true;
   cudaStream_t st = g_ctx.stream;
   std::vector<LPDev> h(count);
-  size_t max_bytes = 0, dyn = 0;
+  size_t max_bytes = 0, dyn = 0, tot_bytes = 0;
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[idx[k]];
     h[k] = lp->dev;
     max_bytes = std::max(max_bytes, (size_t)(lp->m + 1) * lp->ld * sizeof(double));
-    if (psk) {
-      int K = lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn);
-      K = std::min(K, g_ctx.force_k > 0 ? g_ctx.force_k : 4);  // measured: depth 4 is the sweet spot
-      h[k].lzK = K;
-      dyn = std::max(dyn, lz_smem_bytes(lp->m, lp->ld, K));
-    }
+    tot_bytes += 2 * (size_t)(lp->m + 1) * lp->ld * sizeof(double);
   }
   const int max_ctas = psk ? g_ctx.max_ctas_ps : g_ctx.max_ctas;
   // CTAs per LP: by tableau size, bounded by what is co-resident
@@ -1119,6 +1191,18 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   if (!(opts && opts->ctas_per_lp > 0) && count > 1) G = std::max(1, std::min(G, max_ctas / count));
   G = std::max(1, std::min(G, max_ctas));
   int ngroups = std::max(1, std::min(count, max_ctas / G));
+  if (psk) {
+    // pending-update depth: 4 is the measured sweet spot while the tableaux stay in L2
+    // (flush passes are cheap, deeper chains cost decisions); a wide batch of one-CTA LPs
+    // streams its tableaux from HBM, where halving the flush traffic wins (depth 8)
+    const int cap = g_ctx.force_k > 0 ? g_ctx.force_k : (G == 1 && tot_bytes > ((size_t)96 << 20)) ? 8 : 4;
+    for (int k = 0; k < count; k++) {
+      mvb_lp *lp = lps[idx[k]];
+      const int K = std::min(lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn), cap);
+      h[k].lzK = K;
+      dyn = std::max(dyn, lz_smem_bytes(lp->m, lp->ld, K));
+    }
+  }
   if (g_ctx.ctrs_cap < ngroups) {
     if (g_ctx.ctrs) CK(cudaFreeAsync(g_ctx.ctrs, st));
     CK(cudaMallocAsync((void **)&g_ctx.ctrs, (size_t)ngroups * sizeof(unsigned), st));
@@ -1197,6 +1281,7 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
                                mvb_result *out) {
   if (count <= 0) return 0;
   if (!ctx_init(-1)) return -1;
+  if (!flush_clones()) return -1;
   cudaStream_t st = g_ctx.stream;
   std::vector<int> ps_idx, gen_idx;
   for (int k = 0; k < count; k++) {
@@ -1268,6 +1353,7 @@ int mvb_lp_get_basis(mvb_lp *lp, int *head, int *nb, int *at) {
 }
 
 int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
+  if (!flush_clones()) return -1;
   if (nrows <= 0) return 0;
   for (int t = 0; t < nrows; t++)
     if (rows[t] < 0 || rows[t] > lp->m) { g_err = "mvb_lp_get_tab_rows: row out of range"; return -1; }
@@ -1289,6 +1375,7 @@ int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
 }
 
 int mvb_lp_get_tableau(mvb_lp *lp, double *T, double *beta) {
+  if (!flush_clones()) return -1;
   cudaStream_t st = g_ctx.stream;
   CKI(cudaMemcpy2DAsync(T, (size_t)lp->n * sizeof(double), lp->dev.T[lp->curT],
                         (size_t)lp->ld * sizeof(double), (size_t)lp->n * sizeof(double), lp->m + 1,
@@ -1302,6 +1389,7 @@ int mvb_lp_get_tableau(mvb_lp *lp, double *T, double *beta) {
 }
 
 int mvb_lp_get_pivot_log(mvb_lp *lp, int *rowcol, int cap) {
+  if (!flush_clones()) return -1;
   int c = std::min(lp->pivlog_n, cap);
   if (c > 0) {
     CKI(cudaMemcpyAsync(rowcol, lp->pivlog, (size_t)c * 2 * sizeof(int), cudaMemcpyDeviceToHost, g_ctx.stream));

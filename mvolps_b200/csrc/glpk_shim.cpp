@@ -28,7 +28,11 @@ double mv_eff_ub(int type, double ub) {
   return (type == GLP_UP || type == GLP_DB || type == GLP_FX) ? ub : HUGE_VAL;
 }
 double mv_snap(double x) {
-  double r = std::rint(x);
+  /* r = rint(x) without the libm call: below 2^51 adding and subtracting 2^52+2^51
+   * rounds to nearest-even exactly as rint does; copysign keeps rint's signed zero */
+  const double ax = std::fabs(x);
+  if (!(ax < 2251799813685248.0)) return x;  // already integral (or inf/nan)
+  const double r = std::copysign((ax + 6755399441055744.0) - 6755399441055744.0, x);
   return std::fabs(x - r) <= MV_SNAP_TOL ? r : x;
 }
 
@@ -39,6 +43,7 @@ static void drop_engine(glp_prob *P) {
   P->eng_stale = true;
   P->eng_lb.clear();
   P->eng_ub.clear();
+  P->dirty.clear();
   P->head.clear();
   P->nb.clear();
   P->at.clear();
@@ -101,6 +106,7 @@ void glp_copy_prob(glp_prob *dest, glp_prob *src, int names) {
     dest->eng_stale = false;
     dest->eng_lb = src->eng_lb;
     dest->eng_ub = src->eng_ub;
+    dest->dirty = src->dirty;
     dest->head = src->head;
     dest->nb = src->nb;
     dest->at = src->at;
@@ -218,6 +224,7 @@ static void store_bnds(int type, double lb, double ub, int &t, double &l,
 void glp_set_row_bnds(glp_prob *P, int i, int type, double lb, double ub) {
   MvRow &r = row_at(P, i, "glp_set_row_bnds: row out of range");
   store_bnds(type, lb, ub, r.type, r.lb, r.ub, r.stat);
+  if (P->eng && i <= P->eng_rows) P->dirty.push_back((int)P->cols.size() + i - 1);
 }
 
 int glp_get_mat_row(glp_prob *P, int i, int ind[], double val[]) {
@@ -265,6 +272,7 @@ double glp_get_col_ub(glp_prob *P, int j) {
 void glp_set_col_bnds(glp_prob *P, int j, int type, double lb, double ub) {
   MvCol &c = col_at(P, j, "glp_set_col_bnds: column out of range");
   store_bnds(type, lb, ub, c.type, c.lb, c.ub, c.stat);
+  if (P->eng) P->dirty.push_back(j - 1);
 }
 int glp_get_col_kind(glp_prob *P, int j) {
   MvCol &c = col_at(P, j, "glp_get_col_kind");
@@ -276,6 +284,7 @@ void glp_set_col_kind(glp_prob *P, int j, int kind) {
   if (kind == GLP_BV) {
     c.kind = GLP_IV;
     store_bnds(GLP_DB, 0.0, 1.0, c.type, c.lb, c.ub, c.stat);
+    if (P->eng) P->dirty.push_back(j - 1);
   } else if (kind == GLP_CV || kind == GLP_IV) {
     c.kind = kind;
   } else shim_abort("glp_set_col_kind: invalid kind");
@@ -293,16 +302,16 @@ int glp_get_it_cnt(glp_prob *P) { return P->it_cnt; }
 static int sync_engine(glp_prob *P) {
   int m = (int)P->rows.size(), n = (int)P->cols.size();
   if (P->eng && !P->eng_stale && P->eng_rows > m) P->eng_stale = true;
-  std::vector<double> lb(n + m), ub(n + m);
-  for (int j = 0; j < n; j++) {
-    lb[j] = mv_eff_lb(P->cols[j].type, P->cols[j].lb);
-    ub[j] = mv_eff_ub(P->cols[j].type, P->cols[j].ub);
-  }
-  for (int i = 0; i < m; i++) {
-    lb[n + i] = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
-    ub[n + i] = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
-  }
   if (!P->eng || P->eng_stale) {
+    std::vector<double> lb(n + m), ub(n + m);
+    for (int j = 0; j < n; j++) {
+      lb[j] = mv_eff_lb(P->cols[j].type, P->cols[j].lb);
+      ub[j] = mv_eff_ub(P->cols[j].type, P->cols[j].ub);
+    }
+    for (int i = 0; i < m; i++) {
+      lb[n + i] = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
+      ub[n + i] = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
+    }
     if (P->eng) mvb_lp_free(P->eng);
     P->eng = mvb_lp_create(m, n, m + 32 + m / 8);
     if (!P->eng) return -1;
@@ -315,26 +324,48 @@ static int sync_engine(glp_prob *P) {
     if (mvb_lp_load(P->eng, A.data(), cost.data(), lb.data(), ub.data())) return -1;
     P->eng_rows = m;
     P->eng_stale = false;
-    P->eng_lb = lb;
-    P->eng_ub = ub;
+    P->eng_lb = std::move(lb);
+    P->eng_ub = std::move(ub);
+    P->dirty.clear();
     return 0;
   }
-  std::vector<double> a(n);
-  for (int i = P->eng_rows; i < m; i++) {
-    std::fill(a.begin(), a.end(), 0.0);
-    for (size_t t = 0; t < P->rows[i].ind.size(); t++)
-      a[P->rows[i].ind[t] - 1] = P->rows[i].val[t];
-    if (mvb_lp_append_row(P->eng, a.data(), lb[n + i], ub[n + i])) return -1;
-    P->eng_lb.push_back(lb[n + i]);
-    P->eng_ub.push_back(ub[n + i]);
-  }
-  P->eng_rows = m;
-  for (int k = 0; k < n + m; k++) {
-    if (lb[k] != P->eng_lb[k] || ub[k] != P->eng_ub[k]) {
-      if (mvb_lp_set_bounds(P->eng, k, lb[k], ub[k])) return -1;
-      P->eng_lb[k] = lb[k];
-      P->eng_ub[k] = ub[k];
+  const int old_rows = P->eng_rows;
+  if (P->eng_rows < m) {
+    std::vector<double> a(n);
+    for (int i = P->eng_rows; i < m; i++) {
+      std::fill(a.begin(), a.end(), 0.0);
+      for (size_t t = 0; t < P->rows[i].ind.size(); t++)
+        a[P->rows[i].ind[t] - 1] = P->rows[i].val[t];
+      const double l = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
+      const double u = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
+      if (mvb_lp_append_row(P->eng, a.data(), l, u)) return -1;
+      P->eng_lb.push_back(l);
+      P->eng_ub.push_back(u);
     }
+    P->eng_rows = m;
+  }
+  /* bounds set since the last sync (the setters log the engine id): forward the ones
+   * that really changed, in ascending id order as a full scan would */
+  if (!P->dirty.empty()) {
+    std::sort(P->dirty.begin(), P->dirty.end());
+    P->dirty.erase(std::unique(P->dirty.begin(), P->dirty.end()), P->dirty.end());
+    for (int k : P->dirty) {
+      if (k >= n + old_rows) continue;  // a row appended above
+      double l, u;
+      if (k < n) {
+        l = mv_eff_lb(P->cols[k].type, P->cols[k].lb);
+        u = mv_eff_ub(P->cols[k].type, P->cols[k].ub);
+      } else {
+        l = mv_eff_lb(P->rows[k - n].type, P->rows[k - n].lb);
+        u = mv_eff_ub(P->rows[k - n].type, P->rows[k - n].ub);
+      }
+      if (l != P->eng_lb[k] || u != P->eng_ub[k]) {
+        if (mvb_lp_set_bounds(P->eng, k, l, u)) return -1;
+        P->eng_lb[k] = l;
+        P->eng_ub[k] = u;
+      }
+    }
+    P->dirty.clear();
   }
   return 0;
 }
@@ -351,26 +382,30 @@ static int stat_of(int at) {
 /* copy status, primal values and basis back from the engine */
 int mv_pull_solution(glp_prob *P, const mvb_result &res) {
   int m = (int)P->rows.size(), n = (int)P->cols.size();
-  std::vector<double> x(n + m);
+  static thread_local std::vector<double> x;
+  x.resize(n + m);
   P->head.resize(m);
   P->nb.resize(n);
   P->at.resize(n);
   if (mvb_lp_get_primal(P->eng, x.data())) return -1;
   if (mvb_lp_get_basis(P->eng, P->head.data(), P->nb.data(), P->at.data())) return -1;
+  MvCol *cols = P->cols.data();
+  MvRow *rows = P->rows.data();
   for (int i = 0; i < m; i++) {
     int k = P->head[i];
-    if (k < n) P->cols[k].stat = GLP_BS; else P->rows[k - n].stat = GLP_BS;
+    if (k < n) cols[k].stat = GLP_BS; else rows[k - n].stat = GLP_BS;
   }
   for (int j = 0; j < n; j++) {
     int k = P->nb[j], st = stat_of(P->at[j]);
-    if (k < n) P->cols[k].stat = st; else P->rows[k - n].stat = st;
+    if (k < n) cols[k].stat = st; else rows[k - n].stat = st;
   }
   double z = P->c0;
   for (int j = 0; j < n; j++) {
-    P->cols[j].prim = mv_snap(x[j]);
-    z = std::fma(P->cols[j].coef, P->cols[j].prim, z);
+    const double v = mv_snap(x[j]);
+    cols[j].prim = v;
+    z = std::fma(cols[j].coef, v, z);
   }
-  for (int i = 0; i < m; i++) P->rows[i].prim = mv_snap(x[n + i]);
+  for (int i = 0; i < m; i++) rows[i].prim = mv_snap(x[n + i]);
   P->obj_val = z;
   P->it_cnt = res.iters;
   P->last = res;

@@ -34,6 +34,21 @@ class CowVec {
   void push_back(const T &v) { mut().push_back(v); }
 };
 
+// Row/column names are never read through the 34-function boundary, only by the
+// readers' messages: shared, so a problem copy does not duplicate the strings.
+struct MvName {
+  std::shared_ptr<const std::string> p;
+  MvName &operator=(const std::string &s) {
+    p = s.empty() ? nullptr : std::make_shared<const std::string>(s);
+    return *this;
+  }
+  void clear() { p.reset(); }
+  const std::string &str() const {
+    static const std::string none;
+    return p ? *p : none;
+  }
+};
+
 struct MvRow {
   int type = GLP_FR;
   double lb = 0.0, ub = 0.0;
@@ -41,7 +56,7 @@ struct MvRow {
   CowVec<double> val;
   int stat = GLP_BS;
   double prim = 0.0;
-  std::string name;
+  MvName name;
 };
 
 struct MvCol {
@@ -51,7 +66,7 @@ struct MvCol {
   double coef = 0.0;
   int stat = GLP_NS;
   double prim = 0.0;
-  std::string name;
+  MvName name;
 };
 
 struct glp_prob {
@@ -69,6 +84,7 @@ struct glp_prob {
   int eng_rows = 0;            // rows the engine tableau already contains
   bool eng_stale = true;       // matrix/objective changed: rebuild from scratch
   std::vector<double> eng_lb, eng_ub;  // bounds last sent, by engine id
+  std::vector<int> dirty;              // engine ids whose bounds were set since the last sync
   std::vector<int> head, nb, at;       // basis after the last solve
   mvb_result last{};
 };

@@ -260,7 +260,7 @@ struct LpParser {
           apply_bounds(j, true, -HUGE_VAL, true, HUGE_VAL);
           continue;
         }
-        if (peek().kind != T_OP) { err = "bound sense expected after '" + b.P->cols[j - 1].name + "'"; return false; }
+        if (peek().kind != T_OP) { err = "bound sense expected after '" + b.P->cols[j - 1].name.str() + "'"; return false; }
         std::string op = peek().text;
         pos++;
         double v;
