@@ -53,6 +53,8 @@ typedef struct mvb_bnb_stats {
   int split_at;          /* dist: iteration count at which the queue was dealt out (-1: never) */
   int incumbent_rank;    /* dist: rank that found the incumbent (0 in serial runs) */
   long long total_nodes; /* dist: nodes processed by all ranks (serial: = iterations) */
+  int cached_solves;     /* of lp_solves: requests on an LP unchanged since its last optimal solve
+                            (the re-solve of bs.cpp:117 on a copy), answered without a launch */
 } mvb_bnb_stats;
 
 typedef struct mvb_bnb mvb_bnb;

@@ -82,6 +82,7 @@ class BnbStats(C.Structure):
         ("simplex_iters", C.c_longlong), ("has_incumbent", C.c_int), ("incumbent_oid", C.c_int),
         ("incumbent", C.c_double), ("hit_limit", C.c_int), ("event_hash", C.c_ulonglong),
         ("split_at", C.c_int), ("incumbent_rank", C.c_int), ("total_nodes", C.c_longlong),
+        ("cached_solves", C.c_int),
     ]
 
 

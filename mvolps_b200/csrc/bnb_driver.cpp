@@ -17,7 +17,9 @@
 #include <limits>
 #include <map>
 #include <memory>
+#include <charconv>
 #include <sstream>
+#include <type_traits>
 #include <string>
 #include <vector>
 
@@ -27,11 +29,27 @@
 
 namespace {
 
+// Text formatting identical to util.h:124-128 (operator<< into an ostringstream with the
+// default flags: integers in decimal, doubles as %g with precision 6) without building
+// a stream per call -- every node logs several events.
+inline void put(std::string &s, const char *v) { s += v; }
+inline void put(std::string &s, const std::string &v) { s += v; }
+inline void put(std::string &s, double v) {
+  char b[48];
+  auto r = std::to_chars(b, b + sizeof b, v, std::chars_format::general, 6);
+  s.append(b, r.ptr);
+}
+template <typename I, typename = std::enable_if_t<std::is_integral<I>::value>>
+inline void put(std::string &s, I v) {
+  char b[24];
+  auto r = std::to_chars(b, b + sizeof b, v);
+  s.append(b, r.ptr);
+}
 template <typename... Args>
-std::string sstr(Args &&...args) {  // same formatting as util.h:124-128
-  std::ostringstream s;
-  (s << std::dec << ... << args);
-  return s.str();
+std::string sstr(Args &&...args) {
+  std::string s;
+  (put(s, args), ...);
+  return s;
 }
 
 double get_fract(double x) {  // util.cpp:11-23
@@ -130,15 +148,21 @@ struct Driver {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   }
 
-  bool solve_many(const std::vector<glp_prob *> &ps) {
-    if (ps.empty()) return true;
+  bool solve_many(const std::vector<glp_prob *> &all) {
+    if (all.empty()) return true;
+    std::vector<glp_prob *> ps;
     std::vector<mvb_lp *> engs;
     double t0 = now();
-    for (auto *p : ps) {
-      if (mv_sync_engine(p)) return false;
+    for (auto *p : all) {
+      bool changed = false;
+      if (mv_sync_engine(p, &changed)) return false;
+      if (mv_answer_cached(p, changed)) { out->st.cached_solves++; continue; }
+      ps.push_back(p);
       engs.push_back(p->eng);
     }
+    out->st.lp_solves += (int)all.size();
     double t1 = now();
+    if (ps.empty()) { t_sync += t1 - t0; return true; }
     std::vector<mvb_result> res(ps.size());
     mvb_opts o{};
     if (mvb_solve_batch(engs.data(), (int)engs.size(), &o, res.data())) return false;
@@ -149,7 +173,6 @@ struct Driver {
     }
     t_sync += t1 - t0; t_solve += t2 - t1; t_pull += now() - t2;
     out->st.launches++;
-    out->st.lp_solves += (int)ps.size();
     return true;
   }
 

@@ -299,10 +299,12 @@ int glp_get_it_cnt(glp_prob *P) { return P->it_cnt; }
 /* bring the engine's LP in line with the problem object: cold build when the
  * matrix/objective changed, otherwise append the new rows (cut.cpp:23-43) and
  * forward changed bounds (bs.cpp:274,282) */
-static int sync_engine(glp_prob *P) {
+static int sync_engine(glp_prob *P, bool *changed) {
+  *changed = false;
   int m = (int)P->rows.size(), n = (int)P->cols.size();
   if (P->eng && !P->eng_stale && P->eng_rows > m) P->eng_stale = true;
   if (!P->eng || P->eng_stale) {
+    *changed = true;
     std::vector<double> lb(n + m), ub(n + m);
     for (int j = 0; j < n; j++) {
       lb[j] = mv_eff_lb(P->cols[j].type, P->cols[j].lb);
@@ -339,6 +341,7 @@ static int sync_engine(glp_prob *P) {
       const double l = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
       const double u = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
       if (mvb_lp_append_row(P->eng, a.data(), l, u)) return -1;
+      *changed = true;
       P->eng_lb.push_back(l);
       P->eng_ub.push_back(u);
     }
@@ -361,6 +364,7 @@ static int sync_engine(glp_prob *P) {
       }
       if (l != P->eng_lb[k] || u != P->eng_ub[k]) {
         if (mvb_lp_set_bounds(P->eng, k, l, u)) return -1;
+        *changed = true;
         P->eng_lb[k] = l;
         P->eng_ub[k] = u;
       }
@@ -418,7 +422,19 @@ int mv_pull_solution(glp_prob *P, const mvb_result &res) {
   return 0;
 }
 
-int mv_sync_engine(glp_prob *P) { return sync_engine(P); }
+bool mv_answer_cached(glp_prob *P, bool changed) {
+  if (changed || P->status != GLP_OPT || P->last.status != MVB_OPT) return false;
+  P->it_cnt = 0;
+  P->last.iters = P->last.pivots = P->last.flips = 0;
+  return true;
+}
+
+int mv_sync_engine(glp_prob *P, bool *changed) {
+  bool c = false;
+  int rc = sync_engine(P, &c);
+  if (changed) *changed = c;
+  return rc;
+}
 
 extern "C" {
 
@@ -430,10 +446,14 @@ int glp_simplex(glp_prob *P, const glp_smcp *parm) {
     P->status = GLP_UNDEF;
     return GLP_EFAIL;
   }
-  if (sync_engine(P)) {
+  bool changed = false;
+  if (sync_engine(P, &changed)) {
     std::fprintf(stderr, "glp_simplex: engine error: %s\n", mvb_last_error());
     return GLP_EFAIL;
   }
+  /* bs.cpp:117 re-solves a copy of an LP that was solved to optimality as a child
+   * (bs.cpp:279,287): nothing changed, the answer is the one already held */
+  if (mv_answer_cached(P, changed)) return 0;
   mvb_result res;
   mvb_opts opts{};
   if (mvb_solve_batch(&P->eng, 1, &opts, &res)) {

@@ -102,5 +102,10 @@ constexpr double MV_SNAP_TOL = 1e-9;
 double mv_snap(double x);
 
 // glpk_shim.cpp helpers shared with the batched B&B driver
-int mv_sync_engine(glp_prob *P);                            // push deltas to the engine
+// push deltas to the engine; *changed: the engine's LP differs from the one last solved
+int mv_sync_engine(glp_prob *P, bool *changed = nullptr);
+// true when the LP is exactly the one whose optimal solution the object already holds (a
+// solve would start from the optimal tableau, do zero iterations and return the same
+// values); the iteration counters are then set to that zero-iteration solve's
+bool mv_answer_cached(glp_prob *P, bool changed);
 int mv_pull_solution(glp_prob *P, const mvb_result &res);   // read result back
