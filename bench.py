@@ -134,10 +134,11 @@ def main():
                          "node LPs m=256 n=512 dealt over the ranks; shard: configs[4], one tableau column-sharded")
     ap.add_argument("--lps", type=int, default=4096, help="batch: LPs in total")
     ap.add_argument("--distinct", type=int, default=128, help="batch: distinct seeds (the rest are clones)")
-    ap.add_argument("--m", type=int, default=0)
-    ap.add_argument("--n", type=int, default=0)
+    # --rows/--cols: spellings torchrun's own parser does not mistake for its options
+    ap.add_argument("--m", "--rows", dest="m", type=int, default=0)
+    ap.add_argument("--n", "--cols", dest="n", type=int, default=0)
     ap.add_argument("--pivots", type=int, default=300, help="shard: pivot budget per step")
-    ap.add_argument("--nodes", type=int, default=2000, help="bnb: node budget per step")
+    ap.add_argument("--nodes", type=int, default=10000, help="bnb: node budget per step")
     ap.add_argument("--cut-mode", type=int, default=0, help="bnb: 0 none, 1 reference gmi.cpp, 2 textbook GMI")
     ap.add_argument("--batch-width", type=int, default=256, help="bnb: FIFO nodes per engine launch")
     args = ap.parse_args()
