@@ -161,24 +161,24 @@ __host__ __device__ inline int lz_pick_k(int m, int ld, size_t avail) {
 
 __device__ __forceinline__ double *zD(const Lay &l) { return reinterpret_cast<double *>(dyn_smem); }
 __device__ __forceinline__ double *zRho(const Lay &l, int p) {
-  return reinterpret_cast<double *>(dyn_smem + (size_t)(1 + p) * l.nv);
+  return reinterpret_cast<double *>(dyn_smem + (unsigned)(1 + p) * l.nv);
 }
 __device__ __forceinline__ int *zNbv(const Lay &l) {
-  return reinterpret_cast<int *>(dyn_smem + (size_t)(1 + l.K) * l.nv);
+  return reinterpret_cast<int *>(dyn_smem + (unsigned)(1 + l.K) * l.nv);
 }
 __device__ __forceinline__ int *zAtv(const Lay &l) {
-  return reinterpret_cast<int *>(dyn_smem + (size_t)(1 + l.K) * l.nv + l.nv / 2);
+  return reinterpret_cast<int *>(dyn_smem + (unsigned)(1 + l.K) * l.nv + l.nv / 2);
 }
-__device__ __forceinline__ unsigned char *zM(const Lay &l) { return dyn_smem + (size_t)(2 + l.K) * l.nv; }
+__device__ __forceinline__ unsigned char *zM(const Lay &l) { return dyn_smem + (unsigned)(2 + l.K) * l.nv; }
 __device__ __forceinline__ double *zCol(const Lay &l, int p) {
-  return reinterpret_cast<double *>(zM(l) + (size_t)p * l.mv);
+  return reinterpret_cast<double *>(zM(l) + (unsigned)p * l.mv);
 }
 __device__ __forceinline__ double *zBeta(const Lay &l) { return zCol(l, l.K + 1); }
 __device__ __forceinline__ double *zLbB(const Lay &l) { return zCol(l, l.K + 2); }
 __device__ __forceinline__ double *zUbB(const Lay &l) { return zCol(l, l.K + 3); }
 __device__ __forceinline__ int *zHead(const Lay &l) { return reinterpret_cast<int *>(zCol(l, l.K + 4)); }
 __device__ __forceinline__ unsigned char *zTail(const Lay &l, int m) {
-  return zM(l) + (size_t)(l.K + 4) * l.mv + (((size_t)(m + 2) * 4 + 15) & ~(size_t)15);
+  return zM(l) + (unsigned)(l.K + 4) * l.mv + (((unsigned)(m + 2) * 4u + 15u) & ~15u);
 }
 __device__ __forceinline__ Key (*zSlot(const Lay &l, int m))[32] {
   return reinterpret_cast<Key(*)[32]>(zTail(l, m));
@@ -378,14 +378,15 @@ __device__ __noinline__ void lz_col(LZS *S, int q) {
   const size_t ld = (size_t)S->ld;
   const int *pend = zPend(l, m);
   double *dst = zCol(l, np);
-  constexpr int NU = 4;  // rows per thread and pass, all computed unconditionally
+  constexpr int NU = 2;  // rows per thread and pass, all computed unconditionally
   double lq = 0.0, uq = 0.0;
   if (tid == 0) {
     const int kq = zNbv(l)[q];
     lq = ldcg(S->lb + kq);
     uq = ldcg(S->ub + kq);
+    dst[0] = zD(l)[q];  // row 0 of the current tableau is the private reduced-cost vector
   }
-  for (int i0 = tid; i0 <= m; i0 += NU * NT) {
+  for (int i0 = 1 + tid; i0 <= m; i0 += NU * NT) {
     int ii[NU];
     double v[NU];
 #pragma unroll
@@ -419,15 +420,29 @@ __device__ __forceinline__ void lz_issue_row(LZS *S, int r) {
 }
 
 // wait for the raw row, apply the pending updates in place and, when scale is
-// set, turn it into the scaled pivot row rho_q = inv, rho_j = -(v_j * inv)
+// set, turn it into the scaled pivot row rho_q = inv, rho_j = -(v_j * inv).
+// scale == 2 (primal pivot: the step is already in S) also applies the
+// iteration to the private vectors, beta while the row is still in flight:
+//   beta'_i = i == r ? newbr : fma(T_iq, delta, beta_i)
+//   d'_j    = fma(d_q, rho_j, j == q ? 0 : d_j)           (row 0 of the update)
 __device__ __noinline__ void lz_row(LZS *S, int r, int q, int scale) {
   const Lay l = S->lay;
   const int m = S->m, ld = S->ld, np = S->np, tid = threadIdx.x, NT = blockDim.x;
   const double inv = S->inv;
   const int *pend = zPend(l, m);
+  const bool fuse = scale == 2;
+  double dq = 0.0;
+  if (fuse) {
+    const double delta = S->delta, newbr = S->newbr;
+    const double *colN = zCol(l, np);
+    double *beta = zBeta(l);
+    dq = colN[0];
+    for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
+  }
   mbar_wait(zMbar(l, m), S->mphase);
+  PROF(7);
   constexpr int JU = 4;  // columns per thread and pass, all computed unconditionally
-  double *buf = zRho(l, np);
+  double *buf = zRho(l, np), *d = zD(l);
   for (int j0 = tid; j0 < ld; j0 += JU * NT) {
     int jj[JU];
     double v[JU];
@@ -450,7 +465,10 @@ __device__ __noinline__ void lz_row(LZS *S, int r, int q, int scale) {
     }
 #pragma unroll
     for (int u = 0; u < JU; u++)
-      if (j0 + u * NT < ld) buf[jj[u]] = v[u];
+      if (j0 + u * NT < ld) {
+        buf[jj[u]] = v[u];
+        if (fuse) d[jj[u]] = fma(dq, v[u], jj[u] == q ? 0.0 : d[jj[u]]);
+      }
   }
   __syncthreads();
   if (tid == 0) S->mphase ^= 1;
@@ -466,24 +484,28 @@ __device__ __noinline__ int lz_price(LZS *S) {
   const int *atv = zAtv(l), *nbv = zNbv(l);
   // per thread: best score s = |d_j| of an eligible column (FX / ineligible: -1), ties to the
   // lower variable id; branch-free, NJ columns in flight.  Same order as the (~bits, id) keys.
-  double best = -1.0;
+  double best = 0.0;  // eligible scores exceed MVB_TOL_DJ > 0
   int bj = -1, bvar = 0x7fffffff;
   constexpr int NJ = 4;
   for (int j0 = tid; j0 < n; j0 += NJ * NT) {
 #pragma unroll
     for (int u = 0; u < NJ; u++) {
-      const int j = j0 + u * NT, jj = min(j, n - 1);
+      const int jj = min(j0 + u * NT, n - 1);  // clamped repeats of column n-1 never win a tie
       const double dj = d[jj];
       const int f = atv[jj], v = nbv[jj];
-      const double s = f == MVB_AT_LB ? -dj : f == MVB_AT_UB ? dj : f == MVB_AT_FR ? fabs(dj) : -1.0;
-      const double sc = (j < n && s > MVB_TOL_DJ) ? (bland ? 1.0 : s) : -1.0;
-      const bool better = sc > best || (sc == best && sc > 0.0 && v < bvar);
+      // s = -d_j at the lower bound, d_j at the upper bound, |d_j| when free: sign-bit arithmetic
+      const unsigned flip = f == MVB_AT_LB ? 0x80000000u : 0u;
+      const unsigned keep = f == MVB_AT_FR ? 0x7fffffffu : 0xffffffffu;
+      const double s = __hiloint2double((int)(((unsigned)__double2hiint(dj) & keep) ^ flip), __double2loint(dj));
+      const bool elig = f != MVB_AT_FX && s > MVB_TOL_DJ;
+      const double sc = bland ? 1.0 : s;
+      const bool better = elig && (sc > best || (sc == best && v < bvar));
       best = better ? sc : best;
       bj = better ? jj : bj;
       bvar = better ? v : bvar;
     }
   }
-  Key bq = best > 0.0 ? Key{bland ? 0ULL : ~dbits(best), bvar, bj} : key_none();
+  Key bq = bj >= 0 ? Key{bland ? 0ULL : ~dbits(best), bvar, bj} : key_none();
   PROF(8);
 #ifdef MVB_PROF
   {
@@ -513,27 +535,35 @@ __device__ __noinline__ int lz_ratio_primal(LZS *S, int q) {
   const double *colN = zCol(l, S->np), *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l);
   const int *head = zHead(l);
   const int dir = zD(l)[q] < 0.0 ? 1 : -1;
-  Key bi = key_none();
-  constexpr int NU = 2;  // branch-free form of primal_ratio_row (phase 2), NU rows in flight
+  // branch-free form of primal_ratio_row (phase 2): one division per row, NU rows in flight;
+  // t >= +0 so comparing the doubles is comparing their bit patterns
+  double bt = HUGE_VAL;
+  int bvar = 0x7fffffff, bidx = -1;
+  constexpr int NU = 2;
   for (int i0 = 1 + tid; i0 <= m; i0 += NU * NT) {
 #pragma unroll
     for (int u = 0; u < NU; u++) {
       const int i = min(i0 + u * NT, m);
       const double alpha = colN[i], b = beta[i], lo = lbB[i], up = ubB[i];
+      const int hv = head[i];
       const double a = dir > 0 ? alpha : -alpha;
       const bool dec = a < -MVB_TOL_PIV, inc = a > MVB_TOL_PIV;
       const double bound = dec ? lo : up;
-      const bool ok = (dec && bound > -HUGE_VAL) || (inc && bound < HUGE_VAL);
-      double t = 0.0;
-      if (ok) {
-        t = dec ? (b - bound) / (-a) : (bound - b) / a;
-        if (!(t > 0.0)) t = 0.0;
-      }
-      const Key k{ok ? dbits(t) : ~0ULL, ok ? head[i] : 0x7fffffff, ok ? i : -1};
-      if (key_less(k, bi)) bi = k;
+      const bool ok = dec ? bound > -HUGE_VAL : (inc && bound < HUGE_VAL);
+      const double num = ok ? (dec ? b - bound : bound - b) : 0.0;
+      const double den = ok ? fabs(a) : 1.0;  // (b - bound) / (-a) with a < 0, (bound - b) / a with a > 0
+      double t = num / den;
+      if (!(t > 0.0)) t = 0.0;
+      const bool better = ok && (t < bt || (t == bt && hv < bvar));
+      bt = better ? t : bt;
+      bvar = better ? hv : bvar;
+      bidx = better ? i : bidx;
     }
   }
+  Key bi = bidx >= 0 ? Key{dbits(bt), bvar, bidx} : key_none();
+  PROF(13);
   bi = block_argmin_fast(bi, zSlot(l, m), 1);
+  PROF(14);
   const double lq = S->lq, uq = S->uq;
   const int fq = zAtv(l)[q];
   const double tflip = uq - lq;
@@ -551,9 +581,8 @@ __device__ __noinline__ int lz_ratio_primal(LZS *S, int q) {
     r = bi.idx;
     if (tid == 0) {
       lz_issue_row(S, r);
-      double t;
-      int newat;
-      primal_ratio_row(colN[r], dir, 0, beta[r], lbB[r], ubB[r], t, newat);
+      // the leaving variable goes to the bound it runs into (as primal_ratio_row, phase 2)
+      const int newat = (dir > 0 ? colN[r] : -colN[r]) < 0.0 ? MVB_AT_LB : MVB_AT_UB;
       const double delta = dir > 0 ? tmin : -tmin;
       S->newat = newat;
       S->delta = delta;
@@ -657,18 +686,23 @@ __device__ __noinline__ void lz_dual_finish(LZS *S, int r, int q) {
 //   beta'_i = i == r ? newbr : fma(T_iq, delta, beta_i)
 //   d'_j    = fma(d_q, rho_j, j == q ? 0 : d_j)           (row 0 of the update)
 //   basis swap incl. the per-row bounds and the non-basic flag
-__device__ __noinline__ void lz_apply(LZS *S) {
+// np, r, q come in registers: with vectors_done there is no barrier between the callers'
+// last one and thread 0 advancing S->np below
+__device__ __noinline__ void lz_apply(LZS *S, int np, int r, int q, int vectors_done) {
   const Lay l = S->lay;
-  const int m = S->m, ld = S->ld, np = S->np, r = S->r, q = S->q, tid = threadIdx.x, NT = blockDim.x;
-  const double delta = S->delta, newbr = S->newbr;
-  const double *colN = zCol(l, np), *rhoN = zRho(l, np);
-  double *beta = zBeta(l), *d = zD(l);
-  for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
-  if (r) {
-    const double dq = colN[0];
-    for (int j = tid; j < ld; j += NT) d[j] = fma(dq, rhoN[j], j == q ? 0.0 : d[j]);
+  const int m = S->m, ld = S->ld, tid = threadIdx.x, NT = blockDim.x;
+  if (!vectors_done) {  // bound flips and the dual loop; a primal pivot did this inside lz_row
+    const double delta = S->delta, newbr = S->newbr;
+    const double *colN = zCol(l, np), *rhoN = zRho(l, np);
+    double *beta = zBeta(l), *d = zD(l);
+    for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
+    if (r) {
+      const double dq = colN[0];
+      for (int j = tid; j < ld; j += NT) d[j] = fma(dq, rhoN[j], j == q ? 0.0 : d[j]);
+    }
+    __syncthreads();  // everyone has read the step out of S
   }
-  __syncthreads();  // everyone has read the step out of S
+  PROF(15);
   if (tid == 32) {  // basis swap (one warp) ...
     int *nbv = zNbv(l), *atv = zAtv(l), *head = zHead(l), *pend = zPend(l, m);
     double *lbB = zLbB(l), *ubB = zUbB(l);
@@ -761,13 +795,15 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
 
   int status;
   while (true) {
+    int vectors_done = 0, r, q;
+    const int np = S->np;
     if (mode == MVB_MODE_DUAL) {
-      const int r = lz_dual_select(S);
+      r = lz_dual_select(S);
       if (r < 0) { status = r == -1 ? MVB_OPT : MVB_ITLIM; break; }
       PROF(0);
       lz_row(S, r, 0, 0);
       PROF(1);
-      const int q = lz_dual_ratio(S, r);
+      q = lz_dual_ratio(S, r);
       if (q < 0) { status = MVB_NOFEAS; break; }
       PROF(2);
       lz_col(S, q);
@@ -775,19 +811,20 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
       lz_dual_finish(S, r, q);
       PROF(4);
     } else {
-      const int q = lz_price(S);
+      q = lz_price(S);
       if (q < 0) { status = MVB_OPT; break; }
       if (S->ty.iters >= S->max_iters) { status = MVB_ITLIM; break; }
       PROF(0);
       lz_col(S, q);
       PROF(1);
-      const int r = lz_ratio_primal(S, q);
+      r = lz_ratio_primal(S, q);
       if (r < 0) { status = MVB_UNBND; break; }
       PROF(2);
-      if (r > 0) lz_row(S, r, q, 1);
+      if (r > 0) lz_row(S, r, q, 2);
       PROF(3);
+      vectors_done = r > 0;
     }
-    lz_apply(S);
+    lz_apply(S, np, r, q, vectors_done);
     PROF(5);
     if (S->np == K) lz_flush(S);
   }
