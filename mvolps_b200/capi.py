@@ -209,6 +209,9 @@ def load_library(path):
 
 def load_product():
     """The CUDA engine.  No fallback: a missing extension is an error."""
+    alt = os.environ.get("MVOLPS_LIB")  # A/B timing of another BUILD of the same CUDA library
+    if alt:
+        return load_library(alt)
     if not os.path.exists(PRODUCT_LIB):
         raise RuntimeError(
             f"{PRODUCT_LIB} is missing: build it with `python __graft_entry__.py` "

@@ -1192,10 +1192,10 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   G = std::max(1, std::min(G, max_ctas));
   int ngroups = std::max(1, std::min(count, max_ctas / G));
   if (psk) {
-    // pending-update depth: 4 is the measured sweet spot while the tableaux stay in L2
+    // pending-update depth: 5 is the measured sweet spot while the tableaux stay in L2
     // (flush passes are cheap, deeper chains cost decisions); a wide batch of one-CTA LPs
     // streams its tableaux from HBM, where halving the flush traffic wins (depth 8)
-    const int cap = g_ctx.force_k > 0 ? g_ctx.force_k : (G == 1 && tot_bytes > ((size_t)96 << 20)) ? 8 : 4;
+    const int cap = g_ctx.force_k > 0 ? g_ctx.force_k : (G == 1 && tot_bytes > ((size_t)96 << 20)) ? 8 : 5;
     for (int k = 0; k < count; k++) {
       mvb_lp *lp = lps[idx[k]];
       const int K = std::min(lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn), cap);

@@ -499,7 +499,7 @@ __device__ __noinline__ int lz_price(LZS *S) {
       const double s = __hiloint2double((int)(((unsigned)__double2hiint(dj) & keep) ^ flip), __double2loint(dj));
       const bool elig = f != MVB_AT_FX && s > MVB_TOL_DJ;
       const double sc = bland ? 1.0 : s;
-      const bool better = elig && (sc > best || (sc == best && v < bvar));
+      const bool better = elig & ((sc > best) | ((sc == best) & (v < bvar)));  // no short circuit: no branches
       best = better ? sc : best;
       bj = better ? jj : bj;
       bvar = better ? v : bvar;
@@ -550,11 +550,16 @@ __device__ __noinline__ int lz_ratio_primal(LZS *S, int q) {
       const bool dec = a < -MVB_TOL_PIV, inc = a > MVB_TOL_PIV;
       const double bound = dec ? lo : up;
       const bool ok = dec ? bound > -HUGE_VAL : (inc && bound < HUGE_VAL);
-      const double num = ok ? (dec ? b - bound : bound - b) : 0.0;
-      const double den = ok ? fabs(a) : 1.0;  // (b - bound) / (-a) with a < 0, (bound - b) / a with a > 0
+      // (b - bound) / (-a) with a < 0, (bound - b) / a with a > 0.  A zero numerator (degenerate
+      // row) or a row that does not block divides 1/1 instead: 0/x would take the slow path
+      // of the division sequence, and the quotient is forced to 0 below anyway
+      const double num0 = dec ? b - bound : bound - b;
+      const bool live = ok & (num0 != 0.0);
+      const double num = live ? num0 : 1.0;
+      const double den = live ? fabs(a) : 1.0;
       double t = num / den;
-      if (!(t > 0.0)) t = 0.0;
-      const bool better = ok && (t < bt || (t == bt && hv < bvar));
+      if (!live | !(t > 0.0)) t = 0.0;
+      const bool better = ok & ((t < bt) | ((t == bt) & (hv < bvar)));  // no short circuit: no branches
       bt = better ? t : bt;
       bvar = better ? hv : bvar;
       bidx = better ? i : bidx;
@@ -599,6 +604,175 @@ __device__ __noinline__ int lz_ratio_primal(LZS *S, int q) {
 }  // namespace
 
 namespace {
+
+// One primal iteration after pricing chose q, fused so that nothing but the
+// two argmin barriers and one closing barrier separates the phases:
+//   pivot column: rows 1..m gathered from the stale buffer + pending updates
+//   (row 0 is the private d_q), the ratio test runs on the rows a thread just
+//   derived; block argmin (its barrier also publishes the column); then for a
+//   pivot every thread derives the step itself (no broadcast through S):
+//   beta update and basis swap while the TMA row is in flight, row derive +
+//   scale + reduced-cost update in one pass, tally by thread 0.
+// Returns r > 0 (pivot done), 0 (bound flip: S holds the step, lz_apply
+// finishes it) or -1 (unbounded).
+__device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
+  const Lay l = S->lay;
+  const int m = S->m, ld = S->ld, tid = threadIdx.x, NT = blockDim.x;
+  lz_need_tableau(S);
+  PROF(12);
+  const double *T = S->T[S->cT] + q;
+  const size_t lds = (size_t)ld;
+  const int *pend = zPend(l, m);
+  double *colN = zCol(l, np), *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l);
+  int *head = zHead(l);
+  const double dq = zD(l)[q];  // row 0 of the current tableau is the private reduced-cost vector
+  const int dir = dq < 0.0 ? 1 : -1;
+  const int fq = zAtv(l)[q];
+  if (tid == 0) {
+    const int kq = zNbv(l)[q];
+    S->lq = ldcg(S->lb + kq);
+    S->uq = ldcg(S->ub + kq);
+    colN[0] = dq;
+  }
+  double bt = HUGE_VAL;
+  int bvar = 0x7fffffff, bidx = -1;
+  constexpr int NU = 2;  // rows per thread and pass, all computed unconditionally
+  for (int i0 = 1 + tid; i0 <= m; i0 += NU * NT) {
+    int ii[NU];
+    double v[NU];
+#pragma unroll
+    for (int u = 0; u < NU; u++) {
+      ii[u] = min(i0 + u * NT, m);  // clamped: out-of-range lanes redo row m
+      v[u] = ldcg(T + (size_t)ii[u] * lds);
+    }
+    for (int p = 0; p < np; p++) {
+      const double rq = zRho(l, p)[q];
+      const int prp = pend[2 * p];
+      const bool isq = pend[2 * p + 1] == q;
+      const double *cp = zCol(l, p);
+#pragma unroll
+      for (int u = 0; u < NU; u++) v[u] = lz_step(v[u], ii[u] == prp, isq, cp[ii[u]], rq);
+    }
+#pragma unroll
+    for (int u = 0; u < NU; u++) {
+      const int i = ii[u];
+      if (i0 + u * NT <= m) colN[i] = v[u];
+      // ratio test of row i (branch-free primal_ratio_row, phase 2), as lz_ratio_primal
+      const double b = beta[i], lo = lbB[i], up = ubB[i];
+      const int hv = head[i];
+      const double a = dir > 0 ? v[u] : -v[u];
+      const bool dec = a < -MVB_TOL_PIV, inc = a > MVB_TOL_PIV;
+      const double bound = dec ? lo : up;
+      const bool ok = dec ? bound > -HUGE_VAL : (inc && bound < HUGE_VAL);
+      const double num0 = dec ? b - bound : bound - b;
+      const bool live = ok & (num0 != 0.0);
+      const double num = live ? num0 : 1.0;
+      const double den = live ? fabs(a) : 1.0;
+      double t = num / den;
+      if (!live | !(t > 0.0)) t = 0.0;
+      const bool better = ok & ((t < bt) | ((t == bt) & (hv < bvar)));
+      bt = better ? t : bt;
+      bvar = better ? hv : bvar;
+      bidx = better ? i : bidx;
+    }
+  }
+  PROF(1);
+  Key bi = bidx >= 0 ? Key{dbits(bt), bvar, bidx} : key_none();
+  bi = block_argmin_fast(bi, zSlot(l, m), 1);  // the barrier inside also publishes colN, lq, uq
+  PROF(14);
+  const double lq = S->lq, uq = S->uq;
+  const double tflip = uq - lq;
+  const double tmin = bi.idx >= 0 ? __longlong_as_double((long long)bi.k) : HUGE_VAL;
+  if (tflip <= tmin) {
+    if (!(tflip < HUGE_VAL)) return -1;
+    if (tid == 0) {  // bound flip, no basis change
+      S->delta = dir > 0 ? tflip : -tflip;
+      S->newat = fq == MVB_AT_LB ? MVB_AT_UB : MVB_AT_LB;
+      S->degenerate = 0;
+      S->r = 0;
+      S->q = q;
+    }
+    __syncthreads();
+    return 0;
+  }
+  const int r = bi.idx;
+  if (tid == 0) lz_issue_row(S, r);
+  // the step, derived by every thread from the published column
+  const double colr = colN[r];
+  const double inv = 1.0 / colr;
+  const double delta = dir > 0 ? tmin : -tmin;
+  const double newbr = nb_value(fq, lq, uq) + delta;
+  for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
+  if (tid == 32) {  // basis swap incl. the per-row bounds and the non-basic flag
+    int *nbv = zNbv(l), *atv = zAtv(l), *pd = zPend(l, m);
+    // the leaving variable goes to the bound it runs into (as primal_ratio_row, phase 2)
+    const int newat = (dir > 0 ? colr : -colr) < 0.0 ? MVB_AT_LB : MVB_AT_UB;
+    const int kin = nbv[q], kout = head[r];
+    const double lo = lbB[r], uo = ubB[r];
+    head[r] = kin;
+    lbB[r] = lq;
+    ubB[r] = uq;
+    nbv[q] = kout;
+    atv[q] = lo == uo ? MVB_AT_FX : newat;
+    pd[2 * np] = r;
+    pd[2 * np + 1] = q;
+  }
+  if (tid == 0) {  // bookkeeping (as tally_iter)
+    const bool bland = S->degen >= MVB_BLAND_AFTER;
+    Tally &t = S->ty;
+    unsigned long long h = t.hash;
+    h = (h ^ (unsigned long long)S->mode) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)r) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)q) * MVB_FNV_PRIME;
+    t.hash = h;
+    if (S->g == 0 && S->pivlog && t.iters < S->pivlog_cap) {
+      S->pivlog[2 * t.iters] = r;
+      S->pivlog[2 * t.iters + 1] = q;
+    }
+    t.iters++;
+    t.pivots++;
+    t.it2++;
+    if (bland) t.bland++;
+    S->degen = tmin == 0.0 ? S->degen + 1 : 0;
+    S->r = r;
+    S->q = q;
+    S->np = np + 1;
+  }
+  PROF(2);
+  mbar_wait(zMbar(l, m), S->mphase);
+  PROF(7);
+  constexpr int JU = 4;  // columns per thread and pass, all computed unconditionally
+  double *buf = zRho(l, np), *d = zD(l);
+  for (int j0 = tid; j0 < ld; j0 += JU * NT) {
+    int jj[JU];
+    double v[JU];
+#pragma unroll
+    for (int u = 0; u < JU; u++) {
+      jj[u] = min(j0 + u * NT, ld - 1);
+      v[u] = buf[jj[u]];
+    }
+    for (int p = 0; p < np; p++) {
+      const double cr = zCol(l, p)[r];
+      const bool isr = pend[2 * p] == r;
+      const int pqp = pend[2 * p + 1];
+      const double *rp = zRho(l, p);
+#pragma unroll
+      for (int u = 0; u < JU; u++) v[u] = lz_step(v[u], isr, jj[u] == pqp, cr, rp[jj[u]]);
+    }
+#pragma unroll
+    for (int u = 0; u < JU; u++) {
+      const double rho = jj[u] == q ? inv : -(v[u] * inv);
+      if (j0 + u * NT < ld) {
+        buf[jj[u]] = rho;
+        d[jj[u]] = fma(dq, rho, jj[u] == q ? 0.0 : d[jj[u]]);
+      }
+    }
+  }
+  __syncthreads();
+  if (tid == 0) S->mphase ^= 1;
+  PROF(3);
+  return r;
+}
 
 // K5a leaving row of the dual simplex: largest bound violation, lowest
 // variable id on ties.  Returns r >= 1 (its row load is issued), -1 when the
@@ -815,14 +989,12 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
       if (q < 0) { status = MVB_OPT; break; }
       if (S->ty.iters >= S->max_iters) { status = MVB_ITLIM; break; }
       PROF(0);
-      lz_col(S, q);
-      PROF(1);
-      r = lz_ratio_primal(S, q);
+      r = lz_primal_iter(S, q, np);
       if (r < 0) { status = MVB_UNBND; break; }
-      PROF(2);
-      if (r > 0) lz_row(S, r, q, 2);
-      PROF(3);
-      vectors_done = r > 0;
+      if (r > 0) {  // pivot: the private state is already updated
+        if (S->np == K) lz_flush(S);
+        continue;
+      }
     }
     lz_apply(S, np, r, q, vectors_done);
     PROF(5);
