@@ -613,9 +613,17 @@ namespace {
 //   pivot every thread derives the step itself (no broadcast through S):
 //   beta update and basis swap while the TMA row is in flight, row derive +
 //   scale + reduced-cost update in one pass, tally by thread 0.
-// Returns r > 0 (pivot done), 0 (bound flip: S holds the step, lz_apply
-// finishes it) or -1 (unbounded).
-__device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
+//   The same pass prices the NEXT iteration on the fresh reduced costs (rule of
+//   lz_price), so its argmin barrier is also the closing barrier: two barriers
+//   per pivot.
+// Returns r in the low word: r > 0 (pivot done; high word = next entering
+// position or -1), 0 (bound flip: S holds the step, lz_apply finishes it) or
+// -1 (unbounded).
+constexpr int LZ_FXBIT = 0x40000000;  // ratio-test payload: the leaving variable is a fixed one
+__device__ __forceinline__ long long lz_pack(int r, int qn) {
+  return (long long)(((unsigned long long)(unsigned)qn << 32) | (unsigned)r);
+}
+__device__ __noinline__ long long lz_primal_iter(LZS *S, int q, int np) {
   const Lay l = S->lay;
   const int m = S->m, ld = S->ld, tid = threadIdx.x, NT = blockDim.x;
   lz_need_tableau(S);
@@ -628,6 +636,7 @@ __device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
   const double dq = zD(l)[q];  // row 0 of the current tableau is the private reduced-cost vector
   const int dir = dq < 0.0 ? 1 : -1;
   const int fq = zAtv(l)[q];
+  const int degen0 = S->degen;
   if (tid == 0) {
     const int kq = zNbv(l)[q];
     S->lq = ldcg(S->lb + kq);
@@ -673,7 +682,7 @@ __device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
       const bool better = ok & ((t < bt) | ((t == bt) & (hv < bvar)));
       bt = better ? t : bt;
       bvar = better ? hv : bvar;
-      bidx = better ? i : bidx;
+      bidx = better ? (lo == up ? i | LZ_FXBIT : i) : bidx;
     }
   }
   PROF(1);
@@ -684,7 +693,7 @@ __device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
   const double tflip = uq - lq;
   const double tmin = bi.idx >= 0 ? __longlong_as_double((long long)bi.k) : HUGE_VAL;
   if (tflip <= tmin) {
-    if (!(tflip < HUGE_VAL)) return -1;
+    if (!(tflip < HUGE_VAL)) return lz_pack(-1, -1);
     if (tid == 0) {  // bound flip, no basis change
       S->delta = dir > 0 ? tflip : -tflip;
       S->newat = fq == MVB_AT_LB ? MVB_AT_UB : MVB_AT_LB;
@@ -693,9 +702,13 @@ __device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
       S->q = q;
     }
     __syncthreads();
-    return 0;
+    return lz_pack(0, -1);
   }
-  const int r = bi.idx;
+  // payload of the winner: row, the variable basic there, whether that variable is fixed
+  const int r = bi.idx & (LZ_FXBIT - 1), kout = bi.var;
+  // the leaving variable goes to the bound it runs into (as primal_ratio_row, phase 2)
+  const int atq = (bi.idx & LZ_FXBIT) ? MVB_AT_FX
+                                      : ((dir > 0 ? colN[r] : -colN[r]) < 0.0 ? MVB_AT_LB : MVB_AT_UB);
   if (tid == 0) lz_issue_row(S, r);
   // the step, derived by every thread from the published column
   const double colr = colN[r];
@@ -705,15 +718,12 @@ __device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
   for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
   if (tid == 32) {  // basis swap incl. the per-row bounds and the non-basic flag
     int *nbv = zNbv(l), *atv = zAtv(l), *pd = zPend(l, m);
-    // the leaving variable goes to the bound it runs into (as primal_ratio_row, phase 2)
-    const int newat = (dir > 0 ? colr : -colr) < 0.0 ? MVB_AT_LB : MVB_AT_UB;
-    const int kin = nbv[q], kout = head[r];
-    const double lo = lbB[r], uo = ubB[r];
+    const int kin = nbv[q];
     head[r] = kin;
     lbB[r] = lq;
     ubB[r] = uq;
     nbv[q] = kout;
-    atv[q] = lo == uo ? MVB_AT_FX : newat;
+    atv[q] = atq;
     pd[2 * np] = r;
     pd[2 * np + 1] = q;
   }
@@ -743,6 +753,10 @@ __device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
   PROF(7);
   constexpr int JU = 4;  // columns per thread and pass, all computed unconditionally
   double *buf = zRho(l, np), *d = zD(l);
+  const int *atv = zAtv(l), *nbv = zNbv(l);
+  const bool bland = (tmin == 0.0 ? degen0 + 1 : 0) >= MVB_BLAND_AFTER;
+  double best = 0.0;  // next pricing: eligible scores exceed MVB_TOL_DJ > 0
+  int bj = -1, bv = 0x7fffffff;
   for (int j0 = tid; j0 < ld; j0 += JU * NT) {
     int jj[JU];
     double v[JU];
@@ -761,17 +775,35 @@ __device__ __noinline__ int lz_primal_iter(LZS *S, int q, int np) {
     }
 #pragma unroll
     for (int u = 0; u < JU; u++) {
-      const double rho = jj[u] == q ? inv : -(v[u] * inv);
-      if (j0 + u * NT < ld) {
-        buf[jj[u]] = rho;
-        d[jj[u]] = fma(dq, rho, jj[u] == q ? 0.0 : d[jj[u]]);
+      const int j = jj[u];
+      const bool isq = j == q;
+      const double rho = isq ? inv : -(v[u] * inv);
+      const double dn = fma(dq, rho, isq ? 0.0 : d[j]);
+      const bool mine = j0 + u * NT < ld;  // clamped repeats may see d[j] already updated: not priced
+      if (mine) {
+        buf[j] = rho;
+        d[j] = dn;
       }
+      // price column j for the next iteration; position q now holds the leaving variable
+      // (the swap by thread 32 is not ordered with this read, so it comes from registers)
+      const int f = isq ? atq : atv[j], var = isq ? kout : nbv[j];
+      const unsigned flip = f == MVB_AT_LB ? 0x80000000u : 0u;
+      const unsigned keep = f == MVB_AT_FR ? 0x7fffffffu : 0xffffffffu;
+      const double sv = __hiloint2double((int)(((unsigned)__double2hiint(dn) & keep) ^ flip), __double2loint(dn));
+      const bool elig = mine & (f != MVB_AT_FX) & (sv > MVB_TOL_DJ);
+      const double sc = bland ? 1.0 : sv;
+      const bool better = elig & ((sc > best) | ((sc == best) & (var < bv)));
+      best = better ? sc : best;
+      bj = better ? j : bj;
+      bv = better ? var : bv;
     }
   }
-  __syncthreads();
-  if (tid == 0) S->mphase ^= 1;
   PROF(3);
-  return r;
+  Key bq = bj >= 0 ? Key{bland ? 0ULL : ~dbits(best), bv, bj} : key_none();
+  bq = block_argmin_fast(bq, zSlot(l, m), 0);  // also the closing barrier of the iteration
+  if (tid == 0) S->mphase ^= 1;
+  PROF(4);
+  return lz_pack(r, bq.idx);
 }
 
 // K5a leaving row of the dual simplex: largest bound violation, lowest
@@ -968,6 +1000,7 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
   __syncthreads();
 
   int status;
+  int qnext = -2;  // -2: not priced yet (first iteration, after a bound flip)
   while (true) {
     int vectors_done = 0, r, q;
     const int np = S->np;
@@ -985,13 +1018,16 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
       lz_dual_finish(S, r, q);
       PROF(4);
     } else {
-      q = lz_price(S);
+      q = qnext != -2 ? qnext : lz_price(S);
+      qnext = -2;
       if (q < 0) { status = MVB_OPT; break; }
       if (S->ty.iters >= S->max_iters) { status = MVB_ITLIM; break; }
       PROF(0);
-      r = lz_primal_iter(S, q, np);
+      const long long rq = lz_primal_iter(S, q, np);
+      r = (int)(unsigned)rq;
       if (r < 0) { status = MVB_UNBND; break; }
-      if (r > 0) {  // pivot: the private state is already updated
+      if (r > 0) {  // pivot: the private state is updated and the next column priced
+        qnext = (int)(rq >> 32);
         if (S->np == K) lz_flush(S);
         continue;
       }

@@ -19,11 +19,11 @@ r = t.solve(max_iters=3000, ctas_per_lp=G)
 L.mvb_debug_prof(buf.ctypes.data, 0)
 ms = L.mvb_last_kernel_ms()
 p = buf.reshape(256, 16)
-names = ["price(+wait)", "col fetch+derive", "ratio:tail", "row derive", "-", "apply:swap", "flush+arrive", "row:tma wait"]
+names = ["price:argmin tail", "iter:col gather+ratio loop", "iter:step+beta+swap", "iter:row derive+d", "-", "apply(flip)", "flush+arrive", "iter:tma wait"]
 print(f"m={m} n={n} pivots={r['pivots']} kernel {ms:.3f} ms -> {1e3*ms/r['iters']:.2f} us/iter")
 used = p[:, 0] > 0
 print("ctas", used.sum())
-names += ["price:loop", "price:warp1", "price:sync", "price:warp2", "col:barrier wait", "ratio:loop", "ratio:argmin", "apply:loops"]
+names += ["price:loop", "price:warp1", "price:sync", "price:warp2", "iter:group barrier wait", "-", "iter:ratio argmin", "-"]
 for i, nm in enumerate(names):
     c = p[used, i] / r["iters"]
     print(f"{nm:12s} mean {c.mean():8.0f} clk  min {c.min():8.0f}  max {c.max():8.0f}   ({c.mean()/1965:.2f} us)")
