@@ -36,8 +36,8 @@ M, N_COLS, SEED = 1024, 2048, 1234
 ORACLE_LIB = os.path.join(ROOT, "oracle", "_build", "libglpk_oracle.so")
 METRIC = "simplex_pivots_per_sec"
 # DRAM traffic of the timed launch (one full configs[1] solve), from the ncu capture of this very
-# command committed as profiles/r1c_bench_ps_summary.txt: 17.10 MB read + 3.75 MB written
-NCU_DRAM_BYTES_PER_LAUNCH = 17098240 + 3754240
+# command committed as profiles/r1d_bench_ps_summary.txt: 17.55 MB read + 3.98 MB written
+NCU_DRAM_BYTES_PER_LAUNCH = 17550848 + 3976704
 
 
 def peaks():
@@ -249,7 +249,7 @@ def main():
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_PER_LAUNCH, "peak_source": peak_src,
                      "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full, "
-                                       "profiles/r1c_bench_ps_summary.txt (the tableau stays in L2; the algorithmic "
+                                       "profiles/r1d_bench_ps_summary.txt (the tableau stays in L2; the algorithmic "
                                        "bytes per launch are 16*R*C*pivots = 450 GB)",
                      "kernel": "simplex_ps_kernel (one cooperative launch = whole solve; lazy rank-1 updates, K pivots per tableau pass)",
                      "algorithmic_bytes_per_pivot": 16 * (M + 1) * (N_COLS + 1),

@@ -268,6 +268,7 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
   const unsigned nunits = (unsigned)nch * (unsigned)R;  // < 2^31 (checked on the host)
   unsigned u0 = (unsigned)((unsigned long long)nunits * (unsigned)g / (unsigned)G);
   const unsigned u1 = (unsigned)((unsigned long long)nunits * (unsigned)(g + 1) / (unsigned)G);
+  // rows in flight per thread: measured flat between 2 and 4 at K = 5, 6 and 8 spill (tools/ab.sh)
   constexpr int UN = KC <= 4 ? 8 : 4;
   while (u0 < u1) {
     const int ch = (int)(u0 / (unsigned)R);
