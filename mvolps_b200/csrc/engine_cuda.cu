@@ -716,6 +716,8 @@ struct DeviceCtx {
   size_t max_dyn = 0;      // dynamic shared memory simplex_kernel may ask for
   bool no_ps = false;      // MVOLPS_NO_PS=1: general loop only (debugging / A-B timing)
   int force_k = 0;         // MVOLPS_LZ_K=k: cap the pending-update depth (A-B timing)
+  int force_nt = 0;        // MVOLPS_PS_NT=t: CTA width for launches with more LPs than SMs (A-B timing)
+  int last_nt = 0;
 };
 DeviceCtx g_ctx;
 
@@ -756,6 +758,8 @@ bool ctx_init(int device) {
   g_ctx.no_ps = nops && nops[0] == '1';
   const char *fk = getenv("MVOLPS_LZ_K");
   g_ctx.force_k = fk ? atoi(fk) : 0;
+  const char *fnt = getenv("MVOLPS_PS_NT");
+  g_ctx.force_nt = fnt ? atoi(fnt) : 0;
   int per_sm = 0;
   CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_kernel, g_ctx.nt, 0));
   if (per_sm < 1) return fail("simplex_kernel does not fit an SM");
@@ -1183,7 +1187,27 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
     max_bytes = std::max(max_bytes, (size_t)(lp->m + 1) * lp->ld * sizeof(double));
     tot_bytes += 2 * (size_t)(lp->m + 1) * lp->ld * sizeof(double);
   }
-  const int max_ctas = psk ? g_ctx.max_ctas_ps : g_ctx.max_ctas;
+  int max_ctas = psk ? g_ctx.max_ctas_ps : g_ctx.max_ctas;
+  int nt = psk ? g_ctx.nt_ps : g_ctx.nt;
+  if (psk && count > g_ctx.sms && !(opts && opts->ctas_per_lp > 0)) {
+    // more small LPs than SMs (a B&B round): narrower CTAs, several resident per SM, so more
+    // LPs are in flight; the vectors of one LP do not fill 512 threads anyway
+    int span = 0;
+    for (int k = 0; k < count; k++) span = std::max(span, std::max(lps[idx[k]]->ld, lps[idx[k]]->m + 1));
+    const int want = g_ctx.force_nt > 0 ? g_ctx.force_nt : span <= 256 ? 128 : span <= 512 ? 256 : nt;
+    if (want < nt) {
+      size_t dyn_max = 0;
+      for (int k = 0; k < count; k++)
+        dyn_max = std::max(dyn_max, lz_smem_bytes(lps[idx[k]]->m, lps[idx[k]]->ld,
+                                                  std::min(lz_pick_k(lps[idx[k]]->m, lps[idx[k]]->ld, g_ctx.max_dyn), 8)));
+      int per_sm = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_ps_kernel, want, dyn_max));
+      if (per_sm > 1) {
+        nt = want;
+        max_ctas = per_sm * g_ctx.sms;
+      }
+    }
+  }
   // CTAs per LP: by tableau size, bounded by what is co-resident
   const size_t per_cta = psk ? (96 << 10) : (128 << 10);
   int G = (opts && opts->ctas_per_lp > 0) ? opts->ctas_per_lp
@@ -1260,10 +1284,11 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   if (!g_ctx.kev[0]) { CK(cudaEventCreate(&g_ctx.kev[0])); CK(cudaEventCreate(&g_ctx.kev[1])); }
   CK(cudaEventRecord(g_ctx.kev[0], st));
   CK(cudaLaunchCooperativeKernel(psk ? (const void *)simplex_ps_kernel : (const void *)simplex_kernel,
-                                 dim3(ngroups * G), dim3(psk ? g_ctx.nt_ps : g_ctx.nt), args, dyn, st));
+                                 dim3(ngroups * G), dim3(nt), args, dyn, st));
   CK(cudaEventRecord(g_ctx.kev[1], st));
   g_launches++;
   g_ctx.last_G = G;
+  g_ctx.last_nt = nt;
   g_ctx.last_groups = ngroups;
   g_ctx.last_ps = psk;
   CK(cudaMemcpyAsync(g_ctx.h_out, g_ctx.d_out, otot, cudaMemcpyDeviceToHost, st));
@@ -1438,7 +1463,7 @@ int mvb_flush_l2(void) {
 int mvb_last_launch(int *c, int *g, int *t) {
   if (c) *c = g_ctx.last_G;
   if (g) *g = g_ctx.last_groups;
-  if (t) *t = g_ctx.last_ps ? g_ctx.nt_ps : g_ctx.nt;
+  if (t) *t = g_ctx.last_nt;
   return 0;
 }
 
