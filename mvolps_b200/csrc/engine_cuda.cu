@@ -1199,7 +1199,7 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
       size_t dyn_max = 0;
       for (int k = 0; k < count; k++)
         dyn_max = std::max(dyn_max, lz_smem_bytes(lps[idx[k]]->m, lps[idx[k]]->ld,
-                                                  std::min(lz_pick_k(lps[idx[k]]->m, lps[idx[k]]->ld, g_ctx.max_dyn), 8)));
+                                                  std::min(lz_pick_k(lps[idx[k]]->m, lps[idx[k]]->ld, g_ctx.max_dyn), LZ_KMAX)));
       int per_sm = 0;
       CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_ps_kernel, want, dyn_max));
       if (per_sm > 1) {
@@ -1219,11 +1219,13 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
     // pending-update depth: 5 is the measured sweet spot while the tableaux stay in L2
     // (flush passes are cheap, deeper chains cost decisions); a wide batch of one-CTA LPs
     // streams its tableaux from HBM, where halving the flush traffic wins (depth 8)
-    const int cap = g_ctx.force_k > 0 ? g_ctx.force_k : (G == 1 && tot_bytes > ((size_t)96 << 20)) ? 8 : 5;
+    const bool streams = tot_bytes > ((size_t)96 << 20);  // the launch's tableaux do not stay in L2
+    const int cap = g_ctx.force_k > 0 ? g_ctx.force_k : (G == 1 && streams) ? LZ_KMAX : 5;
     for (int k = 0; k < count; k++) {
       mvb_lp *lp = lps[idx[k]];
       const int K = std::min(lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn), cap);
       h[k].lzK = K;
+
       dyn = std::max(dyn, lz_smem_bytes(lp->m, lp->ld, K));
     }
   }

@@ -25,7 +25,7 @@
 namespace {
 
 constexpr int PS_CREG = 8;            // pivot-column values a thread can hold in flight
-constexpr int LZ_KMAX = 8;            // most pending pivots between two flush passes
+constexpr int LZ_KMAX = 8;            // most pending pivots between two flush passes (12 measured: no gain)
 constexpr int MVB_PS_FALLBACK = 100;  // DevResult status: needs the general kernel
 
 
@@ -150,7 +150,7 @@ __host__ __device__ inline unsigned lz_nv(int ld) { return (unsigned)ld * 8u; }
 __host__ __device__ inline unsigned lz_mv(int m) { return ((unsigned)(m + 2) * 8u + 15u) & ~15u; }
 __host__ __device__ inline size_t lz_smem_bytes(int m, int ld, int K) {
   return (size_t)lz_nv(ld) * (K + 2) + (size_t)lz_mv(m) * (K + 4) + (size_t)(m + 2) * 4 + 16 +
-         sizeof(Key) * 64 + 64;
+         sizeof(Key) * 64 + 16 /* mbarrier */ + 8 * LZ_KMAX /* (row, column) of the pending pivots */;
 }
 // largest K <= LZ_KMAX that fits `avail` bytes (0: does not fit at all)
 __host__ __device__ inline int lz_pick_k(int m, int ld, size_t avail) {
@@ -268,7 +268,9 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
   const unsigned nunits = (unsigned)nch * (unsigned)R;  // < 2^31 (checked on the host)
   unsigned u0 = (unsigned)((unsigned long long)nunits * (unsigned)g / (unsigned)G);
   const unsigned u1 = (unsigned)((unsigned long long)nunits * (unsigned)(g + 1) / (unsigned)G);
-  // rows in flight per thread: measured flat between 2 and 4 at K = 5, 6 and 8 spill (tools/ab.sh)
+  // rows in flight per thread: measured flat between 2 and 4 at K = 5, 6 and 8 spill (tools/ab.sh);
+  // an L2 prefetch of the rows ahead gained 5 % on HBM-streaming batches but cost the L2-resident
+  // path 4 % (register pressure), so it is not here
   constexpr int UN = KC <= 4 ? 8 : 4;
   while (u0 < u1) {
     const int ch = (int)(u0 / (unsigned)R);
@@ -1045,7 +1047,7 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
   cT = S->cT;
   ty = S->ty;
 #ifdef MVB_PROF
-  if (tid == 0)
+  if (tid == 0 && blockIdx.x < 256)
     for (int i = 0; i < 16; i++) g_prof[blockIdx.x * 16 + i] += S->prof[i];
 #endif
   // hand the private state back (every CTA holds the same values)
