@@ -13,17 +13,22 @@ work = [tmpl[k % 16].clone() for k in range(nlp)]
 solve_batch(L, work)
 for w, k in zip(work, range(nlp)):
     w.assign(tmpl[k % 16])
-L.mvb_debug_prof.argtypes = [C.c_void_p, C.c_int]
-L.mvb_debug_prof(None, 1)
+have_prof = hasattr(L, "mvb_debug_prof")  # only in -DMVB_PROF builds; without it: timing only
+if have_prof:
+    L.mvb_debug_prof.argtypes = [C.c_void_p, C.c_int]
+    L.mvb_debug_prof(None, 1)
 res = solve_batch(L, work)
 buf = np.zeros(256 * 16, np.int64)
-L.mvb_debug_prof(buf.ctypes.data, 0)
+if have_prof:
+    L.mvb_debug_prof(buf.ctypes.data, 0)
 ms = L.mvb_last_kernel_ms()
 iters = sum(r["iters"] for r in res)
 G, groups, nt = C.c_int(), C.c_int(), C.c_int()
 L.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
 print(f"{nlp} LPs m={m} n={n}: kernel {ms:.2f} ms, {iters} iterations -> {iters / ms / 1e3:.2f} M LP-pivots/s; "
       f"G={G.value} groups={groups.value} threads={nt.value}")
+if not have_prof:
+    sys.exit(0)
 p = buf.reshape(256, 16)
 names = ["price:argmin tail", "iter:col gather+ratio loop", "iter:step+beta+swap", "iter:row derive+d+price", "iter:final argmin",
          "apply(flip)", "flush+arrive", "iter:tma wait", "price:loop", "price:warp1", "price:sync", "price:warp2",
