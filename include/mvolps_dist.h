@@ -21,7 +21,8 @@
  * (2) Open B&B nodes SHARDED across GPUs: node LPs are independent, so each
  *     rank solves its own nodes with mvb_solve_batch; the only exchange is
  *     the incumbent / bound (a max-reduction of one double per round) for
- *     which `mvb_comm::allreduce_max` is provided.
+ *     which `mvb_comm::allreduce_max` is provided.  The driver that does this
+ *     for one tree is mvb_bnb_run_dist (include/mvolps_bnb.h).
  *
  * The communicator is a small vtable so that the same host code runs over
  * NCCL (product; libnccl.so.2 is dlopen'ed, preferring the copy already loaded

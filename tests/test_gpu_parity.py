@@ -152,3 +152,77 @@ def test_full_size_dense_lp_sharded_and_properties(product):
     d = T[0]
     assert np.all(d[at == 0] >= -1e-9) and np.all(d[at == 1] <= 1e-9)     # dual feasible = optimal
     assert np.all(x[:2048] >= -1e-9) and np.all(x[2048:] <= inst["row_ub"] * (1 + 1e-9))
+
+
+def test_queued_clones_chains_and_parent_release(oracle, product):
+    """glp_copy_prob's device copy is queued and carried out by one clone_kernel in front of the next
+    device operation (util.cpp:34, bs.cpp:116): chains of clones, a parent freed before the flush
+    (its slab is parked), an assign over a queued source, and reads of a queued destination must all
+    see the bytes a synchronous copy would have produced."""
+    inst = instances.mdkp(40, 10, 31)
+    a = EngineLP.from_instance(oracle, inst)
+    b = EngineLP.from_instance(product, inst)
+    ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)
+    _assert_same(a, b, ra, rb)
+    x = a.primal()[:40]
+    j = [k for k in range(40) if x[k] != np.floor(x[k])][0]
+    Ta, _ = a.tableau()
+
+    def children(lp):
+        c1 = lp.clone()
+        c2 = c1.clone()            # clone of a queued destination: flushes the queue first
+        c3 = lp.clone()
+        c1.set_bounds(j, -np.inf, np.floor(x[j]))
+        c2.set_bounds(j, np.floor(x[j]) + 1.0, np.inf)
+        return c1, c2, c3
+
+    a1, a2, a3 = children(a)
+    b1, b2, b3 = children(b)
+    Tb3, _ = b3.tableau()          # read of a queued destination
+    assert np.array_equal(Tb3, Ta)
+    b.free()                       # parent released while b3's... (already flushed) and again below
+    b4 = b3.clone()
+    b3.free()                      # source of a queued clone released before the flush
+    Tb4, _ = b4.tableau()
+    assert np.array_equal(Tb4, Ta)
+    b5 = b4.clone()
+    b4.assign(b1)                  # overwriting the source of a queued clone: flushes first
+    Tb5, _ = b5.tableau()
+    assert np.array_equal(Tb5, Ta)
+    for lp in (a3, b5):
+        lp.set_bounds(j, -np.inf, np.floor(x[j]))
+    res_a = solve_batch(oracle, [a1, a2, a3], log_pivots=1)
+    res_b = solve_batch(product, [b1, b2, b5], log_pivots=1)
+    for p, q, r, s in zip([a1, a2, a3], [b1, b2, b5], res_a, res_b):
+        _assert_same(p, q, r, s)
+    # b4 now equals b1 before its solve: same result as a1
+    rb4 = b4.solve(log_pivots=1)
+    assert rb4["pivot_hash"] == res_a[0]["pivot_hash"] and rb4["obj"] == res_a[0]["obj"]
+
+
+def test_many_small_lps_use_narrow_ctas_and_match(oracle, product):
+    """More LPs than SMs in one launch: the engine runs 128/256-thread CTAs, several per SM
+    (launch_solve); results are those of the oracle, LP by LP."""
+    import ctypes as C
+    insts = [instances.mdkp(30 + (k % 7), 8 + (k % 5), 500 + k) for k in range(200)]
+    A = [EngineLP.from_instance(oracle, i) for i in insts]
+    B = [EngineLP.from_instance(product, i) for i in insts]
+    ra = solve_batch(oracle, A, log_pivots=1)
+    rb = solve_batch(product, B, log_pivots=1)
+    G, groups, nt = C.c_int(), C.c_int(), C.c_int()
+    product.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
+    assert G.value == 1 and nt.value == 128 and groups.value > 148
+    for a, b, x, y in zip(A, B, ra, rb):
+        _assert_same(a, b, x, y)
+    # dual warm starts through the same launch shape
+    for a, b in zip(A, B):
+        xa = a.primal()
+        n = a.n
+        frac = [k for k in range(n) if xa[k] != np.floor(xa[k])]
+        if frac:
+            for lp in (a, b):
+                lp.set_bounds(frac[0], -np.inf, np.floor(xa[frac[0]]))
+    ra = solve_batch(oracle, A, log_pivots=1)
+    rb = solve_batch(product, B, log_pivots=1)
+    for a, b, x, y in zip(A, B, ra, rb):
+        _assert_same(a, b, x, y)
