@@ -19,6 +19,12 @@
 // eager kernel becomes one barrier per K pivots.
 // The pivot row travels global->shared by cp.async.bulk (TMA, mbarrier
 // completion); the pivot column is a strided 8-byte gather (ld.global.cg).
+// One iteration is ONE fused function with two block barriers (the two argmin
+// reductions): lz_primal_iter (column + K2 ratio test | step, row, reduced
+// costs, K1 pricing of the next iteration) and lz_dual_iter (row + K5b ratio
+// test | column, step, K5a selection of the next leaving row).  Values a later
+// phase needs travel in registers or in the argmin payload, never through a
+// shared location another thread may already be overwriting.
 // Phase 1 is not implemented here: such LPs are handed to simplex_kernel.
 #pragma once
 
@@ -369,112 +375,10 @@ __device__ __forceinline__ void lz_need_tableau(LZS *S) {
 
 namespace {
 
-// column q of the CURRENT tableau (rows 0..m) into col slot np: strided gather
-// from the stale buffer, then the pending updates in order.  Also fetches the
-// bounds of the variable at position q (S->lq, S->uq).
-__device__ __noinline__ void lz_col(LZS *S, int q) {
-  const Lay l = S->lay;
-  const int m = S->m, np = S->np, tid = threadIdx.x, NT = blockDim.x;
-  lz_need_tableau(S);
-  PROF(12);
-  const double *T = S->T[S->cT] + q;
-  const size_t ld = (size_t)S->ld;
-  const int *pend = zPend(l, m);
-  double *dst = zCol(l, np);
-  constexpr int NU = 2;  // rows per thread and pass, all computed unconditionally
-  double lq = 0.0, uq = 0.0;
-  if (tid == 0) {
-    const int kq = zNbv(l)[q];
-    lq = ldcg(S->lb + kq);
-    uq = ldcg(S->ub + kq);
-    dst[0] = zD(l)[q];  // row 0 of the current tableau is the private reduced-cost vector
-  }
-  for (int i0 = 1 + tid; i0 <= m; i0 += NU * NT) {
-    int ii[NU];
-    double v[NU];
-#pragma unroll
-    for (int u = 0; u < NU; u++) {
-      ii[u] = min(i0 + u * NT, m);  // clamped: out-of-range lanes redo row m, never stored
-      v[u] = ldcg(T + (size_t)ii[u] * ld);
-    }
-    for (int p = 0; p < np; p++) {
-      const double rq = zRho(l, p)[q];
-      const int prp = pend[2 * p];
-      const bool isq = pend[2 * p + 1] == q;
-      const double *cp = zCol(l, p);
-#pragma unroll
-      for (int u = 0; u < NU; u++) v[u] = lz_step(v[u], ii[u] == prp, isq, cp[ii[u]], rq);
-    }
-#pragma unroll
-    for (int u = 0; u < NU; u++)
-      if (i0 + u * NT <= m) dst[ii[u]] = v[u];
-  }
-  if (tid == 0) {
-    S->lq = lq;
-    S->uq = uq;
-  }
-  __syncthreads();
-}
-
 // TMA fetch of row r of the stale tableau into rho slot np (thread 0)
 __device__ __forceinline__ void lz_issue_row(LZS *S, int r) {
   bulk_row_load(zRho(S->lay, S->np), S->T[S->cT] + (size_t)r * S->ld,
                 (unsigned)(S->ld * sizeof(double)), zMbar(S->lay, S->m));
-}
-
-// wait for the raw row, apply the pending updates in place and, when scale is
-// set, turn it into the scaled pivot row rho_q = inv, rho_j = -(v_j * inv).
-// scale == 2 (primal pivot: the step is already in S) also applies the
-// iteration to the private vectors, beta while the row is still in flight:
-//   beta'_i = i == r ? newbr : fma(T_iq, delta, beta_i)
-//   d'_j    = fma(d_q, rho_j, j == q ? 0 : d_j)           (row 0 of the update)
-__device__ __noinline__ void lz_row(LZS *S, int r, int q, int scale) {
-  const Lay l = S->lay;
-  const int m = S->m, ld = S->ld, np = S->np, tid = threadIdx.x, NT = blockDim.x;
-  const double inv = S->inv;
-  const int *pend = zPend(l, m);
-  const bool fuse = scale == 2;
-  double dq = 0.0;
-  if (fuse) {
-    const double delta = S->delta, newbr = S->newbr;
-    const double *colN = zCol(l, np);
-    double *beta = zBeta(l);
-    dq = colN[0];
-    for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
-  }
-  mbar_wait(zMbar(l, m), S->mphase);
-  PROF(7);
-  constexpr int JU = 4;  // columns per thread and pass, all computed unconditionally
-  double *buf = zRho(l, np), *d = zD(l);
-  for (int j0 = tid; j0 < ld; j0 += JU * NT) {
-    int jj[JU];
-    double v[JU];
-#pragma unroll
-    for (int u = 0; u < JU; u++) {
-      jj[u] = min(j0 + u * NT, ld - 1);
-      v[u] = buf[jj[u]];
-    }
-    for (int p = 0; p < np; p++) {
-      const double cr = zCol(l, p)[r];
-      const bool isr = pend[2 * p] == r;
-      const int pqp = pend[2 * p + 1];
-      const double *rp = zRho(l, p);
-#pragma unroll
-      for (int u = 0; u < JU; u++) v[u] = lz_step(v[u], isr, jj[u] == pqp, cr, rp[jj[u]]);
-    }
-    if (scale) {
-#pragma unroll
-      for (int u = 0; u < JU; u++) v[u] = jj[u] == q ? inv : -(v[u] * inv);
-    }
-#pragma unroll
-    for (int u = 0; u < JU; u++)
-      if (j0 + u * NT < ld) {
-        buf[jj[u]] = v[u];
-        if (fuse) d[jj[u]] = fma(dq, v[u], jj[u] == q ? 0.0 : d[jj[u]]);
-      }
-  }
-  __syncthreads();
-  if (tid == 0) S->mphase ^= 1;
 }
 
 // K1 pricing: largest |d_j| among eligible columns, lowest variable id on
@@ -528,85 +432,6 @@ __device__ __noinline__ int lz_price(LZS *S) {
   bq = block_argmin_fast(bq, zSlot(l, S->m), 0);
   return bq.idx;
 }
-
-// K2 ratio test over the pivot column (col slot np), lowest variable id on
-// ties.  Returns r > 0 (pivot; its row load is issued), 0 (bound flip) or -1
-// (unbounded); thread 0 records the step in S.
-__device__ __noinline__ int lz_ratio_primal(LZS *S, int q) {
-  const Lay l = S->lay;
-  const int m = S->m, tid = threadIdx.x, NT = blockDim.x;
-  const double *colN = zCol(l, S->np), *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l);
-  const int *head = zHead(l);
-  const int dir = zD(l)[q] < 0.0 ? 1 : -1;
-  // branch-free form of primal_ratio_row (phase 2): one division per row, NU rows in flight;
-  // t >= +0 so comparing the doubles is comparing their bit patterns
-  double bt = HUGE_VAL;
-  int bvar = 0x7fffffff, bidx = -1;
-  constexpr int NU = 2;
-  for (int i0 = 1 + tid; i0 <= m; i0 += NU * NT) {
-#pragma unroll
-    for (int u = 0; u < NU; u++) {
-      const int i = min(i0 + u * NT, m);
-      const double alpha = colN[i], b = beta[i], lo = lbB[i], up = ubB[i];
-      const int hv = head[i];
-      const double a = dir > 0 ? alpha : -alpha;
-      const bool dec = a < -MVB_TOL_PIV, inc = a > MVB_TOL_PIV;
-      const double bound = dec ? lo : up;
-      const bool ok = dec ? bound > -HUGE_VAL : (inc && bound < HUGE_VAL);
-      // (b - bound) / (-a) with a < 0, (bound - b) / a with a > 0.  A zero numerator (degenerate
-      // row) or a row that does not block divides 1/1 instead: 0/x would take the slow path
-      // of the division sequence, and the quotient is forced to 0 below anyway
-      const double num0 = dec ? b - bound : bound - b;
-      const bool live = ok & (num0 != 0.0);
-      const double num = live ? num0 : 1.0;
-      const double den = live ? fabs(a) : 1.0;
-      double t = num / den;
-      if (!live | !(t > 0.0)) t = 0.0;
-      const bool better = ok & ((t < bt) | ((t == bt) & (hv < bvar)));  // no short circuit: no branches
-      bt = better ? t : bt;
-      bvar = better ? hv : bvar;
-      bidx = better ? i : bidx;
-    }
-  }
-  Key bi = bidx >= 0 ? Key{dbits(bt), bvar, bidx} : key_none();
-  PROF(13);
-  bi = block_argmin_fast(bi, zSlot(l, m), 1);
-  PROF(14);
-  const double lq = S->lq, uq = S->uq;
-  const int fq = zAtv(l)[q];
-  const double tflip = uq - lq;
-  const double tmin = bi.idx >= 0 ? __longlong_as_double((long long)bi.k) : HUGE_VAL;
-  int r;
-  if (tflip <= tmin) {
-    if (!(tflip < HUGE_VAL)) return -1;
-    r = 0;  // bound flip, no basis change
-    if (tid == 0) {
-      S->delta = dir > 0 ? tflip : -tflip;
-      S->newat = fq == MVB_AT_LB ? MVB_AT_UB : MVB_AT_LB;
-      S->degenerate = 0;
-    }
-  } else {
-    r = bi.idx;
-    if (tid == 0) {
-      lz_issue_row(S, r);
-      // the leaving variable goes to the bound it runs into (as primal_ratio_row, phase 2)
-      const int newat = (dir > 0 ? colN[r] : -colN[r]) < 0.0 ? MVB_AT_LB : MVB_AT_UB;
-      const double delta = dir > 0 ? tmin : -tmin;
-      S->newat = newat;
-      S->delta = delta;
-      S->newbr = nb_value(fq, lq, uq) + delta;
-      S->degenerate = tmin == 0.0;
-      S->inv = 1.0 / colN[r];
-    }
-  }
-  if (tid == 0) { S->r = r; S->q = q; }
-  __syncthreads();
-  return r;
-}
-
-}  // namespace
-
-namespace {
 
 // One primal iteration after pricing chose q, fused so that nothing but the
 // two argmin barriers and one closing barrier separates the phases:
@@ -669,7 +494,7 @@ __device__ __noinline__ long long lz_primal_iter(LZS *S, int q, int np) {
     for (int u = 0; u < NU; u++) {
       const int i = ii[u];
       if (i0 + u * NT <= m) colN[i] = v[u];
-      // ratio test of row i (branch-free primal_ratio_row, phase 2), as lz_ratio_primal
+      // ratio test of row i (branch-free primal_ratio_row, phase 2), as the general loop
       const double b = beta[i], lo = lbB[i], up = ubB[i];
       const int hv = head[i];
       const double a = dir > 0 ? v[u] : -v[u];
@@ -812,7 +637,7 @@ __device__ __noinline__ long long lz_primal_iter(LZS *S, int q, int np) {
 // K5a leaving row of the dual simplex: largest bound violation, lowest
 // variable id on ties.  Returns r >= 1 (its row load is issued), -1 when the
 // basis is primal feasible (optimal), -2 at the iteration limit.
-__device__ __noinline__ int lz_dual_select(LZS *S) {
+__device__ __noinline__ int lz_dual_select(LZS *S, int issue) {
   const Lay l = S->lay;
   const int m = S->m, tid = threadIdx.x, NT = blockDim.x;
   const bool bland = S->degen >= MVB_BLAND_AFTER;
@@ -831,106 +656,176 @@ __device__ __noinline__ int lz_dual_select(LZS *S) {
   const int r = best.idx;
   if (r < 0) return -1;
   if (S->ty.iters >= S->max_iters) return -2;
-  lz_need_tableau(S);
-  if (tid == 0) lz_issue_row(S, r);
+  if (issue) {
+    lz_need_tableau(S);
+    if (tid == 0) lz_issue_row(S, r);
+  }
   return r;
 }
 
-// K5b entering column: min |d_j| / |T_rj| over columns that move x_r toward
-// its violated bound, lowest variable id on ties; the row is in rho slot np.
-// Returns q or -1 (primal infeasible).
-__device__ __noinline__ int lz_dual_ratio(LZS *S, int r) {
+// One dual iteration for the leaving row r, fused like lz_primal_iter (two
+// block barriers):
+//   row r by TMA -> pending updates on the thread's own columns (kept in
+//   registers) + K5b dual ratio test -> block argmin (payload: entering
+//   variable and its flag) -> column q gathered on the thread's own rows; the
+//   two tableau elements every thread needs, alpha = T[r][q] and d_q =
+//   T[0][q], are derived redundantly by each thread (no broadcast, no race
+//   with the in-place updates) -> step, beta update, scaled row + reduced
+//   costs, basis swap / tally, and K5a selection of the NEXT leaving row on
+//   the fresh beta -> block argmin = closing barrier.
+// Returns q in the low word (-1: primal infeasible) and the next leaving row
+// in the high word (-1: the basis is primal feasible, optimal).
+__device__ __noinline__ long long lz_dual_iter(LZS *S, int r, int np) {
   const Lay l = S->lay;
-  const int n = S->n, tid = threadIdx.x, NT = blockDim.x;
-  const double *row = zRho(l, S->np), *d = zD(l);
+  const int m = S->m, n = S->n, ld = S->ld, tid = threadIdx.x, NT = blockDim.x;
+  lz_need_tableau(S);
+  if (tid == 0) lz_issue_row(S, r);
+  const int *pend = zPend(l, m);
+  double *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l), *d = zD(l);
+  int *head = zHead(l);
   const int *atv = zAtv(l), *nbv = zNbv(l);
-  const int rs = row_infeas(zBeta(l)[r], zLbB(l)[r], zUbB(l)[r]);
-  Key bq = key_none();
-  for (int j = tid; j < n; j += NT) {
-    const int f = atv[j];
-    if (f == MVB_AT_FX) continue;
-    const double alpha = row[j];
-    const double a = rs < 0 ? alpha : -alpha;
-    const bool ok = (f == MVB_AT_LB && a > MVB_TOL_PIV) || (f == MVB_AT_UB && a < -MVB_TOL_PIV) ||
-                    (f == MVB_AT_FR && (a > MVB_TOL_PIV || a < -MVB_TOL_PIV));
-    if (!ok) continue;
-    const double ratio = fabs(d[j]) / fabs(alpha);
-    const Key k{dbits(ratio), nbv[j], j};
-    if (key_less(k, bq)) bq = k;
-  }
-  bq = block_argmin_fast(bq, zSlot(l, S->m), 1);
-  const int q = bq.idx;
-  if (q < 0) return -1;
-  if (tid == 0) {
-    const double alpha_rq = row[q];
-    S->r = r;
-    S->q = q;
-    S->alpha = alpha_rq;
-    S->inv = 1.0 / alpha_rq;
-    S->degenerate = __longlong_as_double((long long)bq.k) == 0.0;
-  }
-  return q;  // S is read after the barrier inside lz_col
-}
-
-// after lz_col: the step of the dual iteration, then the row is scaled in place
-__device__ __noinline__ void lz_dual_finish(LZS *S, int r, int q) {
-  const Lay l = S->lay;
-  const int ld = S->ld, tid = threadIdx.x, NT = blockDim.x;
-  if (tid == 0) {
-    const double br = zBeta(l)[r], lr = zLbB(l)[r], ur = zUbB(l)[r];
-    const int rs = row_infeas(br, lr, ur);
-    const double target = rs < 0 ? lr : ur;
-    const double delta = (target - br) / S->alpha;
-    S->delta = delta;
-    S->newbr = nb_value(zAtv(l)[q], S->lq, S->uq) + delta;
-    S->newat = rs < 0 ? MVB_AT_LB : MVB_AT_UB;
-  }
-  const double inv = S->inv;
-  double *buf = zRho(l, S->np);
-  for (int j = tid; j < ld; j += NT) buf[j] = j == q ? inv : -(buf[j] * inv);
-  __syncthreads();
-}
-
-// apply the iteration to the private state; the tableau update stays pending
-//   beta'_i = i == r ? newbr : fma(T_iq, delta, beta_i)
-//   d'_j    = fma(d_q, rho_j, j == q ? 0 : d_j)           (row 0 of the update)
-//   basis swap incl. the per-row bounds and the non-basic flag
-// np, r, q come in registers: with vectors_done there is no barrier between the callers'
-// last one and thread 0 advancing S->np below
-__device__ __noinline__ void lz_apply(LZS *S, int np, int r, int q, int vectors_done) {
-  const Lay l = S->lay;
-  const int m = S->m, ld = S->ld, tid = threadIdx.x, NT = blockDim.x;
-  if (!vectors_done) {  // bound flips and the dual loop; a primal pivot did this inside lz_row
-    const double delta = S->delta, newbr = S->newbr;
-    const double *colN = zCol(l, np), *rhoN = zRho(l, np);
-    double *beta = zBeta(l), *d = zD(l);
-    for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(colN[i], delta, beta[i]);
-    if (r) {
-      const double dq = colN[0];
-      for (int j = tid; j < ld; j += NT) d[j] = fma(dq, rhoN[j], j == q ? 0.0 : d[j]);
+  const double br = beta[r], lr = lbB[r], ur = ubB[r];
+  const int rs = row_infeas(br, lr, ur);
+  const int degen0 = S->degen;
+  const double *Tst = S->T[S->cT];
+  const size_t lds = (size_t)ld;
+  double *buf = zRho(l, np), *colN = zCol(l, np);
+  mbar_wait(zMbar(l, m), S->mphase);
+  PROF(1);
+  // ---- row r on the thread's own columns + dual ratio test ----
+  // (the kernel serves LPs up to ld = JU * NT columns in one pass; wider ones loop)
+  constexpr int JU = 4;
+  double bt = HUGE_VAL;
+  int bvar = 0x7fffffff, bidx = -1;
+  for (int j0 = tid; j0 < ld; j0 += JU * NT) {
+    int jj[JU];
+    double v[JU];
+#pragma unroll
+    for (int u = 0; u < JU; u++) {
+      jj[u] = min(j0 + u * NT, ld - 1);
+      v[u] = buf[jj[u]];
     }
-    __syncthreads();  // everyone has read the step out of S
-  }
-  PROF(15);
-  if (tid == 32) {  // basis swap (one warp) ...
-    int *nbv = zNbv(l), *atv = zAtv(l), *head = zHead(l), *pend = zPend(l, m);
-    double *lbB = zLbB(l), *ubB = zUbB(l);
-    if (r) {
-      const int kin = nbv[q], kout = head[r];
-      const double lo = lbB[r], uo = ubB[r];
-      head[r] = kin;
-      lbB[r] = S->lq;
-      ubB[r] = S->uq;
-      nbv[q] = kout;
-      atv[q] = lo == uo ? MVB_AT_FX : S->newat;
-      pend[2 * np] = r;
-      pend[2 * np + 1] = q;
-    } else {
-      atv[q] = S->newat;
+    for (int p = 0; p < np; p++) {
+      const double cr = zCol(l, p)[r];
+      const bool isr = pend[2 * p] == r;
+      const int pqp = pend[2 * p + 1];
+      const double *rp = zRho(l, p);
+#pragma unroll
+      for (int u = 0; u < JU; u++) v[u] = lz_step(v[u], isr, jj[u] == pqp, cr, rp[jj[u]]);
+    }
+#pragma unroll
+    for (int u = 0; u < JU; u++) {
+      const int j = jj[u];
+      const bool mine = j0 + u * NT < ld;
+      if (mine) buf[j] = v[u];  // derived, unscaled: pass 2 reads it back
+      const int f = atv[j], var = nbv[j];
+      const double alpha = v[u];
+      const double a = rs < 0 ? alpha : -alpha;
+      const bool ok = mine & (j < n) &
+                      (((f == MVB_AT_LB) & (a > MVB_TOL_PIV)) | ((f == MVB_AT_UB) & (a < -MVB_TOL_PIV)) |
+                       ((f == MVB_AT_FR) & ((a > MVB_TOL_PIV) | (a < -MVB_TOL_PIV))));
+      const double num0 = fabs(d[j]);
+      const bool live = ok & (num0 != 0.0);  // 0 / x would take the slow path of the division
+      const double t = live ? (num0 / (live ? fabs(alpha) : 1.0)) : 0.0;
+      const bool better = ok & ((t < bt) | ((t == bt) & (var < bvar)));
+      bt = better ? t : bt;
+      bvar = better ? var : bvar;
+      bidx = better ? (j | (f << 28)) : bidx;
     }
   }
-  if (tid == 0) {  // ... while another does the bookkeeping (as tally_iter)
-    const bool bland = S->degen >= MVB_BLAND_AFTER;
+  PROF(2);
+  Key bq = bidx >= 0 ? Key{dbits(bt), bvar, bidx} : key_none();
+  bq = block_argmin_fast(bq, zSlot(l, m), 1);
+  PROF(14);
+  if (bq.idx < 0) return lz_pack(-1, -1);
+  const int q = bq.idx & 0x0fffffff, fq = (bq.idx >> 28) & 3, kin = bq.var;
+  const bool degenerate = __longlong_as_double((long long)bq.k) == 0.0;
+  // ---- column q on the thread's own rows; alpha and d_q derived by every thread ----
+  const double lq = ldcg(S->lb + kin), uq = ldcg(S->ub + kin);
+  constexpr int NU = 2;
+  const double *Tq = Tst + q;
+  double xa = ldcg(Tq + (size_t)r * lds), xd = ldcg(Tq);
+  // first pass of the row loop below also carries the two extra elements through the chain
+  for (int p = 0; p < np; p++) {
+    const double rq = zRho(l, p)[q];
+    const int prp = pend[2 * p];
+    const bool isq = pend[2 * p + 1] == q;
+    const double *cp = zCol(l, p);
+    xa = lz_step(xa, r == prp, isq, cp[r], rq);
+    xd = lz_step(xd, false, isq, cp[0], rq);
+  }
+  const double alpha = xa, dq = xd;
+  const double inv = 1.0 / alpha;
+  const double target = rs < 0 ? lr : ur;
+  const double delta = (target - br) / alpha;
+  const double newbr = nb_value(fq, lq, uq) + delta;
+  const int degen1 = degenerate ? degen0 + 1 : 0;
+  const bool bland = degen1 >= MVB_BLAND_AFTER;
+  if (tid == 0) colN[0] = dq;
+  Key best = key_none();
+  for (int i0 = 1 + tid; i0 <= m; i0 += NU * NT) {
+    int ii[NU];
+    double v[NU];
+#pragma unroll
+    for (int u = 0; u < NU; u++) {
+      ii[u] = min(i0 + u * NT, m);
+      v[u] = ldcg(Tq + (size_t)ii[u] * lds);
+    }
+    for (int p = 0; p < np; p++) {
+      const double rq = zRho(l, p)[q];
+      const int prp = pend[2 * p];
+      const bool isq = pend[2 * p + 1] == q;
+      const double *cp = zCol(l, p);
+#pragma unroll
+      for (int u = 0; u < NU; u++) v[u] = lz_step(v[u], ii[u] == prp, isq, cp[ii[u]], rq);
+    }
+#pragma unroll
+    for (int u = 0; u < NU; u++) {
+      const int i = ii[u];
+      const bool mine = i0 + u * NT <= m;
+      const bool isr = i == r;
+      const double bn = isr ? newbr : fma(v[u], delta, beta[i]);
+      if (mine) {
+        colN[i] = v[u];
+        beta[i] = bn;
+      }
+      // K5a for the next iteration; row r now holds the entering variable (from registers:
+      // the swap by thread 32 is not ordered with this read)
+      const double lo = isr ? lq : lbB[i], up = isr ? uq : ubB[i];
+      const int hv = isr ? kin : head[i];
+      const int s = row_infeas(bn, lo, up);
+      const double viol = s < 0 ? lo - bn : bn - up;
+      const Key k{bland ? 0ULL : ~dbits(viol), hv, i};
+      if (mine && s != 0 && key_less(k, best)) best = k;
+    }
+  }
+  PROF(3);
+  // ---- scaled pivot row + reduced costs on the thread's own columns ----
+  for (int j0 = tid; j0 < ld; j0 += JU * NT) {
+#pragma unroll
+    for (int u = 0; u < JU; u++) {
+      const int j = j0 + u * NT;
+      if (j < ld) {
+        const bool isq = j == q;
+        const double rho = isq ? inv : -(buf[j] * inv);
+        buf[j] = rho;
+        d[j] = fma(dq, rho, isq ? 0.0 : d[j]);
+      }
+    }
+  }
+  if (tid == 32) {  // basis swap incl. the per-row bounds and the non-basic flag
+    int *nbw = zNbv(l), *atw = zAtv(l), *pd = zPend(l, m);
+    const int kout = head[r];
+    head[r] = kin;
+    lbB[r] = lq;
+    ubB[r] = uq;
+    nbw[q] = kout;
+    atw[q] = lr == ur ? MVB_AT_FX : (rs < 0 ? MVB_AT_LB : MVB_AT_UB);
+    pd[2 * np] = r;
+    pd[2 * np + 1] = q;
+  }
+  if (tid == 0) {  // bookkeeping (as tally_iter)
+    const bool bl0 = degen0 >= MVB_BLAND_AFTER;
     Tally &t = S->ty;
     unsigned long long h = t.hash;
     h = (h ^ (unsigned long long)S->mode) * MVB_FNV_PRIME;
@@ -942,11 +837,52 @@ __device__ __noinline__ void lz_apply(LZS *S, int np, int r, int q, int vectors_
       S->pivlog[2 * t.iters + 1] = q;
     }
     t.iters++;
-    if (r) t.pivots++; else t.flips++;
-    if (S->mode == MVB_MODE_PRIMAL2) t.it2++; else t.itd++;
+    t.pivots++;
+    t.itd++;
+    if (bl0) t.bland++;
+    S->degen = degen1;
+    S->r = r;
+    S->q = q;
+    S->lq = lq;
+    S->uq = uq;
+    S->np = np + 1;
+  }
+  PROF(4);
+  best = block_argmin_fast(best, zSlot(l, m), 0);  // also the closing barrier of the iteration
+  if (tid == 0) S->mphase ^= 1;
+  PROF(5);
+  return lz_pack(q, best.idx);
+}
+
+// primal bound flip (lz_primal_iter returned 0, the step is in S): no basis change,
+//   beta'_i = fma(T_iq, delta, beta_i), the entering variable moves to its other bound
+__device__ __noinline__ void lz_flip(LZS *S, int np, int q) {
+  const Lay l = S->lay;
+  const int m = S->m, tid = threadIdx.x, NT = blockDim.x;
+  const double delta = S->delta;
+  const double *colN = zCol(l, np);
+  double *beta = zBeta(l);
+  for (int i = 1 + tid; i <= m; i += NT) beta[i] = fma(colN[i], delta, beta[i]);
+  __syncthreads();  // everyone has read the step out of S
+  PROF(15);
+  if (tid == 32) zAtv(l)[q] = S->newat;
+  if (tid == 0) {  // bookkeeping (as tally_iter)
+    const bool bland = S->degen >= MVB_BLAND_AFTER;
+    Tally &t = S->ty;
+    unsigned long long h = t.hash;
+    h = (h ^ (unsigned long long)S->mode) * MVB_FNV_PRIME;
+    h = (h ^ 0ULL) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)q) * MVB_FNV_PRIME;
+    t.hash = h;
+    if (S->g == 0 && S->pivlog && t.iters < S->pivlog_cap) {
+      S->pivlog[2 * t.iters] = 0;
+      S->pivlog[2 * t.iters + 1] = q;
+    }
+    t.iters++;
+    t.flips++;
+    t.it2++;
     if (bland) t.bland++;
-    S->degen = S->degenerate ? S->degen + 1 : 0;
-    if (r) S->np = np + 1;
+    S->degen = 0;  // a flip is never degenerate
   }
   __syncthreads();
 }
@@ -1004,22 +940,21 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
 
   int status;
   int qnext = -2;  // -2: not priced yet (first iteration, after a bound flip)
+  int rnext = -2;  // dual: -2: leaving row not selected yet (first iteration)
   while (true) {
-    int vectors_done = 0, r, q;
+    int r, q;
     const int np = S->np;
     if (mode == MVB_MODE_DUAL) {
-      r = lz_dual_select(S);
-      if (r < 0) { status = r == -1 ? MVB_OPT : MVB_ITLIM; break; }
+      r = rnext != -2 ? rnext : lz_dual_select(S, 0);
+      if (r == -1) { status = MVB_OPT; break; }
+      if (r == -2 || S->ty.iters >= S->max_iters) { status = MVB_ITLIM; break; }
       PROF(0);
-      lz_row(S, r, 0, 0);
-      PROF(1);
-      q = lz_dual_ratio(S, r);
+      const long long qr = lz_dual_iter(S, r, np);
+      q = (int)(unsigned)qr;
       if (q < 0) { status = MVB_NOFEAS; break; }
-      PROF(2);
-      lz_col(S, q);
-      PROF(3);
-      lz_dual_finish(S, r, q);
-      PROF(4);
+      rnext = (int)(qr >> 32);
+      if (S->np == K) lz_flush(S);
+      continue;
     } else {
       q = qnext != -2 ? qnext : lz_price(S);
       qnext = -2;
@@ -1035,9 +970,8 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
         continue;
       }
     }
-    lz_apply(S, np, r, q, vectors_done);
+    lz_flip(S, np, q);
     PROF(5);
-    if (S->np == K) lz_flush(S);
   }
   __syncthreads();
   lz_flush(S);
