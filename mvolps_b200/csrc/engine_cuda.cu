@@ -690,6 +690,7 @@ struct DeviceCtx {
   bool ready = false;
   int device = -1, sms = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream_upd = nullptr;  // sharded path: the tableau updates (engine_shard.cuh)
   int max_ctas = 0;        // co-resident CTAs of simplex_kernel at NT threads
   int nt = 512;            // threads per CTA (general kernel)
   int nt_ps = MVB_PS_NT;   // threads per CTA (private-state kernel)

@@ -5,11 +5,16 @@
 //
 // Per pivot and rank:  shard_price_kernel  (K1 over the local columns + pack
 // of the candidate column)  ->  ONE all-gather of (key, id, bounds, column)
-// ->  shard_pivot_kernel  (same global winner everywhere by the (value bits,
-// variable id) order, replicated K2 ratio test, K3/K4 on the local columns,
-// tableau A -> B).  The kernel boundary is the only synchronisation; the
-// control block ping-pongs by iteration parity so a finished solve turns the
-// remaining launches of a chunk into no-ops.
+// ->  shard_decide_kernel  (same global winner everywhere by the (value bits,
+// variable id) order, replicated K2 ratio test, step, K3 scaled pivot row)
+// on the decision stream, and  shard_update_kernel  (K4 on the local columns,
+// tableau A -> B) on the update stream.  The decision chain of iteration t+1
+// overlaps the update of iteration t: it reads the buffer that update reads
+// and applies the one pending step on the fly (ShardView), bit for bit what
+// the finished tableau holds.  Kernel boundaries and two events per iteration
+// are the only synchronisation; the control block ping-pongs by iteration
+// parity so a finished solve turns the remaining launches of a chunk into
+// no-ops.
 #pragma once
 #include <dlfcn.h>
 
@@ -20,7 +25,9 @@ namespace {
 struct ShardCtl {
   int status;  // -1 while running, then MVB_*
   int iters, pivots, flips, bland_iters, degen;
-  int cT, cS;
+  int cur, cS;  // tableau buffer that holds the current tableau once the pending update landed; small-state parity
+  int pend;     // 1: the update of the previous iteration (step[par ^ 1]) may still be running on the
+                // update stream, readers take the other buffer and apply that step on the fly
   unsigned long long hash;
 };
 
@@ -31,6 +38,14 @@ struct Cand {  // header of one exchange record; the column (m+1 doubles) follow
 };
 constexpr size_t SHARD_HDR = 64;
 
+struct ShardStep {  // what iteration t leaves for its update kernel and for the readers of t+1
+  int valid;   // 1: a basis change with a tableau update
+  int r;       // pivot row
+  int qloc;    // local position of the entering column, outside [0, nloc) when another rank owns it
+  int wk;      // rank whose record holds the pivot column
+  int src;     // tableau buffer the update reads (it writes src ^ 1)
+};
+
 struct ShardDev {
   int m, nloc, ld, col0, world, max_iters;
   double *T[2];
@@ -39,30 +54,70 @@ struct ShardDev {
   int *nb[2];
   int *at[2];
   double *lb, *ub;  // by variable id, n_global + m (replicated)
-  ShardCtl *ctl;    // [2]
-  unsigned char *send, *recv;
+  ShardCtl *ctl;    // [2] by iteration parity
+  ShardStep *step;  // [2] by iteration parity
+  double *rho[2];   // scaled pivot row over the local columns, by iteration parity
+  unsigned char *send, *recv[2];
   size_t rec_bytes;
   int *pivlog;
   int pivlog_cap;
 };
 
+// The pipeline (mvb_shard_solve): the decision chain of iteration t+1 (price -> all-gather ->
+// decide, on the high-priority stream) runs WHILE the rank-1 update of iteration t streams the
+// tableau on the update stream.  The chain therefore reads the buffer the running update reads
+// (complete: the host makes it wait for update t-1) and applies step t on the fly -- one element
+// costs the same fma the update applies, so every bit is the one the finished tableau will hold:
+//     T_{t+1}[i][j] = i == r ? rho[j] : fma(col[i], rho[j], j == q ? 0 : T_t[i][j])
+struct ShardView {
+  const double *T;     // complete buffer
+  const double *rho;   // pending step: scaled pivot row (local columns); nullptr: nothing pending
+  const double *col;   // pending step: pivot column (m+1)
+  int r, qloc, ld;
+  __device__ __forceinline__ double at(int i, int j) const {
+    const double v = ldcg(T + (size_t)i * ld + j);
+    if (!rho) return v;
+    const double rj = rho[j];
+    return i == r ? rj : fma(col[i], rj, j == qloc ? 0.0 : v);
+  }
+};
+__device__ __forceinline__ ShardView shard_view(const ShardDev &D, const ShardCtl &c, int par) {
+  ShardView v;
+  v.ld = D.ld;
+  if (c.pend) {
+    const ShardStep st = D.step[par ^ 1];
+    v.T = D.T[c.cur ^ 1];
+    v.rho = D.rho[par ^ 1];
+    v.col = reinterpret_cast<const double *>(D.recv[par ^ 1] + (size_t)st.wk * D.rec_bytes + SHARD_HDR);
+    v.r = st.r;
+    v.qloc = st.qloc;
+  } else {
+    v.T = D.T[c.cur];
+    v.rho = nullptr;
+    v.col = nullptr;
+    v.r = -1;
+    v.qloc = -1;
+  }
+  return v;
+}
+
 // K1 over the local columns + gather of the winning column into the send
 // record.  Every CTA of the (small) grid repeats the cheap argmin over the
 // local reduced costs and then gathers its own slice of the column rows, so the
-// strided gather (one 32-byte sector per element) runs on many SMs.
+// strided gather (one 32-byte sector per element) runs on several SMs.
 __global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int par) {
   __shared__ Key red[32];
   const ShardCtl c = D.ctl[par];
   Cand *out = reinterpret_cast<Cand *>(D.send);
   if (c.status != -1) return;
+  const ShardView V = shard_view(D, c, par);
   const bool bland = c.degen >= MVB_BLAND_AFTER;
-  const double *d = D.T[c.cT];
   const int *at = D.at[c.cS], *nb = D.nb[c.cS];
   Key best = key_none();
   for (int j = threadIdx.x; j < D.nloc; j += blockDim.x) {
     const int f = at[j];
     if (f == MVB_AT_FX) continue;
-    const double dj = d[j];
+    const double dj = V.at(0, j);
     if (!dj_eligible(f, dj)) continue;
     const Key k{bland ? 0ULL : ~dbits(fabs(dj)), nb[j], j};
     if (key_less(k, best)) best = k;
@@ -81,17 +136,17 @@ __global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int pa
   }
   if (q < 0) return;
   double *col = reinterpret_cast<double *>(D.send + SHARD_HDR);
-  const double *T = D.T[c.cT] + q;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= D.m; i += gridDim.x * blockDim.x)
-    col[i] = T[(size_t)i * D.ld];
+    col[i] = V.at(i, q);
 }
 
-// rank-1 update of this CTA's share of the local columns, pivot column taken
-// from `colg` (m+1 doubles in global memory), same unit split and arithmetic
-// as tile_update
+// rank-1 update of this CTA's share of the local columns: pivot column from
+// `colg` (m+1 doubles), scaled pivot row from `rhog` (both in global memory),
+// same unit split and arithmetic as tile_update
 __device__ void shard_tile_update(const ShardDev &D, const double *__restrict__ Ts,
-                                  double *__restrict__ Td, int r, int qloc, double inv,
-                                  const double *__restrict__ colg, Smem &sm) {
+                                  double *__restrict__ Td, int r, int qloc,
+                                  const double *__restrict__ rhog, const double *__restrict__ colg,
+                                  Smem &sm) {
   const int R = D.m + 1, ld = D.ld, g = blockIdx.x, G = gridDim.x;
   int tcl = 0;
   while ((1 << tcl) < (ld + 1) / 2 && (2 << tcl) <= (int)blockDim.x) tcl++;
@@ -110,11 +165,7 @@ __device__ void shard_tile_update(const ShardDev &D, const double *__restrict__ 
     const bool act = col < ld;
     const bool qx = col == qloc, qy = col + 1 == qloc;
     double2 rho = make_double2(0.0, 0.0);
-    if (act) {
-      const double2 t = ldcg2(Ts + (size_t)r * ld + col);
-      rho.x = qx ? inv : -(t.x * inv);
-      rho.y = qy ? inv : -(t.y * inv);
-    }
+    if (act) rho = ldcg2(rhog + col);
     for (int s0 = ia; s0 < ib; s0 += STAGE_ROWS) {
       const int s1 = ib < s0 + STAGE_ROWS ? ib : s0 + STAGE_ROWS;
       __syncthreads();
@@ -150,14 +201,20 @@ __device__ void shard_tile_update(const ShardDev &D, const double *__restrict__ 
 
 namespace {
 
-// one iteration on every rank: global winner, replicated ratio test, local update
-__global__ void __launch_bounds__(512, 1) shard_pivot_kernel(ShardDev D, int par) {
+// Decisions of one iteration on every rank (a few CTAs, each repeating the
+// cheap part): global winner, replicated K2 ratio test, the step, the next
+// small state, and the scaled pivot row rho over the local columns (K3) for
+// the update kernel and for the readers of the next iteration.
+__global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int par) {
   __shared__ Smem sm;
   const ShardCtl c = D.ctl[par];
   ShardCtl *next = &D.ctl[par ^ 1];
   const bool lead = blockIdx.x == 0 && threadIdx.x == 0;
+  ShardCtl n = c;
+  n.pend = 0;
+  ShardStep stp{};
   if (c.status != -1) {
-    if (lead) *next = c;
+    if (lead) { *next = n; D.step[par] = stp; }
     return;
   }
   const int m = D.m, tid = threadIdx.x, NT = blockDim.x;
@@ -166,23 +223,22 @@ __global__ void __launch_bounds__(512, 1) shard_pivot_kernel(ShardDev D, int par
   unsigned long long bk = ~0ULL;
   int bvar = 0x7fffffff;
   for (int k = 0; k < D.world; k++) {
-    const Cand *h = reinterpret_cast<const Cand *>(D.recv + (size_t)k * D.rec_bytes);
+    const Cand *h = reinterpret_cast<const Cand *>(D.recv[par] + (size_t)k * D.rec_bytes);
     if (h->pos < 0) continue;
     if (h->key < bk || (h->key == bk && h->var < bvar)) { bk = h->key; bvar = h->var; wk = k; }
   }
-  ShardCtl n = c;
   if (wk < 0) {
     n.status = MVB_OPT;
-    if (lead) *next = n;
+    if (lead) { *next = n; D.step[par] = stp; }
     return;
   }
   if (c.iters >= D.max_iters) {
     n.status = MVB_ITLIM;
-    if (lead) *next = n;
+    if (lead) { *next = n; D.step[par] = stp; }
     return;
   }
-  const Cand cand = *reinterpret_cast<const Cand *>(D.recv + (size_t)wk * D.rec_bytes);
-  const double *col = reinterpret_cast<const double *>(D.recv + (size_t)wk * D.rec_bytes + SHARD_HDR);
+  const Cand cand = *reinterpret_cast<const Cand *>(D.recv[par] + (size_t)wk * D.rec_bytes);
+  const double *col = reinterpret_cast<const double *>(D.recv[par] + (size_t)wk * D.rec_bytes + SHARD_HDR);
   const bool bland = c.degen >= MVB_BLAND_AFTER;
   const double *beta = D.beta[c.cS];
   const int *head = D.head[c.cS];
@@ -207,7 +263,7 @@ __global__ void __launch_bounds__(512, 1) shard_pivot_kernel(ShardDev D, int par
   if (tflip <= tmin) {
     if (!(tflip < HUGE_VAL)) {
       n.status = MVB_UNBND;
-      if (lead) *next = n;
+      if (lead) { *next = n; D.step[par] = stp; }
       return;
     }
     delta = dir > 0 ? tflip : -tflip;
@@ -228,12 +284,12 @@ __global__ void __launch_bounds__(512, 1) shard_pivot_kernel(ShardDev D, int par
     if (D.lb[kout] == D.ub[kout]) newat = MVB_AT_FX;
   }
   const int qloc = cand.pos - D.col0;  // local position of the entering column, if it is ours
-  // next small state (ping-pong), split over the whole grid
+  const int gt = blockIdx.x * NT + tid, stride = gridDim.x * NT;
+  // next small state (ping-pong), split over the grid
   {
     double *bd = D.beta[c.cS ^ 1];
     int *hd = D.head[c.cS ^ 1], *nd = D.nb[c.cS ^ 1], *ad = D.at[c.cS ^ 1];
     const int *ns = D.nb[c.cS], *as = D.at[c.cS];
-    const int gt = blockIdx.x * NT + tid, stride = gridDim.x * NT;
     for (int i = 1 + gt; i <= m; i += stride) {
       bd[i] = i == r ? newbr : fma(col[i], delta, beta[i]);
       hd[i] = i == r ? kin : head[i];
@@ -243,10 +299,18 @@ __global__ void __launch_bounds__(512, 1) shard_pivot_kernel(ShardDev D, int par
       ad[j] = j == qloc ? newat : as[j];
     }
   }
-  if (r) {
+  if (r) {  // K3: rho_q = 1/p, rho_j = -(T_rj * (1/p)) on the current row r (through the view)
+    const ShardView V = shard_view(D, c, par);
     const double inv = 1.0 / col[r];
-    shard_tile_update(D, D.T[c.cT], D.T[c.cT ^ 1], r, qloc, inv, col, sm);
-    n.cT = c.cT ^ 1;
+    double *rho = D.rho[par];
+    for (int j = gt; j < D.ld; j += stride) rho[j] = j == qloc ? inv : -(V.at(r, j) * inv);
+    stp.valid = 1;
+    stp.r = r;
+    stp.qloc = qloc;
+    stp.wk = wk;
+    stp.src = c.cur;
+    n.cur = c.cur ^ 1;
+    n.pend = 1;
   }
   n.cS = c.cS ^ 1;
   if (lead) {
@@ -263,7 +327,18 @@ __global__ void __launch_bounds__(512, 1) shard_pivot_kernel(ShardDev D, int par
     if (r) n.pivots++; else n.flips++;
     if (bland) n.bland_iters++;
     *next = n;
+    D.step[par] = stp;
   }
+}
+
+// K4 of iteration t on the update stream: tableau src -> src ^ 1 with the step
+// the decide kernel left (pivot column in the exchange record, rho in D.rho)
+__global__ void __launch_bounds__(512, 1) shard_update_kernel(ShardDev D, int par) {
+  __shared__ Smem sm;
+  const ShardStep st = D.step[par];
+  if (!st.valid) return;
+  const double *col = reinterpret_cast<const double *>(D.recv[par] + (size_t)st.wk * D.rec_bytes + SHARD_HDR);
+  shard_tile_update(D, D.T[st.src], D.T[st.src ^ 1], st.r, st.qloc, D.rho[par], col, sm);
 }
 
 }  // namespace
@@ -418,6 +493,7 @@ struct mvb_shard {
   std::vector<double> x;           // primal by id after the last solve
   int *pivlog = nullptr; int pivlog_cap = 0, pivlog_n = 0;
   cudaEvent_t ev[2] = {};
+  cudaEvent_t ev_dec[2] = {}, ev_upd[2] = {};  // by iteration parity: decide done / update done
   float last_ms = 0.f;
 };
 
@@ -441,8 +517,9 @@ bool shard_alloc(mvb_shard *s) {
   size_t oa0 = take((size_t)s->ld * sizeof(int)), oa1 = take((size_t)s->ld * sizeof(int));
   size_t olb = take((size_t)(s->nglob + m) * sizeof(double)), oub = take((size_t)(s->nglob + m) * sizeof(double));
   size_t oc = take((size_t)s->ld * sizeof(double));
-  size_t octl = take(2 * sizeof(ShardCtl));
-  size_t osend = take(rec), orecv = take(rec * s->world);
+  size_t octl = take(2 * sizeof(ShardCtl)), ostep = take(2 * sizeof(ShardStep));
+  size_t orho0 = take((size_t)s->ld * sizeof(double)), orho1 = take((size_t)s->ld * sizeof(double));
+  size_t osend = take(rec), orecv0 = take(rec * s->world), orecv1 = take(rec * s->world);
   size_t ofs = take(s->fin_bytes), ofr = take(s->fin_bytes * s->world);
   CK(cudaMallocAsync((void **)&s->slab, off, g_ctx.stream));
   CK(cudaMemsetAsync(s->slab, 0, off, g_ctx.stream));
@@ -457,7 +534,10 @@ bool shard_alloc(mvb_shard *s) {
   d.lb = (double *)(b + olb); d.ub = (double *)(b + oub);
   s->cost = (double *)(b + oc);
   d.ctl = (ShardCtl *)(b + octl);
-  d.send = (unsigned char *)(b + osend); d.recv = (unsigned char *)(b + orecv);
+  d.step = (ShardStep *)(b + ostep);
+  d.rho[0] = (double *)(b + orho0); d.rho[1] = (double *)(b + orho1);
+  d.send = (unsigned char *)(b + osend);
+  d.recv[0] = (unsigned char *)(b + orecv0); d.recv[1] = (unsigned char *)(b + orecv1);
   d.rec_bytes = rec;
   s->fin_send = (unsigned char *)(b + ofs); s->fin_recv = (unsigned char *)(b + ofr);
   return true;
@@ -498,6 +578,10 @@ void mvb_shard_free(mvb_shard *s) {
   if (s->slab) cudaFreeAsync(s->slab, g_ctx.stream);
   if (s->pivlog) cudaFreeAsync(s->pivlog, g_ctx.stream);
   if (s->ev[0]) { cudaEventDestroy(s->ev[0]); cudaEventDestroy(s->ev[1]); }
+  for (int k = 0; k < 2; k++) {
+    if (s->ev_dec[k]) cudaEventDestroy(s->ev_dec[k]);
+    if (s->ev_upd[k]) cudaEventDestroy(s->ev_upd[k]);
+  }
   delete s;
 }
 
@@ -595,36 +679,61 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
     s->dev.pivlog_cap = s->dev.pivlog ? s->pivlog_cap : 0;
     CKI(cudaMemcpyAsync(&s->dev.ctl[0], &init, sizeof(init), cudaMemcpyHostToDevice, st));
     if (!s->ev[0]) { CKI(cudaEventCreate(&s->ev[0])); CKI(cudaEventCreate(&s->ev[1])); }
+    for (int e = 0; e < 2; e++) {
+      if (!s->ev_dec[e]) CKI(cudaEventCreateWithFlags(&s->ev_dec[e], cudaEventDisableTiming));
+      if (!s->ev_upd[e]) CKI(cudaEventCreateWithFlags(&s->ev_upd[e], cudaEventDisableTiming));
+    }
   }
-  auto exchange = [&](bool fin) -> bool {
+  if (!g_ctx.stream_upd) CKI(cudaStreamCreateWithFlags(&g_ctx.stream_upd, cudaStreamNonBlocking));
+  cudaStream_t su = g_ctx.stream_upd;  // the tableau updates; `st` carries the decision chain
+  auto exchange = [&](bool fin, int par) -> bool {
     for (int k = 0; k < nlocal; k++) {
       mvb_shard *s = shards[k];
       const unsigned char *snd = fin ? s->fin_send : s->dev.send;
       const size_t bytes = fin ? s->fin_bytes : s->dev.rec_bytes;
       if (!local) {
-        unsigned char *rcv = fin ? s->fin_recv : s->dev.recv;
+        unsigned char *rcv = fin ? s->fin_recv : s->dev.recv[par];
         if (s->comm->allgather_dev(s->comm->ctx, snd, rcv, bytes, st)) return false;
       } else {
         for (int t = 0; t < nlocal; t++) {
-          unsigned char *rcv = (fin ? shards[t]->fin_recv : shards[t]->dev.recv) + (size_t)s->rank * bytes;
+          unsigned char *rcv = (fin ? shards[t]->fin_recv : shards[t]->dev.recv[par]) + (size_t)s->rank * bytes;
           CK(cudaMemcpyAsync(rcv, snd, bytes, cudaMemcpyDeviceToDevice, st));
         }
       }
     }
     return true;
   };
-  const int grid = std::max(1, g_ctx.max_ctas);
-  const int price_grid = std::max(1, std::min(32, (m + 1 + 1023) / 1024));  // CTAs sharing the column gather
+  // Two streams.  Decision chain of iteration t (st): price -> all-gather -> decide.  Update
+  // stream (su): the rank-1 update of iteration t, after its decide.  The chain of t+1 reads
+  // the buffer update t reads and applies step t on the fly (ShardView), so it needs update
+  // t-1 finished, not update t: it overlaps the running update.  A few SMs are left to the
+  // chain's small kernels (the update is HBM-bound long before it needs every SM).
+  const int grid = std::max(1, g_ctx.max_ctas - 8);
+  const int small_grid = 8;
+  const int price_grid = std::max(1, std::min(small_grid, (m + 1 + 1023) / 1024));  // CTAs sharing the column gather
   const int CHUNK = 32;  // iterations enqueued between two looks at the control block
   int par = 0;
+  long long t_it = 0;
   ShardCtl h{};
   CKI(cudaEventRecord(s0->ev[0], st));
+  CKI(cudaStreamWaitEvent(su, s0->ev[0], 0));  // the update stream starts after the set-up on st
   while (true) {
-    for (int it = 0; it < CHUNK; it++) {
+    for (int it = 0; it < CHUNK; it++, t_it++) {
+      // the view of iteration t is the output of update t-2 (+ step t-1 on the fly)
+      if (t_it >= 2)
+        for (int k = 0; k < nlocal; k++) CKI(cudaStreamWaitEvent(st, shards[k]->ev_upd[par], 0));
       for (int k = 0; k < nlocal; k++) shard_price_kernel<<<price_grid, 1024, 0, st>>>(shards[k]->dev, par);
-      if (!exchange(false)) return -1;
-      for (int k = 0; k < nlocal; k++) shard_pivot_kernel<<<grid, 512, 0, st>>>(shards[k]->dev, par);
-      g_launches += 2 * nlocal;
+      if (!exchange(false, par)) return -1;
+      for (int k = 0; k < nlocal; k++) {
+        shard_decide_kernel<<<small_grid, 512, 0, st>>>(shards[k]->dev, par);
+        CKI(cudaEventRecord(shards[k]->ev_dec[par], st));
+      }
+      for (int k = 0; k < nlocal; k++) {
+        CKI(cudaStreamWaitEvent(su, shards[k]->ev_dec[par], 0));
+        shard_update_kernel<<<grid, 512, 0, su>>>(shards[k]->dev, par);
+        CKI(cudaEventRecord(shards[k]->ev_upd[par], su));
+      }
+      g_launches += 3 * nlocal;
       par ^= 1;
     }
     CKI(cudaGetLastError());
@@ -632,12 +741,17 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
     CKI(cudaStreamSynchronize(st));
     if (h.status != -1) break;
   }
+  // the last updates, then back to one stream
+  for (int k = 0; k < nlocal; k++) {
+    CKI(cudaStreamWaitEvent(st, shards[k]->ev_upd[0], 0));
+    CKI(cudaStreamWaitEvent(st, shards[k]->ev_upd[1], 0));
+  }
   // final gather: positions / flags / costs of every rank, then x and the objective on the host
   for (int k = 0; k < nlocal; k++)
     shard_pack_final<<<32, 256, 0, st>>>(shards[k]->dev, par, shards[k]->cost, shards[k]->maxloc,
                                          shards[k]->fin_send);
   g_launches += nlocal;
-  if (!exchange(true)) return -1;
+  if (!exchange(true, 0)) return -1;
   CKI(cudaEventRecord(s0->ev[1], st));
   for (int k = 0; k < nlocal; k++) {
     mvb_shard *s = shards[k];
