@@ -115,7 +115,11 @@ def run_shard(args, L, rank, world, local, dist, ClockSampler, peaks):
                    "exchange": "one all-gather per pivot: 64 B header + 8*(m+1) B column per rank",
                    "pivot_hash": str(r["pivot_hash"]), "l2": "tableau shard larger than L2"},
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak * world, "unit": "GB/s", "frac": ach / (peak * world),
-                     "traffic": None, "peak_source": src, "kernel": "shard_pivot_kernel (eager rank-1 update of the local columns)"},
+                     "traffic": 8551384000 if world == 1 else None, "peak_source": src,
+                     "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one shard_update_kernel launch at world 1, "
+                                       "ncu --set full, profiles/r1e_shard_update_summary.txt" if world == 1 else None,
+                     "kernel": "shard_update_kernel (eager rank-1 update of the local columns; the price / all-gather / "
+                               "decide chain of the next iteration overlaps it on a second stream)"},
         "gpu_launches": launches, "clocks": clk.summary(),
     }))
 
