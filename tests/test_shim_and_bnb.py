@@ -213,3 +213,48 @@ def test_bnb_live_reference_driver(oracle, ref_bin, tmp_path):
     out = GlpProb.from_file(oracle, path).bnb()
     assert [ln for ln in out["tree"].splitlines() if ln.strip()] == tree
     assert out["solution"].strip() == (sol[-1] if sol else "")
+
+
+def test_bound_setters_are_forwarded_and_unchanged_lps_are_answered_from_the_held_solution(oracle):
+    """The shim forwards only the bounds its setters logged (glp_prob::dirty) and answers a solve of
+    an LP that is unchanged since its optimal solve without touching the engine (bs.cpp:117 re-solves
+    such copies).  Both must be invisible: same values as a cold solve of the same problem."""
+    L = oracle
+    inst = instances.mdkp(30, 8, 77)
+    p = GlpProb.from_instance(L, inst)
+    assert p.simplex() == 0 and p.status() == capi.GLP_OPT
+    x0, z0, it0 = p.col_prim(), p.obj_val(), L.glp_get_it_cnt(p.h)
+    assert it0 > 0
+    # unchanged: zero iterations, same values (also on a copy)
+    assert p.simplex() == 0 and L.glp_get_it_cnt(p.h) == 0
+    assert np.array_equal(p.col_prim(), x0) and p.obj_val() == z0
+    q = p.copy()
+    assert q.simplex() == 0 and L.glp_get_it_cnt(q.h) == 0 and np.array_equal(q.col_prim(), x0)
+    # setting a bound to the value it already has changes nothing
+    j = int(np.argmax(x0 != np.floor(x0))) + 1
+    L.glp_set_col_bnds(q.h, j, L.glp_get_col_type(q.h, j), L.glp_get_col_lb(q.h, j), L.glp_get_col_ub(q.h, j))
+    assert q.simplex() == 0 and L.glp_get_it_cnt(q.h) == 0 and q.obj_val() == z0
+    # a real change is forwarded: warm dual re-solve == cold solve of the changed problem
+    for h in (q.h,):
+        L.glp_set_col_bnds(h, j, capi.GLP_DB, 0.0, float(np.floor(x0[j - 1])))
+        L.glp_set_row_bnds(h, 1, capi.GLP_UP, 0.0, float(np.floor(0.9 * L.glp_get_row_ub(h, 1))))
+    assert q.simplex() == 0 and q.status() == capi.GLP_OPT and L.glp_get_it_cnt(q.h) > 0
+    inst2 = instances.mdkp(30, 8, 77)
+    cold = GlpProb.from_instance(L, inst2)
+    L.glp_set_col_bnds(cold.h, j, capi.GLP_DB, 0.0, float(np.floor(x0[j - 1])))
+    L.glp_set_row_bnds(cold.h, 1, capi.GLP_UP, 0.0, float(np.floor(0.9 * L.glp_get_row_ub(cold.h, 1))))
+    assert cold.simplex() == 0 and cold.status() == capi.GLP_OPT
+    assert abs(cold.obj_val() - q.obj_val()) <= 1e-9 * max(1.0, abs(cold.obj_val()))
+    assert q.obj_val() < z0
+    # the original is untouched by what happened to its copy
+    assert p.simplex() == 0 and p.obj_val() == z0
+
+
+def test_bnb_counts_cached_resolves(oracle, tmp_path):
+    """Every popped non-root node was solved to optimality as a child: its re-solve (bs.cpp:117) is
+    answered from the held solution and counted, results are those of the recorded reference run."""
+    case = _gold()[0]
+    p = _prob(oracle, case, tmp_path)
+    out = p.bnb(**_kwargs(case["flags"]))
+    assert out["lp_solves"] >= out["cached_solves"] > 0
+    assert out["iterations"] == case["iterations"]
