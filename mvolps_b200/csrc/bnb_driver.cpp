@@ -181,11 +181,14 @@ struct Driver {
     violated.clear();
     int status = glp_get_status(a);
     if (status == GLP_NOFEAS || status == GLP_INFEAS || status == GLP_UNBND) return -1;
-    int cols = glp_get_num_cols(a);
+    // same test as through glp_get_col_prim / glp_get_obj_coef / glp_get_col_kind, on the
+    // problem object directly (this runs for every node over every column)
+    const int cols = (int)a->cols.size();
+    const MvCol *c = a->cols.data();
     for (int i = 1; i <= cols; i++) {
-      double x = glp_get_col_prim(a, i);
-      if (x != 0 && glp_get_obj_coef(a, i) != 0)
-        if (std::trunc(x) != x && glp_get_col_kind(a, i) != GLP_CV) violated.push_back(i);
+      const double x = c[i - 1].prim;
+      if (x != 0 && c[i - 1].coef != 0)
+        if (std::trunc(x) != x && c[i - 1].kind != GLP_CV) violated.push_back(i);
     }
     return violated.empty() ? 1 : 0;
   }

@@ -276,7 +276,9 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
   const unsigned u1 = (unsigned)((unsigned long long)nunits * (unsigned)(g + 1) / (unsigned)G);
   // rows in flight per thread: measured flat between 2 and 4 at K = 5, 6 and 8 spill (tools/ab.sh);
   // an L2 prefetch of the rows ahead gained 5 % on HBM-streaming batches but cost the L2-resident
-  // path 4 % (register pressure), so it is not here
+  // path 4 % (register pressure), so it is not here; staging the reads through a 32-48 KB TMA ring
+  // (twice the bytes in flight, depth 6 to make room) measured 6-9 % SLOWER than this register path
+  // at depth 8: during the flush the batch already runs HBM at ~70 % of its copy peak
   constexpr int UN = KC <= 4 ? 8 : 4;
   while (u0 < u1) {
     const int ch = (int)(u0 / (unsigned)R);
@@ -376,8 +378,9 @@ __device__ __forceinline__ void lz_need_tableau(LZS *S) {
 namespace {
 
 // TMA fetch of row r of the stale tableau into rho slot np (thread 0)
-__device__ __forceinline__ void lz_issue_row(LZS *S, int r) {
-  bulk_row_load(zRho(S->lay, S->np), S->T[S->cT] + (size_t)r * S->ld,
+// (np comes from the caller's register: S->np may already have been advanced by the tally thread)
+__device__ __forceinline__ void lz_issue_row(LZS *S, int r, int np) {
+  bulk_row_load(zRho(S->lay, np), S->T[S->cT] + (size_t)r * S->ld,
                 (unsigned)(S->ld * sizeof(double)), zMbar(S->lay, S->m));
 }
 
@@ -538,7 +541,7 @@ __device__ __noinline__ long long lz_primal_iter(LZS *S, int q, int np) {
   // the leaving variable goes to the bound it runs into (as primal_ratio_row, phase 2)
   const int atq = (bi.idx & LZ_FXBIT) ? MVB_AT_FX
                                       : ((dir > 0 ? colN[r] : -colN[r]) < 0.0 ? MVB_AT_LB : MVB_AT_UB);
-  if (tid == 0) lz_issue_row(S, r);  // TMA; per-thread ld.cg of the owned columns measured 2 % slower
+  if (tid == 0) lz_issue_row(S, r, np);  // TMA; per-thread ld.cg of the owned columns measured 2 % slower
   // the step, derived by every thread from the published column
   const double colr = colN[r];
   const double inv = 1.0 / colr;
@@ -659,7 +662,7 @@ __device__ __noinline__ int lz_dual_select(LZS *S, int issue) {
   if (S->ty.iters >= S->max_iters) return -2;
   if (issue) {
     lz_need_tableau(S);
-    if (tid == 0) lz_issue_row(S, r);
+    if (tid == 0) lz_issue_row(S, r, S->np);
   }
   return r;
 }
@@ -680,7 +683,7 @@ __device__ __noinline__ long long lz_dual_iter(LZS *S, int r, int np) {
   const Lay l = S->lay;
   const int m = S->m, n = S->n, ld = S->ld, tid = threadIdx.x, NT = blockDim.x;
   lz_need_tableau(S);
-  if (tid == 0) lz_issue_row(S, r);
+  if (tid == 0) lz_issue_row(S, r, np);
   const int *pend = zPend(l, m);
   double *beta = zBeta(l), *lbB = zLbB(l), *ubB = zUbB(l), *d = zD(l);
   int *head = zHead(l);

@@ -226,3 +226,26 @@ def test_many_small_lps_use_narrow_ctas_and_match(oracle, product):
     rb = solve_batch(product, B, log_pivots=1)
     for a, b, x, y in zip(A, B, ra, rb):
         _assert_same(a, b, x, y)
+
+
+def test_hbm_streaming_batch_matches_oracle(oracle, product):
+    """configs[3] shape: more 256x512 LPs than SMs in one launch, tableaux (340 MB) far beyond L2:
+    256-thread CTAs, two per SM, pending depth 8.  Every copy must reproduce the oracle's pivot
+    sequence of its template (this regime once exposed a race on the TMA slot index)."""
+    import ctypes as C
+    insts = [instances.dense_lp(256, 512, 900 + k) for k in range(16)]
+    ref = []
+    for inst in insts:
+        a = EngineLP.from_instance(oracle, inst)
+        ref.append((a.solve(), a.primal()))
+    tmpl = [EngineLP.from_instance(product, inst) for inst in insts]
+    work = [tmpl[k % 16].clone() for k in range(160)]
+    res = solve_batch(product, work)
+    G, groups, nt = C.c_int(), C.c_int(), C.c_int()
+    product.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
+    assert G.value == 1 and nt.value == 256 and groups.value == 160
+    for k, (w, r) in enumerate(zip(work, res)):
+        ra, xa = ref[k % 16]
+        for key in ("status", "iters", "pivots", "pivot_hash", "obj"):
+            assert r[key] == ra[key], (k, key)
+        assert np.array_equal(w.primal(), xa)
