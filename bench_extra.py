@@ -132,13 +132,14 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks):
     the node budget is per rank."""
     import os
     from mvolps_b200.lp import GlpProb
-    inst = instances.mdkp(args.n or 200, args.m or 50, 2024)
+    inst = instances.mdkp(args.n or 200, args.m or 50, args.inst_seed)
     prob = GlpProb.from_instance(L, inst)
     comm = nccl_comm(L, rank, world, dist) if dist is not None else None
 
     def step(lib, p, c=None):
         t0 = time.perf_counter()
-        out = p.bnb(cut_mode=args.cut_mode, batch_width=args.batch_width, max_iters=args.nodes, comm=c)
+        out = p.bnb(cut_mode=args.cut_mode, batch_width=args.batch_width, max_iters=args.nodes, comm=c,
+                    no_steal=int(args.no_steal))
         return out, time.perf_counter() - t0
 
     for _ in range(max(args.warmup, 1)):
@@ -160,14 +161,16 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks):
         "metric": "bnb_nodes_per_sec", "value": nodes / max_s, "unit": "nodes/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * max_s / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"MDKP {args.n or 200} vars x {args.m or 50} rows seed 2024, FIFO B&B, node budget "
+        "config": {"workload": f"MDKP {args.n or 200} vars x {args.m or 50} rows seed {args.inst_seed}, FIFO B&B, node budget "
                                f"{args.nodes} per rank, cut mode {args.cut_mode}, batch width {args.batch_width} "
                                "(BASELINE configs[2]); host wall clock around mvb_bnb_run[_dist] (host logic + H2D/D2H "
                                "included)" + ("; one tree node-sharded over the ranks, NCCL incumbent max-reduction "
                                               "per round" if world > 1 else ""),
                    "nodes_total": out["total_nodes"], "nodes_rank0": out["iterations"], "split_at": out["split_at"],
                    "lp_solves_rank0": out["lp_solves"], "engine_launches_rank0": out["launches"],
-                   "event_hash_rank0": str(out["event_hash"])},
+                   "event_hash_rank0": str(out["event_hash"]), "incumbent": out["incumbent"],
+                   "hit_limit_rank0": out["hit_limit"], "nodes_sent_rank0": out["nodes_sent"],
+                   "nodes_received_rank0": out["nodes_received"], "steal_rounds": out["steal_rounds"]},
         "gpu_launches": launches, "clocks": clk.summary(),
     }
     if not args.no_cpu_baseline and world == 1:

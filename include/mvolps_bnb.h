@@ -29,6 +29,10 @@ extern "C" {
 #define MVB_CUT_REF 1   /* "-cm 1": literal restatement of gmi.cpp:11-117 + cut.cpp:11-46 */
 #define MVB_CUT_GMI 2   /* textbook Gomory mixed-integer cut from the tableau row */
 
+/* work stealing of the node-sharded run (mvb_bnb_run_dist) */
+#define MVB_STEAL_LOW 4   /* a rank with fewer open nodes than this asks for more */
+#define MVB_STEAL_MAX 256 /* nodes per hand-over */
+
 typedef struct mvb_bnb_params {
   int node_strategy;
   int var_strategy;
@@ -37,6 +41,7 @@ typedef struct mvb_bnb_params {
   int max_iters;   /* node budget: stop after this many loop iterations; <=0: none
                       (the reference's own limit, bs.cpp:320, always applies) */
   int quiet;       /* !=0: do not print the tree / solution to stdout */
+  int no_steal;    /* dist: !=0 disables the node hand-over between ranks (A/B runs, tests) */
 } mvb_bnb_params;
 
 typedef struct mvb_bnb_stats {
@@ -55,6 +60,9 @@ typedef struct mvb_bnb_stats {
   long long total_nodes; /* dist: nodes processed by all ranks (serial: = iterations) */
   int cached_solves;     /* of lp_solves: requests on an LP unchanged since its last optimal solve
                             (the re-solve of bs.cpp:117 on a copy), answered without a launch */
+  int nodes_sent;        /* dist: open nodes this rank handed to poorer ranks */
+  int nodes_received;    /* dist: open nodes this rank took over from richer ranks */
+  int steal_rounds;      /* dist: rounds in which any pair of ranks exchanged nodes */
 } mvb_bnb_stats;
 
 typedef struct mvb_bnb mvb_bnb;
@@ -68,10 +76,17 @@ mvb_bnb *mvb_bnb_run(glp_prob *prob, const mvb_bnb_params *params);
  * least 4 nodes per rank; the open nodes are then dealt round-robin and each
  * rank continues on its own share, one batch per round, exchanging only the
  * incumbent (comm->allreduce_max: the bound test of bs.cpp:210 uses the best
- * incumbent of ALL ranks) and the number of open nodes (termination).  There
- * is no node hand-over after the split.  Exact search: the optimum equals the
- * serial one; node order, oids and tree text are per rank and NOT those of
- * the serial run (the non-sequence-identical mode).
+ * incumbent of ALL ranks) and the per-rank numbers of open nodes (termination
+ * and balancing).  Work stealing: every round all ranks derive the same
+ * matching from those counts -- the poorest rank with fewer than
+ * MVB_STEAL_LOW open nodes is paired with the richest, which hands over half
+ * of the difference (at most MVB_STEAL_MAX nodes, newest first) through
+ * comm->sendrecv_host; a node travels as its column bounds + cut rows + bound
+ * (the root problem is known everywhere) and is re-solved from the slack
+ * basis by the receiver.  Exact search: the optimum equals the serial one;
+ * node order, oids and tree text are per rank and NOT those of the serial
+ * run (the non-sequence-identical mode); a received node hangs
+ * under the root in the receiver's tree.
  * Results per rank: its own tree / events; stats.incumbent is the global
  * optimum on every rank, mvb_bnb_get_incumbent returns the winning x on every
  * rank, stats.iterations counts the nodes this rank processed. */

@@ -23,6 +23,12 @@ typedef struct mvb_comm {
   int (*allreduce_max)(void *ctx, double *vals, int count);
   /* release ctx */
   void (*destroy)(void *ctx);
+  /* node hand-over (work stealing, include/mvolps_bnb.h): blocking exchange of
+   * HOST buffers between the two ranks of a pair.  Send sbytes to rank dst
+   * (dst < 0: nothing to send) and receive rbytes from rank src (src < 0:
+   * nothing to receive); only the ranks of a pair call it.  May be NULL: the
+   * node-sharded tree then runs without hand-over.  0 = ok */
+  int (*sendrecv_host)(void *ctx, const void *send, size_t sbytes, int dst, void *recv, size_t rbytes, int src);
 } mvb_comm;
 
 #ifdef __cplusplus

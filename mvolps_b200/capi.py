@@ -73,7 +73,7 @@ class Opts(C.Structure):
 
 class BnbParams(C.Structure):
     _fields_ = [("node_strategy", C.c_int), ("var_strategy", C.c_int), ("cut_mode", C.c_int),
-                ("batch_width", C.c_int), ("max_iters", C.c_int), ("quiet", C.c_int)]
+                ("batch_width", C.c_int), ("max_iters", C.c_int), ("quiet", C.c_int), ("no_steal", C.c_int)]
 
 
 class BnbStats(C.Structure):
@@ -82,7 +82,8 @@ class BnbStats(C.Structure):
         ("simplex_iters", C.c_longlong), ("has_incumbent", C.c_int), ("incumbent_oid", C.c_int),
         ("incumbent", C.c_double), ("hit_limit", C.c_int), ("event_hash", C.c_ulonglong),
         ("split_at", C.c_int), ("incumbent_rank", C.c_int), ("total_nodes", C.c_longlong),
-        ("cached_solves", C.c_int),
+        ("cached_solves", C.c_int), ("nodes_sent", C.c_int), ("nodes_received", C.c_int),
+        ("steal_rounds", C.c_int),
     ]
 
 
@@ -193,12 +194,14 @@ def _bind(lib):
 ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p)
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, _dp, C.c_int)
 DESTROY_FN = C.CFUNCTYPE(None, C.c_void_p)
+SENDRECV_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.c_int)
 
 
 class Comm(C.Structure):
     """struct mvb_comm (include/mvolps_dist.h): a caller-supplied communicator."""
     _fields_ = [("ctx", C.c_void_p), ("rank", C.c_int), ("world", C.c_int),
-                ("allgather_dev", ALLGATHER_FN), ("allreduce_max", ALLREDUCE_FN), ("destroy", DESTROY_FN)]
+                ("allgather_dev", ALLGATHER_FN), ("allreduce_max", ALLREDUCE_FN), ("destroy", DESTROY_FN),
+                ("sendrecv_host", SENDRECV_FN)]
 
 
 def load_library(path):

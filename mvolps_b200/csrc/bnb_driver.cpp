@@ -143,6 +143,77 @@ struct Driver {
     return n;
   }
 
+  // ---- node hand-over between ranks (work stealing) ----
+  // A node is the root problem + its column bounds + the cut rows appended on
+  // the way down (bs.cpp:274,282; cut.cpp:38-45), so only those travel:
+  // [upperBound, depth, extra rows, per column (type, lb, ub), per extra row
+  // (type, lb, ub, len, (ind, val) x len)], all as doubles.
+  void pack_node(const Node &nd, std::vector<double> &buf) {
+    const glp_prob *a = nd.prob;
+    const size_t m0 = root_prob->rows.size();
+    buf.push_back(nd.upperBound);
+    buf.push_back((double)tree[nd.oid].depth);
+    buf.push_back((double)(a->rows.size() - m0));
+    for (const MvCol &c : a->cols) { buf.push_back(c.type); buf.push_back(c.lb); buf.push_back(c.ub); }
+    for (size_t i = m0; i < a->rows.size(); i++) {
+      const MvRow &r = a->rows[i];
+      buf.push_back(r.type); buf.push_back(r.lb); buf.push_back(r.ub);
+      buf.push_back((double)r.ind.size());
+      for (size_t t = 0; t < r.ind.size(); t++) { buf.push_back(r.ind[t]); buf.push_back(r.val[t]); }
+    }
+  }
+  // rebuilds the node through the glpk boundary (the calls a host program would make), so the
+  // engine mirror sees a fresh LP: its first solve starts from the slack basis
+  std::unique_ptr<Node> unpack_node(const double *&p) {
+    glp_prob *c = glp_create_prob();
+    glp_copy_prob(c, root_prob, GLP_ON);
+    const double ub = *p++;
+    const int depth = (int)*p++;
+    const int extra = (int)*p++;
+    const int n = glp_get_num_cols(c);
+    for (int j = 1; j <= n; j++, p += 3) {
+      const MvCol &r = root_prob->cols[j - 1];
+      if ((int)p[0] != r.type || p[1] != r.lb || p[2] != r.ub) glp_set_col_bnds(c, j, (int)p[0], p[1], p[2]);
+    }
+    std::vector<int> ind;
+    std::vector<double> val;
+    for (int k = 0; k < extra; k++) {
+      const int type = (int)p[0], len = (int)p[3];
+      const int i = glp_add_rows(c, 1);
+      glp_set_row_bnds(c, i, type, p[1], p[2]);
+      ind.assign(1, 0); val.assign(1, 0.0);
+      for (int t = 0; t < len; t++) { ind.push_back((int)p[4 + 2 * t]); val.push_back(p[5 + 2 * t]); }
+      glp_set_mat_row(c, i, len, ind.data(), val.data());
+      p += 4 + 2 * (size_t)len;
+    }
+    auto nd = make_node(c);
+    nd->upperBound = ub;
+    tree[nd->oid] = TreeRec{nd->oid, 1, depth, P_NONE, {}};
+    tree[1].kids.push_back(nd->oid);
+    return nd;
+  }
+  struct StealPair { int donor, thief, k; };
+  // the matching every rank derives from the same open-node counts (cnt < 0: retired rank):
+  // poorest unused rank below MVB_STEAL_LOW with the richest unused rank, half of the
+  // difference, ties to the lowest rank; a rank takes part in one pair per round
+  static std::vector<StealPair> steal_matching(const std::vector<double> &cnt) {
+    std::vector<StealPair> pairs;
+    std::vector<char> used(cnt.size(), 0);
+    while (true) {
+      int lo = -1, hi = -1;
+      for (int r = 0; r < (int)cnt.size(); r++) {
+        if (used[r] || cnt[r] < 0) continue;
+        if (lo < 0 || cnt[r] < cnt[lo]) lo = r;
+        if (hi < 0 || cnt[r] > cnt[hi]) hi = r;
+      }
+      if (lo < 0 || lo == hi || cnt[lo] >= MVB_STEAL_LOW || cnt[hi] - cnt[lo] < 2) break;
+      const int k = std::min<int>((int)((cnt[hi] - cnt[lo]) / 2), MVB_STEAL_MAX);
+      pairs.push_back(StealPair{hi, lo, k});
+      used[lo] = used[hi] = 1;
+    }
+    return pairs;
+  }
+
   double t_sync = 0, t_solve = 0, t_pull = 0, t_copy = 0;  // MVOLPS_BNB_TIMING=1 prints them
   static double now() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -420,15 +491,48 @@ bool Driver::run() {
   };
 
   const bool dist = comm != nullptr && comm->world > 1;
+  const bool steal = dist && !pr.no_steal && comm->sendrecv_host != nullptr;
   bool split = false;        // dist: the queue has been dealt out, ranks now work on their own share
   bool retired = false;      // dist: this rank hit its budget and only takes part in the exchanges
   int inc_rank = 0;
   out->st.split_at = -1;
   while (true) {
     if (dist && split) {     // termination is global: somebody still has open nodes
-      double alive = retired ? 0.0 : (double)open.size();
-      if (!reduce_max(&alive, 1)) return false;
-      if (alive == 0.0) break;
+      std::vector<double> cnt(comm->world, -inf);
+      cnt[comm->rank] = retired ? -1.0 : (double)open.size();
+      if (!reduce_max(cnt.data(), comm->world)) return false;
+      if (*std::max_element(cnt.begin(), cnt.end()) <= 0.0) break;
+      if (steal) {           // work stealing: poor ranks take over open nodes of rich ones
+        const auto pairs = steal_matching(cnt);
+        if (!pairs.empty()) out->st.steal_rounds++;
+        for (const StealPair &sp : pairs) {
+          if (sp.donor == comm->rank) {
+            std::vector<double> buf(1, 0.0);
+            for (int k = 0; k < sp.k; k++) {  // newest first
+              pack_node(*open.back(), buf);
+              open.pop_back();
+            }
+            buf[0] = (double)buf.size();
+            if (comm->sendrecv_host(comm->ctx, buf.data(), sizeof(double), sp.thief, nullptr, 0, -1)) return false;
+            if (comm->sendrecv_host(comm->ctx, buf.data(), buf.size() * sizeof(double), sp.thief, nullptr, 0, -1))
+              return false;
+            out->st.nodes_sent += sp.k;
+          } else if (sp.thief == comm->rank) {
+            double len = 0;
+            if (comm->sendrecv_host(comm->ctx, nullptr, 0, -1, &len, sizeof(double), sp.donor)) return false;
+            std::vector<double> buf((size_t)len);
+            if (comm->sendrecv_host(comm->ctx, nullptr, 0, -1, buf.data(), buf.size() * sizeof(double), sp.donor))
+              return false;
+            const double *p = buf.data() + 1;
+            for (int k = 0; k < sp.k; k++) {
+              auto nd = unpack_node(p);
+              ev_line("candidate", nd->oid, sstr(" ", nd->upperBound));
+              open.push_back(std::move(nd));
+            }
+            out->st.nodes_received += sp.k;
+          }
+        }
+      }
     } else if (open.empty() || stop) {
       break;
     }

@@ -357,6 +357,10 @@ struct NcclApi {
   int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
   int (*CommDestroy)(void *) = nullptr;
   const char *(*GetErrorString)(int) = nullptr;
+  int (*Send)(const void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+  int (*Recv)(void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
 };
 NcclApi g_nccl;
 
@@ -373,6 +377,10 @@ bool nccl_load() {
   g_nccl.AllReduce = (decltype(g_nccl.AllReduce))dlsym(h, "ncclAllReduce");
   g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(h, "ncclCommDestroy");
   g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(h, "ncclGetErrorString");
+  g_nccl.Send = (decltype(g_nccl.Send))dlsym(h, "ncclSend");
+  g_nccl.Recv = (decltype(g_nccl.Recv))dlsym(h, "ncclRecv");
+  g_nccl.GroupStart = (decltype(g_nccl.GroupStart))dlsym(h, "ncclGroupStart");
+  g_nccl.GroupEnd = (decltype(g_nccl.GroupEnd))dlsym(h, "ncclGroupEnd");
   if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.AllReduce ||
       !g_nccl.CommDestroy)
     return fail("NCCL library lacks a required symbol");
@@ -383,6 +391,8 @@ bool nccl_load() {
 struct NcclCtx {
   void *comm = nullptr;
   double *dbuf = nullptr;  // device scratch for the small host reductions
+  char *xbuf = nullptr;    // device staging of the node hand-over (grown on demand)
+  size_t xcap = 0;
 };
 
 int nccl_allgather(void *ctx, const void *send, void *recv, size_t bytes, void *stream) {
@@ -401,10 +411,34 @@ int nccl_allreduce_max(void *ctx, double *vals, int count) {
   if (cudaMemcpyAsync(vals, c->dbuf, count * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
   return cudaStreamSynchronize(st) == cudaSuccess ? 0 : -1;
 }
+// node hand-over between the two ranks of a pair: host buffer -> device staging -> ncclSend /
+// ncclRecv over NVLink -> host buffer (a hand-over is a few hundred KB once in a while)
+int nccl_sendrecv_host(void *ctx, const void *send, size_t sbytes, int dst, void *recv, size_t rbytes, int src) {
+  NcclCtx *c = (NcclCtx *)ctx;
+  const size_t need = std::max(sbytes, rbytes);
+  if (need > c->xcap) {
+    if (c->xbuf) cudaFree(c->xbuf);
+    c->xcap = 0;
+    if (cudaMalloc((void **)&c->xbuf, need * 2) != cudaSuccess) { g_err = "sendrecv_host: cudaMalloc failed"; return -1; }
+    c->xcap = need * 2;
+  }
+  cudaStream_t st = g_ctx.stream;
+  if (dst >= 0 && src >= 0) { g_err = "sendrecv_host: a rank either sends or receives"; return -1; }
+  if (dst >= 0) {
+    if (cudaMemcpyAsync(c->xbuf, send, sbytes, cudaMemcpyHostToDevice, st) != cudaSuccess) return -1;
+    if (g_nccl.Send(c->xbuf, sbytes, /*ncclChar*/ 0, dst, c->comm, st)) { g_err = "ncclSend failed"; return -1; }
+  }
+  if (src >= 0) {
+    if (g_nccl.Recv(c->xbuf, rbytes, /*ncclChar*/ 0, src, c->comm, st)) { g_err = "ncclRecv failed"; return -1; }
+    if (cudaMemcpyAsync(recv, c->xbuf, rbytes, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
+  }
+  return cudaStreamSynchronize(st) == cudaSuccess ? 0 : -1;
+}
 void nccl_destroy(void *ctx) {
   NcclCtx *c = (NcclCtx *)ctx;
   if (c->comm) g_nccl.CommDestroy(c->comm);
   if (c->dbuf) cudaFree(c->dbuf);
+  if (c->xbuf) cudaFree(c->xbuf);
   delete c;
 }
 
@@ -435,6 +469,7 @@ mvb_comm *mvb_comm_nccl(const void *id, int rank, int world) {
   m->allgather_dev = nccl_allgather;
   m->allreduce_max = nccl_allreduce_max;
   m->destroy = nccl_destroy;
+  m->sendrecv_host = (g_nccl.Send && g_nccl.Recv) ? nccl_sendrecv_host : nullptr;
   return m;
 }
 

@@ -113,7 +113,18 @@ def torch_comm(dist):
             vals[i] = float(t[i])
         return 0
 
+    def sendrecv_host(ctx, send, sbytes, dst, recv, rbytes, src):
+        if dst >= 0:
+            t = torch.frombuffer((C.c_char * sbytes).from_address(send), dtype=torch.uint8)
+            dist.send(t.clone(), dst)
+        if src >= 0:
+            t = torch.empty(rbytes, dtype=torch.uint8)
+            dist.recv(t, src)
+            C.memmove(recv, t.numpy().ctypes.data, rbytes)
+        return 0
+
     cb = capi.ALLREDUCE_FN(allreduce_max)
-    comm = capi.Comm(None, dist.get_rank(), dist.get_world_size(), capi.ALLGATHER_FN(), cb, capi.DESTROY_FN())
-    comm._keep = cb
+    sr = capi.SENDRECV_FN(sendrecv_host)
+    comm = capi.Comm(None, dist.get_rank(), dist.get_world_size(), capi.ALLGATHER_FN(), cb, capi.DESTROY_FN(), sr)
+    comm._keep = (cb, sr)
     return comm

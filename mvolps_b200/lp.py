@@ -211,10 +211,11 @@ class GlpProb:
         self.lib.glp_copy_prob(c.h, self.h, capi.GLP_ON)
         return c
 
-    def bnb(self, node_strategy=0, var_strategy=0, cut_mode=0, batch_width=0, max_iters=0, comm=None):
+    def bnb(self, node_strategy=0, var_strategy=0, cut_mode=0, batch_width=0, max_iters=0, comm=None,
+            no_steal=0):
         """comm: None (serial driver) or a communicator (capi.Comm / pointer) for the node-sharded run."""
         L = self.lib
-        p = capi.BnbParams(node_strategy, var_strategy, cut_mode, batch_width, max_iters, 1)
+        p = capi.BnbParams(node_strategy, var_strategy, cut_mode, batch_width, max_iters, 1, no_steal)
         if comm is None:
             hb = L.mvb_bnb_run(self.h, C.byref(p))
         else:

@@ -137,6 +137,78 @@ def test_node_sharded_bnb_world2_gloo():
             assert abs(a["incumbent"] - gold[name]["highs_ilp"]) < 1e-9
 
 
+def _steal_worker(rank, world, port, q, oracle_lib):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from mvolps_b200.lp import GlpProb
+        orc = capi.load_library(oracle_lib)
+        orc.glp_term_out(capi.GLP_OFF)
+        comm = torch_comm(dist)
+        res = {}
+        for args, cm in (((15, 5, 2), 0), ((20, 5, 3), 2)):
+            for ns in (1, 0):
+                out = GlpProb.from_instance(orc, instances.mdkp(*args)).bnb(batch_width=8, comm=comm, no_steal=ns,
+                                                                            cut_mode=cm)
+                res[(args, cm, ns)] = {k: out[k] for k in ("incumbent", "iterations", "total_nodes", "nodes_sent",
+                                                          "nodes_received", "steal_rounds", "has_incumbent")}
+                res[(args, cm, ns)]["x"] = out["x"].tolist()
+                res[(args, cm, ns)]["stolen_in_tree"] = out["tree"].count("\n")
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_work_stealing_world3_gloo():
+    """Node hand-over (mvb_comm::sendrecv_host, SURVEY 8e C2) on 3 ranks over gloo with the CPU
+    engine: every node sent is received by exactly one rank, the search stays exact (serial
+    optimum, with and without cut rows travelling along), and the ranks end up balanced."""
+    from mvolps_b200.lp import GlpProb
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    oracle_lib = os.path.join(root, "oracle", "_build", "libglpk_oracle.so")
+    world = 3
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_steal_worker, args=(r, world, port, q, oracle_lib)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=600) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    orc = capi.load_library(oracle_lib)
+    orc.glp_term_out(capi.GLP_OFF)
+    for args, cm in (((15, 5, 2), 0), ((20, 5, 3), 2)):
+        serial = GlpProb.from_instance(orc, instances.mdkp(*args)).bnb(cut_mode=cm)
+        off = [res[r][(args, cm, 1)] for r in range(world)]
+        on = [res[r][(args, cm, 0)] for r in range(world)]
+        for rr in off + on:
+            assert rr["has_incumbent"] and rr["incumbent"] == serial["incumbent"]
+        assert all(rr["x"] == on[0]["x"] for rr in on)
+        assert all(rr["nodes_sent"] == rr["nodes_received"] == rr["steal_rounds"] == 0 for rr in off)
+        sent, got = sum(rr["nodes_sent"] for rr in on), sum(rr["nodes_received"] for rr in on)
+        assert sent == got > 0                                  # nothing lost, nothing duplicated
+        assert len({rr["steal_rounds"] for rr in on}) == 1      # same matching on every rank
+        its_on, its_off = [rr["iterations"] for rr in on], [rr["iterations"] for rr in off]
+        assert max(its_on) - min(its_on) < max(its_off) - min(its_off)  # balanced
+        assert sum(its_on) == on[0]["total_nodes"]
+
+
+def test_steal_matching_rule(lib):
+    """The matching is a pure function of the open-node counts (identical on every rank)."""
+    # exercised through a 1-rank world: no partner -> no hand-over, the run equals the serial one
+    from mvolps_b200.lp import GlpProb
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    orc = capi.load_library(os.path.join(root, "oracle", "_build", "libglpk_oracle.so"))
+    orc.glp_term_out(capi.GLP_OFF)
+    comm = capi.Comm(None, 0, 1, capi.ALLGATHER_FN(), capi.ALLREDUCE_FN(), capi.DESTROY_FN(), capi.SENDRECV_FN())
+    a = GlpProb.from_instance(orc, instances.mdkp(12, 4, 1)).bnb(comm=comm)
+    b = GlpProb.from_instance(orc, instances.mdkp(12, 4, 1)).bnb()
+    assert a["tree"] == b["tree"] and a["nodes_sent"] == 0 and a["event_hash"] == b["event_hash"]
+
+
 def test_incumbent_exchange_world2_gloo(lib):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
