@@ -15,6 +15,17 @@
 // are the only synchronisation; the control block ping-pongs by iteration
 // parity so a finished solve turns the remaining launches of a chunk into
 // no-ops.
+//
+// Exchange step, one process per GPU: the price kernel PUSHES its record
+// straight into every peer's mailbox over NVLink (peer pointers from CUDA IPC)
+// and raises a per-sender arrival counter there; the decide kernel waits on
+// the counters in its own memory.  No collective launch, no host in between:
+// the pack, the transfer and the hand-shake are part of the two kernels that
+// produce and consume the record.  The mailbox has SHARD_SLOTS records per
+// sender (slot = iteration mod SHARD_SLOTS) because a fast rank may run up to
+// two iterations ahead of a peer whose update kernels still read older
+// columns.  ncclAllGather into the same slots is kept as the path of
+// MVOLPS_SHARD_EXCHANGE=nccl (A/B runs) and when IPC is not available.
 #pragma once
 #include <dlfcn.h>
 
@@ -44,7 +55,12 @@ struct ShardStep {  // what iteration t leaves for its update kernel and for the
   int qloc;    // local position of the entering column, outside [0, nloc) when another rank owns it
   int wk;      // rank whose record holds the pivot column
   int src;     // tableau buffer the update reads (it writes src ^ 1)
+  int slot;    // mailbox slot that holds the records of this iteration
 };
+constexpr int SHARD_SLOTS = 4;       // mailbox depth (iterations in flight across the ranks: 3)
+constexpr int SHARD_MAX_PEERS = 16;
+constexpr int SHARD_ST_TIMEOUT = 100;  // ctl.status: a peer's record did not arrive
+constexpr unsigned long long SHARD_WAIT_NS = 10ULL * 1000 * 1000 * 1000;
 
 struct ShardDev {
   int m, nloc, ld, col0, world, max_iters;
@@ -57,8 +73,13 @@ struct ShardDev {
   ShardCtl *ctl;    // [2] by iteration parity
   ShardStep *step;  // [2] by iteration parity
   double *rho[2];   // scaled pivot row over the local columns, by iteration parity
-  unsigned char *send, *recv[2];
+  unsigned char *send, *recv[SHARD_SLOTS];  // recv[slot]: world records, by sender rank
   size_t rec_bytes;
+  // peer exchange (nullptr / 0 when the host copies or NCCL moves the records)
+  int rank, push;
+  unsigned long long *flag;                    // [SHARD_SLOTS][world] arrival counters, in this rank's mailbox
+  unsigned char *peer[SHARD_MAX_PEERS];        // base of every rank's mailbox as mapped here (own included)
+  size_t flag_off;                             // offset of the counters inside a mailbox
   int *pivlog;
   int pivlog_cap;
 };
@@ -88,7 +109,7 @@ __device__ __forceinline__ ShardView shard_view(const ShardDev &D, const ShardCt
     const ShardStep st = D.step[par ^ 1];
     v.T = D.T[c.cur ^ 1];
     v.rho = D.rho[par ^ 1];
-    v.col = reinterpret_cast<const double *>(D.recv[par ^ 1] + (size_t)st.wk * D.rec_bytes + SHARD_HDR);
+    v.col = reinterpret_cast<const double *>(D.recv[st.slot] + (size_t)st.wk * D.rec_bytes + SHARD_HDR);
     v.r = st.r;
     v.qloc = st.qloc;
   } else {
@@ -105,11 +126,10 @@ __device__ __forceinline__ ShardView shard_view(const ShardDev &D, const ShardCt
 // record.  Every CTA of the (small) grid repeats the cheap argmin over the
 // local reduced costs and then gathers its own slice of the column rows, so the
 // strided gather (one 32-byte sector per element) runs on several SMs.
-__global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int par) {
+__global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int par, int slot) {
   __shared__ Key red[32];
   const ShardCtl c = D.ctl[par];
-  Cand *out = reinterpret_cast<Cand *>(D.send);
-  if (c.status != -1) return;
+  if (c.status != -1) return;  // finished on every rank alike: nobody waits for a record
   const ShardView V = shard_view(D, c, par);
   const bool bland = c.degen >= MVB_BLAND_AFTER;
   const int *at = D.at[c.cS], *nb = D.nb[c.cS];
@@ -124,6 +144,9 @@ __global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int pa
   }
   best = block_argmin(best, red);  // result on every thread, identical in every CTA
   const int q = best.idx;
+  // where the record goes: the send buffer (host copy / NCCL) or this rank's place in every mailbox
+  const int ndst = D.push ? D.world : 1;
+  const size_t place = (size_t)slot * D.world * D.rec_bytes + (size_t)D.rank * D.rec_bytes;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     Cand h{};
     h.key = q >= 0 ? best.k : ~0ULL;
@@ -132,12 +155,49 @@ __global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int pa
     h.flag = q >= 0 ? at[q] : 0;
     h.lq = q >= 0 ? D.lb[best.var] : 0.0;
     h.uq = q >= 0 ? D.ub[best.var] : 0.0;
-    *out = h;
+    for (int k = 0; k < ndst; k++) *reinterpret_cast<Cand *>(D.push ? D.peer[k] + place : D.send) = h;
   }
-  if (q < 0) return;
-  double *col = reinterpret_cast<double *>(D.send + SHARD_HDR);
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= D.m; i += gridDim.x * blockDim.x)
-    col[i] = V.at(i, q);
+  if (q >= 0)
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i <= D.m; i += gridDim.x * blockDim.x) {
+      const double v = V.at(i, q);
+      for (int k = 0; k < ndst; k++)
+        reinterpret_cast<double *>((D.push ? D.peer[k] + place : D.send) + SHARD_HDR)[i] = v;
+    }
+  if (!D.push) return;
+  // arrival: this CTA's stores are ordered before its increment of the sender's counter in
+  // every mailbox (bar.sync, then fence.sys + atomic by one thread); the receiver expects
+  // gridDim.x increments per use of the slot
+  __syncthreads();
+  if (threadIdx.x < D.world) {
+    __threadfence_system();
+    unsigned long long *f = reinterpret_cast<unsigned long long *>(D.peer[threadIdx.x] + D.flag_off) +
+                            (size_t)slot * D.world + D.rank;
+    atomicAdd_system(f, 1ULL);
+  }
+}
+
+// the records of `slot` from every rank have landed (pushed by the peers' price kernels):
+// one thread per sender spins on its counter with acquire loads; false on time-out
+__device__ bool shard_wait_records(const ShardDev &D, int slot, unsigned long long expect, int *flagS) {
+  if (threadIdx.x == 0) *flagS = 1;
+  __syncthreads();
+  if (threadIdx.x < D.world) {
+    const unsigned long long *f = D.flag + (size_t)slot * D.world + threadIdx.x;
+    unsigned long long t0 = 0, v;
+    unsigned spins = 0;
+    while (true) {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(f) : "memory");
+      if (v >= expect) break;
+      if ((++spins & 1023u) == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+        if (!t0) t0 = now;
+        else if (now - t0 > SHARD_WAIT_NS) { *flagS = 0; break; }
+      }
+    }
+  }
+  __syncthreads();
+  return *flagS != 0;
 }
 
 // rank-1 update of this CTA's share of the local columns: pivot column from
@@ -205,15 +265,23 @@ namespace {
 // cheap part): global winner, replicated K2 ratio test, the step, the next
 // small state, and the scaled pivot row rho over the local columns (K3) for
 // the update kernel and for the readers of the next iteration.
-__global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int par) {
+__global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int par, int slot,
+                                                              unsigned long long expect) {
   __shared__ Smem sm;
+  __shared__ int arrived;
   const ShardCtl c = D.ctl[par];
   ShardCtl *next = &D.ctl[par ^ 1];
   const bool lead = blockIdx.x == 0 && threadIdx.x == 0;
   ShardCtl n = c;
   n.pend = 0;
   ShardStep stp{};
+  stp.slot = slot;
   if (c.status != -1) {
+    if (lead) { *next = n; D.step[par] = stp; }
+    return;
+  }
+  if (D.push && !shard_wait_records(D, slot, expect, &arrived)) {
+    n.status = SHARD_ST_TIMEOUT;
     if (lead) { *next = n; D.step[par] = stp; }
     return;
   }
@@ -223,7 +291,7 @@ __global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int pa
   unsigned long long bk = ~0ULL;
   int bvar = 0x7fffffff;
   for (int k = 0; k < D.world; k++) {
-    const Cand *h = reinterpret_cast<const Cand *>(D.recv[par] + (size_t)k * D.rec_bytes);
+    const Cand *h = reinterpret_cast<const Cand *>(D.recv[slot] + (size_t)k * D.rec_bytes);
     if (h->pos < 0) continue;
     if (h->key < bk || (h->key == bk && h->var < bvar)) { bk = h->key; bvar = h->var; wk = k; }
   }
@@ -237,8 +305,8 @@ __global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int pa
     if (lead) { *next = n; D.step[par] = stp; }
     return;
   }
-  const Cand cand = *reinterpret_cast<const Cand *>(D.recv[par] + (size_t)wk * D.rec_bytes);
-  const double *col = reinterpret_cast<const double *>(D.recv[par] + (size_t)wk * D.rec_bytes + SHARD_HDR);
+  const Cand cand = *reinterpret_cast<const Cand *>(D.recv[slot] + (size_t)wk * D.rec_bytes);
+  const double *col = reinterpret_cast<const double *>(D.recv[slot] + (size_t)wk * D.rec_bytes + SHARD_HDR);
   const bool bland = c.degen >= MVB_BLAND_AFTER;
   const double *beta = D.beta[c.cS];
   const int *head = D.head[c.cS];
@@ -337,7 +405,7 @@ __global__ void __launch_bounds__(512, 1) shard_update_kernel(ShardDev D, int pa
   __shared__ Smem sm;
   const ShardStep st = D.step[par];
   if (!st.valid) return;
-  const double *col = reinterpret_cast<const double *>(D.recv[par] + (size_t)st.wk * D.rec_bytes + SHARD_HDR);
+  const double *col = reinterpret_cast<const double *>(D.recv[st.slot] + (size_t)st.wk * D.rec_bytes + SHARD_HDR);
   shard_tile_update(D, D.T[st.src], D.T[st.src ^ 1], st.r, st.qloc, D.rho[par], col, sm);
 }
 
@@ -554,7 +622,8 @@ bool shard_alloc(mvb_shard *s) {
   size_t oc = take((size_t)s->ld * sizeof(double));
   size_t octl = take(2 * sizeof(ShardCtl)), ostep = take(2 * sizeof(ShardStep));
   size_t orho0 = take((size_t)s->ld * sizeof(double)), orho1 = take((size_t)s->ld * sizeof(double));
-  size_t osend = take(rec), orecv0 = take(rec * s->world), orecv1 = take(rec * s->world);
+  size_t osend = take(rec), orecv[SHARD_SLOTS];
+  for (int k = 0; k < SHARD_SLOTS; k++) orecv[k] = take(rec * s->world);
   size_t ofs = take(s->fin_bytes), ofr = take(s->fin_bytes * s->world);
   CK(cudaMallocAsync((void **)&s->slab, off, g_ctx.stream));
   CK(cudaMemsetAsync(s->slab, 0, off, g_ctx.stream));
@@ -572,10 +641,86 @@ bool shard_alloc(mvb_shard *s) {
   d.step = (ShardStep *)(b + ostep);
   d.rho[0] = (double *)(b + orho0); d.rho[1] = (double *)(b + orho1);
   d.send = (unsigned char *)(b + osend);
-  d.recv[0] = (unsigned char *)(b + orecv0); d.recv[1] = (unsigned char *)(b + orecv1);
+  for (int k = 0; k < SHARD_SLOTS; k++) d.recv[k] = (unsigned char *)(b + orecv[k]);
   d.rec_bytes = rec;
+  d.rank = s->rank;
+  d.push = 0;
+  d.flag = nullptr;
+  d.flag_off = 0;
   s->fin_send = (unsigned char *)(b + ofs); s->fin_recv = (unsigned char *)(b + ofr);
   return true;
+}
+
+// ---- peer mailbox: one per process, exported through CUDA IPC, mapped by every peer ----
+// layout (identical on every rank): SHARD_SLOTS x world records, then SHARD_SLOTS x world counters
+struct PeerMail {
+  unsigned char *base = nullptr;
+  size_t rec = 0, flag_off = 0, bytes = 0;
+  int world = 0;
+  unsigned char *peer[SHARD_MAX_PEERS] = {};
+  bool failed = false;  // IPC is not available here: every rank stays on ncclAllGather
+};
+PeerMail g_mail;
+
+// collective over the ranks of s->comm; 1: s->dev points into the mailboxes, 0: no peer path, -1: error
+int shard_peer_setup(mvb_shard *s) {
+  const mvb_comm *cm = s->comm;
+  const char *mode = getenv("MVOLPS_SHARD_EXCHANGE");
+  if (mode && !strcmp(mode, "nccl")) return 0;
+  if (s->world < 2 || s->world > SHARD_MAX_PEERS || !cm->allgather_dev || !cm->allreduce_max) return 0;
+  if (g_mail.failed) return 0;
+  cudaStream_t st = g_ctx.stream;
+  const size_t rec = s->dev.rec_bytes;
+  if (!g_mail.base || g_mail.rec != rec || g_mail.world != s->world) {
+    // (a mailbox of another shape stays mapped until the process ends: peers may hold it open)
+    PeerMail nm;
+    nm.rec = rec;
+    nm.world = s->world;
+    nm.flag_off = align_up((size_t)SHARD_SLOTS * s->world * rec, 256);
+    nm.bytes = std::max<size_t>(nm.flag_off + (size_t)SHARD_SLOTS * s->world * sizeof(unsigned long long), 1 << 16);
+    double bad = 0.0;
+    cudaIpcMemHandle_t mine{};
+    std::vector<cudaIpcMemHandle_t> all(s->world);
+    if (cudaMalloc((void **)&nm.base, nm.bytes) != cudaSuccess || cudaIpcGetMemHandle(&mine, nm.base) != cudaSuccess) {
+      cudaGetLastError();
+      bad = 1.0;
+    }
+    if (nm.base) {  // the handles travel through the mailbox itself (not in use yet)
+      cudaMemcpyAsync(nm.base, &mine, sizeof(mine), cudaMemcpyHostToDevice, st);
+      if (cm->allgather_dev(cm->ctx, nm.base, nm.base + 4096, sizeof(mine), st)) { g_err = "peer set-up: all-gather failed"; return -1; }
+      cudaMemcpyAsync(all.data(), nm.base + 4096, sizeof(mine) * s->world, cudaMemcpyDeviceToHost, st);
+      if (cudaStreamSynchronize(st) != cudaSuccess) bad = 1.0;
+    }
+    if (bad == 0.0)
+      for (int k = 0; k < s->world; k++) {
+        if (k == s->rank) { nm.peer[k] = nm.base; continue; }
+        void *p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, all[k], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+          cudaGetLastError();
+          bad = 1.0;
+          break;
+        }
+        nm.peer[k] = (unsigned char *)p;
+      }
+    if (cm->allreduce_max(cm->ctx, &bad, 1)) { g_err = "peer set-up: reduction failed"; return -1; }
+    if (bad != 0.0) {
+      if (getenv("MVOLPS_VERBOSE")) std::fprintf(stderr, "mvolps: CUDA IPC unavailable, exchange stays on ncclAllGather\n");
+      g_mail.failed = true;
+      return 0;
+    }
+    g_mail = nm;
+  }
+  ShardDev &d = s->dev;
+  for (int k = 0; k < SHARD_SLOTS; k++) d.recv[k] = g_mail.base + (size_t)k * s->world * rec;
+  for (int k = 0; k < s->world; k++) d.peer[k] = g_mail.peer[k];
+  d.flag = (unsigned long long *)(g_mail.base + g_mail.flag_off);
+  d.flag_off = g_mail.flag_off;
+  d.push = 1;
+  // counters back to zero, and nobody pushes before every rank has done so: the (stream-ordered)
+  // all-gather below completes only after every rank has enqueued its memset
+  cudaMemsetAsync(d.flag, 0, (size_t)SHARD_SLOTS * s->world * sizeof(unsigned long long), st);
+  if (cm->allgather_dev(cm->ctx, s->fin_send, s->fin_recv, 16, st)) { g_err = "peer set-up: barrier failed"; return -1; }
+  return 1;
 }
 
 // final gather record: nb[maxloc] | at[maxloc] | cost[maxloc]
@@ -721,17 +866,22 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
   }
   if (!g_ctx.stream_upd) CKI(cudaStreamCreateWithFlags(&g_ctx.stream_upd, cudaStreamNonBlocking));
   cudaStream_t su = g_ctx.stream_upd;  // the tableau updates; `st` carries the decision chain
-  auto exchange = [&](bool fin, int par) -> bool {
+  // one process per GPU: records are pushed into the peers' mailboxes by the price kernel itself
+  const int pst = local ? 0 : shard_peer_setup(s0);
+  if (pst < 0) return -1;
+  const bool push = pst == 1;
+  auto exchange = [&](bool fin, int slot) -> bool {
+    if (push && !fin) return true;
     for (int k = 0; k < nlocal; k++) {
       mvb_shard *s = shards[k];
       const unsigned char *snd = fin ? s->fin_send : s->dev.send;
       const size_t bytes = fin ? s->fin_bytes : s->dev.rec_bytes;
       if (!local) {
-        unsigned char *rcv = fin ? s->fin_recv : s->dev.recv[par];
+        unsigned char *rcv = fin ? s->fin_recv : s->dev.recv[slot];
         if (s->comm->allgather_dev(s->comm->ctx, snd, rcv, bytes, st)) return false;
       } else {
         for (int t = 0; t < nlocal; t++) {
-          unsigned char *rcv = (fin ? shards[t]->fin_recv : shards[t]->dev.recv[par]) + (size_t)s->rank * bytes;
+          unsigned char *rcv = (fin ? shards[t]->fin_recv : shards[t]->dev.recv[slot]) + (size_t)s->rank * bytes;
           CK(cudaMemcpyAsync(rcv, snd, bytes, cudaMemcpyDeviceToDevice, st));
         }
       }
@@ -757,10 +907,12 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
       // the view of iteration t is the output of update t-2 (+ step t-1 on the fly)
       if (t_it >= 2)
         for (int k = 0; k < nlocal; k++) CKI(cudaStreamWaitEvent(st, shards[k]->ev_upd[par], 0));
-      for (int k = 0; k < nlocal; k++) shard_price_kernel<<<price_grid, 1024, 0, st>>>(shards[k]->dev, par);
-      if (!exchange(false, par)) return -1;
+      const int slot = (int)(t_it % SHARD_SLOTS);
+      const unsigned long long expect = (unsigned long long)price_grid * (unsigned long long)(t_it / SHARD_SLOTS + 1);
+      for (int k = 0; k < nlocal; k++) shard_price_kernel<<<price_grid, 1024, 0, st>>>(shards[k]->dev, par, slot);
+      if (!exchange(false, slot)) return -1;
       for (int k = 0; k < nlocal; k++) {
-        shard_decide_kernel<<<small_grid, 512, 0, st>>>(shards[k]->dev, par);
+        shard_decide_kernel<<<small_grid, 512, 0, st>>>(shards[k]->dev, par, slot, expect);
         CKI(cudaEventRecord(shards[k]->ev_dec[par], st));
       }
       for (int k = 0; k < nlocal; k++) {
@@ -776,6 +928,7 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
     CKI(cudaStreamSynchronize(st));
     if (h.status != -1) break;
   }
+  if (h.status == SHARD_ST_TIMEOUT) { g_err = "mvb_shard_solve: a peer's record did not arrive (peer exchange timed out)"; return -1; }
   // the last updates, then back to one stream
   for (int k = 0; k < nlocal; k++) {
     CKI(cudaStreamWaitEvent(st, shards[k]->ev_upd[0], 0));
