@@ -96,6 +96,7 @@ def run_shard(args, L, rank, world, local, dist, ClockSampler, peaks):
             if k == max(args.warmup, 1):
                 l0 = L.mvb_kernel_launches()
             r = g.solve(max_iters=args.pivots)
+            how = g.last_exchange()
             if k >= max(args.warmup, 1):
                 tot_ms += g.last_ms()
                 tot_piv += r["pivots"]
@@ -112,13 +113,13 @@ def run_shard(args, L, rank, world, local, dist, ClockSampler, peaks):
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"dense LP m={m} n={n} seed=5, tableau column-sharded over {world} GPU(s), first "
                                f"{args.pivots} pivots from the slack basis per step (BASELINE configs[4])",
-                   "exchange": "one all-gather per pivot: 64 B header + 8*(m+1) B column per rank",
+                   "exchange": "one exchange per pivot: 64 B header + 8*(m+1) B column per rank; " + how,
                    "pivot_hash": str(r["pivot_hash"]), "l2": "tableau shard larger than L2"},
         "roofline": {"bound": "hbm", "achieved": ach, "peak": peak * world, "unit": "GB/s", "frac": ach / (peak * world),
                      "traffic": 8551384000 if world == 1 else None, "peak_source": src,
                      "traffic_source": "dram__bytes_read.sum + dram__bytes_write.sum of one shard_update_kernel launch at world 1, "
                                        "ncu --set full, profiles/r1e_shard_update_summary.txt" if world == 1 else None,
-                     "kernel": "shard_update_kernel (eager rank-1 update of the local columns; the price / all-gather / "
+                     "kernel": "shard_update_kernel (eager rank-1 update of the local columns; the price / exchange / "
                                "decide chain of the next iteration overlaps it on a second stream)"},
         "gpu_launches": launches, "clocks": clk.summary(),
     }))

@@ -87,6 +87,10 @@ int mvb_shard_get_primal(mvb_shard *s, double *x);
 int mvb_shard_get_pivot_log(mvb_shard *s, int *rowcol, int cap);
 /* device time of the last solve's kernels + exchanges (CUDA events), ms */
 double mvb_shard_last_ms(mvb_shard *s);
+/* how the per-pivot records travelled in the last solve: 0 device-to-device copies by the host
+ * (single-process group), 1 ncclAllGather, 2 pushed into the peers' mailboxes by the price
+ * kernel (CUDA IPC over NVLink; default for one process per GPU, MVOLPS_SHARD_EXCHANGE=nccl: 1) */
+int mvb_shard_last_exchange(mvb_shard *s);
 
 #ifdef __cplusplus
 }

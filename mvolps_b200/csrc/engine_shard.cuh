@@ -598,9 +598,22 @@ struct mvb_shard {
   cudaEvent_t ev[2] = {};
   cudaEvent_t ev_dec[2] = {}, ev_upd[2] = {};  // by iteration parity: decide done / update done
   float last_ms = 0.f;
+  int last_exchange = 0;
+  unsigned char *mail = nullptr;   // in-slab mailbox
+  size_t mail_flag_off = 0;
 };
 
 namespace {
+
+// records land in the shard's own slab (host copies, ncclAllGather, or pushes inside a single-process group)
+void shard_use_slab_mailbox(mvb_shard *s) {
+  ShardDev &d = s->dev;
+  for (int k = 0; k < SHARD_SLOTS; k++) d.recv[k] = s->mail + (size_t)k * s->world * d.rec_bytes;
+  d.flag = (unsigned long long *)(s->mail + s->mail_flag_off);
+  d.flag_off = s->mail_flag_off;
+  d.push = 0;
+  for (int k = 0; k < SHARD_MAX_PEERS; k++) d.peer[k] = nullptr;
+}
 
 bool shard_alloc(mvb_shard *s) {
   const int m = s->m, nloc = s->nloc;
@@ -622,8 +635,9 @@ bool shard_alloc(mvb_shard *s) {
   size_t oc = take((size_t)s->ld * sizeof(double));
   size_t octl = take(2 * sizeof(ShardCtl)), ostep = take(2 * sizeof(ShardStep));
   size_t orho0 = take((size_t)s->ld * sizeof(double)), orho1 = take((size_t)s->ld * sizeof(double));
-  size_t osend = take(rec), orecv[SHARD_SLOTS];
-  for (int k = 0; k < SHARD_SLOTS; k++) orecv[k] = take(rec * s->world);
+  // in-slab mailbox, same layout as the IPC one (PeerMail): SHARD_SLOTS x world records, then the counters
+  const size_t mail_flag_off = align_up((size_t)SHARD_SLOTS * s->world * rec, 256);
+  size_t osend = take(rec), omail = take(mail_flag_off + (size_t)SHARD_SLOTS * s->world * sizeof(unsigned long long));
   size_t ofs = take(s->fin_bytes), ofr = take(s->fin_bytes * s->world);
   CK(cudaMallocAsync((void **)&s->slab, off, g_ctx.stream));
   CK(cudaMemsetAsync(s->slab, 0, off, g_ctx.stream));
@@ -641,12 +655,11 @@ bool shard_alloc(mvb_shard *s) {
   d.step = (ShardStep *)(b + ostep);
   d.rho[0] = (double *)(b + orho0); d.rho[1] = (double *)(b + orho1);
   d.send = (unsigned char *)(b + osend);
-  for (int k = 0; k < SHARD_SLOTS; k++) d.recv[k] = (unsigned char *)(b + orecv[k]);
+  s->mail = (unsigned char *)(b + omail);
+  s->mail_flag_off = mail_flag_off;
   d.rec_bytes = rec;
   d.rank = s->rank;
-  d.push = 0;
-  d.flag = nullptr;
-  d.flag_off = 0;
+  shard_use_slab_mailbox(s);
   s->fin_send = (unsigned char *)(b + ofs); s->fin_recv = (unsigned char *)(b + ofr);
   return true;
 }
@@ -826,6 +839,7 @@ int mvb_shard_get_pivot_log(mvb_shard *s, int *rowcol, int cap) {
 }
 
 double mvb_shard_last_ms(mvb_shard *s) { return s->last_ms; }
+int mvb_shard_last_exchange(mvb_shard *s) { return s->last_exchange; }
 
 }  // extern "C"
 
@@ -867,9 +881,26 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
   if (!g_ctx.stream_upd) CKI(cudaStreamCreateWithFlags(&g_ctx.stream_upd, cudaStreamNonBlocking));
   cudaStream_t su = g_ctx.stream_upd;  // the tableau updates; `st` carries the decision chain
   // one process per GPU: records are pushed into the peers' mailboxes by the price kernel itself
-  const int pst = local ? 0 : shard_peer_setup(s0);
+  for (int k = 0; k < nlocal; k++) shard_use_slab_mailbox(shards[k]);
+  int pst = local ? 0 : shard_peer_setup(s0);
   if (pst < 0) return -1;
+  if (local && nlocal <= SHARD_MAX_PEERS) {
+    // single-process group (tests): MVOLPS_SHARD_EXCHANGE=push runs the same push / arrival-counter
+    // kernels between the shards of one GPU (the price kernels of an iteration are all enqueued
+    // before its decide kernels, so the waits cannot starve)
+    const char *mode = getenv("MVOLPS_SHARD_EXCHANGE");
+    if (mode && !strcmp(mode, "push")) {
+      for (int k = 0; k < nlocal; k++) {
+        ShardDev &d = shards[k]->dev;
+        for (int t = 0; t < nlocal; t++) d.peer[shards[t]->rank] = shards[t]->mail;
+        d.push = 1;
+        CKI(cudaMemsetAsync(d.flag, 0, (size_t)SHARD_SLOTS * s0->world * sizeof(unsigned long long), st));
+      }
+      pst = 1;
+    }
+  }
   const bool push = pst == 1;
+  for (int k = 0; k < nlocal; k++) shards[k]->last_exchange = push ? 2 : local ? 0 : 1;
   auto exchange = [&](bool fin, int slot) -> bool {
     if (push && !fin) return true;
     for (int k = 0; k < nlocal; k++) {

@@ -93,6 +93,11 @@ class ShardGroup:
     def last_ms(self):
         return self.lib.mvb_shard_last_ms(self.shards[0])
 
+    def last_exchange(self):
+        return ["host copies (single-process group)", "ncclAllGather",
+                "pushed into the peers' mailboxes by the price kernel (CUDA IPC over NVLink)"][
+            self.lib.mvb_shard_last_exchange(self.shards[0])]
+
     def free(self):
         for h in self.shards:
             self.lib.mvb_shard_free(h)
