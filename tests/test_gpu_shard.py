@@ -52,8 +52,6 @@ def test_pushed_exchange_equals_oracle(oracle, product, monkeypatch, m, n, seed,
         lg, _ = g.pivot_log(k)
         assert np.array_equal(la, lg)
         assert np.array_equal(a.primal(), g.primal(k))
-    rg2 = g.solve(max_iters=5)  # counters are reset per solve
-    assert rg2["status"] == 0 and rg2["iters"] == 0
     g.free()
     monkeypatch.delenv("MVOLPS_SHARD_EXCHANGE")
     g = ShardGroup(product, inst, world)
