@@ -215,6 +215,7 @@ struct Driver {
   }
 
   double t_sync = 0, t_solve = 0, t_pull = 0, t_copy = 0;  // MVOLPS_BNB_TIMING=1 prints them
+  double t_consume = 0, t_final = 0, t_total = 0;
   static double now() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   }
@@ -463,6 +464,7 @@ void Driver::gen_cuts(glp_prob *a) {
 namespace {
 
 bool Driver::run() {
+  const double t_run0 = now();
   const double inf = std::numeric_limits<double>::infinity();
   std::deque<std::unique_ptr<Node>> open;  // leafContainer, bs.cpp:79
   std::vector<std::string> evs;            // event lines (candidates filled late)
@@ -555,6 +557,7 @@ bool Driver::run() {
     }
     std::vector<Pending> kids;
     size_t consumed = 0;
+    const double tcons0 = now();
     for (auto &nd : batch) {
       consumed++;
       Node *node = nd.get();
@@ -624,6 +627,7 @@ bool Driver::run() {
       if (pr.max_iters > 0 && count >= pr.max_iters) { out->st.hit_limit = 1; stop = true; }
       if (stop) break;
     }
+    t_consume += now() - tcons0;
     // nodes of the batch not consumed because the loop stopped go back unopened
     for (size_t k = batch.size(); k-- > consumed;)
       if (batch[k] && batch[k]->prob) open.push_front(std::move(batch[k]));
@@ -686,6 +690,7 @@ bool Driver::run() {
   }
   out->st.incumbent_rank = inc_rank;
 
+  const double tfin0 = now();
   std::ostringstream ts;
   print_tree(1, ts);
   out->tree = ts.str();
@@ -700,9 +705,12 @@ bool Driver::run() {
     }
   }
   for (auto &kv : tree) { hash_mix((unsigned)kv.first); hash_mix((unsigned)kv.second.prune); }
+  t_final = now() - tfin0;
   if (getenv("MVOLPS_BNB_TIMING"))
-    std::fprintf(stderr, "bnb timing: sync %.1f ms, solve %.1f ms, pull %.1f ms, copy_prob %.1f ms\n",
-                 1e3 * t_sync, 1e3 * t_solve, 1e3 * t_pull, 1e3 * t_copy);
+    std::fprintf(stderr, "bnb timing: sync %.1f ms, solve %.1f ms, pull %.1f ms, copy_prob %.1f ms, consume (incl. copy) "
+                 "%.1f ms, final text %.1f ms, run %.1f ms\n",
+                 1e3 * t_sync, 1e3 * t_solve, 1e3 * t_pull, 1e3 * t_copy, 1e3 * t_consume, 1e3 * t_final,
+                 1e3 * (now() - t_run0));
   out->st.iterations = count;
   out->st.oids = next_id - 1;
   out->st.event_hash = ehash;
