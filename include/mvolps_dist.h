@@ -6,7 +6,10 @@
  *     Rank k owns the global non-basic positions [col0, col0+ncols) of every
  *     tableau row; beta, basis heads and bounds are replicated.  Per pivot:
  *       local pricing (K1) -> candidate (key, variable id, its column, m+1
- *       doubles) -> ONE all-gather -> every rank picks the same global
+ *       doubles) -> ONE exchange (one process per GPU: the pricing kernel
+ *       pushes its record into every peer's CUDA-IPC mailbox over NVLink and
+ *       the deciding kernel waits on arrival counters; ncclAllGather with
+ *       MVOLPS_SHARD_EXCHANGE=nccl) -> every rank picks the same global
  *       entering column by the total order (value bits, variable id), runs the
  *       ratio test (K2) on it redundantly, and applies the rank-1 update (K3,
  *       K4) to its own columns; the pivot row is local to every shard.
@@ -20,9 +23,11 @@
  *
  * (2) Open B&B nodes SHARDED across GPUs: node LPs are independent, so each
  *     rank solves its own nodes with mvb_solve_batch; the only exchange is
- *     the incumbent / bound (a max-reduction of one double per round) for
- *     which `mvb_comm::allreduce_max` is provided.  The driver that does this
- *     for one tree is mvb_bnb_run_dist (include/mvolps_bnb.h).
+ *     the incumbent / bound and the open-node counts (max-reductions of a
+ *     few doubles per round, `mvb_comm::allreduce_max`) plus the occasional
+ *     node hand-over between a rich and a poor rank (work stealing,
+ *     `mvb_comm::sendrecv_host`).  The driver that does this for one tree is
+ *     mvb_bnb_run_dist (include/mvolps_bnb.h).
  *
  * The communicator is a small vtable so that the same host code runs over
  * NCCL (product; libnccl.so.2 is dlopen'ed, preferring the copy already loaded
