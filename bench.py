@@ -142,6 +142,8 @@ def main():
     ap.add_argument("--cut-mode", type=int, default=0, help="bnb: 0 none, 1 reference gmi.cpp, 2 textbook GMI")
     ap.add_argument("--batch-width", type=int, default=256, help="bnb: FIFO nodes per engine launch")
     ap.add_argument("--inst-seed", type=int, default=2024, help="bnb: instance seed (2024 = BASELINE configs[2])")
+    ap.add_argument("--node-strategy", type=int, default=0, help="bnb: 0 FIFO (reference default), 1 best-first")
+    ap.add_argument("--no-speculation", action="store_true", help="bnb, best-first: one node per launch")
     ap.add_argument("--no-steal", action="store_true", help="bnb, N > 1: no node hand-over between the ranks")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

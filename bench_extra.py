@@ -140,7 +140,8 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks):
     def step(lib, p, c=None):
         t0 = time.perf_counter()
         out = p.bnb(cut_mode=args.cut_mode, batch_width=args.batch_width, max_iters=args.nodes, comm=c,
-                    no_steal=int(args.no_steal))
+                    no_steal=int(args.no_steal), node_strategy=args.node_strategy,
+                    no_speculation=int(args.no_speculation))
         return out, time.perf_counter() - t0
 
     for _ in range(max(args.warmup, 1)):
@@ -162,7 +163,7 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks):
         "metric": "bnb_nodes_per_sec", "value": nodes / max_s, "unit": "nodes/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": 1e3 * max_s / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"MDKP {args.n or 200} vars x {args.m or 50} rows seed {args.inst_seed}, FIFO B&B, node budget "
+        "config": {"workload": f"MDKP {args.n or 200} vars x {args.m or 50} rows seed {args.inst_seed}, {'best-first' if args.node_strategy else 'FIFO'} B&B, node budget "
                                f"{args.nodes} per rank, cut mode {args.cut_mode}, batch width {args.batch_width} "
                                "(BASELINE configs[2]); host wall clock around mvb_bnb_run[_dist] (host logic + H2D/D2H "
                                "included)" + ("; one tree node-sharded over the ranks, NCCL incumbent max-reduction "
@@ -171,7 +172,8 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks):
                    "lp_solves_rank0": out["lp_solves"], "engine_launches_rank0": out["launches"],
                    "event_hash_rank0": str(out["event_hash"]), "incumbent": out["incumbent"],
                    "hit_limit_rank0": out["hit_limit"], "nodes_sent_rank0": out["nodes_sent"],
-                   "nodes_received_rank0": out["nodes_received"], "steal_rounds": out["steal_rounds"]},
+                   "nodes_received_rank0": out["nodes_received"], "steal_rounds": out["steal_rounds"], "spec_nodes": out["spec_nodes"],
+                   "spec_adopted": out["spec_adopted"]},
         "gpu_launches": launches, "clocks": clk.summary(),
     }
     if not args.no_cpu_baseline and world == 1:

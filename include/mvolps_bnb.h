@@ -42,6 +42,8 @@ typedef struct mvb_bnb_params {
                       (the reference's own limit, bs.cpp:320, always applies) */
   int quiet;       /* !=0: do not print the tree / solution to stdout */
   int no_steal;    /* dist: !=0 disables the node hand-over between ranks (A/B runs, tests) */
+  int no_speculation; /* MVB_NODE_BEST: !=0 solves the two children of one node per launch, as the
+                         reference order suggests, instead of speculating over batch_width nodes */
 } mvb_bnb_params;
 
 typedef struct mvb_bnb_stats {
@@ -63,6 +65,9 @@ typedef struct mvb_bnb_stats {
   int nodes_sent;        /* dist: open nodes this rank handed to poorer ranks */
   int nodes_received;    /* dist: open nodes this rank took over from richer ranks */
   int steal_rounds;      /* dist: rounds in which any pair of ranks exchanged nodes */
+  int spec_nodes;        /* best-first: nodes whose children were solved ahead of their turn */
+  int spec_adopted;      /* ... of which the serial order branched (the rest were fathomed first
+                            or are still open) */
 } mvb_bnb_stats;
 
 typedef struct mvb_bnb mvb_bnb;

@@ -73,7 +73,8 @@ class Opts(C.Structure):
 
 class BnbParams(C.Structure):
     _fields_ = [("node_strategy", C.c_int), ("var_strategy", C.c_int), ("cut_mode", C.c_int),
-                ("batch_width", C.c_int), ("max_iters", C.c_int), ("quiet", C.c_int), ("no_steal", C.c_int)]
+                ("batch_width", C.c_int), ("max_iters", C.c_int), ("quiet", C.c_int), ("no_steal", C.c_int),
+                ("no_speculation", C.c_int)]
 
 
 class BnbStats(C.Structure):
@@ -83,7 +84,7 @@ class BnbStats(C.Structure):
         ("incumbent", C.c_double), ("hit_limit", C.c_int), ("event_hash", C.c_ulonglong),
         ("split_at", C.c_int), ("incumbent_rank", C.c_int), ("total_nodes", C.c_longlong),
         ("cached_solves", C.c_int), ("nodes_sent", C.c_int), ("nodes_received", C.c_int),
-        ("steal_rounds", C.c_int),
+        ("steal_rounds", C.c_int), ("spec_nodes", C.c_int), ("spec_adopted", C.c_int),
     ]
 
 

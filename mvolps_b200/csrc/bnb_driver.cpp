@@ -61,11 +61,24 @@ double get_fract(double x) {  // util.cpp:11-23
 
 enum Prune { P_INTG, P_FEAS, P_BNDS, P_NONE };  // util.h:27
 
+// Best-first speculation: the two children of an open node, built and solved ahead of the
+// node's turn (they are pure functions of the node's own LP solution when no cuts are added)
+struct Spec {
+  glp_prob *down = nullptr, *up = nullptr;  // S2 (bs.cpp:274) and S3 (bs.cpp:282)
+  int pick = 0;
+  ~Spec() {
+    if (down) glp_delete_prob(down);
+    if (up) glp_delete_prob(up);
+  }
+};
+
 struct Node {  // NodeData, util.h:35-54
   glp_prob *prob = nullptr;
   double upperBound = std::numeric_limits<double>::infinity();
   bool initial = false;
   int oid = 0;
+  bool spec_tried = false;      // looked at by a speculation pass (with or without children built)
+  std::unique_ptr<Spec> spec;
   ~Node() { if (prob) glp_delete_prob(prob); }
 };
 
@@ -215,12 +228,14 @@ struct Driver {
   }
 
   double t_sync = 0, t_solve = 0, t_pull = 0, t_copy = 0;  // MVOLPS_BNB_TIMING=1 prints them
-  double t_consume = 0, t_final = 0, t_total = 0;
+  double t_consume = 0, t_final = 0, t_spec = 0, t_pick = 0;
   static double now() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   }
 
-  bool solve_many(const std::vector<glp_prob *> &all) {
+  // counted = false: speculative solves; they enter lp_solves / simplex_iters when (and if) the
+  // serial order adopts them, so the statistics are those of the unspeculated run
+  bool solve_many(const std::vector<glp_prob *> &all, bool counted = true) {
     if (all.empty()) return true;
     std::vector<glp_prob *> ps;
     std::vector<mvb_lp *> engs;
@@ -228,11 +243,11 @@ struct Driver {
     for (auto *p : all) {
       bool changed = false;
       if (mv_sync_engine(p, &changed)) return false;
-      if (mv_answer_cached(p, changed)) { out->st.cached_solves++; continue; }
+      if (mv_answer_cached(p, changed)) { if (counted) out->st.cached_solves++; continue; }
       ps.push_back(p);
       engs.push_back(p->eng);
     }
-    out->st.lp_solves += (int)all.size();
+    if (counted) out->st.lp_solves += (int)all.size();
     double t1 = now();
     if (ps.empty()) { t_sync += t1 - t0; return true; }
     std::vector<mvb_result> res(ps.size());
@@ -241,7 +256,7 @@ struct Driver {
     double t2 = now();
     for (size_t k = 0; k < ps.size(); k++) {
       if (mv_pull_solution(ps[k], res[k])) return false;
-      out->st.simplex_iters += res[k].iters;
+      if (counted) out->st.simplex_iters += res[k].iters;
     }
     t_sync += t1 - t0; t_solve += t2 - t1; t_pull += now() - t2;
     out->st.launches++;
@@ -289,14 +304,68 @@ struct Driver {
     return vars.front();
   }
 
+  // best-first only: upperBound / spec_tried of open[k], mirrored in contiguous arrays so that
+  // the per-pop scan (util.cpp:170-187 walks the whole container) reads doubles, not nodes
+  std::vector<double> open_ub;
+  std::vector<char> open_tried;
+
   size_t pick_node(const std::deque<std::unique_ptr<Node>> &q) {  // util.cpp:154-188
     if (pr.node_strategy == MVB_NODE_BEST) {
       size_t best = 0;
+      const double *ub = open_ub.data();
       for (size_t k = 1; k < q.size(); k++)
-        if (q[best]->upperBound < q[k]->upperBound) best = k;
+        if (ub[best] < ub[k]) best = k;
       return best;
     }
     return 0;
+  }
+
+  // Best-first speculation.  With "-bs 1" the reference pops ONE node per
+  // iteration, so the device would see two child LPs per launch.  Without cuts the children of
+  // an open node depend on nothing but that node's own LP solution (violated list, branching
+  // variable, floor/ceil of its value: util.cpp:190-230, bs.cpp:269-288), so they can be built
+  // and solved before the node's turn: when the best node has not been looked at yet, its
+  // children and those of the next `width - 1` unvisited nodes in pop order are solved as one
+  // launch.  The serial loop below then adopts them (ids, events, incumbent, prune tags in the
+  // reference's order) and a speculated node that gets fathomed first simply drops them.
+  bool speculate(std::deque<std::unique_ptr<Node>> &open, size_t best, double bestLower, int width) {
+    std::vector<size_t> cand;
+    for (size_t k = 0; k < open.size(); k++)
+      if (k != best && !open_tried[k]) cand.push_back(k);
+    const size_t take = std::min<size_t>((size_t)std::max(width - 1, 0), cand.size());
+    std::partial_sort(cand.begin(), cand.begin() + take, cand.end(), [&](size_t a, size_t b) {
+      const double ua = open_ub[a], ub = open_ub[b];
+      return ua > ub || (ua == ub && a < b);  // pick_node's order: first maximum
+    });
+    cand.resize(take);
+    cand.insert(cand.begin(), best);
+    std::vector<glp_prob *> ps;
+    std::vector<int> vars;
+    for (size_t k : cand) {
+      Node *nd = open[k].get();
+      nd->spec_tried = true;
+      open_tried[k] = 1;
+      glp_prob *a = nd->prob;
+      bool changed = false;
+      if (mv_sync_engine(a, &changed)) return false;
+      if (!mv_answer_cached(a, changed)) continue;  // not solved yet (root): the serial path does it
+      if (classify(a, vars) != 0) continue;          // integral or infeasible: no children
+      if (!(glp_get_obj_val(a) > bestLower)) continue;  // fathomed already
+      auto sp = std::make_unique<Spec>();
+      sp->pick = pick_var(a, vars);
+      const double bound = glp_get_col_prim(a, sp->pick);
+      sp->down = glp_create_prob();
+      glp_copy_prob(sp->down, a, GLP_ON);
+      sp->up = glp_create_prob();
+      glp_copy_prob(sp->up, a, GLP_ON);
+      glp_set_col_bnds(sp->down, sp->pick, GLP_UP, 0, std::floor(bound));  // bs.cpp:274
+      glp_set_col_bnds(sp->up, sp->pick, GLP_LO, std::ceil(bound), 0);     // bs.cpp:282
+      ps.push_back(sp->down);
+      ps.push_back(sp->up);
+      nd->spec = std::move(sp);
+      out->st.spec_nodes++;
+    }
+    return solve_many(ps, /*counted=*/false);
   }
 
   void gen_cuts(glp_prob *a);
@@ -479,6 +548,8 @@ bool Driver::run() {
     auto s1 = make_node(c);
     s1->initial = true;
     tree[s1->oid] = TreeRec{s1->oid, 0, 0, P_NONE, {}};
+    open_ub.push_back(s1->upperBound);
+    open_tried.push_back(0);
     open.push_back(std::move(s1));
   }
   double bestLower = -inf;
@@ -490,7 +561,10 @@ bool Driver::run() {
   struct Pending {  // children awaiting their LP solve (bs.cpp:279,287)
     std::unique_ptr<Node> node;
     size_t ev_slot;
+    bool solved;  // adopted from a speculation pass
   };
+  const bool spec_on = pr.node_strategy == MVB_NODE_BEST && pr.cut_mode == MVB_CUT_NONE && width > 1 &&
+                       !pr.no_speculation;
 
   const bool dist = comm != nullptr && comm->world > 1;
   const bool steal = dist && !pr.no_steal && comm->sendrecv_host != nullptr;
@@ -541,9 +615,20 @@ bool Driver::run() {
     // ---- the nodes this round pops, in pop order ----
     std::vector<std::unique_ptr<Node>> batch;
     if (pr.node_strategy == MVB_NODE_BEST) {
+      const double tp0 = now();
       size_t idx = pick_node(open);
+      t_pick += now() - tp0;
+      if (spec_on && !open[idx]->spec_tried && !open[idx]->initial) {
+        const double ts0 = now();
+        if (!speculate(open, idx, bestLower, width)) return false;
+        t_spec += now() - ts0;
+      }
+      const double tp1 = now();
       batch.push_back(std::move(open[idx]));
       open.erase(open.begin() + idx);
+      open_ub.erase(open_ub.begin() + idx);
+      open_tried.erase(open_tried.begin() + idx);
+      t_pick += now() - tp1;
     } else {
       size_t w = std::min<size_t>(width, open.size());
       if (pr.max_iters > 0) w = std::min<size_t>(w, (size_t)std::max(1, pr.max_iters - count));
@@ -602,25 +687,38 @@ bool Driver::run() {
         if (pr.cut_mode != MVB_CUT_NONE) gen_cuts(a);
         int pick = pick_var(a, vars);
         double bound = glp_get_col_prim(a, pick);
-        // S2/S3 are copies of a (util.cpp:34); a itself is dead afterwards, so
-        // S3 takes it over instead of copying a third time
-        const double tc0 = now();
-        glp_prob *c2 = glp_create_prob();
-        glp_copy_prob(c2, a, GLP_ON);
-        t_copy += now() - tc0;
-        auto s2 = make_node(c2);
-        node->prob = nullptr;
-        auto s3 = make_node(a);
-        glp_set_col_bnds(s2->prob, pick, GLP_UP, 0, std::floor(bound));  // bs.cpp:274
-        glp_set_col_bnds(s3->prob, pick, GLP_LO, std::ceil(bound), 0);   // bs.cpp:282
+        std::unique_ptr<Node> s2, s3;
+        const bool adopted = node->spec && node->spec->pick == pick;
+        if (adopted) {
+          // the children were built and solved ahead of time (speculate): they enter the
+          // statistics now, as the two solves of bs.cpp:279,287
+          s2 = make_node(node->spec->down);
+          s3 = make_node(node->spec->up);
+          node->spec->down = node->spec->up = nullptr;
+          out->st.lp_solves += 2;
+          out->st.simplex_iters += s2->prob->last.iters + s3->prob->last.iters;
+          out->st.spec_adopted++;
+        } else {
+          // S2/S3 are copies of a (util.cpp:34); a itself is dead afterwards, so
+          // S3 takes it over instead of copying a third time
+          const double tc0 = now();
+          glp_prob *c2 = glp_create_prob();
+          glp_copy_prob(c2, a, GLP_ON);
+          t_copy += now() - tc0;
+          s2 = make_node(c2);
+          node->prob = nullptr;
+          s3 = make_node(a);
+          glp_set_col_bnds(s2->prob, pick, GLP_UP, 0, std::floor(bound));  // bs.cpp:274
+          glp_set_col_bnds(s3->prob, pick, GLP_LO, std::ceil(bound), 0);   // bs.cpp:282
+        }
         for (Node *s : {s2.get(), s3.get()}) {
           tree[s->oid] = TreeRec{s->oid, node->oid, tree[node->oid].depth + 1, P_NONE, {}};
           tree[node->oid].kids.push_back(s->oid);
         }
         size_t e2 = ev_line("candidate", s2->oid, "");
         size_t e3 = ev_line("candidate", s3->oid, "");
-        kids.push_back(Pending{std::move(s2), e2});
-        kids.push_back(Pending{std::move(s3), e3});
+        kids.push_back(Pending{std::move(s2), e2, adopted});
+        kids.push_back(Pending{std::move(s3), e3, adopted});
         if (count > 200000) { out->st.hit_limit = 1; stop = true; }  // bs.cpp:320-323 (exit(-1) there)
       }
       count++;
@@ -634,11 +732,16 @@ bool Driver::run() {
     // ---- LP solves #2/#3 of the new children (bs.cpp:279,287), one launch ----
     {
       std::vector<glp_prob *> ps;
-      for (auto &k : kids) ps.push_back(k.node->prob);
+      for (auto &k : kids)
+        if (!k.solved) ps.push_back(k.node->prob);
       if (!solve_many(ps)) return false;
       for (auto &k : kids) {
         k.node->upperBound = glp_get_obj_val(k.node->prob);
         evs[k.ev_slot] += sstr(" ", k.node->upperBound);
+        if (pr.node_strategy == MVB_NODE_BEST) {
+          open_ub.push_back(k.node->upperBound);
+          open_tried.push_back(0);
+        }
         open.push_back(std::move(k.node));
       }
     }
@@ -708,8 +811,9 @@ bool Driver::run() {
   t_final = now() - tfin0;
   if (getenv("MVOLPS_BNB_TIMING"))
     std::fprintf(stderr, "bnb timing: sync %.1f ms, solve %.1f ms, pull %.1f ms, copy_prob %.1f ms, consume (incl. copy) "
-                 "%.1f ms, final text %.1f ms, run %.1f ms\n",
+                 "%.1f ms, final text %.1f ms, pick_node %.1f ms, speculate (incl. its solves) %.1f ms, run %.1f ms\n",
                  1e3 * t_sync, 1e3 * t_solve, 1e3 * t_pull, 1e3 * t_copy, 1e3 * t_consume, 1e3 * t_final,
+                 1e3 * t_pick, 1e3 * t_spec,
                  1e3 * (now() - t_run0));
   out->st.iterations = count;
   out->st.oids = next_id - 1;

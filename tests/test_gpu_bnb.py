@@ -66,6 +66,18 @@ def test_bnb_larger_tree_product_equals_oracle(oracle, product, cut_mode):
     assert b["iterations"] == 600 or b["hit_limit"] == 0
 
 
+def test_best_first_speculation_product_equals_unspeculated_oracle(oracle, product):
+    """Best-first on the GPU with the children of 32 nodes per launch == the oracle run that solves
+    one node's children per launch (two clones of one parent tableau per speculated node)."""
+    inst = instances.mdkp(40, 10, 7)
+    a = GlpProb.from_instance(oracle, inst).bnb(node_strategy=1, no_speculation=1, max_iters=800)
+    b = GlpProb.from_instance(product, inst).bnb(node_strategy=1, batch_width=32, max_iters=800)
+    for k in SAME:
+        if k != "launches":
+            assert a[k] == b[k], k
+    assert b["spec_adopted"] > 0 and b["launches"] < a["launches"] / 3
+
+
 def test_shim_accessors_and_tab_rows_on_the_device(oracle, product):
     """glp_simplex / glp_get_* / glp_eval_tab_row (gmi.cpp:36) through the product shim: bit-equal to
     the oracle shim, rows read off the device tableau."""

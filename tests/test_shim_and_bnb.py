@@ -173,6 +173,24 @@ def test_bnb_batch_width_invariance(oracle, width, tmp_path):
         assert out["launches"] < base["launches"]
 
 
+@pytest.mark.parametrize("args,vs,width", [((12, 4, 1), 0, 64), ((15, 5, 2), 2, 8), ((20, 5, 3), 1, 2)])
+def test_best_first_speculation_is_sequence_identical(oracle, args, vs, width):
+    """-bs 1 (util.cpp:170-187 pops one node per iteration): the children of the next `width` nodes in
+    pop order are solved ahead of their turn in one launch; the serial order adopts them, so tree,
+    events, ids, incumbent AND the solve statistics are those of the one-node-per-launch run."""
+    inst = instances.mdkp(*args)
+    base = GlpProb.from_instance(oracle, inst).bnb(node_strategy=1, var_strategy=vs, no_speculation=1)
+    out = GlpProb.from_instance(oracle, inst).bnb(node_strategy=1, var_strategy=vs, batch_width=width)
+    for k in ("tree", "solution", "events", "event_hash", "iterations", "oids", "incumbent", "incumbent_oid",
+              "lp_solves", "cached_solves", "simplex_iters"):
+        assert out[k] == base[k], k
+    assert base["spec_nodes"] == 0 and out["spec_nodes"] >= out["spec_adopted"] > 0
+    assert out["launches"] < base["launches"]
+    # with cuts the children depend on the cut pool at branching time: no speculation
+    cut = GlpProb.from_instance(oracle, inst).bnb(node_strategy=1, cut_mode=2, batch_width=width, max_iters=40)
+    assert cut["spec_nodes"] == 0
+
+
 @pytest.mark.parametrize("name", ["small3", "mdkp_12x4_s1", "mdkp_12x4_s4_cm1"])
 def test_bnb_optimum_vs_highs(oracle, name, tmp_path):
     case = [c for c in _gold() if c["name"] == name][0]
