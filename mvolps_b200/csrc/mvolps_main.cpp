@@ -36,7 +36,8 @@ int main(int argc, char **argv) {
               << "  -bs [{0|1}]    node choice: FIFO | best bound\n"
               << "  -cm [{0|1|2}]  cuts: off | reference gmi.cpp formula | textbook GMI\n"
               << "  -bw N          FIFO nodes solved per device launch (default 256)\n"
-              << "  -nl N          node budget\n";
+              << "  -nl N          node budget\n"
+              << "  -ev FILE       write the event stream (message.h:141-226 fields, one event per line)\n";
     return 0;
   }
   glp_term_out(GLP_OFF);
@@ -65,6 +66,12 @@ int main(int argc, char **argv) {
   if (mvb_device_init(0)) { std::fprintf(stderr, "%s\n", mvb_last_error()); return 2; }
   mvb_bnb *h = mvb_bnb_run(prob, &p);
   if (!h) return 2;
+  if (in.has("-ev")) {  // file sink of what the reference sends to its visualiser (message.cpp:32-191)
+    std::FILE *f = std::fopen(in.get("-ev").c_str(), "w");
+    if (!f) { std::fprintf(stderr, "cannot write %s\n", in.get("-ev").c_str()); return -1; }
+    std::fputs(mvb_bnb_event_text(h), f);
+    std::fclose(f);
+  }
   if (!in.has("-s") && !in.has("--silent")) {
     const mvb_bnb_stats *st = mvb_bnb_get_stats(h);
     std::printf("[%s] %d iterations, %d LP solves in %d launches, %lld simplex iterations\n",
