@@ -25,6 +25,9 @@ extern "C" {
 #define MVB_VAR_VO 0    /* "-vs 0": first violated (util.cpp:192-195) */
 #define MVB_VAR_VFP 1   /* "-vs 1": as the reference: evaluated on the unsolved root object */
 #define MVB_VAR_VGO 2   /* "-vs 2": largest positive objective coefficient */
+#define MVB_VAR_VFP_NODE 3 /* not in the reference: VFP as util.cpp:197-213 intends it, the violated
+                              variable whose fractional part in the NODE's LP solution is closest
+                              to 1/2 (first on ties); "-vs 3" of mvolps_b200 */
 #define MVB_CUT_NONE 0  /* "-cm 0" */
 #define MVB_CUT_REF 1   /* "-cm 1": literal restatement of gmi.cpp:11-117 + cut.cpp:11-46 */
 #define MVB_CUT_GMI 2   /* textbook Gomory mixed-integer cut from the tableau row */

@@ -281,7 +281,15 @@ struct Driver {
   }
 
   int pick_var(glp_prob *a, const std::vector<int> &vars) {  // util.cpp:190-230
-    (void)a;
+    if (pr.var_strategy == MVB_VAR_VFP_NODE) {  // the same loop on the node's own solution
+      double best = std::abs(get_fract(glp_get_col_prim(a, vars.front())) - 0.5);
+      int index = vars.front();
+      for (int i : vars) {
+        double cur = std::abs(get_fract(glp_get_col_prim(a, i)) - 0.5);
+        if (cur < best) { best = cur; index = i; }
+      }
+      return index;
+    }
     if (pr.var_strategy == MVB_VAR_VFP) {
       // evaluated on the never-solved root object, as the reference does
       double best = std::abs(get_fract(glp_get_col_prim(root_prob, vars.front())) - 0.5);

@@ -32,7 +32,8 @@ int main(int argc, char **argv) {
     std::cout << "Usage: mvolps_b200 [OPTION]\n"
               << "  -f [FILENAME.{mps|lp}]\n"
               << "  -s/--silent  -v/--verbose  -d/--debug  -so/--solver-output\n"
-              << "  -vs [{0|1|2}]  variable choice: order | fractional part | objective impact\n"
+              << "  -vs [{0|1|2|3}] variable choice: order | fractional part (as the reference: on the root object) |\n"
+              << "                 objective impact | fractional part of the node's own solution\n"
               << "  -bs [{0|1}]    node choice: FIFO | best bound\n"
               << "  -cm [{0|1|2}]  cuts: off | reference gmi.cpp formula | textbook GMI\n"
               << "  -bw N          FIFO nodes solved per device launch (default 256)\n"
@@ -59,7 +60,7 @@ int main(int argc, char **argv) {
     dst = v;
     return true;
   };
-  if (!ival("-bs", 0, 1, p.node_strategy) || !ival("-vs", 0, 2, p.var_strategy) ||
+  if (!ival("-bs", 0, 1, p.node_strategy) || !ival("-vs", 0, 3, p.var_strategy) ||
       !ival("-cm", 0, 2, p.cut_mode) || !ival("-bw", 1, 1 << 20, p.batch_width) ||
       !ival("-nl", 1, 1 << 30, p.max_iters))
     return -1;

@@ -191,6 +191,22 @@ def test_best_first_speculation_is_sequence_identical(oracle, args, vs, width):
     assert cut["spec_nodes"] == 0
 
 
+def test_node_level_vfp_strategy(oracle, tmp_path):
+    """-vs 3 (not in the reference): util.cpp:197-213's rule on the node's own LP solution instead of
+    the never-solved root object.  Same optimum on small3 in fewer nodes; -vs 1 stays the reference's
+    behaviour (== -vs 0); speculation under best-first stays sequence-identical."""
+    case = [c for c in _gold() if c["name"] == "small3"][0]
+    vo = _prob(oracle, case, tmp_path).bnb(var_strategy=0)
+    vfp_ref = _prob(oracle, case, tmp_path).bnb(var_strategy=1)
+    vfp = _prob(oracle, case, tmp_path).bnb(var_strategy=3)
+    assert vfp_ref["tree"] == vo["tree"]
+    assert vfp["incumbent"] == vo["incumbent"] == case["highs_ilp"]
+    assert vfp["iterations"] < vo["iterations"]
+    a = _prob(oracle, case, tmp_path).bnb(var_strategy=3, node_strategy=1, no_speculation=1)
+    b = _prob(oracle, case, tmp_path).bnb(var_strategy=3, node_strategy=1, batch_width=8)
+    assert a["tree"] == b["tree"] and a["events"] == b["events"] and a["simplex_iters"] == b["simplex_iters"]
+
+
 @pytest.mark.parametrize("name", ["small3", "mdkp_12x4_s1", "mdkp_12x4_s4_cm1"])
 def test_bnb_optimum_vs_highs(oracle, name, tmp_path):
     case = [c for c in _gold() if c["name"] == name][0]
