@@ -200,7 +200,7 @@ def test_node_level_vfp_strategy(oracle, tmp_path):
     vfp_ref = _prob(oracle, case, tmp_path).bnb(var_strategy=1)
     vfp = _prob(oracle, case, tmp_path).bnb(var_strategy=3)
     assert vfp_ref["tree"] == vo["tree"]
-    assert vfp["incumbent"] == vo["incumbent"] == case["highs_ilp"]
+    assert vfp["incumbent"] == vo["incumbent"] and abs(vfp["incumbent"] - case["highs_ilp"]) <= 1e-9 * abs(case["highs_ilp"])
     assert vfp["iterations"] < vo["iterations"]
     a = _prob(oracle, case, tmp_path).bnb(var_strategy=3, node_strategy=1, no_speculation=1)
     b = _prob(oracle, case, tmp_path).bnb(var_strategy=3, node_strategy=1, batch_width=8)
