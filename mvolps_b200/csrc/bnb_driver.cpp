@@ -21,7 +21,6 @@
 #include <sstream>
 #include <type_traits>
 #include <string>
-#include <thread>
 #include <vector>
 
 #include "../../include/mvolps_bnb.h"
@@ -230,8 +229,6 @@ struct Driver {
 
   double t_sync = 0, t_solve = 0, t_pull = 0, t_copy = 0;  // MVOLPS_BNB_TIMING=1 prints them
   double t_consume = 0, t_final = 0, t_spec = 0, t_pick = 0;
-  // host threads of the per-LP loops (MVOLPS_HOST_THREADS, default 2; 1 = all on the caller's thread)
-  int host_threads = getenv("MVOLPS_HOST_THREADS") ? std::atoi(getenv("MVOLPS_HOST_THREADS")) : 2;
   static double now() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   }
@@ -257,26 +254,10 @@ struct Driver {
     mvb_opts o{};
     if (mvb_solve_batch(engs.data(), (int)engs.size(), &o, res.data())) return false;
     double t2 = now();
-    // results into the problem objects: independent per LP and bound by cache misses on the node
-    // objects (each was last touched when it was copied), so a second host thread takes half
-    {
-      auto pull = [&](size_t lo, size_t hi, int *rc) {
-        for (size_t k = lo; k < hi; k++)
-          if (mv_pull_solution(ps[k], res[k])) *rc = -1;
-      };
-      int rc0 = 0, rc1 = 0;
-      if (host_threads > 1 && ps.size() >= 32) {
-        const size_t half = ps.size() / 2;
-        std::thread helper(pull, half, ps.size(), &rc1);
-        pull(0, half, &rc0);
-        helper.join();
-      } else {
-        pull(0, ps.size(), &rc0);
-      }
-      if (rc0 || rc1) return false;
+    for (size_t k = 0; k < ps.size(); k++) {
+      if (mv_pull_solution(ps[k], res[k])) return false;
+      if (counted) out->st.simplex_iters += res[k].iters;
     }
-    if (counted)
-      for (size_t k = 0; k < ps.size(); k++) out->st.simplex_iters += res[k].iters;
     t_sync += t1 - t0; t_solve += t2 - t1; t_pull += now() - t2;
     out->st.launches++;
     return true;
@@ -585,35 +566,6 @@ bool Driver::run() {
   bool stop = false;
   int width = pr.batch_width > 0 ? pr.batch_width : 256;
 
-  struct CopyTask {  // S2 = copy of the branched node's problem, then the two bound changes
-    glp_prob *dest, *src;
-    int pick;
-    double bound;
-  };
-  // the host halves of a round's copies are independent (each reads one parent, writes one child)
-  // and bound by cache misses on the parents: two host threads; the engine halves and the bound
-  // setters (engine mirror state) stay on the caller's thread, in node order
-  auto flush_copies = [&](std::vector<CopyTask> &cp) {
-    const double tc0 = now();
-    auto host = [&](size_t lo, size_t hi) {
-      for (size_t k = lo; k < hi; k++) mv_copy_prob_host(cp[k].dest, cp[k].src, GLP_ON);
-    };
-    if (host_threads > 1 && cp.size() >= 32) {
-      const size_t half = cp.size() / 2;
-      std::thread helper(host, half, cp.size());
-      host(0, half);
-      helper.join();
-    } else {
-      host(0, cp.size());
-    }
-    for (CopyTask &t : cp) {
-      mv_copy_prob_engine(t.dest, t.src);
-      glp_set_col_bnds(t.dest, t.pick, GLP_UP, 0, std::floor(t.bound));  // bs.cpp:274
-      glp_set_col_bnds(t.src, t.pick, GLP_LO, std::ceil(t.bound), 0);    // bs.cpp:282
-    }
-    cp.clear();
-    t_copy += now() - tc0;
-  };
   struct Pending {  // children awaiting their LP solve (bs.cpp:279,287)
     std::unique_ptr<Node> node;
     size_t ev_slot;
@@ -697,7 +649,6 @@ bool Driver::run() {
       if (!solve_many(ps)) return false;
     }
     std::vector<Pending> kids;
-    std::vector<CopyTask> copies;
     size_t consumed = 0;
     const double tcons0 = now();
     for (auto &nd : batch) {
@@ -757,13 +708,16 @@ bool Driver::run() {
           out->st.spec_adopted++;
         } else {
           // S2/S3 are copies of a (util.cpp:34); a itself is dead afterwards, so
-          // S3 takes it over instead of copying a third time.  The copy itself is deferred to
-          // the end of the round (flush_copies): nothing reads S2 before its solve.
+          // S3 takes it over instead of copying a third time
+          const double tc0 = now();
           glp_prob *c2 = glp_create_prob();
+          glp_copy_prob(c2, a, GLP_ON);
+          t_copy += now() - tc0;
           s2 = make_node(c2);
           node->prob = nullptr;
           s3 = make_node(a);
-          copies.push_back(CopyTask{c2, a, pick, bound});
+          glp_set_col_bnds(s2->prob, pick, GLP_UP, 0, std::floor(bound));  // bs.cpp:274
+          glp_set_col_bnds(s3->prob, pick, GLP_LO, std::ceil(bound), 0);   // bs.cpp:282
         }
         for (Node *s : {s2.get(), s3.get()}) {
           tree[s->oid] = TreeRec{s->oid, node->oid, tree[node->oid].depth + 1, P_NONE, {}};
@@ -780,7 +734,6 @@ bool Driver::run() {
       if (stop) break;
     }
     t_consume += now() - tcons0;
-    flush_copies(copies);
     // nodes of the batch not consumed because the loop stopped go back unopened
     for (size_t k = batch.size(); k-- > consumed;)
       if (batch[k] && batch[k]->prob) open.push_front(std::move(batch[k]));

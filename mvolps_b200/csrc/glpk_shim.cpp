@@ -49,41 +49,6 @@ static void drop_engine(glp_prob *P) {
   P->at.clear();
 }
 
-// glp_copy_prob in two halves (the batched B&B driver runs the first one for all the copies of a
-// round on two host threads; it touches nothing but dest and src)
-void mv_copy_prob_host(glp_prob *dest, const glp_prob *src, int names) {
-  dest->dir = src->dir;
-  dest->c0 = src->c0;
-  dest->rows = src->rows;
-  dest->cols = src->cols;
-  dest->status = src->status;
-  dest->obj_val = src->obj_val;
-  dest->it_cnt = src->it_cnt;
-  if (names) dest->name = src->name;
-  else {
-    for (auto &r : dest->rows) r.name.clear();
-    for (auto &c : dest->cols) c.name.clear();
-  }
-  if (src->eng && !src->eng_stale) {
-    dest->eng_rows = src->eng_rows;
-    dest->eng_lb = src->eng_lb;
-    dest->eng_ub = src->eng_ub;
-    dest->dirty = src->dirty;
-    dest->head = src->head;
-    dest->nb = src->nb;
-    dest->at = src->at;
-    dest->last = src->last;
-  }
-}
-// the engine half: queues the device copy of the tableau (engine state is global: caller's thread)
-void mv_copy_prob_engine(glp_prob *dest, glp_prob *src) {
-  if (src->eng && !src->eng_stale) {
-    dest->eng = mvb_lp_clone(src->eng);
-    if (!dest->eng) shim_abort(mvb_last_error());
-    dest->eng_stale = false;
-  }
-}
-
 static MvRow &row_at(glp_prob *P, int i, const char *fn) {
   if (i < 1 || i > (int)P->rows.size()) shim_abort(fn);
   return P->rows[i - 1];
@@ -122,8 +87,31 @@ void glp_delete_prob(glp_prob *P) {
 void glp_copy_prob(glp_prob *dest, glp_prob *src, int names) {
   if (dest == src) shim_abort("glp_copy_prob: copying problem object to itself");
   glp_erase_prob(dest);
-  mv_copy_prob_host(dest, src, names);
-  mv_copy_prob_engine(dest, src);
+  dest->dir = src->dir;
+  dest->c0 = src->c0;
+  dest->rows = src->rows;
+  dest->cols = src->cols;
+  dest->status = src->status;
+  dest->obj_val = src->obj_val;
+  dest->it_cnt = src->it_cnt;
+  if (names) dest->name = src->name;
+  else {
+    for (auto &r : dest->rows) r.name.clear();
+    for (auto &c : dest->cols) c.name.clear();
+  }
+  if (src->eng && !src->eng_stale) {
+    dest->eng = mvb_lp_clone(src->eng);
+    if (!dest->eng) shim_abort(mvb_last_error());
+    dest->eng_rows = src->eng_rows;
+    dest->eng_stale = false;
+    dest->eng_lb = src->eng_lb;
+    dest->eng_ub = src->eng_ub;
+    dest->dirty = src->dirty;
+    dest->head = src->head;
+    dest->nb = src->nb;
+    dest->at = src->at;
+    dest->last = src->last;
+  }
 }
 
 int glp_read_lp(glp_prob *P, const void *parm, const char *fname) {

@@ -102,9 +102,6 @@ constexpr double MV_SNAP_TOL = 1e-9;
 double mv_snap(double x);
 
 // glpk_shim.cpp helpers shared with the batched B&B driver
-// glp_copy_prob(dest, src, names) == these two on an empty dest; the first touches only dest and src
-void mv_copy_prob_host(glp_prob *dest, const glp_prob *src, int names);
-void mv_copy_prob_engine(glp_prob *dest, glp_prob *src);
 // push deltas to the engine; *changed: the engine's LP differs from the one last solved
 int mv_sync_engine(glp_prob *P, bool *changed = nullptr);
 // true when the LP is exactly the one whose optimal solution the object already holds (a
