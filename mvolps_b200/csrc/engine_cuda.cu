@@ -702,6 +702,10 @@ struct DeviceCtx {
   BoundPatch *d_patch = nullptr, *h_patch = nullptr; size_t patch_cap = 0;
   std::vector<std::pair<size_t, char *>> free_slabs;  // recycled LP slabs (size, pointer)
   size_t free_bytes = 0;
+  // small slabs are carved out of chunks (one driver allocation per chunk instead of one per open
+  // B&B node); a carved slab is only ever recycled, its chunk stays reserved until the process ends
+  std::vector<std::pair<char *, size_t>> chunks;  // (base, bytes)
+  size_t chunk_bytes = 0;
   // deferred clones (glp_copy_prob, util.cpp:34 / bs.cpp:116): queued here and carried out
   // by ONE clone_kernel launch in front of the next device operation
   std::vector<CloneJob> clone_jobs;
@@ -848,6 +852,17 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
       g_ctx.free_slabs.pop_back();
       break;
     }
+  if (!lp->slab && lp->slab_bytes <= ((size_t)4 << 20) && g_ctx.chunk_bytes < ((size_t)16 << 30)) {
+    // a growing tree needs one new slab per branched node (util.cpp:25-42): carve them
+    const size_t per = std::min<size_t>(256, std::max<size_t>(8, ((size_t)32 << 20) / lp->slab_bytes));
+    char *base = nullptr;
+    CK(cudaMallocAsync((void **)&base, per * lp->slab_bytes, g_ctx.stream));
+    g_ctx.chunks.emplace_back(base, per * lp->slab_bytes);
+    g_ctx.chunk_bytes += per * lp->slab_bytes;
+    for (size_t k = 1; k < per; k++) g_ctx.free_slabs.emplace_back(lp->slab_bytes, base + k * lp->slab_bytes);
+    g_ctx.free_bytes += (per - 1) * lp->slab_bytes;
+    lp->slab = base;
+  }
   if (!lp->slab) CK(cudaMallocAsync((void **)&lp->slab, lp->slab_bytes, g_ctx.stream));
   char *s = lp->slab;
   LPDev &d = lp->dev;
@@ -867,10 +882,17 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
   return true;
 }
 
+bool slab_is_carved(const char *slab) {
+  for (auto &c : g_ctx.chunks)
+    if (slab >= c.first && slab < c.first + c.second) return true;
+  return false;
+}
+
 void slab_recycle(size_t bytes, char *slab) {
   // node LPs come and go in equal sizes (util.cpp:25-42): keep up to 1 GiB of slabs for reuse
-  if (bytes <= ((size_t)64 << 20) && g_ctx.free_bytes + bytes <= ((size_t)1 << 30) &&
-      g_ctx.free_slabs.size() < 8192) {
+  // (carved slabs always: they cannot be handed back one by one)
+  if ((bytes <= ((size_t)64 << 20) && g_ctx.free_bytes + bytes <= ((size_t)1 << 30) &&
+       g_ctx.free_slabs.size() < 8192) || slab_is_carved(slab)) {
     g_ctx.free_slabs.emplace_back(bytes, slab);
     g_ctx.free_bytes += bytes;
   } else {
