@@ -224,14 +224,33 @@ struct LpParser {
       if (peek().kind != T_OP) { err = "constraint sense expected near '" + peek().text + "'"; return false; }
       std::string op = peek().text;
       pos++;
-      double rhs;
-      if (!parse_number(rhs)) return false;
-      rhs -= lhs_const;
+      bool ranged = false;
+      double rlo = 0.0, rhi = 0.0, rhs = 0.0;
+      if (coefs.empty() && op != "=") {
+        // double-sided row: "lo <= expr <= hi" (or "hi >= expr >= lo")
+        const double left = lhs_const;
+        double mid_const = 0.0;
+        if (!parse_expr(coefs, mid_const)) return false;
+        if (coefs.empty() || peek().kind != T_OP || peek().text != op) {
+          err = "double-sided constraint needs the same sense twice";
+          return false;
+        }
+        pos++;
+        double right;
+        if (!parse_number(right)) return false;
+        rlo = (op == "<=" ? left : right) - mid_const;
+        rhi = (op == "<=" ? right : left) - mid_const;
+        ranged = true;
+      } else {
+        if (!parse_number(rhs)) return false;
+        rhs -= lhs_const;
+      }
       b.P->rows.emplace_back();
       int i = (int)b.P->rows.size();
       MvRow &r = b.P->rows[i - 1];
       r.name = rname.empty() ? "r." + std::to_string(i) : rname;
-      if (op == "<=") set_typed(r.type, r.lb, r.ub, r.stat, false, 0, true, rhs);
+      if (ranged) set_typed(r.type, r.lb, r.ub, r.stat, rlo > -HUGE_VAL, rlo, rhi < HUGE_VAL, rhi);
+      else if (op == "<=") set_typed(r.type, r.lb, r.ub, r.stat, false, 0, true, rhs);
       else if (op == ">=") set_typed(r.type, r.lb, r.ub, r.stat, true, rhs, false, 0);
       else set_typed(r.type, r.lb, r.ub, r.stat, true, rhs, true, rhs);
       r.stat = GLP_BS;
