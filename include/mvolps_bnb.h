@@ -99,6 +99,11 @@ mvb_bnb *mvb_bnb_run(glp_prob *prob, const mvb_bnb_params *params);
  * optimum on every rank, mvb_bnb_get_incumbent returns the winning x on every
  * rank, stats.iterations counts the nodes this rank processed. */
 mvb_bnb *mvb_bnb_run_dist(glp_prob *prob, const mvb_bnb_params *params, const mvb_comm *comm);
+/* The hand-over plan of one round of mvb_bnb_run_dist, a pure function of the per-rank open-node
+ * counts (cnt[r] < 0: rank r has retired): fills donor[i] -> thief[i], nodes[i] for up to cap
+ * pairs and returns the number of pairs.  Exposed for tests and for hosts that run their own
+ * exchange. */
+int mvb_bnb_steal_plan(const double *cnt, int world, int *donor, int *thief, int *nodes, int cap);
 void mvb_bnb_free(mvb_bnb *h);
 const mvb_bnb_stats *mvb_bnb_get_stats(const mvb_bnb *h);
 /* tree exactly as PrettyPrintTree prints it (tree_print.h:12-22, bs.cpp:331-341) */

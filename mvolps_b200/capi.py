@@ -45,7 +45,7 @@ ENGINE_SYMBOLS = [
     "mvb_lp_get_tableau", "mvb_lp_get_pivot_log",
 ]
 BNB_SYMBOLS = [
-    "mvb_bnb_run", "mvb_bnb_run_dist", "mvb_bnb_free", "mvb_bnb_get_stats", "mvb_bnb_tree_text",
+    "mvb_bnb_run", "mvb_bnb_run_dist", "mvb_bnb_steal_plan", "mvb_bnb_free", "mvb_bnb_get_stats", "mvb_bnb_tree_text",
     "mvb_bnb_solution_text", "mvb_bnb_event_text", "mvb_bnb_get_incumbent",
 ]
 DIST_SYMBOLS = [  # include/mvolps_dist.h: exported by the product only
@@ -158,6 +158,7 @@ def _bind(lib):
         "mvb_lp_get_pivot_log": (C.c_int, [_P, _ip, C.c_int]),
         "mvb_bnb_run": (_P, [_P, C.POINTER(BnbParams)]),
         "mvb_bnb_run_dist": (_P, [_P, C.POINTER(BnbParams), _P]),
+        "mvb_bnb_steal_plan": (C.c_int, [_dp, C.c_int, _ip, _ip, _ip, C.c_int]),
         "mvb_bnb_free": (None, [_P]),
         "mvb_bnb_get_stats": (C.POINTER(BnbStats), [_P]),
         "mvb_bnb_tree_text": (C.c_char_p, [_P]),

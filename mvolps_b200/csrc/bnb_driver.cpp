@@ -862,6 +862,17 @@ mvb_bnb *mvb_bnb_run_dist(glp_prob *prob, const mvb_bnb_params *params, const mv
   return bnb_run(prob, params, comm);
 }
 
+int mvb_bnb_steal_plan(const double *cnt, int world, int *donor, int *thief, int *nodes, int cap) {
+  const auto pairs = Driver::steal_matching(std::vector<double>(cnt, cnt + world));
+  int n = 0;
+  for (const auto &p : pairs) {
+    if (n >= cap) break;
+    donor[n] = p.donor; thief[n] = p.thief; nodes[n] = p.k;
+    n++;
+  }
+  return n;
+}
+
 void mvb_bnb_free(mvb_bnb *h) { delete h; }
 const mvb_bnb_stats *mvb_bnb_get_stats(const mvb_bnb *h) { return &h->st; }
 const char *mvb_bnb_tree_text(const mvb_bnb *h) { return h->tree.c_str(); }

@@ -196,9 +196,43 @@ def test_work_stealing_world3_gloo():
         assert sum(its_on) == on[0]["total_nodes"]
 
 
+def _plan(lib, cnt):
+    cnt = np.asarray(cnt, dtype=np.float64)
+    d, t, k = (np.zeros(8, np.int32) for _ in range(3))
+    n = lib.mvb_bnb_steal_plan(capi.dptr(cnt), len(cnt), capi.iptr(d), capi.iptr(t), capi.iptr(k), 8)
+    return [(int(d[i]), int(t[i]), int(k[i])) for i in range(n)]
+
+
 def test_steal_matching_rule(lib):
-    """The matching is a pure function of the open-node counts (identical on every rank)."""
-    # exercised through a 1-rank world: no partner -> no hand-over, the run equals the serial one
+    """The matching is a pure function of the open-node counts (identical on every rank): the
+    poorest rank below MVB_STEAL_LOW = 4 takes half of the difference from the richest, one pair
+    per rank and round, ties to the lowest rank, at most MVB_STEAL_MAX = 256 nodes, retired ranks
+    (count < 0) neither give nor take."""
+    assert _plan(lib, [10, 10, 10]) == []                       # nobody is short
+    assert _plan(lib, [0, 100]) == [(1, 0, 50)]
+    assert _plan(lib, [100, 0]) == [(0, 1, 50)]
+    assert _plan(lib, [3, 4]) == []                             # difference < 2
+    assert _plan(lib, [0, 1]) == []
+    assert _plan(lib, [0, 2]) == [(1, 0, 1)]
+    assert _plan(lib, [0, 0, 40, 20]) == [(2, 0, 20), (3, 1, 10)]  # two pairs, poorest/lowest rank first
+    assert _plan(lib, [5000, 0]) == [(0, 1, 256)]               # capped
+    assert _plan(lib, [-1, 0, 9]) == [(2, 1, 4)]                # rank 0 retired
+    assert _plan(lib, [-1, -1, 7]) == []
+    assert _plan(lib, [2, 3, 50, 1]) == [(2, 3, 24)]            # ranks 0 and 1 are short too, but 3 - 2 < 2
+    # conservation and monotonicity on random counts
+    rng = np.random.default_rng(0)
+    for _ in range(200):
+        cnt = rng.integers(-1, 600, size=int(rng.integers(2, 9))).astype(float)
+        used = set()
+        for d, t, k in _plan(lib, cnt):
+            assert d not in used and t not in used and d != t
+            used |= {d, t}
+            assert cnt[t] < 4 and cnt[d] - cnt[t] >= 2 and 1 <= k <= min(256, (cnt[d] - cnt[t]) // 2)
+            assert cnt[d] - k >= cnt[t] + k - 1                 # the donor stays at least as rich
+
+
+def test_one_rank_world_equals_serial():
+    # a 1-rank world: no partner -> no hand-over, the run equals the serial one
     from mvolps_b200.lp import GlpProb
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     orc = capi.load_library(os.path.join(root, "oracle", "_build", "libglpk_oracle.so"))
