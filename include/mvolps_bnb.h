@@ -47,6 +47,8 @@ typedef struct mvb_bnb_params {
   int no_steal;    /* dist: !=0 disables the node hand-over between ranks (A/B runs, tests) */
   int no_speculation; /* MVB_NODE_BEST: !=0 solves the two children of one node per launch, as the
                          reference order suggests, instead of speculating over batch_width nodes */
+  int timed_events;   /* !=0: every line of mvb_bnb_event_text starts with the milliseconds since the
+                         start of the run (BaseMessagePOD::timeSpan, message.h:142-146) */
 } mvb_bnb_params;
 
 typedef struct mvb_bnb_stats {

@@ -74,7 +74,7 @@ class Opts(C.Structure):
 class BnbParams(C.Structure):
     _fields_ = [("node_strategy", C.c_int), ("var_strategy", C.c_int), ("cut_mode", C.c_int),
                 ("batch_width", C.c_int), ("max_iters", C.c_int), ("quiet", C.c_int), ("no_steal", C.c_int),
-                ("no_speculation", C.c_int)]
+                ("no_speculation", C.c_int), ("timed_events", C.c_int)]
 
 
 class BnbStats(C.Structure):

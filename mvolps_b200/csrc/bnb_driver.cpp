@@ -545,7 +545,9 @@ bool Driver::run() {
   const double inf = std::numeric_limits<double>::infinity();
   std::deque<std::unique_ptr<Node>> open;  // leafContainer, bs.cpp:79
   std::vector<std::string> evs;            // event lines (candidates filled late)
+  std::vector<double> ev_ms;               // timed_events: BaseMessagePOD::timeSpan (message.h:142-146)
   auto ev_line = [&](const char *type, int oid, const std::string &fields) {
+    if (pr.timed_events) ev_ms.push_back(1e3 * (now() - t_run0));
     evs.push_back(sstr(type, " ", oid, " ", pid_of(oid), " ", dir_of(oid), fields));
     return evs.size() - 1;
   };
@@ -806,7 +808,11 @@ bool Driver::run() {
   print_tree(1, ts);
   out->tree = ts.str();
   out->solution = solution;
-  for (auto &l : evs) {
+  for (size_t e = 0; e < evs.size(); e++) {
+    const std::string &l = evs[e];
+    // timed: "timeSpan type oid pid direction fields", the field order of message.h:141-226; events
+    // of one device batch carry the time at which the host consumed them
+    if (pr.timed_events) out->events += sstr(ev_ms[e], " ");
     out->events += l + "\n";
     // hash type, oid, pid (the leading three fields), not the fp fields
     int sp = 0;

@@ -38,7 +38,7 @@ int main(int argc, char **argv) {
               << "  -cm [{0|1|2}]  cuts: off | reference gmi.cpp formula | textbook GMI\n"
               << "  -bw N          FIFO nodes solved per device launch (default 256)\n"
               << "  -nl N          node budget\n"
-              << "  -ev FILE       write the event stream (message.h:141-226 fields, one event per line)\n";
+              << "  -ev FILE       write the event stream, timeSpan type oid pid dir ... (message.h:141-226)\n";
     return 0;
   }
   glp_term_out(GLP_OFF);
@@ -64,6 +64,7 @@ int main(int argc, char **argv) {
       !ival("-cm", 0, 2, p.cut_mode) || !ival("-bw", 1, 1 << 20, p.batch_width) ||
       !ival("-nl", 1, 1 << 30, p.max_iters))
     return -1;
+  p.timed_events = in.has("-ev");
   if (mvb_device_init(0)) { std::fprintf(stderr, "%s\n", mvb_last_error()); return 2; }
   mvb_bnb *h = mvb_bnb_run(prob, &p);
   if (!h) return 2;

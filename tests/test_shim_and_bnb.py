@@ -235,6 +235,17 @@ def test_bnb_node_budget_and_events(oracle, tmp_path):
     assert re.match(r"^\w+ \d+ -?\d+ ", ev[0])
 
 
+def test_timed_event_stream(oracle, tmp_path):
+    """timed_events: the reference's field order (message.h:141-226: timeSpan first), same events."""
+    case = [c for c in _gold() if c["name"] == "small3"][0]
+    plain = _prob(oracle, case, tmp_path).bnb()
+    timed = _prob(oracle, case, tmp_path).bnb(timed_events=1)
+    a, b = plain["events"].splitlines(), timed["events"].splitlines()
+    assert len(a) == len(b) > 0 and plain["event_hash"] == timed["event_hash"]
+    ts = [float(l.split(" ", 1)[0]) for l in b]
+    assert [l.split(" ", 1)[1] for l in b] == a and ts == sorted(ts) and ts[0] >= 0.0
+
+
 def test_bnb_live_reference_driver(oracle, ref_bin, tmp_path):
     """Where /root/reference was compiled (oracle/_ref): run it now and compare stdout."""
     inst = instances.mdkp(11, 4, 9)
