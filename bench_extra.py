@@ -185,4 +185,44 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks):
         line["cpu_baseline"] = {"value": oo["iterations"] / dt, "unit": "nodes/s", "cores": os.cpu_count(),
                                 "kind": "port", "sample": f"same driver on the oracle engine, {oo['iterations']} nodes, "
                                 f"{dt:.1f} s; event hash {'equal' if oo['event_hash'] == out['event_hash'] else 'DIFFERENT'}"}
+        ref = reference_driver_nodes_per_sec(inst, args)
+        if ref is not None:
+            line["cpu_baseline_reference_driver"] = ref
     print(json.dumps(line))
+
+
+def reference_driver_nodes_per_sec(inst, args, seconds=10.0):
+    """the reference's UNMODIFIED driver (2test.cpp bs.cpp util.cpp cut.cpp gmi.cpp
+    message.cpp compiled where they lie under /root/reference by oracle/Makefile -> oracle/_ref/
+    mvolps_ref_oracle) on the CPU oracle shim, single-threaded like the reference, default logging,
+    on the same instance.  It has no node budget (bs.cpp:320 stops at 200 000 iterations), so it
+    runs for `seconds` and the nodes it got through are read off its own log: printInfo
+    (util.cpp:414-473) logs one solution line per popped feasible node (a slight under-count:
+    infeasible nodes log none)."""
+    import os
+    import re
+    import subprocess
+    import tempfile
+    exe = os.path.join(os.path.dirname(os.path.abspath(__file__)), "oracle", "_ref", "mvolps_ref_oracle")
+    if not os.path.exists(exe):
+        return None
+    with tempfile.TemporaryDirectory() as td:
+        lp = os.path.join(td, "inst.lp")
+        instances.write_lp(inst, lp)
+        cmd = [exe, "-f", lp, "-cm", str(min(args.cut_mode, 1)), "-bs", str(args.node_strategy)]
+        t0 = time.perf_counter()
+        try:
+            out = subprocess.run(cmd, capture_output=True, text=True, timeout=seconds).stdout
+            done = True
+        except subprocess.TimeoutExpired as e:
+            out = e.stdout.decode(errors="replace") if isinstance(e.stdout, bytes) else (e.stdout or "")
+            done = False
+        dt = time.perf_counter() - t0
+    popped = sum(1 for ln in out.splitlines() if "*(x[" in ln)
+    m = re.search(r"Solution found after (\d+) iterations", out)
+    nodes = int(m.group(1)) if (done and m) else popped
+    if nodes == 0:
+        return None
+    return {"value": nodes / dt, "unit": "nodes/s", "cores": 1, "kind": "reference",
+            "sample": f"unmodified reference driver (oracle/_ref/mvolps_ref_oracle) on the oracle shim, default logging, "
+                      f"{'ran to the end' if done else 'stopped after'} {dt:.1f} s, {nodes} nodes by its own log"}
