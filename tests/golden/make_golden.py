@@ -51,6 +51,9 @@ BNB_CASES = [  # (name, generator, args, reference CLI flags)
     ("mdkp_15x5_s2", "mdkp", [15, 5, 2], []),
     ("mdkp_10x3_s3_best", "mdkp", [10, 3, 3], ["-bs", "1"]),
     ("mdkp_12x4_s4_cm1", "mdkp", [12, 4, 4], ["-cm", "1"]),
+    ("mdkp_15x5_s2_best", "mdkp", [15, 5, 2], ["-bs", "1"]),
+    ("mdkp_12x4_s1_vfp", "mdkp", [12, 4, 1], ["-vs", "1"]),
+    ("mdkp_20x5_s3_best_vgo", "mdkp", [20, 5, 3], ["-bs", "1", "-vs", "2"]),
 ]
 
 
