@@ -249,3 +249,44 @@ def test_hbm_streaming_batch_matches_oracle(oracle, product):
         for key in ("status", "iters", "pivots", "pivot_hash", "obj"):
             assert r[key] == ra[key], (k, key)
         assert np.array_equal(w.primal(), xa)
+
+
+def _kat_instances():
+    """The hand-checked LPs of tests/test_oracle_kats.py (Klee-Minty cube, a transportation problem
+    with equality rows, a degenerate vertex, Beale's cycling example)."""
+    INF = float("inf")
+
+    def inst(A, c, lo, hi, sense="max"):
+        A = np.array(A, dtype=np.float64)
+        n = A.shape[1]
+        return dict(A=A, c=np.array(c, float), sense=sense, row_lb=np.array(lo, float), row_ub=np.array(hi, float),
+                    col_lb=np.zeros(n), col_ub=np.full(n, INF), integer=np.zeros(n, bool))
+
+    n = 8
+    km = np.zeros((n, n))
+    for i in range(n):
+        for j in range(i):
+            km[i, j] = 2.0 * 2.0 ** (i - j)
+        km[i, i] = 1.0
+    yield "klee_minty_8", inst(km, [2.0 ** (n - 1 - j) for j in range(n)], [-INF] * n,
+                               [5.0 ** (i + 1) for i in range(n)]), -(5.0 ** n)
+    cost = np.array([[8, 6, 10, 9], [9, 12, 13, 7], [14, 9, 16, 5]], float)
+    A = np.zeros((7, 12))
+    for i in range(3):
+        A[i, 4 * i: 4 * i + 4] = 1
+    for j in range(4):
+        A[3 + j, j::4] = 1
+    rhs = [20, 30, 25, 10, 25, 15, 25]
+    yield "transportation", inst(A, cost.ravel(), rhs, rhs, sense="min"), 585.0
+    yield "degenerate_vertex", inst([[1, 0], [0, 1], [1, 1], [1, 2]], [1, 1], [-INF] * 4, [2, 2, 4, 6]), -4.0
+    yield "beale", inst([[0.25, -8, -1, 9], [0.5, -12, -0.5, 3], [0, 0, 1, 0]], [0.75, -20, 0.5, -6],
+                        [-INF] * 3, [0, 0, 1]), -1.25
+
+
+@pytest.mark.parametrize("name,inst,obj", list(_kat_instances()), ids=[k[0] for k in _kat_instances()])
+def test_known_answer_lps_on_the_gpu(oracle, product, name, inst, obj):
+    """Known optima reached by the CUDA engine with the oracle's pivots, bit for bit (exponentially
+    many Dantzig pivots, phase 1 on equality rows, degenerate ties, the Bland switch)."""
+    a, b, ra, rb = _pair(oracle, product, inst)
+    _assert_same(a, b, ra, rb)
+    assert rb["status"] == 0 and abs(rb["obj"] - obj) <= 1e-9 * max(1.0, abs(obj))
