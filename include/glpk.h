@@ -121,6 +121,11 @@ int glp_add_cols(glp_prob *P, int ncs);
 void glp_set_col_kind(glp_prob *P, int j, int kind);
 double glp_get_row_prim(glp_prob *P, int i);
 int glp_get_it_cnt(glp_prob *P); /* simplex iterations of the last solve */
+/* Not GLPK: the tolerance within which a primal value is reported as the integer next to it
+ * (default 1e-9, environment MVOLPS_SNAP_TOL; 0 = report the raw tableau values).  It stands in
+ * front of the reference's exact integrality test (util.cpp:435-451).  tol < 0 only queries;
+ * returns the previous value. */
+double mvb_glp_snap_tol(double tol);
 
 #ifdef __cplusplus
 }

@@ -32,6 +32,12 @@ extern "C" {
 #define MVB_CUT_REF 1   /* "-cm 1": literal restatement of gmi.cpp:11-117 + cut.cpp:11-46 */
 #define MVB_CUT_GMI 2   /* textbook Gomory mixed-integer cut from the tableau row */
 
+/* modes of the node-sharded run (mvb_bnb_run_dist) */
+#define MVB_DIST_STEAL 0 /* every rank walks its own share of the tree; exact optimum, per-rank oids */
+#define MVB_DIST_SYNC 1  /* round-synchronous: the LPs of a round are dealt over the ranks, results are
+                            exchanged and consumed in the serial order: oids, prune tags, tree text and
+                            event stream are those of the serial run on every rank */
+
 /* work stealing of the node-sharded run (mvb_bnb_run_dist) */
 #define MVB_STEAL_LOW 4   /* a rank with fewer open nodes than this asks for more */
 #define MVB_STEAL_MAX 256 /* nodes per hand-over */
@@ -49,6 +55,21 @@ typedef struct mvb_bnb_params {
                          reference order suggests, instead of speculating over batch_width nodes */
   int timed_events;   /* !=0: every line of mvb_bnb_event_text starts with the milliseconds since the
                          start of the run (BaseMessagePOD::timeSpan, message.h:142-146) */
+  /* ---- fields below: 0 = the reference's behaviour ---- */
+  int total_budget;   /* dist: !=0: max_iters is the node budget of the WHOLE job (after the queue is
+                         dealt out every rank gets an equal share of what is left), not per rank */
+  int cut_select;     /* which cut of the node becomes its new row: 0 = the last one pooled, whichever
+                         node produced it (cut.cpp:16-21, the reference's "TODO heuristic"); 1 = among the
+                         cuts THIS node generated, the one its LP solution violates most (largest
+                         (lb - a.x)/|a|, first on ties); none generated: no row */
+  int root_heuristic; /* !=0: before branching on the root, round its LP solution down (integer columns)
+                         and, when that point is feasible, take it as the first incumbent (event
+                         "heuristic"); not in the reference */
+  int dist_mode;      /* mvb_bnb_run_dist: MVB_DIST_STEAL (0) or MVB_DIST_SYNC (1), see below */
+  double cut_skip;    /* "-cf x" (2test.cpp:135-149 parses it into _cutChance, util.cpp:259-261, which the
+                         reference never reads): cuts are generated at a branched node with probability
+                         1 - cut_skip, decided by a fixed hash of the node's oid (reproducible); 0 = at
+                         every branched node, as the reference does */
 } mvb_bnb_params;
 
 typedef struct mvb_bnb_stats {
@@ -73,6 +94,7 @@ typedef struct mvb_bnb_stats {
   int spec_nodes;        /* best-first: nodes whose children were solved ahead of their turn */
   int spec_adopted;      /* ... of which the serial order branched (the rest were fathomed first
                             or are still open) */
+  int launches_aux;      /* batched tableau-row gathers of the cut step (one per round with cuts) */
 } mvb_bnb_stats;
 
 typedef struct mvb_bnb mvb_bnb;

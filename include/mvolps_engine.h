@@ -123,6 +123,11 @@ int mvb_lp_get_basis(mvb_lp *lp, int *head, int *nb, int *at);
 /* gather tableau rows (1-based row numbers, 0 = reduced-cost row) into
  * out[nrows*n]; columns follow the non-basic positions (see get_basis) */
 int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out);
+/* the same for `count` LPs in ONE device pass (all branching candidates of a B&B round,
+ * bs.cpp:249-258 / gmi.cpp:36): LP k contributes nrows[k] rows, its row numbers follow
+ * those of LP k-1 in `rows`, its rows (n_k doubles each) follow those of LP k-1 in `out` */
+int mvb_lp_get_tab_rows_batch(mvb_lp *const *lps, int count, const int *rows, const int *nrows,
+                              double *out);
 /* whole current tableau ((m+1)*n) and beta (m+1, [0] unused); parity tests */
 int mvb_lp_get_tableau(mvb_lp *lp, double *T, double *beta);
 /* copies up to cap (row,col) pairs of the last solve; returns total logged */

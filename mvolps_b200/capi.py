@@ -35,13 +35,13 @@ GLPK_SYMBOLS = [  # the 34 symbols the reference leaves undefined
     "glp_set_col_bnds", "glp_get_col_kind", "glp_get_col_prim", "glp_get_col_stat",
     "glp_simplex", "glp_get_status", "glp_eval_tab_row",
 ]
-GLPK_EXTRA_SYMBOLS = ["glp_add_cols", "glp_set_col_kind", "glp_get_row_prim", "glp_get_it_cnt"]
+GLPK_EXTRA_SYMBOLS = ["glp_add_cols", "glp_set_col_kind", "glp_get_row_prim", "glp_get_it_cnt", "mvb_glp_snap_tol"]
 ENGINE_SYMBOLS = [
     "mvb_backend", "mvb_last_error", "mvb_device_init", "mvb_kernel_launches",
     "mvb_timer_record", "mvb_timer_elapsed_ms", "mvb_flush_l2", "mvb_last_launch", "mvb_last_kernel_ms",
     "mvb_lp_create", "mvb_lp_free", "mvb_lp_load", "mvb_lp_clone", "mvb_lp_assign",
     "mvb_lp_dims", "mvb_lp_set_bounds", "mvb_lp_append_row", "mvb_solve_batch",
-    "mvb_lp_get_primal", "mvb_lp_get_basis", "mvb_lp_get_tab_rows",
+    "mvb_lp_get_primal", "mvb_lp_get_basis", "mvb_lp_get_tab_rows", "mvb_lp_get_tab_rows_batch",
     "mvb_lp_get_tableau", "mvb_lp_get_pivot_log",
 ]
 BNB_SYMBOLS = [
@@ -74,7 +74,9 @@ class Opts(C.Structure):
 class BnbParams(C.Structure):
     _fields_ = [("node_strategy", C.c_int), ("var_strategy", C.c_int), ("cut_mode", C.c_int),
                 ("batch_width", C.c_int), ("max_iters", C.c_int), ("quiet", C.c_int), ("no_steal", C.c_int),
-                ("no_speculation", C.c_int), ("timed_events", C.c_int)]
+                ("no_speculation", C.c_int), ("timed_events", C.c_int), ("total_budget", C.c_int),
+                ("cut_select", C.c_int), ("root_heuristic", C.c_int), ("dist_mode", C.c_int),
+                ("cut_skip", C.c_double)]
 
 
 class BnbStats(C.Structure):
@@ -85,6 +87,7 @@ class BnbStats(C.Structure):
         ("split_at", C.c_int), ("incumbent_rank", C.c_int), ("total_nodes", C.c_longlong),
         ("cached_solves", C.c_int), ("nodes_sent", C.c_int), ("nodes_received", C.c_int),
         ("steal_rounds", C.c_int), ("spec_nodes", C.c_int), ("spec_adopted", C.c_int),
+        ("launches_aux", C.c_int),
     ]
 
 
@@ -132,6 +135,7 @@ def _bind(lib):
         "glp_simplex": (C.c_int, [_P, _P]),
         "glp_get_status": (C.c_int, [_P]),
         "glp_get_it_cnt": (C.c_int, [_P]),
+        "mvb_glp_snap_tol": (C.c_double, [C.c_double]),
         "glp_eval_tab_row": (C.c_int, [_P, C.c_int, _ip, _dp]),
         "mvb_backend": (C.c_char_p, []),
         "mvb_last_error": (C.c_char_p, []),
@@ -154,6 +158,7 @@ def _bind(lib):
         "mvb_lp_get_primal": (C.c_int, [_P, _dp]),
         "mvb_lp_get_basis": (C.c_int, [_P, _ip, _ip, _ip]),
         "mvb_lp_get_tab_rows": (C.c_int, [_P, _ip, C.c_int, _dp]),
+        "mvb_lp_get_tab_rows_batch": (C.c_int, [C.POINTER(_P), C.c_int, _ip, _ip, _dp]),
         "mvb_lp_get_tableau": (C.c_int, [_P, _dp, _dp]),
         "mvb_lp_get_pivot_log": (C.c_int, [_P, _ip, C.c_int]),
         "mvb_bnb_run": (_P, [_P, C.POINTER(BnbParams)]),

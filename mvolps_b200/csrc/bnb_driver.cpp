@@ -117,7 +117,6 @@ struct Driver {
   // so once any column was rejected (oid = -1, gmi.cpp:20,25) every later cut
   // is dropped.  MVB_CUT_REF models exactly that; MVB_CUT_GMI pools every cut.
   int ref_oid_slot = 0;
-  std::ostringstream ev;
   unsigned long long ehash = MVB_FNV_OFFSET;
 
   const mvb_comm *comm = nullptr;  // node-sharded run (mvb_bnb_run_dist)
@@ -138,16 +137,6 @@ struct Driver {
     return oid % 2 == 0 ? "R" : "L";
   }
   int pid_of(int oid) { return oid == 1 ? 0 : tree[oid].pid; }  // bs.cpp:27-34
-
-  template <typename... F>
-  void event(const char *type, int oid, F &&...fields) {
-    ev << type << " " << oid << " " << pid_of(oid) << " " << dir_of(oid);
-    ((ev << " " << fields), ...);
-    ev << "\n";
-    for (const char *c = type; *c; c++) hash_mix((unsigned char)*c);
-    hash_mix((unsigned)oid);
-    hash_mix((unsigned)pid_of(oid));
-  }
 
   std::unique_ptr<Node> make_node(glp_prob *take) {  // NodeData ctor, util.cpp:25-37
     auto n = std::make_unique<Node>();
@@ -228,7 +217,7 @@ struct Driver {
   }
 
   double t_sync = 0, t_solve = 0, t_pull = 0, t_copy = 0;  // MVOLPS_BNB_TIMING=1 prints them
-  double t_consume = 0, t_final = 0, t_spec = 0, t_pick = 0;
+  double t_consume = 0, t_final = 0, t_spec = 0, t_pick = 0, t_rows = 0;
   static double now() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   }
@@ -376,10 +365,70 @@ struct Driver {
     return solve_many(ps, /*counted=*/false);
   }
 
-  void gen_cuts(glp_prob *a);
+  bool cuts_wanted(int oid) const;
+  std::vector<int> row_of;  // scratch of cut_rows_of
+  void cut_rows_of(glp_prob *a, std::vector<int> &js, std::vector<int> &rows);
+  void gen_cuts(glp_prob *a, const double *trows);
   void gen_cut_ref(glp_prob *a, int j, const double *trow);
   void gen_cut_gmi(glp_prob *a, int j, const double *trow);
-  int add_cut_constraint(glp_prob *a);
+  int add_cut_constraint(glp_prob *a, int cID);
+  int deepest_cut(glp_prob *a, size_t first);
+
+  // K7 for a whole round: the tableau rows the cut step (bs.cpp:249-258, gmi.cpp:36) will read,
+  // for every node of the batch that can still branch (a superset: the incumbent only improves
+  // while the batch is consumed), gathered by ONE engine call.  off[k]: offset of node k's rows
+  // in buf, or npos when it has none.
+  static constexpr size_t npos = (size_t)-1;
+  bool prefetch_cut_rows(const std::vector<std::unique_ptr<Node>> &batch, double bestLower,
+                         std::vector<double> &buf, std::vector<size_t> &off) {
+    off.assign(batch.size(), npos);
+    std::vector<mvb_lp *> lps;
+    std::vector<int> rows, nrows, js, r1, vars;
+    size_t tot = 0;
+    for (size_t k = 0; k < batch.size(); k++) {
+      Node *nd = batch[k].get();
+      glp_prob *a = nd->prob;
+      if (!cuts_wanted(nd->oid) || classify(a, vars) != 0) continue;
+      if (glp_get_obj_val(a) <= bestLower) continue;  // fathomed whatever happens (bs.cpp:210)
+      cut_rows_of(a, js, r1);
+      off[k] = tot;
+      tot += r1.size() * a->cols.size();
+      if (r1.empty()) continue;
+      lps.push_back(a->eng);
+      nrows.push_back((int)r1.size());
+      rows.insert(rows.end(), r1.begin(), r1.end());
+    }
+    buf.resize(tot);
+    if (lps.empty()) return true;
+    const double t0 = now();
+    const int rc = mvb_lp_get_tab_rows_batch(lps.data(), (int)lps.size(), rows.data(), nrows.data(), buf.data());
+    t_rows += now() - t0;
+    out->st.launches_aux++;
+    return rc == 0;
+  }
+
+  // root_heuristic: the root LP solution with its integer columns rounded down; feasible -> objective
+  bool floor_point(glp_prob *a, std::vector<double> &x, double &obj) {
+    const int n = (int)a->cols.size(), m = (int)a->rows.size();
+    x.assign(n + 1, 0.0);
+    obj = a->c0;
+    for (int j = 1; j <= n; j++) {
+      const MvCol &c = a->cols[j - 1];
+      double v = c.prim;
+      if (c.kind != GLP_CV) v = std::floor(v);
+      if (v < mv_eff_lb(c.type, c.lb) || v > mv_eff_ub(c.type, c.ub)) return false;
+      x[j] = v;
+      obj = std::fma(c.coef, v, obj);
+    }
+    for (int i = 0; i < m; i++) {
+      const MvRow &r = a->rows[i];
+      double act = 0.0;
+      for (size_t t = 0; t < r.ind.size(); t++) act += r.val[t] * x[r.ind[t]];
+      const double tol = 1e-9 * (1.0 + std::fabs(act));
+      if (act < mv_eff_lb(r.type, r.lb) - tol || act > mv_eff_ub(r.type, r.ub) + tol) return false;
+    }
+    return true;
+  }
 
   void print_tree(int oid, std::ostringstream &os) {  // tree_print.h:12-22
     TreeRec &t = tree[oid];
@@ -399,15 +448,37 @@ struct Driver {
 
 namespace {
 
-// CutPool::addCutConstraint, cut.cpp:11-46: the LAST pooled cut becomes a new
-// GLP_LO row of a (which is not re-solved before its children are cloned)
-int Driver::add_cut_constraint(glp_prob *a) {
+// CutPool::addCutConstraint, cut.cpp:11-46: pooled cut cID (the reference always
+// passes -1 = the LAST pooled cut) becomes a new GLP_LO row of a (which is not
+// re-solved before its children are cloned)
+int Driver::add_cut_constraint(glp_prob *a, int cID) {
   if (pool.empty()) return -1;
-  const Cut &c = pool.back();
+  if (cID < 0) cID = (int)pool.size() - 1;
+  const Cut &c = pool[cID];
   int index = glp_add_rows(a, 1);
   glp_set_mat_row(a, index, (int)c.inds.size() - 1, c.inds.data(), c.vals.data());
   glp_set_row_bnds(a, index, GLP_LO, c.lb, 0);
-  return (int)pool.size() - 1;
+  return cID;
+}
+
+// cut_select = 1 (the "heuristic to pick the best cut" cut.cpp:16-19 leaves as a TODO): among
+// the cuts pool[first..) the one the node's LP solution violates most, (lb - a.x)/|a|, first
+// on ties; -1 when none of them is violated
+int Driver::deepest_cut(glp_prob *a, size_t first) {
+  int best = -1;
+  double bestv = 0.0;
+  for (size_t k = first; k < pool.size(); k++) {
+    const Cut &c = pool[k];
+    double act = 0.0, nrm = 0.0;
+    for (size_t t = 1; t < c.inds.size(); t++) {
+      act += c.vals[t] * a->cols[c.inds[t] - 1].prim;
+      nrm += c.vals[t] * c.vals[t];
+    }
+    if (!(nrm > 0.0)) continue;
+    const double v = (c.lb - act) / std::sqrt(nrm);
+    if (v > bestv) { bestv = v; best = (int)k; }
+  }
+  return best;
 }
 
 // literal restatement of generateCut3, gmi.cpp:11-117 (see SURVEY.md 3.4 for
@@ -512,28 +583,60 @@ void Driver::gen_cut_gmi(glp_prob *a, int j, const double *trow) {
   pool.push_back(std::move(c));
 }
 
-// bs.cpp:249-258: every basic GLP_IV column generates; rows are gathered from
-// the engine tableau in one call so only those rows cross PCIe
-void Driver::gen_cuts(glp_prob *a) {
+// "-cf" (2test.cpp:135-149): whether the cut step of bs.cpp:249-258 runs at the node with this
+// oid; a fixed hash of the oid, so a run is reproducible and identical on every rank
+bool Driver::cuts_wanted(int oid) const {
+  if (!(pr.cut_skip > 0.0)) return true;
+  unsigned long long z = (unsigned long long)oid * 0x9E3779B97F4A7C15ULL;  // splitmix64 finaliser
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  z ^= z >> 31;
+  return (double)(z >> 11) * (1.0 / 9007199254740992.0) >= pr.cut_skip;
+}
+
+// the tableau rows gen_cuts needs from node a: one per column that generates (basic, of an
+// admitted kind), in column order; js[k] < 0 marks a rejected column (no row)
+void Driver::cut_rows_of(glp_prob *a, std::vector<int> &js, std::vector<int> &rows) {
   int m = glp_get_num_rows(a), n = glp_get_num_cols(a);
-  std::vector<int> js, rows;
+  js.clear();
+  rows.clear();
+  row_of.assign(n, 0);
+  for (int i = 0; i < m; i++)
+    if (a->head[i] < n) row_of[a->head[i]] = i + 1;
   for (int j = 1; j <= n; j++) {
     int kind = glp_get_col_kind(a, j);
     bool ok = pr.cut_mode == MVB_CUT_REF ? kind == GLP_IV : kind != GLP_CV;
-    if (!ok || glp_get_col_stat(a, j) != GLP_BS) { js.push_back(-j); rows.push_back(0); continue; }
-    for (int i = 0; i < m; i++)
-      if (a->head[i] == j - 1) { js.push_back(j); rows.push_back(i + 1); break; }
+    if (!ok || glp_get_col_stat(a, j) != GLP_BS || !row_of[j - 1]) { js.push_back(-j); continue; }
+    js.push_back(j);
+    rows.push_back(row_of[j - 1]);
   }
-  if (!js.empty()) {
-    std::vector<double> t((size_t)js.size() * n);
-    if (mvb_lp_get_tab_rows(a->eng, rows.data(), (int)rows.size(), t.data())) return;
-    for (size_t k = 0; k < js.size(); k++) {
-      if (js[k] < 0) { ref_oid_slot = -1; continue; }  // rejected column
-      if (pr.cut_mode == MVB_CUT_GMI) gen_cut_gmi(a, js[k], t.data() + k * n);
-      else if (ref_oid_slot != -1) gen_cut_ref(a, js[k], t.data() + k * n);
-    }
+}
+
+// bs.cpp:249-258: every basic GLP_IV column generates; the rows were gathered from the engine
+// tableaus of all branching candidates of the round in one call (prefetch_cut_rows), so only
+// those rows cross PCIe, once per round
+void Driver::gen_cuts(glp_prob *a, const double *t) {
+  int n = glp_get_num_cols(a);
+  std::vector<int> js, rows;
+  cut_rows_of(a, js, rows);
+  const size_t pool0 = pool.size();
+  size_t k = 0;
+  for (int j : js) {
+    if (j < 0) { ref_oid_slot = -1; continue; }  // rejected column
+    if (pr.cut_mode == MVB_CUT_GMI) gen_cut_gmi(a, j, t + k * n);
+    else if (ref_oid_slot != -1) gen_cut_ref(a, j, t + k * n);
+    k++;
   }
-  add_cut_constraint(a);
+  if (pr.cut_select == 1) {
+    const int pick = deepest_cut(a, pool0);
+    if (pick >= 0) add_cut_constraint(a, pick);
+  } else if (pr.cut_mode == MVB_CUT_GMI) {
+    // a textbook GMI cut uses the node's own bounds: it holds in this node's subtree only, so
+    // the row must be one this node produced (none produced: none added)
+    if (pool.size() > pool0) add_cut_constraint(a, -1);
+  } else {
+    add_cut_constraint(a, -1);  // cut.cpp:16-21: the last pooled cut, whichever node made it
+  }
 }
 
 }  // namespace
@@ -567,6 +670,7 @@ bool Driver::run() {
   int count = 0;
   bool stop = false;
   int width = pr.batch_width > 0 ? pr.batch_width : 256;
+  int limit = pr.max_iters;  // node budget of this rank (total_budget: re-derived when the queue is dealt out)
 
   struct Pending {  // children awaiting their LP solve (bs.cpp:279,287)
     std::unique_ptr<Node> node;
@@ -641,7 +745,7 @@ bool Driver::run() {
       t_pick += now() - tp1;
     } else {
       size_t w = std::min<size_t>(width, open.size());
-      if (pr.max_iters > 0) w = std::min<size_t>(w, (size_t)std::max(1, pr.max_iters - count));
+      if (limit > 0) w = std::min<size_t>(w, (size_t)std::max(1, limit - count));
       for (size_t k = 0; k < w; k++) { batch.push_back(std::move(open.front())); open.pop_front(); }
     }
     // ---- LP solve #1 of every popped node (bs.cpp:114-117), one launch ----
@@ -650,6 +754,9 @@ bool Driver::run() {
       for (auto &nd : batch) ps.push_back(nd->prob);
       if (!solve_many(ps)) return false;
     }
+    std::vector<double> cut_buf;
+    std::vector<size_t> cut_off;
+    if (pr.cut_mode != MVB_CUT_NONE && !prefetch_cut_rows(batch, bestLower, cut_buf, cut_off)) return false;
     std::vector<Pending> kids;
     size_t consumed = 0;
     const double tcons0 = now();
@@ -664,6 +771,19 @@ bool Driver::run() {
       if (node->initial) {  // bs.cpp:134-149
         if (status == -1) { rec.prune = P_FEAS; stop = true; break; }
         if (status == 1) { node->upperBound = glp_get_obj_val(a); rec.prune = P_INTG; stop = true; break; }
+      }
+      if (node->initial && pr.root_heuristic && status == 0) {
+        std::vector<double> hx;
+        double hobj;
+        if (floor_point(a, hx, hobj) && hobj > bestLower) {
+          bestLower = hobj;
+          ev_line("heuristic", node->oid, sstr(" ", hobj));
+          solution = sstr("[", node->oid, "] Heuristic solution (root LP rounded down) = ", hobj, "\n");
+          out->incumbent = hx;
+          out->st.has_incumbent = 1;
+          out->st.incumbent_oid = node->oid;
+          out->st.incumbent = bestLower;
+        }
       }
       node->upperBound = glp_get_obj_val(a);
       if (status == 1) {  // bs.cpp:158-193
@@ -694,7 +814,23 @@ bool Driver::run() {
         double acc = 0;
         for (int i : vars) acc += get_fract(glp_get_col_prim(a, i));
         ev_line("branched", node->oid, sstr(" ", node->upperBound, " ", acc, " ", vars.size(), " 1 2"));
-        if (pr.cut_mode != MVB_CUT_NONE) gen_cuts(a);
+        if (pr.cut_mode != MVB_CUT_NONE && cuts_wanted(node->oid)) {
+          const size_t bk = consumed - 1;
+          std::vector<double> one;
+          const double *trows = cut_off[bk] != npos ? cut_buf.data() + cut_off[bk] : nullptr;
+          if (!trows) {  // not prefetched (cannot happen with the superset rule; kept as a safe path)
+            std::vector<int> js, r1;
+            cut_rows_of(a, js, r1);
+            one.resize(r1.size() * a->cols.size());
+            if (!r1.empty() && mvb_lp_get_tab_rows(a->eng, r1.data(), (int)r1.size(), one.data())) return false;
+            trows = one.data();
+          }
+          const size_t rows0 = a->rows.size();
+          gen_cuts(a, trows);
+          // the new row goes to a's engine now (queued; all rows of the round are formed by one
+          // kernel), so the children clone a tableau that already holds it
+          if (a->rows.size() != rows0 && mv_sync_engine(a)) return false;
+        }
         int pick = pick_var(a, vars);
         double bound = glp_get_col_prim(a, pick);
         std::unique_ptr<Node> s2, s3;
@@ -732,7 +868,7 @@ bool Driver::run() {
         if (count > 200000) { out->st.hit_limit = 1; stop = true; }  // bs.cpp:320-323 (exit(-1) there)
       }
       count++;
-      if (pr.max_iters > 0 && count >= pr.max_iters) { out->st.hit_limit = 1; stop = true; }
+      if (limit > 0 && count >= limit) { out->st.hit_limit = 1; stop = true; }
       if (stop) break;
     }
     t_consume += now() - tcons0;
@@ -764,6 +900,8 @@ bool Driver::run() {
         open.swap(mine);
         split = true;
         out->st.split_at = count;
+        if (pr.total_budget && limit > 0)  // every rank gets an equal share of what is left of the budget
+          limit = count + std::max(1, (limit - count + comm->world - 1) / comm->world);
       }
       if (split) {
         if (stop) { retired = true; stop = false; open.clear(); }
@@ -796,8 +934,14 @@ bool Driver::run() {
     std::vector<double> cnt(comm->world, -inf);
     cnt[comm->rank] = (double)count;
     if (!reduce_max(cnt.data(), comm->world)) return false;
-    out->st.total_nodes = 0;
-    for (double c : cnt) out->st.total_nodes += (long long)c;
+    // the lock-step ramp-up (and a run that never dealt its queue out) is replicated work: its
+    // nodes count once, not once per rank
+    const int sa = out->st.split_at;
+    if (sa < 0) out->st.total_nodes = count;
+    else {
+      out->st.total_nodes = sa;
+      for (double c : cnt) out->st.total_nodes += (long long)c - sa;
+    }
   } else {
     out->st.total_nodes = count;
   }
@@ -825,9 +969,9 @@ bool Driver::run() {
   t_final = now() - tfin0;
   if (getenv("MVOLPS_BNB_TIMING"))
     std::fprintf(stderr, "bnb timing: sync %.1f ms, solve %.1f ms, pull %.1f ms, copy_prob %.1f ms, consume (incl. copy) "
-                 "%.1f ms, final text %.1f ms, pick_node %.1f ms, speculate (incl. its solves) %.1f ms, run %.1f ms\n",
+                 "%.1f ms, final text %.1f ms, pick_node %.1f ms, speculate (incl. its solves) %.1f ms, cut rows %.1f ms, run %.1f ms\n",
                  1e3 * t_sync, 1e3 * t_solve, 1e3 * t_pull, 1e3 * t_copy, 1e3 * t_consume, 1e3 * t_final,
-                 1e3 * t_pick, 1e3 * t_spec,
+                 1e3 * t_pick, 1e3 * t_spec, 1e3 * t_rows,
                  1e3 * (now() - t_run0));
   out->st.iterations = count;
   out->st.oids = next_id - 1;

@@ -686,6 +686,22 @@ __global__ void __launch_bounds__(256) clone_kernel(const CloneJob *jobs) {
   for (; i < n16; i += step) d[i] = s[i];
 }
 
+// a queued cut row: tableau row m+1 of L (L.m = rows before the append) from the dense
+// coefficients at `a_off` doubles into the coefficient arena
+struct AppendJob {
+  LPDev L;
+  int cT, cS;
+  unsigned long long a_off;
+  double lb, ub;  // bounds of the new auxiliary variable (id n + m)
+};
+
+// one row of one tableau into the staging buffer (K7 of a whole B&B round)
+struct GatherJob {
+  const double *src;
+  double *dst;
+  int n, pad;
+};
+
 struct DeviceCtx {
   bool ready = false;
   int device = -1, sms = 0;
@@ -712,6 +728,14 @@ struct DeviceCtx {
   std::vector<std::pair<size_t, char *>> zombies;  // slabs released while a queued clone may read them
   CloneJob *d_jobs = nullptr; size_t jobs_cap = 0;
   unsigned clone_epoch = 1;  // bumped by every flush: marks which handles take part in queued clones
+  // deferred cut rows (cut.cpp:23-43 -> mvb_lp_append_row): queued like the clones and formed by ONE
+  // append_rows_kernel launch, in front of the queued clones (a child is cloned from the parent
+  // that has just received its cut row)
+  std::vector<struct AppendJob> append_jobs;
+  std::vector<double> append_a;                  // the rows' coefficients, n doubles per job
+  char *d_append = nullptr; size_t append_cap = 0;  // device copy: jobs, then coefficients
+  // pinned staging of the batched row gather (mvb_lp_get_tab_rows_batch)
+  char *h_gather = nullptr; size_t gather_cap = 0;
   cudaEvent_t ev[16] = {};
   cudaEvent_t kev[2] = {};
   char *flush = nullptr; size_t flush_bytes = 0;
@@ -808,6 +832,7 @@ struct mvb_lp {
   std::vector<char> outbox;         // host copy of the outbox
   unsigned clone_epoch = 0;         // == g_ctx.clone_epoch: source (1) / destination (2) of a queued clone
   int clone_role = 0;
+  unsigned append_epoch = 0;        // == g_ctx.clone_epoch: a cut row of this LP is queued
 };
 
 namespace {
@@ -903,7 +928,7 @@ void slab_recycle(size_t bytes, char *slab) {
 void lp_release(mvb_lp *lp) {
   if (lp->slab) {
     // a queued clone may still have to read (or write) this slab: park it until the flush
-    if (!g_ctx.clone_jobs.empty()) g_ctx.zombies.emplace_back(lp->slab_bytes, lp->slab);
+    if (!g_ctx.clone_jobs.empty() || !g_ctx.append_jobs.empty()) g_ctx.zombies.emplace_back(lp->slab_bytes, lp->slab);
     else slab_recycle(lp->slab_bytes, lp->slab);
   }
   if (lp->pivlog) cudaFreeAsync(lp->pivlog, g_ctx.stream);
@@ -912,12 +937,39 @@ void lp_release(mvb_lp *lp) {
   lp->pivlog_cap = 0;
 }
 
-// carry out the queued clones: one H2D of the job list + one kernel, stream-ordered in
-// front of whatever the caller enqueues next
+__global__ void append_rows_kernel(const AppendJob *jobs, const double *arena);
+
+// carry out the queued cut-row appends, then the queued clones: one H2D of each job list + one
+// kernel each, stream-ordered in front of whatever the caller enqueues next
 bool flush_clones() {
-  if (g_ctx.clone_jobs.empty()) return true;
   cudaStream_t st = g_ctx.stream;
+  if (!g_ctx.append_jobs.empty()) {
+    std::vector<AppendJob> &aj = g_ctx.append_jobs;
+    const size_t jb = align_up(aj.size() * sizeof(AppendJob), 256), ab = g_ctx.append_a.size() * sizeof(double);
+    if (g_ctx.append_cap < jb + ab) {
+      if (g_ctx.d_append) CK(cudaFreeAsync(g_ctx.d_append, st));
+      g_ctx.append_cap = std::max((jb + ab) * 2, (size_t)1 << 20);
+      CK(cudaMallocAsync((void **)&g_ctx.d_append, g_ctx.append_cap, st));
+    }
+    // pageable sources: the driver stages them before returning, so the vectors may be reused at once
+    CK(cudaMemcpyAsync(g_ctx.d_append, aj.data(), aj.size() * sizeof(AppendJob), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(g_ctx.d_append + jb, g_ctx.append_a.data(), ab, cudaMemcpyHostToDevice, st));
+    int maxld = 0;
+    for (const AppendJob &j : aj) maxld = std::max(maxld, j.L.ld);
+    append_rows_kernel<<<dim3((unsigned)((maxld + 127) / 128), (unsigned)aj.size()), 128, 0, st>>>(
+        (const AppendJob *)g_ctx.d_append, (const double *)(g_ctx.d_append + jb));
+    CK(cudaGetLastError());
+    g_launches++;
+    aj.clear();
+    g_ctx.append_a.clear();
+  }
   std::vector<CloneJob> &jobs = g_ctx.clone_jobs;
+  if (jobs.empty()) {
+    for (auto &z : g_ctx.zombies) slab_recycle(z.first, z.second);
+    g_ctx.zombies.clear();
+    g_ctx.clone_epoch++;
+    return true;
+  }
   if (g_ctx.jobs_cap < jobs.size()) {
     if (g_ctx.d_jobs) CK(cudaFreeAsync(g_ctx.d_jobs, st));
     g_ctx.jobs_cap = std::max(jobs.size() * 2, (size_t)1024);
@@ -1054,7 +1106,7 @@ int mvb_lp_assign(mvb_lp *dst, const mvb_lp *src) {
   // destination, or overwriting a queued source/destination) is flushed first.
   const unsigned ep = g_ctx.clone_epoch;
   const bool src_is_dst = src->clone_epoch == ep && (src->clone_role & 2);
-  const bool dst_busy = dst->clone_epoch == ep && dst->clone_role != 0;
+  const bool dst_busy = (dst->clone_epoch == ep && dst->clone_role != 0) || dst->append_epoch == ep;
   if (src_is_dst || dst_busy || g_ctx.clone_jobs.size() >= 32768) {
     if (!flush_clones()) return -1;
   }
@@ -1111,36 +1163,37 @@ int mvb_lp_set_bounds(mvb_lp *lp, int k, double lb, double ub) {
 namespace {
 
 // tableau row of a new constraint a.x: a_N + sum_i a_{head[i]} T[i,:], terms in
-// row order, one fma each (specification: oracle mvb_lp_append_row)
-__global__ void append_row_kernel(LPDev L, int cT, int cS, const double *a) {
+// row order, one fma each (specification: oracle mvb_lp_append_row); blockIdx.y = job
+__global__ void append_rows_kernel(const AppendJob *jobs, const double *arena) {
+  const AppendJob &J = jobs[blockIdx.y];
+  const LPDev &L = J.L;
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   const int m = L.m, n = L.n, ld = L.ld;
   if (p >= ld) return;
-  const double *T = L.T[cT];
+  const double *a = arena + J.a_off;
+  const double *T = L.T[J.cT];
   double acc = 0.0;
   if (p < n) {
-    const int k = L.nb[cS][p];
+    const int k = L.nb[J.cS][p];
     acc = k < n ? a[k] : 0.0;
     for (int i = 1; i <= m; i++) {
-      const int h = L.head[cS][i];
+      const int h = L.head[J.cS][i];
       if (h < n && a[h] != 0.0) acc = fma(a[h], T[(size_t)i * ld + p], acc);
     }
   }
-  L.T[cT][(size_t)(m + 1) * ld + p] = acc;
+  L.T[J.cT][(size_t)(m + 1) * ld + p] = acc;
   if (p == 0) {
-    L.head[cS][m + 1] = n + m;
-    L.beta[cS][m + 1] = 0.0;
+    L.head[J.cS][m + 1] = n + m;
+    L.beta[J.cS][m + 1] = 0.0;
+    L.lb[n + m] = J.lb;
+    L.ub[n + m] = J.ub;
   }
 }
 
-// K7: gather tableau rows into a contiguous staging buffer
-__global__ void gather_rows_kernel(const double *T, int ld, int n, const int *rows, int nrows,
-                                   double *out) {
-  const int t = blockIdx.y;
-  if (t >= nrows) return;
-  const double *src = T + (size_t)rows[t] * ld;
-  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
-    out[(size_t)t * n + j] = src[j];
+// K7: gather tableau rows into a contiguous staging buffer; blockIdx.x = row job
+__global__ void gather_rows_kernel(const GatherJob *jobs) {
+  const GatherJob j = jobs[blockIdx.x];
+  for (int c = threadIdx.x; c < j.n; c += blockDim.x) j.dst[c] = j.src[c];
 }
 
 bool lp_grow(mvb_lp *lp, int mcap) {
@@ -1172,26 +1225,32 @@ bool lp_grow(mvb_lp *lp, int mcap) {
 }  // namespace
 
 extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double ub) {
-  if (!flush_clones()) return -1;
-  if (lp->m + 1 > lp->mcap && !lp_grow(lp, lp->mcap + 16 + lp->mcap / 4)) return -1;
+  // queued: the rows of a B&B round are formed by one kernel (flush_clones).  An LP that takes
+  // part in a queued clone, already has a queued row, or must grow is brought up to date first.
+  const bool in_clone = lp->clone_epoch == g_ctx.clone_epoch && lp->clone_role != 0;
+  const bool grows = lp->m + 1 > lp->mcap;
+  if (in_clone || grows || lp->append_epoch == g_ctx.clone_epoch || g_ctx.append_jobs.size() >= 16384) {
+    if (!flush_clones()) return -1;
+  }
+  if (grows && !lp_grow(lp, lp->mcap + 16 + lp->mcap / 4)) return -1;
   const int n = lp->n, m = lp->m;
-  cudaStream_t st = g_ctx.stream;
-  if (!lp_push_small(lp)) return -1;  // flags of the current state must be on the device
-  if (!ensure_stage((size_t)n * sizeof(double))) return -1;
-  CKI(cudaMemcpyAsync(g_ctx.stage, a, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
   lp->dev.m = m;
-  append_row_kernel<<<(lp->ld + 127) / 128, 128, 0, st>>>(lp->dev, lp->curT, lp->curS,
-                                                          (const double *)g_ctx.stage);
-  CKI(cudaGetLastError());
-  g_launches++;
+  AppendJob j;
+  j.L = lp->dev;
+  j.cT = lp->curT;
+  j.cS = lp->curS;
+  j.a_off = g_ctx.append_a.size();
+  j.lb = lb;
+  j.ub = ub;
+  g_ctx.append_a.insert(g_ctx.append_a.end(), a, a + n);
+  g_ctx.append_jobs.push_back(j);
+  lp->append_epoch = g_ctx.clone_epoch;
   lp->m = m + 1;
   lp->dev.m = m + 1;
   lp->lb.push_back(lb);
   lp->ub.push_back(ub);
   lp->head.push_back(n + m);
   lp->x.push_back(0.0);
-  lp->bounds_dirty = true;
-  CKI(cudaStreamSynchronize(st));  // `a` and the staging buffer are free again
   return 0;
 }
 
@@ -1402,26 +1461,47 @@ int mvb_lp_get_basis(mvb_lp *lp, int *head, int *nb, int *at) {
   return 0;
 }
 
-int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
+int mvb_lp_get_tab_rows_batch(mvb_lp *const *lps, int count, const int *rows, const int *nrows, double *out) {
   if (!flush_clones()) return -1;
-  if (nrows <= 0) return 0;
-  for (int t = 0; t < nrows; t++)
-    if (rows[t] < 0 || rows[t] > lp->m) { g_err = "mvb_lp_get_tab_rows: row out of range"; return -1; }
+  size_t njobs = 0, odoubles = 0;
+  for (int k = 0; k < count; k++) {
+    if (nrows[k] < 0) { g_err = "mvb_lp_get_tab_rows: negative row count"; return -1; }
+    njobs += (size_t)nrows[k];
+    odoubles += (size_t)nrows[k] * lps[k]->n;
+  }
+  if (!njobs) return 0;
   cudaStream_t st = g_ctx.stream;
-  const size_t rb = align_up((size_t)nrows * sizeof(int), 256);
-  const size_t ob = (size_t)nrows * lp->n * sizeof(double);
-  if (!ensure_stage(rb + ob)) return -1;
-  int *drows = (int *)g_ctx.stage;
-  double *dout = (double *)(g_ctx.stage + rb);
-  CKI(cudaMemcpyAsync(drows, rows, (size_t)nrows * sizeof(int), cudaMemcpyHostToDevice, st));
-  dim3 grid((lp->n + 255) / 256, nrows);
-  grid.x = std::min<unsigned>(grid.x, 64);
-  gather_rows_kernel<<<grid, 256, 0, st>>>(lp->dev.T[lp->curT], lp->ld, lp->n, drows, nrows, dout);
+  const size_t jb = align_up(njobs * sizeof(GatherJob), 256), ob = odoubles * sizeof(double);
+  if (!ensure_stage(jb + ob)) return -1;
+  if (g_ctx.gather_cap < jb + ob) {
+    if (g_ctx.h_gather) CKI(cudaFreeHost(g_ctx.h_gather));
+    g_ctx.gather_cap = std::max((jb + ob) * 2, (size_t)1 << 20);
+    CKI(cudaMallocHost((void **)&g_ctx.h_gather, g_ctx.gather_cap));
+  }
+  GatherJob *hj = (GatherJob *)g_ctx.h_gather;
+  double *dout = (double *)(g_ctx.stage + jb);
+  size_t t = 0, o = 0;
+  for (int k = 0; k < count; k++) {
+    mvb_lp *lp = lps[k];
+    for (int r = 0; r < nrows[k]; r++, t++) {
+      const int row = rows[t];
+      if (row < 0 || row > lp->m) { g_err = "mvb_lp_get_tab_rows: row out of range"; return -1; }
+      hj[t] = GatherJob{lp->dev.T[lp->curT] + (size_t)row * lp->ld, dout + o, lp->n, 0};
+      o += lp->n;
+    }
+  }
+  CKI(cudaMemcpyAsync(g_ctx.stage, hj, njobs * sizeof(GatherJob), cudaMemcpyHostToDevice, st));
+  gather_rows_kernel<<<(unsigned)njobs, 128, 0, st>>>((const GatherJob *)g_ctx.stage);
   CKI(cudaGetLastError());
   g_launches++;
-  CKI(cudaMemcpyAsync(out, dout, ob, cudaMemcpyDeviceToHost, st));
+  CKI(cudaMemcpyAsync(g_ctx.h_gather + jb, dout, ob, cudaMemcpyDeviceToHost, st));
   CKI(cudaStreamSynchronize(st));
+  std::memcpy(out, g_ctx.h_gather + jb, ob);
   return 0;
+}
+
+int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
+  return mvb_lp_get_tab_rows_batch(&lp, 1, rows, &nrows, out);
 }
 
 int mvb_lp_get_tableau(mvb_lp *lp, double *T, double *beta) {

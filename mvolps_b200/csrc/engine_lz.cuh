@@ -76,8 +76,10 @@ __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned coun
 }
 __device__ __forceinline__ void bulk_row_load(double *dst, const double *src, unsigned bytes,
                                               unsigned long long *bar) {
-  // order earlier generic-proxy accesses of dst before the async-proxy write
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  // order earlier generic-proxy accesses before the async-proxy copy: of dst (shared), and of the
+  // source row, which other CTAs wrote with st.cg in the last flush pass and this CTA acquired at
+  // the group barrier (global)
+  asm volatile("fence.proxy.async;" ::: "memory");
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
   asm volatile(
@@ -85,6 +87,9 @@ __device__ __forceinline__ void bulk_row_load(double *dst, const double *src, un
           smem_u32(dst)),
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
+}
+__device__ __forceinline__ void mbar_inval(unsigned long long *bar) {
+  asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
   asm volatile(
@@ -981,6 +986,9 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
   lz_flush(S);
   lz_need_tableau(S);
   __syncthreads();
+  // the next LP of this CTA lays its shared memory out afresh: the barrier object must not stay
+  // valid (re-initialising a live mbarrier is undefined)
+  if (tid == 0) mbar_inval(zMbar(l, m));
   gen = S->gen;
   cT = S->cT;
   ty = S->ty;

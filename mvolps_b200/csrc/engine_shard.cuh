@@ -699,10 +699,12 @@ int shard_peer_setup(mvb_shard *s) {
       bad = 1.0;
     }
     if (nm.base) {  // the handles travel through the mailbox itself (not in use yet)
-      cudaMemcpyAsync(nm.base, &mine, sizeof(mine), cudaMemcpyHostToDevice, st);
+      if (cudaMemcpyAsync(nm.base, &mine, sizeof(mine), cudaMemcpyHostToDevice, st) != cudaSuccess) bad = 1.0;
+      // (the collective runs even after a local failure: every rank must take part; `bad` is agreed below)
       if (cm->allgather_dev(cm->ctx, nm.base, nm.base + 4096, sizeof(mine), st)) { g_err = "peer set-up: all-gather failed"; return -1; }
-      cudaMemcpyAsync(all.data(), nm.base + 4096, sizeof(mine) * s->world, cudaMemcpyDeviceToHost, st);
+      if (cudaMemcpyAsync(all.data(), nm.base + 4096, sizeof(mine) * s->world, cudaMemcpyDeviceToHost, st) != cudaSuccess) bad = 1.0;
       if (cudaStreamSynchronize(st) != cudaSuccess) bad = 1.0;
+      if (bad != 0.0) cudaGetLastError();
     }
     if (bad == 0.0)
       for (int k = 0; k < s->world; k++) {
@@ -731,8 +733,9 @@ int shard_peer_setup(mvb_shard *s) {
   d.push = 1;
   // counters back to zero, and nobody pushes before every rank has done so: the (stream-ordered)
   // all-gather below completes only after every rank has enqueued its memset
-  cudaMemsetAsync(d.flag, 0, (size_t)SHARD_SLOTS * s->world * sizeof(unsigned long long), st);
+  const bool zeroed = cudaMemsetAsync(d.flag, 0, (size_t)SHARD_SLOTS * s->world * sizeof(unsigned long long), st) == cudaSuccess;
   if (cm->allgather_dev(cm->ctx, s->fin_send, s->fin_recv, 16, st)) { g_err = "peer set-up: barrier failed"; return -1; }
+  if (!zeroed) { g_err = "peer set-up: cannot reset the arrival counters"; return -1; }
   return 1;
 }
 

@@ -27,13 +27,29 @@ double mv_eff_lb(int type, double lb) {
 double mv_eff_ub(int type, double ub) {
   return (type == GLP_UP || type == GLP_DB || type == GLP_FX) ? ub : HUGE_VAL;
 }
+/* Integer snap of the values the shim reports (glp_get_col_prim / glp_get_row_prim / the
+ * objective computed from them).  The reference tests integrality EXACTLY (util.cpp:435-451,
+ * trunc(x) != x) on what GLPK returns; a dense tableau that is never refactorised returns e.g.
+ * 0.3/0.1 = 2.9999999999999996 for a vertex at 3, which that test would branch on (and the up
+ * child x >= 3 is then infeasible by one ulp: the optimum would be lost).  Values within
+ * g_snap_tol of an integer are therefore reported as that integer.  MVOLPS_SNAP_TOL=0 (or
+ * mvb_glp_snap_tol(0)) turns it off; DESIGN.md section 5, tests/test_shim_and_bnb.py. */
+static double g_snap_tol = [] {
+  const char *e = std::getenv("MVOLPS_SNAP_TOL");
+  return e ? std::atof(e) : MV_SNAP_TOL;
+}();
+extern "C" double mvb_glp_snap_tol(double tol) {
+  const double old = g_snap_tol;
+  if (tol >= 0.0) g_snap_tol = tol;
+  return old;
+}
 double mv_snap(double x) {
   /* r = rint(x) without the libm call: below 2^51 adding and subtracting 2^52+2^51
    * rounds to nearest-even exactly as rint does; copysign keeps rint's signed zero */
   const double ax = std::fabs(x);
   if (!(ax < 2251799813685248.0)) return x;  // already integral (or inf/nan)
   const double r = std::copysign((ax + 6755399441055744.0) - 6755399441055744.0, x);
-  return std::fabs(x - r) <= MV_SNAP_TOL ? r : x;
+  return std::fabs(x - r) <= g_snap_tol ? r : x;
 }
 
 static void drop_engine(glp_prob *P) {
@@ -41,6 +57,7 @@ static void drop_engine(glp_prob *P) {
   P->eng = nullptr;
   P->eng_rows = 0;
   P->eng_stale = true;
+  P->eng_changed = true;
   P->eng_lb.clear();
   P->eng_ub.clear();
   P->dirty.clear();
@@ -104,6 +121,7 @@ void glp_copy_prob(glp_prob *dest, glp_prob *src, int names) {
     if (!dest->eng) shim_abort(mvb_last_error());
     dest->eng_rows = src->eng_rows;
     dest->eng_stale = false;
+    dest->eng_changed = src->eng_changed;
     dest->eng_lb = src->eng_lb;
     dest->eng_ub = src->eng_ub;
     dest->dirty = src->dirty;
@@ -172,7 +190,16 @@ double glp_get_obj_coef(glp_prob *P, int j) {
   return col_at(P, j, "glp_get_obj_coef: column out of range").coef;
 }
 void glp_set_obj_coef(glp_prob *P, int j, double coef) {
-  if (j == 0) { P->c0 = coef; return; }
+  if (j == 0) {
+    // the constant term does not touch the LP: a held solution keeps its point, its value moves
+    if (coef != P->c0 && P->status != GLP_UNDEF) {
+      double z = coef;
+      for (const MvCol &c : P->cols) z = std::fma(c.coef, c.prim, z);
+      P->obj_val = z;
+    }
+    P->c0 = coef;
+    return;
+  }
   MvCol &c = col_at(P, j, "glp_set_obj_coef: column out of range");
   if (c.coef != coef) P->eng_stale = true;
   c.coef = coef;
@@ -299,7 +326,15 @@ int glp_get_it_cnt(glp_prob *P) { return P->it_cnt; }
 /* bring the engine's LP in line with the problem object: cold build when the
  * matrix/objective changed, otherwise append the new rows (cut.cpp:23-43) and
  * forward changed bounds (bs.cpp:274,282) */
+static int sync_engine_delta(glp_prob *P, bool *changed);
 static int sync_engine(glp_prob *P, bool *changed) {
+  bool now = false;
+  const int rc = sync_engine_delta(P, &now);
+  if (now) P->eng_changed = true;
+  *changed = P->eng_changed;
+  return rc;
+}
+static int sync_engine_delta(glp_prob *P, bool *changed) {
   *changed = false;
   int m = (int)P->rows.size(), n = (int)P->cols.size();
   if (P->eng && !P->eng_stale && P->eng_rows > m) P->eng_stale = true;
@@ -413,6 +448,7 @@ int mv_pull_solution(glp_prob *P, const mvb_result &res) {
   P->obj_val = z;
   P->it_cnt = res.iters;
   P->last = res;
+  P->eng_changed = false;
   switch (res.status) {
     case MVB_OPT: P->status = GLP_OPT; break;
     case MVB_NOFEAS: P->status = GLP_NOFEAS; break;
@@ -441,10 +477,30 @@ extern "C" {
 int glp_simplex(glp_prob *P, const glp_smcp *parm) {
   (void)parm;
   int m = (int)P->rows.size(), n = (int)P->cols.size();
-  if (m == 0 || n == 0) {
-    /* GLPK reports "problem has no rows/columns"; MVOLPS never gets here */
+  if (n == 0) {
     P->status = GLP_UNDEF;
     return GLP_EFAIL;
+  }
+  if (m == 0) {
+    /* no rows: every column sits at the bound its cost prefers (GLPK solves such problems
+     * too); nothing to send to the engine.  MVOLPS never gets here. */
+    double z = P->c0;
+    P->status = GLP_OPT;
+    for (MvCol &c : P->cols) {
+      const double cost = P->dir == GLP_MAX ? -c.coef : c.coef;
+      const double l = mv_eff_lb(c.type, c.lb), u = mv_eff_ub(c.type, c.ub);
+      double v;
+      if (c.type == GLP_FX) { v = c.lb; c.stat = GLP_NS; }
+      else if (cost > 0.0 || (cost == 0.0 && l > -HUGE_VAL)) { v = l; c.stat = GLP_NL; }
+      else if (cost < 0.0 || u < HUGE_VAL) { v = u; c.stat = GLP_NU; }
+      else { v = 0.0; c.stat = GLP_NF; }
+      if (!(v > -HUGE_VAL && v < HUGE_VAL)) { P->status = GLP_UNBND; v = 0.0; }
+      c.prim = v;
+      z = std::fma(c.coef, v, z);
+    }
+    P->obj_val = z;
+    P->it_cnt = 0;
+    return 0;
   }
   bool changed = false;
   if (sync_engine(P, &changed)) {

@@ -83,6 +83,8 @@ struct glp_prob {
   mvb_lp *eng = nullptr;
   int eng_rows = 0;            // rows the engine tableau already contains
   bool eng_stale = true;       // matrix/objective changed: rebuild from scratch
+  bool eng_changed = true;     // the engine's LP differs from the one the held solution belongs to
+                               // (sticky across syncs and copies until the next solve is pulled)
   std::vector<double> eng_lb, eng_ub;  // bounds last sent, by engine id
   std::vector<int> dirty;              // engine ids whose bounds were set since the last sync
   std::vector<int> head, nb, at;       // basis after the last solve

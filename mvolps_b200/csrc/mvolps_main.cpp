@@ -36,6 +36,9 @@ int main(int argc, char **argv) {
               << "                 objective impact | fractional part of the node's own solution\n"
               << "  -bs [{0|1}]    node choice: FIFO | best bound\n"
               << "  -cm [{0|1|2}]  cuts: off | reference gmi.cpp formula | textbook GMI\n"
+              << "  -cf X          cut frequency in [0, 1]: share of the branched nodes that generate cuts (with -cm)\n"
+              << "  -cs [{0|1}]    which cut becomes the node's new row: last pooled (reference) | most violated of the node's own\n"
+              << "  -rh            root heuristic: the root LP solution rounded down as first incumbent\n"
               << "  -bw N          FIFO nodes solved per device launch (default 256)\n"
               << "  -nl N          node budget\n"
               << "  -ev FILE       write the event stream, timeSpan type oid pid dir ... (message.h:141-226)\n";
@@ -62,8 +65,17 @@ int main(int argc, char **argv) {
   };
   if (!ival("-bs", 0, 1, p.node_strategy) || !ival("-vs", 0, 3, p.var_strategy) ||
       !ival("-cm", 0, 2, p.cut_mode) || !ival("-bw", 1, 1 << 20, p.batch_width) ||
-      !ival("-nl", 1, 1 << 30, p.max_iters))
+      !ival("-nl", 1, 1 << 30, p.max_iters) || !ival("-cs", 0, 1, p.cut_select))
     return -1;
+  if (in.has("-cm") && in.has("-cf")) {  // 2test.cpp:135-149: read only together with -cm
+    const double chance = std::atof(in.get("-cf").c_str());
+    if (!(chance <= 1.0 && chance >= 0.0)) {
+      std::fprintf(stderr, "Cut Frequency parameter must be in range [0.0, 1.0]\n");
+      return -1;
+    }
+    p.cut_skip = 1.0 - chance;
+  }
+  p.root_heuristic = in.has("-rh");
   p.timed_events = in.has("-ev");
   if (mvb_device_init(0)) { std::fprintf(stderr, "%s\n", mvb_last_error()); return 2; }
   mvb_bnb *h = mvb_bnb_run(prob, &p);

@@ -583,6 +583,16 @@ int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
   return 0;
 }
 
+int mvb_lp_get_tab_rows_batch(mvb_lp *const *lps, int count, const int *rows, const int *nrows,
+                              double *out) {
+  for (int k = 0; k < count; k++) {
+    if (mvb_lp_get_tab_rows(lps[k], rows, nrows[k], out)) return -1;
+    rows += nrows[k];
+    out += (size_t)nrows[k] * lps[k]->n;
+  }
+  return 0;
+}
+
 int mvb_lp_get_tableau(mvb_lp *lp, double *T, double *beta) {
   for (int i = 0; i <= lp->m; i++)
     memcpy(T + (size_t)i * lp->n, lp->T + (size_t)i * lp->ld, lp->n * sizeof(double));

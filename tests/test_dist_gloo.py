@@ -131,7 +131,8 @@ def test_node_sharded_bnb_world2_gloo():
         assert a["x"] == b["x"] and a["inc_rank"] == b["inc_rank"] and a["total"] == b["total"]
         assert abs(np.dot(instances.mdkp(*args)["c"], a["x"]) - a["incumbent"]) < 1e-9
         assert a["split_at"] == b["split_at"] and a["split_at"] >= 0
-        assert a["iterations"] + b["iterations"] - a["split_at"] == a["total"] - a["split_at"]
+        # the lock-step ramp-up is replicated work and counts once
+        assert a["total"] == a["split_at"] + (a["iterations"] - a["split_at"]) + (b["iterations"] - b["split_at"])
         assert 0 < a["iterations"] < a["total"] and 0 < b["iterations"] < b["total"]
         if name == "mdkp_12x4_s1":
             assert abs(a["incumbent"] - gold[name]["highs_ilp"]) < 1e-9
@@ -151,7 +152,7 @@ def _steal_worker(rank, world, port, q, oracle_lib):
             for ns in (1, 0):
                 out = GlpProb.from_instance(orc, instances.mdkp(*args)).bnb(batch_width=8, comm=comm, no_steal=ns,
                                                                             cut_mode=cm)
-                res[(args, cm, ns)] = {k: out[k] for k in ("incumbent", "iterations", "total_nodes", "nodes_sent",
+                res[(args, cm, ns)] = {k: out[k] for k in ("incumbent", "iterations", "total_nodes", "nodes_sent", "split_at",
                                                           "nodes_received", "steal_rounds", "has_incumbent")}
                 res[(args, cm, ns)]["x"] = out["x"].tolist()
                 res[(args, cm, ns)]["stolen_in_tree"] = out["tree"].count("\n")
@@ -193,7 +194,8 @@ def test_work_stealing_world3_gloo():
         assert len({rr["steal_rounds"] for rr in on}) == 1      # same matching on every rank
         its_on, its_off = [rr["iterations"] for rr in on], [rr["iterations"] for rr in off]
         assert max(its_on) - min(its_on) < max(its_off) - min(its_off)  # balanced
-        assert sum(its_on) == on[0]["total_nodes"]
+        res_split = on[0]["split_at"]
+        assert sum(its_on) - (world - 1) * res_split == on[0]["total_nodes"]
 
 
 def _plan(lib, cnt):

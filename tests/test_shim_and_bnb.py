@@ -303,3 +303,132 @@ def test_bnb_counts_cached_resolves(oracle, tmp_path):
     out = p.bnb(**_kwargs(case["flags"]))
     assert out["lp_solves"] >= out["cached_solves"] > 0
     assert out["iterations"] == case["iterations"]
+
+
+# ---------------------------------------------------------------- round-2 driver options
+def test_cut_frequency_and_selection(oracle, tmp_path):
+    """-cf (2test.cpp:135-149 parses it, util.cpp:259-261 stores it, nothing reads it): here the
+    share of branched nodes that run the cut step, decided by a hash of the oid -> reproducible;
+    cut_select 1 = the rule cut.cpp:16-19 leaves as a TODO (most violated cut of the node's own).
+    Textbook GMI cuts never cut off the optimum whatever the frequency / selection."""
+    for name in ("small3", "mdkp_12x4_s1", "mdkp_12x4_s4_cm1"):
+        case = [c for c in _gold() if c["name"] == name][0]
+        base = _prob(oracle, case, tmp_path).bnb(cut_mode=0)
+        full = _prob(oracle, case, tmp_path).bnb(cut_mode=2)
+        assert _prob(oracle, case, tmp_path).bnb(cut_mode=2, cut_freq=1.0)["event_hash"] == full["event_hash"]
+        none = _prob(oracle, case, tmp_path).bnb(cut_mode=2, cut_freq=0.0)
+        assert none["tree"] == base["tree"] and none["launches_aux"] == 0  # chance 0: the cut step never runs
+        half = _prob(oracle, case, tmp_path).bnb(cut_mode=2, cut_freq=0.5)
+        half2 = _prob(oracle, case, tmp_path).bnb(cut_mode=2, cut_freq=0.5)
+        assert half["events"] == half2["events"]  # reproducible
+        sel = _prob(oracle, case, tmp_path).bnb(cut_mode=2, cut_select=1)
+        for out in (full, half, sel):
+            assert out["has_incumbent"] and abs(out["incumbent"] - base["incumbent"]) <= 1e-9 * abs(base["incumbent"]), name
+
+
+def test_gmi_rows_come_from_the_node_itself(oracle, tmp_path):
+    """A node whose columns produce no textbook cut gets no row (it used to inherit the last cut of
+    another subtree, valid only under that subtree's bounds).  With every row valid in the subtree
+    it is added to, a tree that closes never loses the true ILP optimum (HiGHS); it may end above it,
+    at a point with a negative entry, because a down child loses its lower bound (bs.cpp:274)."""
+    from scipy.optimize import Bounds, LinearConstraint, milp
+    closed = 0
+    for args in ((12, 4, 1), (12, 4, 4), (11, 4, 9), (14, 5, 3), (16, 4, 6), (10, 3, 5)):
+        inst = instances.mdkp(*args)
+        cut = GlpProb.from_instance(oracle, inst).bnb(cut_mode=2, max_iters=20000)
+        if cut["hit_limit"]:
+            continue
+        closed += 1
+        ref = milp(-inst["c"], constraints=LinearConstraint(inst["A"], -np.inf, inst["row_ub"]),
+                   integrality=np.ones(args[0]), bounds=Bounds(0, 3))
+        assert cut["has_incumbent"] and cut["incumbent"] >= -ref.fun - 1e-9, args
+        if np.all(cut["x"] >= 0):
+            assert abs(cut["incumbent"] + ref.fun) <= 1e-9 * abs(ref.fun), args
+    assert closed >= 3
+
+
+def test_root_heuristic_gives_first_incumbent(oracle):
+    inst = instances.mdkp(40, 10, 7)
+    plain = GlpProb.from_instance(oracle, inst).bnb(max_iters=300)
+    heur = GlpProb.from_instance(oracle, inst).bnb(max_iters=300, root_heuristic=1)
+    assert heur["has_incumbent"] and heur["events"].splitlines()[1].startswith("heuristic 1 ")
+    x = heur["x"] if not plain["has_incumbent"] or heur["incumbent"] >= plain["incumbent"] else None
+    if x is not None:
+        assert np.all(inst["A"] @ x <= inst["row_ub"] + 1e-9) and np.array_equal(x, np.round(x))
+        assert abs(inst["c"] @ x - heur["incumbent"]) < 1e-9
+    # with an incumbent from the start the bound test (bs.cpp:210) can only prune more
+    assert heur["oids"] <= plain["oids"]
+
+
+def test_batched_row_gather_equals_single_calls(oracle):
+    """mvb_lp_get_tab_rows_batch (all cut candidates of a round in one engine call) == one
+    mvb_lp_get_tab_rows per LP."""
+    import ctypes as C
+    from mvolps_b200.lp import EngineLP
+    lps = [EngineLP.from_instance(oracle, instances.dense_lp(12 + k, 20, k)) for k in range(4)]
+    for lp in lps:
+        lp.solve()
+    rows = [[0, 3, 5], [], [12, 1], [7]]
+    flat = np.array(sum(rows, []), np.int32)
+    cnt = np.array([len(r) for r in rows], np.int32)
+    out = np.zeros((len(flat), 20))
+    arr = (C.c_void_p * 4)(*[lp.h for lp in lps])
+    assert oracle.mvb_lp_get_tab_rows_batch(arr, 4, capi.iptr(flat), capi.iptr(cnt), capi.dptr(out)) == 0
+    k = 0
+    for lp, r in zip(lps, rows):
+        if r:
+            assert np.array_equal(lp.tab_rows(r), out[k:k + len(r)])
+        k += len(r)
+
+
+def test_integer_snap_and_what_happens_without_it(oracle, tmp_path):
+    """The shim reports values within 1e-9 of an integer as that integer, in front of the
+    reference's exact test trunc(x) != x (util.cpp:435-451).  max x, 0.1 x <= 0.3, x integer: the
+    vertex is 0.3/0.1 = 2.9999999999999996 in fp64.  With the snap the root's violated list is
+    empty (integral root: bs.cpp:134-149 stops there); without it x is on the violated list, the
+    root branches on it and the tree has three nodes."""
+    lp = tmp_path / "snap.lp"
+    lp.write_text("Maximize\n obj: x\nSubject To\n c1: 0.1 x <= 0.3\nBounds\n 0 <= x <= 10\nGeneral\n x\nEnd\n")
+    assert 0.3 / 0.1 != 3.0
+    old = oracle.mvb_glp_snap_tol(-1.0)
+    assert old == 1e-9
+    try:
+        p = GlpProb.from_file(oracle, str(lp))
+        p.simplex()
+        assert p.col_prim()[0] == 3.0
+        a = GlpProb.from_file(oracle, str(lp)).bnb()
+        assert a["oids"] == 1 and a["tree"].strip() == "-1 I"
+        oracle.mvb_glp_snap_tol(0.0)
+        p = GlpProb.from_file(oracle, str(lp))
+        p.simplex()
+        assert p.col_prim()[0] == 0.3 / 0.1  # the raw tableau value
+        b = GlpProb.from_file(oracle, str(lp)).bnb()
+        assert b["oids"] == 3 and "branched 1 " in b["events"]  # x was on the violated list
+        assert [ln.strip() for ln in b["tree"].splitlines() if ln.strip()] == ["-1", "-2 I", "-3 I"]
+    finally:
+        oracle.mvb_glp_snap_tol(old)
+
+
+def test_rowless_problem_and_objective_constant(oracle):
+    """GLPK solves bound-only problems (no rows); a change of the constant term moves the held
+    objective value without a re-solve."""
+    L = oracle
+    p = GlpProb(L)
+    L.glp_set_obj_dir(p.h, capi.GLP_MAX)
+    L.glp_add_cols(p.h, 3)
+    for j, (t, lo, hi, c) in enumerate([(capi.GLP_DB, 0.0, 4.0, 2.0), (capi.GLP_DB, -1.0, 5.0, -3.0),
+                                        (capi.GLP_FX, 7.0, 7.0, 1.0)], 1):
+        L.glp_set_col_bnds(p.h, j, t, lo, hi)
+        L.glp_set_obj_coef(p.h, j, c)
+    assert p.simplex() == 0 and p.status() == capi.GLP_OPT
+    assert list(p.col_prim()) == [4.0, -1.0, 7.0] and p.obj_val() == 8.0 + 3.0 + 7.0
+    L.glp_set_obj_coef(p.h, 0, 100.0)
+    assert p.obj_val() == 118.0
+    L.glp_set_col_bnds(p.h, 1, capi.GLP_LO, 0.0, 0.0)
+    assert p.simplex() == 0 and p.status() == capi.GLP_UNBND
+    q = GlpProb.from_file(L, SMALL3)
+    q.simplex()
+    z = q.obj_val()
+    L.glp_set_obj_coef(q.h, 0, 5.0)
+    assert abs(q.obj_val() - (z + 5.0)) < 1e-9
+    assert q.simplex() == 0 and L.glp_get_it_cnt(q.h) == 0 and abs(q.obj_val() - (z + 5.0)) < 1e-9
