@@ -95,6 +95,7 @@ typedef struct mvb_bnb_stats {
   int spec_adopted;      /* ... of which the serial order branched (the rest were fathomed first
                             or are still open) */
   int launches_aux;      /* batched tableau-row gathers of the cut step (one per round with cuts) */
+  int solved_here;       /* LP solves this rank's device ran (MVB_DIST_SYNC: its share of lp_solves) */
 } mvb_bnb_stats;
 
 typedef struct mvb_bnb mvb_bnb;

@@ -29,6 +29,10 @@ typedef struct mvb_comm {
    * nothing to receive); only the ranks of a pair call it.  May be NULL: the
    * node-sharded tree then runs without hand-over.  0 = ok */
   int (*sendrecv_host)(void *ctx, const void *send, size_t sbytes, int dst, void *recv, size_t rbytes, int src);
+  /* all-gather of `bytes` bytes per rank, HOST buffers (recv holds world*bytes, by rank): the
+   * result exchange of the round-synchronous tree (MVB_DIST_SYNC, include/mvolps_bnb.h).  May be
+   * NULL: that mode is then refused.  0 = ok */
+  int (*allgather_host)(void *ctx, const void *send, void *recv, size_t bytes);
 } mvb_comm;
 
 #ifdef __cplusplus

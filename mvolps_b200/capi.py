@@ -87,7 +87,7 @@ class BnbStats(C.Structure):
         ("split_at", C.c_int), ("incumbent_rank", C.c_int), ("total_nodes", C.c_longlong),
         ("cached_solves", C.c_int), ("nodes_sent", C.c_int), ("nodes_received", C.c_int),
         ("steal_rounds", C.c_int), ("spec_nodes", C.c_int), ("spec_adopted", C.c_int),
-        ("launches_aux", C.c_int),
+        ("launches_aux", C.c_int), ("solved_here", C.c_int),
     ]
 
 
@@ -203,13 +203,14 @@ ALLGATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size
 ALLREDUCE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, _dp, C.c_int)
 DESTROY_FN = C.CFUNCTYPE(None, C.c_void_p)
 SENDRECV_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_size_t, C.c_int)
+ALLGATHER_HOST_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t)
 
 
 class Comm(C.Structure):
     """struct mvb_comm (include/mvolps_dist.h): a caller-supplied communicator."""
     _fields_ = [("ctx", C.c_void_p), ("rank", C.c_int), ("world", C.c_int),
                 ("allgather_dev", ALLGATHER_FN), ("allreduce_max", ALLREDUCE_FN), ("destroy", DESTROY_FN),
-                ("sendrecv_host", SENDRECV_FN)]
+                ("sendrecv_host", SENDRECV_FN), ("allgather_host", ALLGATHER_HOST_FN)]
 
 
 def load_library(path):

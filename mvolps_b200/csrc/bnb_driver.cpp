@@ -13,6 +13,7 @@
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <deque>
 #include <limits>
 #include <map>
@@ -222,6 +223,26 @@ struct Driver {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   }
 
+  // ---- round-synchronous mode (MVB_DIST_SYNC): every rank runs this very driver
+  // and takes the same decisions; after the replicated ramp-up every open node gets an OWNER
+  // rank that alone keeps its device tableau (children inherit it); the LPs of a round are solved
+  // by their owners and the solutions exchanged (one all-gather per launch), then consumed in the
+  // serial order: oids, prune tags, events and tree text are the serial run's on every rank.
+  bool sync_mode = false, dealt = false;
+  static size_t rec_bytes(const glp_prob *p) {
+    const size_t m = p->rows.size(), n = p->cols.size();
+    return (sizeof(mvb_result) + 8 * (n + m) + 4 * (m + 2 * n) + 7) / 8 * 8;
+  }
+  bool allgather_segments(const std::vector<size_t> &seg, const std::vector<char> &mine, std::vector<char> &all,
+                          size_t &stride) {
+    stride = 8;
+    for (size_t b : seg) stride = std::max(stride, b);
+    std::vector<char> send(stride, 0);
+    std::copy(mine.begin(), mine.end(), send.begin());
+    all.resize(stride * seg.size());
+    return comm->allgather_host(comm->ctx, send.data(), all.data(), stride) == 0;
+  }
+
   // counted = false: speculative solves; they enter lp_solves / simplex_iters when (and if) the
   // serial order adopts them, so the statistics are those of the unspeculated run
   bool solve_many(const std::vector<glp_prob *> &all, bool counted = true) {
@@ -234,22 +255,72 @@ struct Driver {
       if (mv_sync_engine(p, &changed)) return false;
       if (mv_answer_cached(p, changed)) { if (counted) out->st.cached_solves++; continue; }
       ps.push_back(p);
-      engs.push_back(p->eng);
+      if (!p->ghost) engs.push_back(p->eng);
     }
     if (counted) out->st.lp_solves += (int)all.size();
     double t1 = now();
     if (ps.empty()) { t_sync += t1 - t0; return true; }
-    std::vector<mvb_result> res(ps.size());
+    std::vector<mvb_result> res(std::max<size_t>(engs.size(), 1));
     mvb_opts o{};
-    if (mvb_solve_batch(engs.data(), (int)engs.size(), &o, res.data())) return false;
+    if (!engs.empty() && mvb_solve_batch(engs.data(), (int)engs.size(), &o, res.data())) return false;
+    out->st.solved_here += (int)engs.size();
     double t2 = now();
-    for (size_t k = 0; k < ps.size(); k++) {
-      if (mv_pull_solution(ps[k], res[k])) return false;
-      if (counted) out->st.simplex_iters += res[k].iters;
+    if (!(sync_mode && dealt)) {
+      for (size_t k = 0; k < ps.size(); k++) {
+        if (mv_pull_solution(ps[k], res[k])) return false;
+        if (counted) out->st.simplex_iters += res[k].iters;
+      }
+    } else {
+      // records of my LPs, in batch order: result | x | head | nb | at
+      std::vector<size_t> seg(comm->world, 0);
+      for (auto *p : ps) seg[p->owner] += rec_bytes(p);
+      std::vector<char> mine(seg[comm->rank]), allrec;
+      size_t off = 0, e = 0;
+      for (auto *p : ps) {
+        if (p->ghost) continue;
+        const size_t m = p->rows.size(), n = p->cols.size();
+        char *r = mine.data() + off;
+        std::memcpy(r, &res[e++], sizeof(mvb_result));
+        double *x = (double *)(r + sizeof(mvb_result));
+        int *hd = (int *)(x + n + m);
+        if (mvb_lp_get_primal(p->eng, x) || mvb_lp_get_basis(p->eng, hd, hd + m, hd + m + n)) return false;
+        off += rec_bytes(p);
+      }
+      size_t stride = 0;
+      if (!allgather_segments(seg, mine, allrec, stride)) return false;
+      std::vector<size_t> cur(comm->world, 0);
+      for (auto *p : ps) {
+        const size_t m = p->rows.size(), n = p->cols.size();
+        const char *r = allrec.data() + (size_t)p->owner * stride + cur[p->owner];
+        cur[p->owner] += rec_bytes(p);
+        mvb_result rr;
+        std::memcpy(&rr, r, sizeof rr);
+        const double *x = (const double *)(r + sizeof(mvb_result));
+        const int *hd = (const int *)(x + n + m);
+        mv_install_solution(p, rr, x, hd, hd + m, hd + m + n);
+        if (counted) out->st.simplex_iters += rr.iters;
+      }
     }
     t_sync += t1 - t0; t_solve += t2 - t1; t_pull += now() - t2;
     out->st.launches++;
     return true;
+  }
+
+  // sync mode, end of the ramp-up: owners are dealt round-robin over the open nodes; a rank gives
+  // up the device tableau of every node it does not own
+  void deal_owners(std::deque<std::unique_ptr<Node>> &open) {
+    for (size_t k = 0; k < open.size(); k++) {
+      const int owner = (int)(k % (size_t)comm->world);
+      Node *nd = open[k].get();
+      std::vector<glp_prob *> objs{nd->prob};
+      if (nd->spec) { objs.push_back(nd->spec->down); objs.push_back(nd->spec->up); }
+      for (glp_prob *p : objs) {
+        if (!p) continue;
+        if (owner != comm->rank) mv_make_ghost(p, owner);
+        else p->owner = owner;
+      }
+    }
+    dealt = true;
   }
 
   // printInfo, util.cpp:414-473: -1 infeasible, 1 integral, 0 otherwise
@@ -399,12 +470,52 @@ struct Driver {
       rows.insert(rows.end(), r1.begin(), r1.end());
     }
     buf.resize(tot);
-    if (lps.empty()) return true;
-    const double t0 = now();
-    const int rc = mvb_lp_get_tab_rows_batch(lps.data(), (int)lps.size(), rows.data(), nrows.data(), buf.data());
-    t_rows += now() - t0;
+    if (!(sync_mode && dealt)) {
+      if (lps.empty()) return true;
+      const double t0 = now();
+      const int rc = mvb_lp_get_tab_rows_batch(lps.data(), (int)lps.size(), rows.data(), nrows.data(), buf.data());
+      t_rows += now() - t0;
+      out->st.launches_aux++;
+      return rc == 0;
+    }
+    // sync mode: every rank gathers the rows of the nodes it owns, one all-gather shares them
+    if (tot == 0) return true;
+    std::vector<size_t> seg(comm->world, 0);
+    std::vector<mvb_lp *> my_lps;
+    std::vector<int> my_rows, my_nrows;
+    {
+      size_t t = 0;
+      for (size_t k = 0; k < batch.size(); k++) {
+        if (off[k] == npos) continue;
+        glp_prob *a = batch[k]->prob;
+        const size_t next = [&] { for (size_t j = k + 1; j < batch.size(); j++) if (off[j] != npos) return off[j]; return tot; }();
+        const size_t cnt = (next - off[k]) / a->cols.size();
+        seg[a->owner] += (next - off[k]) * sizeof(double);
+        if (cnt && !a->ghost) {
+          my_lps.push_back(a->eng);
+          my_nrows.push_back((int)cnt);
+          my_rows.insert(my_rows.end(), rows.begin() + t, rows.begin() + t + cnt);
+        }
+        t += cnt;
+      }
+    }
+    std::vector<char> mine(seg[comm->rank]), allrows;
+    if (!my_lps.empty() &&
+        mvb_lp_get_tab_rows_batch(my_lps.data(), (int)my_lps.size(), my_rows.data(), my_nrows.data(), (double *)mine.data()))
+      return false;
     out->st.launches_aux++;
-    return rc == 0;
+    size_t stride = 0;
+    if (!allgather_segments(seg, mine, allrows, stride)) return false;
+    std::vector<size_t> cur(comm->world, 0);
+    for (size_t k = 0; k < batch.size(); k++) {
+      if (off[k] == npos) continue;
+      glp_prob *a = batch[k]->prob;
+      const size_t next = [&] { for (size_t j = k + 1; j < batch.size(); j++) if (off[j] != npos) return off[j]; return tot; }();
+      const size_t bytes = (next - off[k]) * sizeof(double);
+      std::memcpy(buf.data() + off[k], allrows.data() + (size_t)a->owner * stride + cur[a->owner], bytes);
+      cur[a->owner] += bytes;
+    }
+    return true;
   }
 
   // root_heuristic: the root LP solution with its integer columns rounded down; feasible -> objective
@@ -680,7 +791,8 @@ bool Driver::run() {
   const bool spec_on = pr.node_strategy == MVB_NODE_BEST && pr.cut_mode == MVB_CUT_NONE && width > 1 &&
                        !pr.no_speculation;
 
-  const bool dist = comm != nullptr && comm->world > 1;
+  sync_mode = comm != nullptr && comm->world > 1 && pr.dist_mode == MVB_DIST_SYNC;
+  const bool dist = comm != nullptr && comm->world > 1 && !sync_mode;
   const bool steal = dist && !pr.no_steal && comm->sendrecv_host != nullptr;
   bool split = false;        // dist: the queue has been dealt out, ranks now work on their own share
   bool retired = false;      // dist: this rank hit its budget and only takes part in the exchanges
@@ -891,6 +1003,10 @@ bool Driver::run() {
         open.push_back(std::move(k.node));
       }
     }
+    if (sync_mode && !dealt && !stop && open.size() >= (size_t)2 * comm->world) {
+      deal_owners(open);
+      out->st.split_at = count;
+    }
     if (dist) {
       if (!split && !stop && pr.node_strategy != MVB_NODE_BEST && open.size() >= (size_t)4 * comm->world) {
         // deal the FIFO queue round-robin; from here on every rank owns its share
@@ -991,6 +1107,11 @@ static mvb_bnb *bnb_run(glp_prob *prob, const mvb_bnb_params *params, const mvb_
   d.comm = comm;
   if (comm && comm->world > 1 && !comm->allreduce_max) {
     std::fprintf(stderr, "mvb_bnb_run_dist: communicator has no allreduce_max\n");
+    delete h;
+    return nullptr;
+  }
+  if (comm && comm->world > 1 && p.dist_mode == MVB_DIST_SYNC && !comm->allgather_host) {
+    std::fprintf(stderr, "mvb_bnb_run_dist: MVB_DIST_SYNC needs a communicator with allgather_host\n");
     delete h;
     return nullptr;
   }

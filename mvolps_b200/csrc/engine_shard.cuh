@@ -429,6 +429,7 @@ struct NcclApi {
   int (*Recv)(void *, size_t, int, int, void *, cudaStream_t) = nullptr;
   int (*GroupStart)() = nullptr;
   int (*GroupEnd)() = nullptr;
+  int (*CommCount)(void *, int *) = nullptr;
 };
 NcclApi g_nccl;
 
@@ -449,6 +450,7 @@ bool nccl_load() {
   g_nccl.Recv = (decltype(g_nccl.Recv))dlsym(h, "ncclRecv");
   g_nccl.GroupStart = (decltype(g_nccl.GroupStart))dlsym(h, "ncclGroupStart");
   g_nccl.GroupEnd = (decltype(g_nccl.GroupEnd))dlsym(h, "ncclGroupEnd");
+  g_nccl.CommCount = (decltype(g_nccl.CommCount))dlsym(h, "ncclCommCount");
   if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllGather || !g_nccl.AllReduce ||
       !g_nccl.CommDestroy)
     return fail("NCCL library lacks a required symbol");
@@ -502,6 +504,25 @@ int nccl_sendrecv_host(void *ctx, const void *send, size_t sbytes, int dst, void
   }
   return cudaStreamSynchronize(st) == cudaSuccess ? 0 : -1;
 }
+// result exchange of the round-synchronous tree: host buffers through device staging and
+// ncclAllGather over NVLink (a round moves a few KB per solved LP)
+int nccl_allgather_host(void *ctx, const void *send, void *recv, size_t bytes) {
+  NcclCtx *c = (NcclCtx *)ctx;
+  int world = 0;
+  if (!g_nccl.CommCount || g_nccl.CommCount(c->comm, &world)) { g_err = "allgather_host: ncclCommCount failed"; return -1; }
+  const size_t need = bytes * (size_t)(world + 1);
+  if (need > c->xcap) {
+    if (c->xbuf) cudaFree(c->xbuf);
+    c->xcap = 0;
+    if (cudaMalloc((void **)&c->xbuf, need * 2) != cudaSuccess) { g_err = "allgather_host: cudaMalloc failed"; return -1; }
+    c->xcap = need * 2;
+  }
+  cudaStream_t st = g_ctx.stream;
+  if (cudaMemcpyAsync(c->xbuf, send, bytes, cudaMemcpyHostToDevice, st) != cudaSuccess) return -1;
+  if (g_nccl.AllGather(c->xbuf, c->xbuf + bytes, bytes, /*ncclChar*/ 0, c->comm, st)) { g_err = "ncclAllGather failed"; return -1; }
+  if (cudaMemcpyAsync(recv, c->xbuf + bytes, bytes * world, cudaMemcpyDeviceToHost, st) != cudaSuccess) return -1;
+  return cudaStreamSynchronize(st) == cudaSuccess ? 0 : -1;
+}
 void nccl_destroy(void *ctx) {
   NcclCtx *c = (NcclCtx *)ctx;
   if (c->comm) g_nccl.CommDestroy(c->comm);
@@ -538,6 +559,7 @@ mvb_comm *mvb_comm_nccl(const void *id, int rank, int world) {
   m->allreduce_max = nccl_allreduce_max;
   m->destroy = nccl_destroy;
   m->sendrecv_host = (g_nccl.Send && g_nccl.Recv) ? nccl_sendrecv_host : nullptr;
+  m->allgather_host = nccl_allgather_host;
   return m;
 }
 
@@ -551,6 +573,8 @@ mvb_comm *mvb_comm_local(int rank, int world) {
   m->allgather_dev = nullptr;
   m->allreduce_max = nullptr;
   m->destroy = nullptr;
+  m->sendrecv_host = nullptr;
+  m->allgather_host = nullptr;
   return m;
 }
 

@@ -55,6 +55,8 @@ double mv_snap(double x) {
 static void drop_engine(glp_prob *P) {
   if (P->eng) mvb_lp_free(P->eng);
   P->eng = nullptr;
+  P->ghost = false;
+  P->owner = 0;
   P->eng_rows = 0;
   P->eng_stale = true;
   P->eng_changed = true;
@@ -116,9 +118,13 @@ void glp_copy_prob(glp_prob *dest, glp_prob *src, int names) {
     for (auto &r : dest->rows) r.name.clear();
     for (auto &c : dest->cols) c.name.clear();
   }
-  if (src->eng && !src->eng_stale) {
-    dest->eng = mvb_lp_clone(src->eng);
-    if (!dest->eng) shim_abort(mvb_last_error());
+  if ((src->eng || src->ghost) && !src->eng_stale) {
+    if (!src->ghost) {
+      dest->eng = mvb_lp_clone(src->eng);
+      if (!dest->eng) shim_abort(mvb_last_error());
+    }
+    dest->ghost = src->ghost;
+    dest->owner = src->owner;
     dest->eng_rows = src->eng_rows;
     dest->eng_stale = false;
     dest->eng_changed = src->eng_changed;
@@ -251,7 +257,7 @@ static void store_bnds(int type, double lb, double ub, int &t, double &l,
 void glp_set_row_bnds(glp_prob *P, int i, int type, double lb, double ub) {
   MvRow &r = row_at(P, i, "glp_set_row_bnds: row out of range");
   store_bnds(type, lb, ub, r.type, r.lb, r.ub, r.stat);
-  if (P->eng && i <= P->eng_rows) P->dirty.push_back((int)P->cols.size() + i - 1);
+  if ((P->eng || P->ghost) && i <= P->eng_rows) P->dirty.push_back((int)P->cols.size() + i - 1);
 }
 
 int glp_get_mat_row(glp_prob *P, int i, int ind[], double val[]) {
@@ -299,7 +305,7 @@ double glp_get_col_ub(glp_prob *P, int j) {
 void glp_set_col_bnds(glp_prob *P, int j, int type, double lb, double ub) {
   MvCol &c = col_at(P, j, "glp_set_col_bnds: column out of range");
   store_bnds(type, lb, ub, c.type, c.lb, c.ub, c.stat);
-  if (P->eng) P->dirty.push_back(j - 1);
+  if (P->eng || P->ghost) P->dirty.push_back(j - 1);
 }
 int glp_get_col_kind(glp_prob *P, int j) {
   MvCol &c = col_at(P, j, "glp_get_col_kind");
@@ -311,7 +317,7 @@ void glp_set_col_kind(glp_prob *P, int j, int kind) {
   if (kind == GLP_BV) {
     c.kind = GLP_IV;
     store_bnds(GLP_DB, 0.0, 1.0, c.type, c.lb, c.ub, c.stat);
-    if (P->eng) P->dirty.push_back(j - 1);
+    if (P->eng || P->ghost) P->dirty.push_back(j - 1);
   } else if (kind == GLP_CV || kind == GLP_IV) {
     c.kind = kind;
   } else shim_abort("glp_set_col_kind: invalid kind");
@@ -337,8 +343,9 @@ static int sync_engine(glp_prob *P, bool *changed) {
 static int sync_engine_delta(glp_prob *P, bool *changed) {
   *changed = false;
   int m = (int)P->rows.size(), n = (int)P->cols.size();
-  if (P->eng && !P->eng_stale && P->eng_rows > m) P->eng_stale = true;
-  if (!P->eng || P->eng_stale) {
+  const bool ghost = P->ghost;  // mirror only: the owner's rank makes the engine calls
+  if ((P->eng || ghost) && !P->eng_stale && P->eng_rows > m) P->eng_stale = true;
+  if ((!P->eng && !ghost) || P->eng_stale) {
     *changed = true;
     std::vector<double> lb(n + m), ub(n + m);
     for (int j = 0; j < n; j++) {
@@ -349,16 +356,18 @@ static int sync_engine_delta(glp_prob *P, bool *changed) {
       lb[n + i] = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
       ub[n + i] = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
     }
-    if (P->eng) mvb_lp_free(P->eng);
-    P->eng = mvb_lp_create(m, n, m + 32 + m / 8);
-    if (!P->eng) return -1;
-    std::vector<double> A((size_t)m * n, 0.0), cost(n);
-    for (int i = 0; i < m; i++)
-      for (size_t t = 0; t < P->rows[i].ind.size(); t++)
-        A[(size_t)i * n + P->rows[i].ind[t] - 1] = P->rows[i].val[t];
-    for (int j = 0; j < n; j++)
-      cost[j] = P->dir == GLP_MAX ? -P->cols[j].coef : P->cols[j].coef;
-    if (mvb_lp_load(P->eng, A.data(), cost.data(), lb.data(), ub.data())) return -1;
+    if (!ghost) {
+      if (P->eng) mvb_lp_free(P->eng);
+      P->eng = mvb_lp_create(m, n, m + 32 + m / 8);
+      if (!P->eng) return -1;
+      std::vector<double> A((size_t)m * n, 0.0), cost(n);
+      for (int i = 0; i < m; i++)
+        for (size_t t = 0; t < P->rows[i].ind.size(); t++)
+          A[(size_t)i * n + P->rows[i].ind[t] - 1] = P->rows[i].val[t];
+      for (int j = 0; j < n; j++)
+        cost[j] = P->dir == GLP_MAX ? -P->cols[j].coef : P->cols[j].coef;
+      if (mvb_lp_load(P->eng, A.data(), cost.data(), lb.data(), ub.data())) return -1;
+    }
     P->eng_rows = m;
     P->eng_stale = false;
     P->eng_lb = std::move(lb);
@@ -375,7 +384,7 @@ static int sync_engine_delta(glp_prob *P, bool *changed) {
         a[P->rows[i].ind[t] - 1] = P->rows[i].val[t];
       const double l = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
       const double u = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
-      if (mvb_lp_append_row(P->eng, a.data(), l, u)) return -1;
+      if (!ghost && mvb_lp_append_row(P->eng, a.data(), l, u)) return -1;
       *changed = true;
       P->eng_lb.push_back(l);
       P->eng_ub.push_back(u);
@@ -398,7 +407,7 @@ static int sync_engine_delta(glp_prob *P, bool *changed) {
         u = mv_eff_ub(P->rows[k - n].type, P->rows[k - n].ub);
       }
       if (l != P->eng_lb[k] || u != P->eng_ub[k]) {
-        if (mvb_lp_set_bounds(P->eng, k, l, u)) return -1;
+        if (!ghost && mvb_lp_set_bounds(P->eng, k, l, u)) return -1;
         *changed = true;
         P->eng_lb[k] = l;
         P->eng_ub[k] = u;
@@ -422,20 +431,31 @@ static int stat_of(int at) {
 int mv_pull_solution(glp_prob *P, const mvb_result &res) {
   int m = (int)P->rows.size(), n = (int)P->cols.size();
   static thread_local std::vector<double> x;
+  static thread_local std::vector<int> head, nb, at;
   x.resize(n + m);
-  P->head.resize(m);
-  P->nb.resize(n);
-  P->at.resize(n);
+  head.resize(m);
+  nb.resize(n);
+  at.resize(n);
   if (mvb_lp_get_primal(P->eng, x.data())) return -1;
-  if (mvb_lp_get_basis(P->eng, P->head.data(), P->nb.data(), P->at.data())) return -1;
+  if (mvb_lp_get_basis(P->eng, head.data(), nb.data(), at.data())) return -1;
+  mv_install_solution(P, res, x.data(), head.data(), nb.data(), at.data());
+  return 0;
+}
+
+void mv_install_solution(glp_prob *P, const mvb_result &res, const double *x, const int *head,
+                         const int *nb, const int *at) {
+  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  P->head.assign(head, head + m);
+  P->nb.assign(nb, nb + n);
+  P->at.assign(at, at + n);
   MvCol *cols = P->cols.data();
   MvRow *rows = P->rows.data();
   for (int i = 0; i < m; i++) {
-    int k = P->head[i];
+    int k = head[i];
     if (k < n) cols[k].stat = GLP_BS; else rows[k - n].stat = GLP_BS;
   }
   for (int j = 0; j < n; j++) {
-    int k = P->nb[j], st = stat_of(P->at[j]);
+    int k = nb[j], st = stat_of(at[j]);
     if (k < n) cols[k].stat = st; else rows[k - n].stat = st;
   }
   double z = P->c0;
@@ -455,7 +475,13 @@ int mv_pull_solution(glp_prob *P, const mvb_result &res) {
     case MVB_UNBND: P->status = GLP_UNBND; break;
     default: P->status = res.primal_feasible ? GLP_FEAS : GLP_INFEAS; break;
   }
-  return 0;
+}
+
+void mv_make_ghost(glp_prob *P, int owner) {
+  if (P->eng) mvb_lp_free(P->eng);
+  P->eng = nullptr;
+  P->ghost = true;
+  P->owner = owner;
 }
 
 bool mv_answer_cached(glp_prob *P, bool changed) {
@@ -502,6 +528,7 @@ int glp_simplex(glp_prob *P, const glp_smcp *parm) {
     P->it_cnt = 0;
     return 0;
   }
+  if (P->ghost) shim_abort("glp_simplex: the object is a ghost of a multi-GPU tree (no device tableau on this rank)");
   bool changed = false;
   if (sync_engine(P, &changed)) {
     std::fprintf(stderr, "glp_simplex: engine error: %s\n", mvb_last_error());

@@ -85,6 +85,12 @@ struct glp_prob {
   bool eng_stale = true;       // matrix/objective changed: rebuild from scratch
   bool eng_changed = true;     // the engine's LP differs from the one the held solution belongs to
                                // (sticky across syncs and copies until the next solve is pulled)
+  // Round-synchronous multi-GPU tree (MVB_DIST_SYNC): every rank holds every node's problem object
+  // and takes the same decisions, but only the node's OWNER holds its device tableau.  On the
+  // other ranks the object is a ghost: the mirror below is kept exactly as on the owner (so
+  // `changed`, cached answers and copies behave identically) and solutions arrive by exchange.
+  bool ghost = false;
+  int owner = 0;
   std::vector<double> eng_lb, eng_ub;  // bounds last sent, by engine id
   std::vector<int> dirty;              // engine ids whose bounds were set since the last sync
   std::vector<int> head, nb, at;       // basis after the last solve
@@ -111,3 +117,9 @@ int mv_sync_engine(glp_prob *P, bool *changed = nullptr);
 // values); the iteration counters are then set to that zero-iteration solve's
 bool mv_answer_cached(glp_prob *P, bool changed);
 int mv_pull_solution(glp_prob *P, const mvb_result &res);   // read result back
+// the same from caller-held arrays (x: n+m by engine id; head: m; nb, at: n): how a ghost
+// receives the solution its owner computed
+void mv_install_solution(glp_prob *P, const mvb_result &res, const double *x, const int *head,
+                         const int *nb, const int *at);
+// give up the device tableau but keep the mirror: the object becomes a ghost owned by `owner`
+void mv_make_ghost(glp_prob *P, int owner);

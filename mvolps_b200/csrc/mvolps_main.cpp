@@ -8,8 +8,12 @@
 #include <string>
 #include <vector>
 
+#include <sys/wait.h>
+#include <unistd.h>
+
 #include "../../include/glpk.h"
 #include "../../include/mvolps_bnb.h"
+#include "../../include/mvolps_dist.h"
 #include "../../include/mvolps_engine.h"
 
 namespace {
@@ -39,6 +43,9 @@ int main(int argc, char **argv) {
               << "  -cf X          cut frequency in [0, 1]: share of the branched nodes that generate cuts (with -cm)\n"
               << "  -cs [{0|1}]    which cut becomes the node's new row: last pooled (reference) | most violated of the node's own\n"
               << "  -rh            root heuristic: the root LP solution rounded down as first incumbent\n"
+              << "  -np N          one tree over N GPUs of this box: one process per GPU (forked here), NCCL over NVLink\n"
+              << "  -dm [{0|1}]    with -np: node-sharded with work stealing (exact optimum, per-rank trees) |\n"
+              << "                 round-synchronous (tree, ids and events of the serial run)\n"
               << "  -bw N          FIFO nodes solved per device launch (default 256)\n"
               << "  -nl N          node budget\n"
               << "  -ev FILE       write the event stream, timeSpan type oid pid dir ... (message.h:141-226)\n";
@@ -77,9 +84,46 @@ int main(int argc, char **argv) {
   }
   p.root_heuristic = in.has("-rh");
   p.timed_events = in.has("-ev");
-  if (mvb_device_init(0)) { std::fprintf(stderr, "%s\n", mvb_last_error()); return 2; }
-  mvb_bnb *h = mvb_bnb_run(prob, &p);
+  int np = 1;
+  if (!ival("-np", 1, 16, np) || !ival("-dm", 0, 1, p.dist_mode)) return -1;
+  // -np N: fork one process per GPU BEFORE any CUDA call; rank 0's NCCL id travels through pipes
+  int rank = 0;
+  std::vector<int> id_pipe(2 * (size_t)np, -1);
+  std::vector<pid_t> kids;
+  if (np > 1) {
+    for (int r = 1; r < np; r++)
+      if (pipe(&id_pipe[2 * r])) { std::perror("pipe"); return 2; }
+    std::fflush(stdout);
+    for (int r = 1; r < np; r++) {
+      pid_t c = fork();
+      if (c < 0) { std::perror("fork"); return 2; }
+      if (c == 0) { rank = r; kids.clear(); break; }
+      kids.push_back(c);
+    }
+  }
+  if (mvb_device_init(rank)) { std::fprintf(stderr, "rank %d: %s\n", rank, mvb_last_error()); return 2; }
+  mvb_comm *comm = nullptr;
+  if (np > 1) {
+    unsigned char id[MVB_NCCL_ID_BYTES];
+    if (rank == 0) {
+      if (mvb_nccl_unique_id(id)) { std::fprintf(stderr, "%s\n", mvb_last_error()); return 2; }
+      for (int r = 1; r < np; r++)
+        if (write(id_pipe[2 * r + 1], id, sizeof id) != (ssize_t)sizeof id) { std::perror("write"); return 2; }
+    } else if (read(id_pipe[2 * rank], id, sizeof id) != (ssize_t)sizeof id) {
+      std::perror("read");
+      return 2;
+    }
+    comm = mvb_comm_nccl(id, rank, np);
+    if (!comm) { std::fprintf(stderr, "rank %d: %s\n", rank, mvb_last_error()); return 2; }
+    if (rank != 0) p.quiet = 1;
+  }
+  mvb_bnb *h = comm ? mvb_bnb_run_dist(prob, &p, comm) : mvb_bnb_run(prob, &p);
   if (!h) return 2;
+  if (rank != 0) {  // the other ranks have done their share; rank 0 reports
+    mvb_bnb_free(h);
+    mvb_comm_free(comm);
+    return 0;
+  }
   if (in.has("-ev")) {  // file sink of what the reference sends to its visualiser (message.cpp:32-191)
     std::FILE *f = std::fopen(in.get("-ev").c_str(), "w");
     if (!f) { std::fprintf(stderr, "cannot write %s\n", in.get("-ev").c_str()); return -1; }
@@ -90,8 +134,18 @@ int main(int argc, char **argv) {
     const mvb_bnb_stats *st = mvb_bnb_get_stats(h);
     std::printf("[%s] %d iterations, %d LP solves in %d launches, %lld simplex iterations\n",
                 mvb_backend(), st->iterations, st->lp_solves, st->launches, st->simplex_iters);
+    if (np > 1)
+      std::printf("[%d GPUs, %s] %lld nodes in all, incumbent %.12g (rank %d), rank 0 solved %d LPs, sent %d / received %d nodes\n",
+                  np, p.dist_mode == MVB_DIST_SYNC ? "round-synchronous" : "node-sharded", st->total_nodes, st->incumbent,
+                  st->incumbent_rank, st->solved_here, st->nodes_sent, st->nodes_received);
   }
   mvb_bnb_free(h);
+  if (comm) mvb_comm_free(comm);
   glp_delete_prob(prob);
-  return 0;
+  int exit_code = 0;
+  for (pid_t c : kids) {
+    int stc = 0;
+    if (waitpid(c, &stc, 0) < 0 || !WIFEXITED(stc) || WEXITSTATUS(stc) != 0) exit_code = 3;
+  }
+  return exit_code;
 }

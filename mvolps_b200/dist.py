@@ -128,8 +128,17 @@ def torch_comm(dist):
             C.memmove(recv, t.numpy().ctypes.data, rbytes)
         return 0
 
+    def allgather_host(ctx, send, recv, nbytes):
+        t = torch.frombuffer((C.c_char * nbytes).from_address(send), dtype=torch.uint8).clone()
+        outs = [torch.empty(nbytes, dtype=torch.uint8) for _ in range(dist.get_world_size())]
+        dist.all_gather(outs, t)
+        for r, o in enumerate(outs):
+            C.memmove(recv + r * nbytes, o.numpy().ctypes.data, nbytes)
+        return 0
+
     cb = capi.ALLREDUCE_FN(allreduce_max)
     sr = capi.SENDRECV_FN(sendrecv_host)
-    comm = capi.Comm(None, dist.get_rank(), dist.get_world_size(), capi.ALLGATHER_FN(), cb, capi.DESTROY_FN(), sr)
-    comm._keep = (cb, sr)
+    ag = capi.ALLGATHER_HOST_FN(allgather_host)
+    comm = capi.Comm(None, dist.get_rank(), dist.get_world_size(), capi.ALLGATHER_FN(), cb, capi.DESTROY_FN(), sr, ag)
+    comm._keep = (cb, sr, ag)
     return comm

@@ -263,3 +263,66 @@ def test_incumbent_exchange_world2_gloo(lib):
     assert rounds[2][:2] == (1202.0, 0)      # tie: lowest rank owns it
     assert rounds[3] == (1150.0, 0, 1202.0, 0)  # a worse round does not replace the incumbent
     assert res[0][4] is True and res[0][5] is True
+
+
+def _sync_worker(rank, world, port, q, oracle_lib, cases):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from mvolps_b200.lp import GlpProb
+        orc = capi.load_library(oracle_lib)
+        orc.glp_term_out(capi.GLP_OFF)
+        comm = torch_comm(dist)
+        res = []
+        for args, kw in cases:
+            out = GlpProb.from_instance(orc, instances.mdkp(*args)).bnb(comm=comm, dist_mode=1, **kw)
+            res.append({k: out[k] for k in ("tree", "events", "event_hash", "solution", "iterations", "oids", "incumbent",
+                                            "lp_solves", "cached_solves", "simplex_iters", "solved_here", "split_at",
+                                            "total_nodes", "launches")})
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+SYNC_CASES = [((12, 4, 1), dict(batch_width=16)), ((15, 5, 2), dict(batch_width=64, max_iters=1500)),
+              ((14, 4, 4), dict(batch_width=8, cut_mode=2, max_iters=600)),
+              ((12, 4, 4), dict(batch_width=8, cut_mode=1)),
+              ((20, 5, 3), dict(node_strategy=1, var_strategy=2, batch_width=8)),
+              ((16, 4, 6), dict(batch_width=32, cut_mode=2, cut_freq=0.5, cut_select=1, max_iters=800))]
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_round_synchronous_tree_is_the_serial_tree(world):
+    """MVB_DIST_SYNC (SURVEY 8e's default mode) over gloo with the CPU engine: the LPs of a round
+    are solved by their owner ranks, the solutions (and the tableau rows of the cut step) travel by
+    all-gather, and every rank consumes them in the serial order -> tree text, event stream,
+    solution string, oids and all counters equal the 1-process run, on every rank; the device work
+    is split (solved_here)."""
+    from mvolps_b200.lp import GlpProb
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    oracle_lib = os.path.join(root, "oracle", "_build", "libglpk_oracle.so")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sync_worker, args=(r, world, port, q, oracle_lib, SYNC_CASES)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=600) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    orc = capi.load_library(oracle_lib)
+    orc.glp_term_out(capi.GLP_OFF)
+    for k, (args, kw) in enumerate(SYNC_CASES):
+        serial = GlpProb.from_instance(orc, instances.mdkp(*args)).bnb(**kw)
+        for r in range(world):
+            out = res[r][k]
+            for key in ("tree", "events", "event_hash", "solution", "iterations", "oids", "incumbent", "lp_solves",
+                        "cached_solves", "simplex_iters", "launches"):
+                assert out[key] == serial[key], (args, kw, r, key)
+            assert out["total_nodes"] == serial["iterations"] and out["split_at"] >= 0
+        here = [res[r][k]["solved_here"] for r in range(world)]
+        assert all(h > 0 for h in here)
+        # after the ramp-up every LP is solved exactly once, by its owner
+        assert max(here) < serial["lp_solves"] - serial["cached_solves"]
