@@ -38,7 +38,7 @@ GLPK_SYMBOLS = [  # the 34 symbols the reference leaves undefined
 GLPK_EXTRA_SYMBOLS = ["glp_add_cols", "glp_set_col_kind", "glp_get_row_prim", "glp_get_it_cnt", "mvb_glp_snap_tol"]
 ENGINE_SYMBOLS = [
     "mvb_backend", "mvb_last_error", "mvb_device_init", "mvb_kernel_launches",
-    "mvb_timer_record", "mvb_timer_elapsed_ms", "mvb_flush_l2", "mvb_last_launch", "mvb_last_kernel_ms",
+    "mvb_timer_record", "mvb_timer_elapsed_ms", "mvb_flush_l2", "mvb_last_launch", "mvb_last_kernel_ms", "mvb_last_kernel_mode", "mvb_engine_option",
     "mvb_lp_create", "mvb_lp_free", "mvb_lp_load", "mvb_lp_clone", "mvb_lp_assign",
     "mvb_lp_dims", "mvb_lp_set_bounds", "mvb_lp_append_row", "mvb_solve_batch",
     "mvb_lp_get_primal", "mvb_lp_get_basis", "mvb_lp_get_tab_rows", "mvb_lp_get_tab_rows_batch",
@@ -145,6 +145,8 @@ def _bind(lib):
         "mvb_timer_elapsed_ms": (C.c_double, [C.c_int, C.c_int]),
         "mvb_flush_l2": (C.c_int, []),
         "mvb_last_kernel_ms": (C.c_double, []),
+        "mvb_last_kernel_mode": (C.c_int, []),
+        "mvb_engine_option": (C.c_int, [C.c_char_p, C.c_int]),
         "mvb_last_launch": (C.c_int, [_ip, _ip, _ip]),
         "mvb_lp_create": (_P, [C.c_int, C.c_int, C.c_int]),
         "mvb_lp_free": (None, [_P]),

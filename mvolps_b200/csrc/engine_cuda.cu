@@ -71,6 +71,13 @@ struct LPDev {
   int lzK;          // pending-update depth of the lazy loop for this launch
   int npatch;       // bound patches to apply before the solve
   const BoundPatch *patch;
+  // hand-over from the general kernel to the private-state kernel once phase 1 has reached a
+  // primal feasible basis: ps_ok = the LP fits the private-state kernel (general kernel: stop
+  // there); carry = 1: continue a solve (tallies below, beta[curS] valid, mode primal phase 2)
+  const double *srcT;  // resident kernel: load the tableau from here instead of T[curT] (fused clone), or null
+  int ps_ok, carry;
+  int c_iters, c_pivots, c_flips, c_it1, c_it2, c_itd, c_bland, c_pad;
+  unsigned long long c_hash;
 };
 
 namespace {
@@ -400,6 +407,7 @@ __device__ __forceinline__ bool primal_ratio_row(double alpha, int dir, int s, d
 }  // namespace
 
 #include "engine_lz.cuh"
+#include "engine_res.cuh"
 
 namespace {
 
@@ -414,19 +422,26 @@ __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &
   Tally ty;
   int status = MVB_ITLIM, degen = 0;
 
-  // values of the non-basic variables, then beta = T v
-  for (int j = g * NT + tid; j < n; j += G * NT) {
-    const int k = ldcg(L.nb[cS] + j);
-    L.vnb[j] = nb_value(ldcg(L.at[cS] + j), ldcg(L.lb + k), ldcg(L.ub + k));
-  }
-  group_sync(ctr, G, gen);
-  compute_beta(L, cT, cS, g, G);
-  group_sync(ctr, G, gen);
-
   int mode;
-  if (count_primal_infeas(L, cS, sm) == 0) mode = MVB_MODE_PRIMAL2;
-  else if (count_dual_infeas(L, cT, cS, sm) == 0) mode = MVB_MODE_DUAL;
-  else mode = MVB_MODE_PRIMAL1;
+  if (L.carry) {
+    // second leg of a solve whose phase 1 ran in the general kernel: the state is exactly what
+    // that loop left (beta is NOT rebuilt: the oracle does not rebuild it at the phase switch)
+    ty.iters = L.c_iters; ty.pivots = L.c_pivots; ty.flips = L.c_flips; ty.it1 = L.c_it1;
+    ty.it2 = L.c_it2; ty.itd = L.c_itd; ty.bland = L.c_bland; ty.hash = L.c_hash;
+    mode = MVB_MODE_PRIMAL2;
+  } else {
+    // values of the non-basic variables, then beta = T v
+    for (int j = g * NT + tid; j < n; j += G * NT) {
+      const int k = ldcg(L.nb[cS] + j);
+      L.vnb[j] = nb_value(ldcg(L.at[cS] + j), ldcg(L.lb + k), ldcg(L.ub + k));
+    }
+    group_sync(ctr, G, gen);
+    compute_beta(L, cT, cS, g, G);
+    group_sync(ctr, G, gen);
+    if (count_primal_infeas(L, cS, sm) == 0) mode = MVB_MODE_PRIMAL2;
+    else if (count_dual_infeas(L, cT, cS, sm) == 0) mode = MVB_MODE_DUAL;
+    else mode = MVB_MODE_PRIMAL1;
+  }
 
   if (PSK) {
     if (mode == MVB_MODE_PRIMAL1) {  // needs the general kernel: nothing has been changed yet
@@ -492,7 +507,12 @@ __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &
     } else {
       const bool phase1 = mode == MVB_MODE_PRIMAL1;
       if (phase1) {
-        if (count_primal_infeas(L, cS, sm) == 0) { mode = MVB_MODE_PRIMAL2; degen = 0; continue; }
+        if (count_primal_infeas(L, cS, sm) == 0) {
+          mode = MVB_MODE_PRIMAL2;
+          degen = 0;
+          if (L.ps_ok) { status = MVB_PS_HANDOVER; break; }  // phase 2 runs in the private-state kernel
+          continue;
+        }
         p1_partials(L, cT, cS, g, G);
         group_sync(ctr, G, gen);
       }
@@ -741,9 +761,15 @@ struct DeviceCtx {
   char *flush = nullptr; size_t flush_bytes = 0;
   int last_G = 0, last_groups = 0;
   bool last_ps = false;
+  double batch_kernel_ms = 0.0;   // device time of the solve kernels of the last mvb_solve_batch (all its launches)
+  int batch_solve_launches = 0;
   int max_ctas_ps = 0;     // co-resident CTAs of simplex_ps_kernel with max_dyn
   size_t max_dyn = 0;      // dynamic shared memory simplex_kernel may ask for
   bool no_ps = false;      // MVOLPS_NO_PS=1: general loop only (debugging / A-B timing)
+  bool no_res = false;       // MVOLPS_NO_RES=1: never use the resident (tableau in shared memory) kernel
+  size_t max_dyn_res = 0;    // dynamic shared memory simplex_res_kernel may ask for
+  int last_kind = 0;         // kernel of the last solve launch: 0 general, 1 private-state (lazy), 2 resident
+  bool no_handover = false;  // MVOLPS_NO_HANDOVER=1: phase 2 after a phase 1 stays in the general loop (A-B timing)
   int force_k = 0;         // MVOLPS_LZ_K=k: cap the pending-update depth (A-B timing)
   int force_nt = 0;        // MVOLPS_PS_NT=t: CTA width for launches with more LPs than SMs (A-B timing)
   int last_nt = 0;
@@ -785,6 +811,16 @@ bool ctx_init(int device) {
   CK(cudaFuncSetAttribute(simplex_ps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_ctx.max_dyn));
   const char *nops = getenv("MVOLPS_NO_PS");
   g_ctx.no_ps = nops && nops[0] == '1';
+  const char *nores = getenv("MVOLPS_NO_RES");
+  g_ctx.no_res = nores && nores[0] == '1';
+  {
+    cudaFuncAttributes fr;
+    CK(cudaFuncGetAttributes(&fr, simplex_res_kernel));
+    g_ctx.max_dyn_res = (size_t)optin > fr.sharedSizeBytes + 1024 ? (size_t)optin - fr.sharedSizeBytes - 1024 : 0;
+    CK(cudaFuncSetAttribute(simplex_res_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_ctx.max_dyn_res));
+  }
+  const char *noh = getenv("MVOLPS_NO_HANDOVER");
+  g_ctx.no_handover = noh && noh[0] == '1';
   const char *fk = getenv("MVOLPS_LZ_K");
   g_ctx.force_k = fk ? atoi(fk) : 0;
   const char *fnt = getenv("MVOLPS_PS_NT");
@@ -833,6 +869,7 @@ struct mvb_lp {
   unsigned clone_epoch = 0;         // == g_ctx.clone_epoch: source (1) / destination (2) of a queued clone
   int clone_role = 0;
   unsigned append_epoch = 0;        // == g_ctx.clone_epoch: a cut row of this LP is queued
+  bool res_ok = false;              // the last solve request fits the resident kernel
 };
 
 namespace {
@@ -1257,7 +1294,8 @@ extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double 
 namespace {
 
 // one cooperative launch over the LPs `idx` (indices into lps), results into the outboxes
-bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opts *opts, bool psk) {
+bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opts *opts, int kind) {
+  const bool psk = kind == 1, res = kind == 2;
   const int count = (int)idx.size();
   if (!count) return true;
   cudaStream_t st = g_ctx.stream;
@@ -1310,6 +1348,20 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
 
       dyn = std::max(dyn, lz_smem_bytes(lp->m, lp->ld, K));
     }
+  }
+  int res_grid = 0;
+  if (res) {
+    // one CTA per LP, as many CTAs as are co-resident with the largest tableau of the launch
+    // (grid-stride over the LPs: a CTA takes the next LP when it has stored the last one)
+    dyn = 0;
+    for (int k = 0; k < count; k++) dyn = std::max(dyn, res_smem_bytes(lps[idx[k]]->m, lps[idx[k]]->ld));
+    int per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_res_kernel, RES_NT, dyn));
+    if (per_sm < 1) return fail("simplex_res_kernel does not fit an SM");
+    res_grid = std::min(count, per_sm * g_ctx.sms);
+    G = 1;
+    ngroups = res_grid;
+    nt = RES_NT;
   }
   if (g_ctx.ctrs_cap < ngroups) {
     if (g_ctx.ctrs) CK(cudaFreeAsync(g_ctx.ctrs, st));
@@ -1367,16 +1419,27 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   void *args[] = {(void *)&dl, (void *)&cnt, (void *)&G, (void *)&ctrs, (void *)&tcl};
   if (!g_ctx.kev[0]) { CK(cudaEventCreate(&g_ctx.kev[0])); CK(cudaEventCreate(&g_ctx.kev[1])); }
   CK(cudaEventRecord(g_ctx.kev[0], st));
-  CK(cudaLaunchCooperativeKernel(psk ? (const void *)simplex_ps_kernel : (const void *)simplex_kernel,
-                                 dim3(ngroups * G), dim3(nt), args, dyn, st));
+  if (res) {
+    simplex_res_kernel<<<res_grid, RES_NT, dyn, st>>>(dl, cnt);
+    CK(cudaGetLastError());
+  } else {
+    CK(cudaLaunchCooperativeKernel(psk ? (const void *)simplex_ps_kernel : (const void *)simplex_kernel,
+                                   dim3(ngroups * G), dim3(nt), args, dyn, st));
+  }
   CK(cudaEventRecord(g_ctx.kev[1], st));
   g_launches++;
   g_ctx.last_G = G;
   g_ctx.last_nt = nt;
   g_ctx.last_groups = ngroups;
   g_ctx.last_ps = psk;
+  g_ctx.last_kind = kind;
   CK(cudaMemcpyAsync(g_ctx.h_out, g_ctx.d_out, otot, cudaMemcpyDeviceToHost, st));
   CK(cudaStreamSynchronize(st));
+  {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, g_ctx.kev[0], g_ctx.kev[1]) == cudaSuccess) g_ctx.batch_kernel_ms += ms;
+    g_ctx.batch_solve_launches++;
+  }
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[idx[k]];
     std::memcpy(lp->outbox.data(), g_ctx.h_out + ooff[k], lp->out_bytes);
@@ -1392,7 +1455,9 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
   if (!ctx_init(-1)) return -1;
   if (!flush_clones()) return -1;
   cudaStream_t st = g_ctx.stream;
-  std::vector<int> ps_idx, gen_idx;
+  g_ctx.batch_kernel_ms = 0.0;
+  g_ctx.batch_solve_launches = 0;
+  std::vector<int> ps_idx, gen_idx, res_idx;
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[k];
     if (!lp_push_small(lp)) return -1;
@@ -1413,17 +1478,46 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     lp->dev.pivlog_cap = lp->dev.pivlog ? lp->pivlog_cap : 0;
     const bool fits = !g_ctx.no_ps && lp->m >= 1 && lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn) >= 1 &&
                       lp->m + 1 <= PS_CREG * g_ctx.nt_ps;
-    (fits ? ps_idx : gen_idx).push_back(k);
+    lp->dev.ps_ok = fits && !g_ctx.no_handover;
+    lp->dev.carry = 0;
+    lp->dev.srcT = nullptr;
+    // resident kernel: the whole tableau fits one CTA's shared memory (a B&B node LP)
+    const size_t rb = g_ctx.no_res || lp->m < 1 ? 0 : res_smem_bytes(lp->m, lp->ld);
+    lp->res_ok = rb > 0 && rb <= g_ctx.max_dyn_res && !(opts && opts->ctas_per_lp > 0);  // an explicit group size asks for the lazy loop
+    if (lp->res_ok) lp->dev.ps_ok = !g_ctx.no_handover;
+    (lp->res_ok ? res_idx : fits ? ps_idx : gen_idx).push_back(k);
   }
-  // private-state kernel first; what needs phase 1 (or does not fit) goes to the general one
-  if (!launch_solve(lps, ps_idx, opts, true)) return -1;
-  for (int k : ps_idx) {
-    mvb_lp *lp = lps[k];
-    const DevResult *dr = (const DevResult *)(lp->outbox.data() + ((const char *)lp->dev.res - (lp->slab + lp->out_off)));
-    if (dr->r.status == MVB_PS_FALLBACK) gen_idx.push_back(k);
-  }
+  auto dev_result = [](mvb_lp *lp) {
+    return (const DevResult *)(lp->outbox.data() + ((const char *)lp->dev.res - (lp->slab + lp->out_off)));
+  };
+  // resident and private-state kernels first; what needs phase 1 (or fits neither) goes to the general one
+  if (!launch_solve(lps, res_idx, opts, 2)) return -1;
+  if (!launch_solve(lps, ps_idx, opts, 1)) return -1;
+  for (int k : res_idx)
+    if (dev_result(lps[k])->r.status == MVB_PS_FALLBACK) gen_idx.push_back(k);
+  for (int k : ps_idx)
+    if (dev_result(lps[k])->r.status == MVB_PS_FALLBACK) gen_idx.push_back(k);
   std::sort(gen_idx.begin(), gen_idx.end());
-  if (!launch_solve(lps, gen_idx, opts, false)) return -1;
+  if (!launch_solve(lps, gen_idx, opts, 0)) return -1;
+  // ... which hands an LP back as soon as its phase 1 has found a primal feasible basis: phase 2
+  // (the bulk of the iterations) then runs in the private-state kernel, carrying the tallies on
+  std::vector<int> hand_idx, hand_res;
+  for (int k : gen_idx) {
+    mvb_lp *lp = lps[k];
+    const DevResult *dr = dev_result(lp);
+    if (dr->r.status != MVB_PS_HANDOVER) continue;
+    lp->curT = lp->dev.curT = dr->curT;
+    lp->curS = lp->dev.curS = dr->curS;
+    lp->dev.carry = 1;
+    lp->dev.c_iters = dr->r.iters; lp->dev.c_pivots = dr->r.pivots; lp->dev.c_flips = dr->r.flips;
+    lp->dev.c_it1 = dr->r.iters_primal1; lp->dev.c_it2 = dr->r.iters_primal2; lp->dev.c_itd = dr->r.iters_dual;
+    lp->dev.c_bland = dr->r.bland_iters; lp->dev.c_hash = dr->r.pivot_hash;
+    (lp->res_ok ? hand_res : hand_idx).push_back(k);
+  }
+  if (!launch_solve(lps, hand_res, opts, 2)) return -1;
+  if (!launch_solve(lps, hand_idx, opts, 1)) return -1;
+  for (int k : hand_res) lps[k]->dev.carry = 0;
+  for (int k : hand_idx) lps[k]->dev.carry = 0;
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[k];
     const char *ob = lp->outbox.data();
@@ -1548,10 +1642,8 @@ double mvb_timer_elapsed_ms(int a, int b) {
 }
 
 double mvb_last_kernel_ms(void) {
-  float ms = -1.0f;
-  if (!g_ctx.kev[1] || cudaEventSynchronize(g_ctx.kev[1]) != cudaSuccess) return -1.0;
-  if (cudaEventElapsedTime(&ms, g_ctx.kev[0], g_ctx.kev[1]) != cudaSuccess) return -1.0;
-  return ms;
+  if (!g_ctx.kev[1]) return -1.0;
+  return g_ctx.batch_kernel_ms;  // every launch of the last mvb_solve_batch has been waited for
 }
 
 int mvb_flush_l2(void) {
@@ -1563,6 +1655,22 @@ int mvb_flush_l2(void) {
   static int v = 0;
   CKI(cudaMemsetAsync(g_ctx.flush, ++v & 0xff, g_ctx.flush_bytes, g_ctx.stream));
   return 0;
+}
+
+int mvb_last_kernel_mode(void) { return g_ctx.last_kind; }
+
+int mvb_engine_option(const char *name, int value) {
+  if (!ctx_init(-1) || !name) return -1;
+  int old = -1;
+  auto flag = [&](bool &f) { old = f; if (value >= 0) f = value != 0; };
+  auto num = [&](int &f) { old = f; if (value >= 0) f = value; };
+  if (!strcmp(name, "no_res")) flag(g_ctx.no_res);
+  else if (!strcmp(name, "no_ps")) flag(g_ctx.no_ps);
+  else if (!strcmp(name, "no_handover")) flag(g_ctx.no_handover);
+  else if (!strcmp(name, "lz_k")) num(g_ctx.force_k);
+  else if (!strcmp(name, "ps_nt")) num(g_ctx.force_nt);
+  else { g_err = std::string("mvb_engine_option: unknown option ") + name; return -1; }
+  return old;
 }
 
 int mvb_last_launch(int *c, int *g, int *t) {

@@ -33,6 +33,8 @@ namespace {
 constexpr int PS_CREG = 8;            // pivot-column values a thread can hold in flight
 constexpr int LZ_KMAX = 8;            // most pending pivots between two flush passes (12 measured: no gain)
 constexpr int MVB_PS_FALLBACK = 100;  // DevResult status: needs the general kernel
+constexpr int MVB_PS_HANDOVER = 101;  // DevResult status of the general kernel: phase 1 has reached a primal
+                                      // feasible basis, phase 2 goes to the private-state kernel
 
 
 __device__ __forceinline__ Key warp_argmin(Key v) {
@@ -76,10 +78,9 @@ __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned coun
 }
 __device__ __forceinline__ void bulk_row_load(double *dst, const double *src, unsigned bytes,
                                               unsigned long long *bar) {
-  // order earlier generic-proxy accesses before the async-proxy copy: of dst (shared), and of the
-  // source row, which other CTAs wrote with st.cg in the last flush pass and this CTA acquired at
-  // the group barrier (global)
-  asm volatile("fence.proxy.async;" ::: "memory");
+  // order earlier generic-proxy accesses of dst before the async-proxy write (the source rows in
+  // global memory, written with st.cg by the last flush pass, are fenced once per flush: lz_need_tableau)
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
   asm volatile(
@@ -373,6 +374,9 @@ __device__ __forceinline__ void lz_need_tableau(LZS *S) {
         asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(S->ctr) : "memory");
       } while (seen < target);
     }
+    // thread 0 issues the bulk (async-proxy) row copies: the rows the group has just written through
+    // the generic proxy and this thread has acquired must be ordered before them (once per flush)
+    if (threadIdx.x == 0) asm volatile("fence.proxy.async.global;" ::: "memory");
     __syncthreads();
     if (threadIdx.x == 0) S->must_wait = 0;
   }

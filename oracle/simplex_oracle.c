@@ -65,6 +65,8 @@ int mvb_timer_record(int slot) {
 double mvb_timer_elapsed_ms(int a, int b) { return g_slots[b & 15] - g_slots[a & 15]; }
 int mvb_flush_l2(void) { return 0; }
 double mvb_last_kernel_ms(void) { return 0.0; }
+int mvb_last_kernel_mode(void) { return -1; }
+int mvb_engine_option(const char *name, int value) { (void)name; (void)value; return -1; }
 int mvb_last_launch(int *c, int *g, int *t) { if (c) *c = 0; if (g) *g = 0; if (t) *t = 0; return 0; }
 
 static int round_up(int x, int a) { return (x + a - 1) / a * a; }

@@ -28,5 +28,18 @@ print("batch", [r["iters"] for r in solve_batch(L, lps)])
 g = ShardGroup(L, instances.dense_lp(33, 70, 3), 3)
 print("shard", g.solve()["iters"])
 g.free()
+os.environ["MVOLPS_SHARD_EXCHANGE"] = "push"   # the fused exchange: pushes into the peers' mailboxes + arrival counters
+g = ShardGroup(L, instances.dense_lp(33, 70, 3), 3)
+print("shard push", g.solve()["iters"], g.last_exchange())
+g.free()
+del os.environ["MVOLPS_SHARD_EXCHANGE"]
+# more LPs than SMs: the narrow-CTA launch shape (128 / 256 threads, several CTAs per SM)
+many = [EngineLP.from_instance(L, instances.dense_lp(12 + k % 5, 20 + k % 7, 300 + k % 11)) for k in range(160)]
+print("wide batch", sum(r["iters"] for r in solve_batch(L, many)))
+wide = [EngineLP.from_instance(L, instances.dense_lp(40, 300, 400 + k % 3)) for k in range(150)]
+print("wide batch 256", sum(r["iters"] for r in solve_batch(L, wide)))
+# B&B rounds with queued clones, queued cut rows and the batched row gather
+inst = instances.mdkp(20, 5, 3)
+print("bnb cuts", GlpProb.from_instance(L, inst).bnb(cut_mode=2, batch_width=16, max_iters=120)["launches_aux"])
 p = GlpProb.from_file(L, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "examples", "small3.lp"))
 print("bnb", p.bnb(cut_mode=2)["iterations"])

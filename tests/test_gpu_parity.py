@@ -208,9 +208,14 @@ def test_many_small_lps_use_narrow_ctas_and_match(oracle, product):
     A = [EngineLP.from_instance(oracle, i) for i in insts]
     B = [EngineLP.from_instance(product, i) for i in insts]
     ra = solve_batch(oracle, A, log_pivots=1)
-    rb = solve_batch(product, B, log_pivots=1)
+    old = product.mvb_engine_option(b"no_res", 1)  # the lazy private-state loop, not the resident kernel
+    try:
+        rb = solve_batch(product, B, log_pivots=1)
+    finally:
+        product.mvb_engine_option(b"no_res", old)
     G, groups, nt = C.c_int(), C.c_int(), C.c_int()
     product.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
+    assert product.mvb_last_kernel_mode() == 1
     assert G.value == 1 and nt.value == 128 and groups.value > 148
     for a, b, x, y in zip(A, B, ra, rb):
         _assert_same(a, b, x, y)
