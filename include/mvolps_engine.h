@@ -130,6 +130,9 @@ int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *opts,
 int mvb_lp_get_primal(mvb_lp *lp, double *x);
 /* head[m]: id basic in row i (0-based); nb[n]: id at position j; at[n]: MVB_AT_* */
 int mvb_lp_get_basis(mvb_lp *lp, int *head, int *nb, int *at);
+/* the same without a copy: pointers to the engine's own arrays of the last solve (x[n+m], head[m],
+ * nb[n], at[n]), valid until the LP is solved again, changed or freed */
+int mvb_lp_solution_view(mvb_lp *lp, const double **x, const int **head, const int **nb, const int **at);
 /* gather tableau rows (1-based row numbers, 0 = reduced-cost row) into
  * out[nrows*n]; columns follow the non-basic positions (see get_basis) */
 int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out);

@@ -84,9 +84,19 @@ struct Node {  // NodeData, util.h:35-54
 };
 
 struct TreeRec {
-  int oid, pid, depth;
+  int oid = 0, pid = 0, depth = 0;  // oid 0: no such node
   Prune prune = P_NONE;
   std::vector<int> kids;
+};
+
+// the tree, indexed by object id (ids are dense: util.cpp:25-37 hands them out 1, 2, 3, ...); a deque
+// so that references stay valid while children are added
+struct TreeTab {
+  std::deque<TreeRec> v;
+  TreeRec &operator[](int oid) {
+    if ((size_t)oid >= v.size()) v.resize((size_t)oid + 1);
+    return v[(size_t)oid];
+  }
 };
 
 struct Cut {  // CutContainer, cut.h:7-13
@@ -110,8 +120,19 @@ struct Driver {
   glp_prob *root_prob;
   mvb_bnb *out;
   int next_id = 1;
-  std::map<int, TreeRec> tree;
+  TreeTab tree;
+  // CutPool (cut.h:15-23).  The reference keeps every cut it ever generated and only ever reads
+  // the last one (cut.cpp:16-21); here the cuts of finished nodes are dropped except the last, and
+  // pool_base counts them so that the pool "size" (cut ids) stays the reference's
   std::vector<Cut> pool;
+  size_t pool_base = 0;
+  void pool_trim() {
+    if (pool.size() <= 1) return;
+    pool_base += pool.size() - 1;
+    Cut last = std::move(pool.back());
+    pool.clear();
+    pool.push_back(std::move(last));
+  }
   // gmi.cpp never sets CutContainer::oid on success and bs.cpp:252 tests it
   // (`result.oid != -1`): the test reads whatever the caller's stack slot last
   // held.  As compiled by g++ -O2 that slot is stable across loop iterations,
@@ -153,14 +174,15 @@ struct Driver {
   // (type, lb, ub, len, (ind, val) x len)], all as doubles.
   void pack_node(const Node &nd, std::vector<double> &buf) {
     const glp_prob *a = nd.prob;
-    const size_t m0 = root_prob->rows.size();
+    const size_t m0 = (size_t)root_prob->nrows();
     buf.push_back(nd.upperBound);
     buf.push_back((double)tree[nd.oid].depth);
-    buf.push_back((double)(a->rows.size() - m0));
-    for (const MvCol &c : a->cols) { buf.push_back(c.type); buf.push_back(c.lb); buf.push_back(c.ub); }
-    for (size_t i = m0; i < a->rows.size(); i++) {
-      const MvRow &r = a->rows[i];
-      buf.push_back(r.type); buf.push_back(r.lb); buf.push_back(r.ub);
+    buf.push_back((double)((size_t)a->nrows() - m0));
+    for (const MvBnd &c : a->cbnd) { buf.push_back(c.type); buf.push_back(c.lb); buf.push_back(c.ub); }
+    for (size_t i = m0; i < (size_t)a->nrows(); i++) {
+      const MvRowM &r = a->rowm[i];
+      const MvBnd &b = a->rbnd[i];
+      buf.push_back(b.type); buf.push_back(b.lb); buf.push_back(b.ub);
       buf.push_back((double)r.ind.size());
       for (size_t t = 0; t < r.ind.size(); t++) { buf.push_back(r.ind[t]); buf.push_back(r.val[t]); }
     }
@@ -175,7 +197,7 @@ struct Driver {
     const int extra = (int)*p++;
     const int n = glp_get_num_cols(c);
     for (int j = 1; j <= n; j++, p += 3) {
-      const MvCol &r = root_prob->cols[j - 1];
+      const MvBnd &r = root_prob->cbnd[j - 1];
       if ((int)p[0] != r.type || p[1] != r.lb || p[2] != r.ub) glp_set_col_bnds(c, j, (int)p[0], p[1], p[2]);
     }
     std::vector<int> ind;
@@ -230,7 +252,7 @@ struct Driver {
   // serial order: oids, prune tags, events and tree text are the serial run's on every rank.
   bool sync_mode = false, dealt = false;
   static size_t rec_bytes(const glp_prob *p) {
-    const size_t m = p->rows.size(), n = p->cols.size();
+    const size_t m = (size_t)p->nrows(), n = (size_t)p->ncols();
     return (sizeof(mvb_result) + 8 * (n + m) + 4 * (m + 2 * n) + 7) / 8 * 8;
   }
   bool allgather_segments(const std::vector<size_t> &seg, const std::vector<char> &mine, std::vector<char> &all,
@@ -278,7 +300,7 @@ struct Driver {
       size_t off = 0, e = 0;
       for (auto *p : ps) {
         if (p->ghost) continue;
-        const size_t m = p->rows.size(), n = p->cols.size();
+        const size_t m = (size_t)p->nrows(), n = (size_t)p->ncols();
         char *r = mine.data() + off;
         std::memcpy(r, &res[e++], sizeof(mvb_result));
         double *x = (double *)(r + sizeof(mvb_result));
@@ -290,7 +312,7 @@ struct Driver {
       if (!allgather_segments(seg, mine, allrec, stride)) return false;
       std::vector<size_t> cur(comm->world, 0);
       for (auto *p : ps) {
-        const size_t m = p->rows.size(), n = p->cols.size();
+        const size_t m = (size_t)p->nrows(), n = (size_t)p->ncols();
         const char *r = allrec.data() + (size_t)p->owner * stride + cur[p->owner];
         cur[p->owner] += rec_bytes(p);
         mvb_result rr;
@@ -330,10 +352,11 @@ struct Driver {
     if (status == GLP_NOFEAS || status == GLP_INFEAS || status == GLP_UNBND) return -1;
     // same test as through glp_get_col_prim / glp_get_obj_coef / glp_get_col_kind, on the
     // problem object directly (this runs for every node over every column)
-    const int cols = (int)a->cols.size();
-    const MvCol *c = a->cols.data();
+    const int cols = a->ncols();
+    const MvColM *c = a->colm.data();
+    const double *prim = a->cprim.data();
     for (int i = 1; i <= cols; i++) {
-      const double x = c[i - 1].prim;
+      const double x = prim[i - 1];
       if (x != 0 && c[i - 1].coef != 0)
         if (std::trunc(x) != x && c[i - 1].kind != GLP_CV) violated.push_back(i);
     }
@@ -463,7 +486,7 @@ struct Driver {
       if (glp_get_obj_val(a) <= bestLower) continue;  // fathomed whatever happens (bs.cpp:210)
       cut_rows_of(a, js, r1);
       off[k] = tot;
-      tot += r1.size() * a->cols.size();
+      tot += r1.size() * (size_t)a->ncols();
       if (r1.empty()) continue;
       lps.push_back(a->eng);
       nrows.push_back((int)r1.size());
@@ -489,7 +512,7 @@ struct Driver {
         if (off[k] == npos) continue;
         glp_prob *a = batch[k]->prob;
         const size_t next = [&] { for (size_t j = k + 1; j < batch.size(); j++) if (off[j] != npos) return off[j]; return tot; }();
-        const size_t cnt = (next - off[k]) / a->cols.size();
+        const size_t cnt = (next - off[k]) / (size_t)a->ncols();
         seg[a->owner] += (next - off[k]) * sizeof(double);
         if (cnt && !a->ghost) {
           my_lps.push_back(a->eng);
@@ -520,23 +543,24 @@ struct Driver {
 
   // root_heuristic: the root LP solution with its integer columns rounded down; feasible -> objective
   bool floor_point(glp_prob *a, std::vector<double> &x, double &obj) {
-    const int n = (int)a->cols.size(), m = (int)a->rows.size();
+    const int n = a->ncols(), m = a->nrows();
     x.assign(n + 1, 0.0);
     obj = a->c0;
     for (int j = 1; j <= n; j++) {
-      const MvCol &c = a->cols[j - 1];
-      double v = c.prim;
-      if (c.kind != GLP_CV) v = std::floor(v);
+      const MvBnd &c = a->cbnd[j - 1];
+      double v = a->cprim[j - 1];
+      if (a->colm[j - 1].kind != GLP_CV) v = std::floor(v);
       if (v < mv_eff_lb(c.type, c.lb) || v > mv_eff_ub(c.type, c.ub)) return false;
       x[j] = v;
-      obj = std::fma(c.coef, v, obj);
+      obj = std::fma(a->colm[j - 1].coef, v, obj);
     }
     for (int i = 0; i < m; i++) {
-      const MvRow &r = a->rows[i];
+      const MvRowM &r = a->rowm[i];
+      const MvBnd &b = a->rbnd[i];
       double act = 0.0;
       for (size_t t = 0; t < r.ind.size(); t++) act += r.val[t] * x[r.ind[t]];
       const double tol = 1e-9 * (1.0 + std::fabs(act));
-      if (act < mv_eff_lb(r.type, r.lb) - tol || act > mv_eff_ub(r.type, r.ub) + tol) return false;
+      if (act < mv_eff_lb(b.type, b.lb) - tol || act > mv_eff_ub(b.type, b.ub) + tol) return false;
     }
     return true;
   }
@@ -569,7 +593,7 @@ int Driver::add_cut_constraint(glp_prob *a, int cID) {
   int index = glp_add_rows(a, 1);
   glp_set_mat_row(a, index, (int)c.inds.size() - 1, c.inds.data(), c.vals.data());
   glp_set_row_bnds(a, index, GLP_LO, c.lb, 0);
-  return cID;
+  return (int)pool_base + cID;
 }
 
 // cut_select = 1 (the "heuristic to pick the best cut" cut.cpp:16-19 leaves as a TODO): among
@@ -582,7 +606,7 @@ int Driver::deepest_cut(glp_prob *a, size_t first) {
     const Cut &c = pool[k];
     double act = 0.0, nrm = 0.0;
     for (size_t t = 1; t < c.inds.size(); t++) {
-      act += c.vals[t] * a->cols[c.inds[t] - 1].prim;
+      act += c.vals[t] * a->cprim[c.inds[t] - 1];
       nrm += c.vals[t] * c.vals[t];
     }
     if (!(nrm > 0.0)) continue;
@@ -626,7 +650,7 @@ void Driver::gen_cut_ref(glp_prob *a, int j, const double *trow) {
     rhs -= temp * ub;
   }
   for (int i = 1; i <= m; i++) {
-    const MvRow &r = a->rows[i - 1];
+    const MvRowM &r = a->rowm[i - 1];
     for (size_t k = 1; k <= r.val.size(); k++)  // indexes by position, as gmi.cpp:86-88
       work[m + k] += work[i] * r.val[k - 1];
   }
@@ -660,11 +684,11 @@ void Driver::gen_cut_gmi(glp_prob *a, int j, const double *trow) {
     bool is_int = false;
     double bound;
     if (v < n) {
-      const MvCol &c = a->cols[v];
+      const MvBnd &c = a->cbnd[v];
       bound = at == MVB_AT_LB ? c.lb : c.ub;
-      is_int = c.kind == GLP_IV && std::trunc(bound) == bound;
+      is_int = a->colm[v].kind == GLP_IV && std::trunc(bound) == bound;
     } else {
-      const MvRow &r = a->rows[v - n];
+      const MvBnd &r = a->rbnd[v - n];
       bound = at == MVB_AT_LB ? r.lb : r.ub;
     }
     // x_j = beta + sum alpha*(x_k - v_k): y = x_k - l (at LB) or u - x_k (at UB)
@@ -682,7 +706,7 @@ void Driver::gen_cut_gmi(glp_prob *a, int j, const double *trow) {
     rhs += gk * s * bound;
     if (v < n) g[v + 1] += gk * s;
     else {
-      const MvRow &r = a->rows[v - n];
+      const MvRowM &r = a->rowm[v - n];
       for (size_t t = 0; t < r.ind.size(); t++) g[r.ind[t]] += gk * s * r.val[t];
     }
   }
@@ -730,6 +754,7 @@ void Driver::gen_cuts(glp_prob *a, const double *t) {
   int n = glp_get_num_cols(a);
   std::vector<int> js, rows;
   cut_rows_of(a, js, rows);
+  pool_trim();
   const size_t pool0 = pool.size();
   size_t k = 0;
   for (int j : js) {
@@ -933,15 +958,15 @@ bool Driver::run() {
           if (!trows) {  // not prefetched (cannot happen with the superset rule; kept as a safe path)
             std::vector<int> js, r1;
             cut_rows_of(a, js, r1);
-            one.resize(r1.size() * a->cols.size());
+            one.resize(r1.size() * (size_t)a->ncols());
             if (!r1.empty() && mvb_lp_get_tab_rows(a->eng, r1.data(), (int)r1.size(), one.data())) return false;
             trows = one.data();
           }
-          const size_t rows0 = a->rows.size();
+          const size_t rows0 = (size_t)a->nrows();
           gen_cuts(a, trows);
           // the new row goes to a's engine now (queued; all rows of the round are formed by one
           // kernel), so the children clone a tableau that already holds it
-          if (a->rows.size() != rows0 && mv_sync_engine(a)) return false;
+          if ((size_t)a->nrows() != rows0 && mv_sync_engine(a)) return false;
         }
         int pick = pick_var(a, vars);
         double bound = glp_get_col_prim(a, pick);
@@ -1081,7 +1106,8 @@ bool Driver::run() {
       hash_mix((unsigned char)ch);
     }
   }
-  for (auto &kv : tree) { hash_mix((unsigned)kv.first); hash_mix((unsigned)kv.second.prune); }
+  for (const TreeRec &t : tree.v)
+    if (t.oid) { hash_mix((unsigned)t.oid); hash_mix((unsigned)t.prune); }
   t_final = now() - tfin0;
   if (getenv("MVOLPS_BNB_TIMING"))
     std::fprintf(stderr, "bnb timing: sync %.1f ms, solve %.1f ms, pull %.1f ms, copy_prob %.1f ms, consume (incl. copy) "

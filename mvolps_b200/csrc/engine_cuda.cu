@@ -30,6 +30,7 @@
 
 #include "../../include/mvolps_engine.h"
 #include "../../include/mvolps_spec.h"
+#include "cow_vec.hpp"
 
 #ifndef MVB_PS_NT
 #define MVB_PS_NT 512  // threads per CTA of the private-state kernel
@@ -858,14 +859,16 @@ struct mvb_lp {
   size_t slab_bytes = 0, t_bytes = 0, small_off = 0, small_bytes = 0, out_off = 0, out_bytes = 0;
   LPDev dev{};
   int curT = 0, curS = 0;
-  std::vector<double> lb, ub;       // by variable id (n + m)
-  std::vector<int> head, nb, at;    // basis mirror (valid: mirror_ok)
-  std::vector<double> x;            // primal by id after the last solve
-  bool bounds_dirty = false, at_dirty = false;
+  // host mirror of the last solve's small state, copy-on-write: a clone (one per open B&B node,
+  // util.cpp:25-42) shares it until either side is solved again.  Bounds have no host mirror:
+  // they live on the device and change through patches / the append kernel only.
+  CowVec<int> head, nb, at;         // basis
+  CowVec<double> x;                 // primal by id
+  bool at_dirty = false;            // `at` was set on the host (load) and is not on the device yet
   std::vector<BoundPatch> patches;  // set_bounds calls not yet on the device
   mvb_result res{};
   int *pivlog = nullptr; int pivlog_cap = 0, pivlog_n = 0;
-  std::vector<char> outbox;         // host copy of the outbox
+  DevResult dres{};                 // result block of the last launch this LP took part in
   unsigned clone_epoch = 0;         // == g_ctx.clone_epoch: source (1) / destination (2) of a queued clone
   int clone_role = 0;
   unsigned append_epoch = 0;        // == g_ctx.clone_epoch: a cut row of this LP is queued
@@ -940,7 +943,6 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
   d.ohead = (int *)(s + ooh); d.onb = (int *)(s + oon); d.oat = (int *)(s + ooa);
   d.pivlog = nullptr; d.pivlog_cap = 0;
   lp->curT = lp->curS = 0;
-  lp->outbox.resize(lp->out_bytes);
   return true;
 }
 
@@ -1039,21 +1041,10 @@ int nb_flag_for(double l, double u, int keep) {
   return MVB_AT_FR;
 }
 
-// push host bounds / flags that changed since the last solve
+// push the non-basic flags a load set on the host
 bool lp_push_small(mvb_lp *lp) {
-  const int n = lp->n, m = lp->m;
-  if (lp->bounds_dirty && lp->at_dirty) lp->patches.clear();
-  else if (lp->bounds_dirty || lp->at_dirty) {  // mixed: keep it simple, push everything
-    lp->bounds_dirty = lp->at_dirty = true;
-    lp->patches.clear();
-  }
-  if (lp->bounds_dirty) {
-    CK(cudaMemcpyAsync(lp->dev.lb, lp->lb.data(), (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, g_ctx.stream));
-    CK(cudaMemcpyAsync(lp->dev.ub, lp->ub.data(), (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, g_ctx.stream));
-    lp->bounds_dirty = false;
-  }
   if (lp->at_dirty) {
-    CK(cudaMemcpyAsync(lp->dev.at[lp->curS], lp->at.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, g_ctx.stream));
+    CK(cudaMemcpyAsync(lp->dev.at[lp->curS], lp->at.data(), (size_t)lp->n * sizeof(int), cudaMemcpyHostToDevice, g_ctx.stream));
     lp->at_dirty = false;
   }
   return true;
@@ -1110,19 +1101,20 @@ int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost, const double *l
     CKI(cudaMemcpy2DAsync(d.T[0] + ld, (size_t)ld * sizeof(double), A, (size_t)n * sizeof(double),
                           (size_t)n * sizeof(double), m, cudaMemcpyHostToDevice, st));
   CKI(cudaMemcpyAsync(d.cost, cost, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, st));
-  lp->lb.assign(lb, lb + n + m);
-  lp->ub.assign(ub, ub + n + m);
-  lp->head.resize(m);
-  lp->nb.resize(n);
-  lp->at.resize(n);
-  for (int i = 0; i < m; i++) lp->head[i] = n + i;
-  for (int j = 0; j < n; j++) { lp->nb[j] = j; lp->at[j] = nb_flag_for(lb[j], ub[j], MVB_AT_LB); }
+  CKI(cudaMemcpyAsync(d.lb, lb, (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, st));
+  CKI(cudaMemcpyAsync(d.ub, ub, (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, st));
+  {
+    std::vector<int> &hd = lp->head.fresh(m), &nb = lp->nb.fresh(n), &at = lp->at.fresh(n);
+    for (int i = 0; i < m; i++) hd[i] = n + i;
+    for (int j = 0; j < n; j++) { nb[j] = j; at[j] = nb_flag_for(lb[j], ub[j], MVB_AT_LB); }
+  }
   if (m > 0)
     CKI(cudaMemcpyAsync(d.head[0] + 1, lp->head.data(), (size_t)m * sizeof(int), cudaMemcpyHostToDevice, st));
   CKI(cudaMemcpyAsync(d.nb[0], lp->nb.data(), (size_t)n * sizeof(int), cudaMemcpyHostToDevice, st));
-  lp->bounds_dirty = lp->at_dirty = true;
+  lp->patches.clear();
+  lp->at_dirty = true;
   if (!lp_push_small(lp)) return -1;
-  lp->x.assign(n + m, 0.0);
+  std::fill(lp->x.fresh(n + m).begin(), lp->x.mut().end(), 0.0);
   lp->res = mvb_result{};
   lp->res.status = MVB_UNSOLVED;
   CKI(cudaStreamSynchronize(st));
@@ -1154,9 +1146,7 @@ int mvb_lp_assign(mvb_lp *dst, const mvb_lp *src) {
   dst->clone_role = 2;
   g_ctx.clone_jobs.push_back(CloneJob{src->slab + from, dst->slab + from,
                                       (unsigned long long)(src->t_bytes + src->small_bytes)});
-  dst->lb = src->lb; dst->ub = src->ub;
-  dst->head = src->head; dst->nb = src->nb; dst->at = src->at; dst->x = src->x;
-  dst->bounds_dirty = src->bounds_dirty;
+  dst->head = src->head; dst->nb = src->nb; dst->at = src->at; dst->x = src->x;  // shared, copy-on-write
   dst->at_dirty = src->at_dirty;
   dst->patches = src->patches;
   dst->res = src->res;
@@ -1173,24 +1163,18 @@ mvb_lp *mvb_lp_clone(const mvb_lp *src) {
 
 int mvb_lp_set_bounds(mvb_lp *lp, int k, double lb, double ub) {
   if (k < 0 || k >= lp->n + lp->m) { g_err = "mvb_lp_set_bounds: variable id"; return -1; }
-  lp->lb[k] = lb;
-  lp->ub[k] = ub;
+  // the change travels as a patch the next solve kernel applies (bounds have no host mirror)
   int pos = -1, flag = 0;
+  const int *nb = lp->nb.data();
   for (int j = 0; j < lp->n; j++)
-    if (lp->nb[j] == k) {
+    if (nb[j] == k) {
       pos = j;
       flag = nb_flag_for(lb, ub, lp->at[j]);
-      lp->at[j] = flag;
+      if (flag != lp->at[j]) lp->at.w(j) = flag;
       break;
     }
-  if (lp->bounds_dirty && (lp->at_dirty || pos < 0)) return 0;  // a bulk push is pending anyway
   for (auto &p : lp->patches)
     if (p.var == k) { p.lb = lb; p.ub = ub; p.pos = pos; p.flag = flag; return 0; }
-  if (lp->patches.size() >= 256) {  // too many: fall back to the bulk push
-    lp->bounds_dirty = lp->at_dirty = true;
-    lp->patches.clear();
-    return 0;
-  }
   lp->patches.push_back(BoundPatch{k, pos, flag, 0, lb, ub});
   return 0;
 }
@@ -1246,6 +1230,8 @@ bool lp_grow(mvb_lp *lp, int mcap) {
   CK(cudaMemcpyAsync(d.nb[0], s.nb[lp->curS], (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(d.at[0], s.at[lp->curS], (size_t)n * sizeof(int), cudaMemcpyDeviceToDevice, st));
   CK(cudaMemcpyAsync(d.cost, s.cost, (size_t)n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(d.lb, s.lb, (size_t)(n + m) * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpyAsync(d.ub, s.ub, (size_t)(n + m) * sizeof(double), cudaMemcpyDeviceToDevice, st));
   lp_release(lp);
   lp->slab = nl.slab; nl.slab = nullptr;
   lp->slab_bytes = nl.slab_bytes; lp->t_bytes = nl.t_bytes;
@@ -1254,8 +1240,6 @@ bool lp_grow(mvb_lp *lp, int mcap) {
   lp->mcap = nl.mcap;
   lp->dev = nl.dev;
   lp->curT = lp->curS = 0;
-  lp->outbox.resize(lp->out_bytes);
-  lp->bounds_dirty = true;  // lb/ub are re-sent from the host mirror
   return true;
 }
 
@@ -1284,8 +1268,6 @@ extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double 
   lp->append_epoch = g_ctx.clone_epoch;
   lp->m = m + 1;
   lp->dev.m = m + 1;
-  lp->lb.push_back(lb);
-  lp->ub.push_back(ub);
   lp->head.push_back(n + m);
   lp->x.push_back(0.0);
   return 0;
@@ -1440,9 +1422,23 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
     if (cudaEventElapsedTime(&ms, g_ctx.kev[0], g_ctx.kev[1]) == cudaSuccess) g_ctx.batch_kernel_ms += ms;
     g_ctx.batch_solve_launches++;
   }
+  // results of this launch into the host mirrors (an LP that reports MVB_PS_FALLBACK /
+  // MVB_PS_HANDOVER is launched again and overwritten)
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[idx[k]];
-    std::memcpy(lp->outbox.data(), g_ctx.h_out + ooff[k], lp->out_bytes);
+    const char *ob = g_ctx.h_out + ooff[k];
+    const char *base = lp->slab + lp->out_off;
+    const DevResult *dr = (const DevResult *)(ob + ((const char *)lp->dev.res - base));
+    lp->dres = *dr;
+    if (dr->r.status == MVB_PS_FALLBACK) continue;
+    const double *x = (const double *)(ob + ((const char *)lp->dev.xval - base));
+    const int *oh = (const int *)(ob + ((const char *)lp->dev.ohead - base));
+    const int *on = (const int *)(ob + ((const char *)lp->dev.onb - base));
+    const int *oa = (const int *)(ob + ((const char *)lp->dev.oat - base));
+    lp->x.assign(x, x + lp->n + lp->m);
+    lp->head.assign(oh, oh + lp->m);
+    lp->nb.assign(on, on + lp->n);
+    lp->at.assign(oa, oa + lp->n);
   }
   return true;
 }
@@ -1487,9 +1483,7 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     if (lp->res_ok) lp->dev.ps_ok = !g_ctx.no_handover;
     (lp->res_ok ? res_idx : fits ? ps_idx : gen_idx).push_back(k);
   }
-  auto dev_result = [](mvb_lp *lp) {
-    return (const DevResult *)(lp->outbox.data() + ((const char *)lp->dev.res - (lp->slab + lp->out_off)));
-  };
+  auto dev_result = [](mvb_lp *lp) { return (const DevResult *)&lp->dres; };
   // resident and private-state kernels first; what needs phase 1 (or fits neither) goes to the general one
   if (!launch_solve(lps, res_idx, opts, 2)) return -1;
   if (!launch_solve(lps, ps_idx, opts, 1)) return -1;
@@ -1520,20 +1514,10 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
   for (int k : hand_idx) lps[k]->dev.carry = 0;
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[k];
-    const char *ob = lp->outbox.data();
-    const char *base = lp->slab + lp->out_off;
-    const DevResult *dr = (const DevResult *)(ob + ((const char *)lp->dev.res - base));
-    const double *x = (const double *)(ob + ((const char *)lp->dev.xval - base));
-    const int *oh = (const int *)(ob + ((const char *)lp->dev.ohead - base));
-    const int *on = (const int *)(ob + ((const char *)lp->dev.onb - base));
-    const int *oa = (const int *)(ob + ((const char *)lp->dev.oat - base));
+    const DevResult *dr = &lp->dres;
     lp->res = dr->r;
     lp->curT = dr->curT;
     lp->curS = dr->curS;
-    lp->x.assign(x, x + lp->n + lp->m);
-    lp->head.assign(oh, oh + lp->m);
-    lp->nb.assign(on, on + lp->n);
-    lp->at.assign(oa, oa + lp->n);
     lp->pivlog_n = lp->dev.pivlog ? std::min(dr->r.iters, lp->pivlog_cap) : 0;
     out[k] = dr->r;
   }
@@ -1545,6 +1529,15 @@ extern "C" {
 int mvb_lp_get_primal(mvb_lp *lp, double *x) {
   if ((int)lp->x.size() != lp->n + lp->m) { g_err = "mvb_lp_get_primal: no solution"; return -1; }
   std::memcpy(x, lp->x.data(), lp->x.size() * sizeof(double));
+  return 0;
+}
+
+int mvb_lp_solution_view(mvb_lp *lp, const double **x, const int **head, const int **nb, const int **at) {
+  if ((int)lp->x.size() != lp->n + lp->m) { g_err = "mvb_lp_solution_view: no solution"; return -1; }
+  *x = lp->x.data();
+  *head = lp->head.data();
+  *nb = lp->nb.data();
+  *at = lp->at.data();
   return 0;
 }
 

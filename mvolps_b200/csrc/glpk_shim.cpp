@@ -60,21 +60,42 @@ static void drop_engine(glp_prob *P) {
   P->eng_rows = 0;
   P->eng_stale = true;
   P->eng_changed = true;
-  P->eng_lb.clear();
-  P->eng_ub.clear();
   P->dirty.clear();
   P->head.clear();
   P->nb.clear();
   P->at.clear();
 }
 
-static MvRow &row_at(glp_prob *P, int i, const char *fn) {
-  if (i < 1 || i > (int)P->rows.size()) shim_abort(fn);
-  return P->rows[i - 1];
+// 0-based index of row i / column j after the range check GLPK makes
+static size_t row_at(glp_prob *P, int i, const char *fn) {
+  if (i < 1 || i > P->nrows()) shim_abort(fn);
+  return (size_t)i - 1;
 }
-static MvCol &col_at(glp_prob *P, int j, const char *fn) {
-  if (j < 1 || j > (int)P->cols.size()) shim_abort(fn);
-  return P->cols[j - 1];
+static size_t col_at(glp_prob *P, int j, const char *fn) {
+  if (j < 1 || j > P->ncols()) shim_abort(fn);
+  return (size_t)j - 1;
+}
+
+void mv_add_rows(glp_prob *P, int count) {
+  const size_t m = P->rbnd.size() + (size_t)count;
+  P->rowm.mut().resize(m);
+  P->rbnd.mut().resize(m, MV_ROW_BND0);
+  P->rstat.mut().resize(m, GLP_BS);
+  P->rprim.mut().resize(m, 0.0);
+}
+void mv_add_cols(glp_prob *P, int count) {
+  const size_t n = P->cbnd.size() + (size_t)count;
+  P->colm.mut().resize(n);
+  P->cbnd.mut().resize(n, MV_COL_BND0);
+  P->cstat.mut().resize(n, GLP_NS);
+  P->cprim.mut().resize(n, 0.0);
+}
+
+// the setters note a variable's bounds as the engine holds them the first time they touch it
+static void note_dirty(glp_prob *P, int id, const MvBnd &old) {
+  for (const MvDirty &d : P->dirty)
+    if (d.id == id) return;
+  P->dirty.push_back(MvDirty{id, mv_eff_lb(old.type, old.lb), mv_eff_ub(old.type, old.ub)});
 }
 
 extern "C" {
@@ -88,8 +109,10 @@ void glp_erase_prob(glp_prob *P) {
   glp_prob fresh;
   P->dir = fresh.dir;
   P->c0 = 0.0;
-  P->rows.clear();
-  P->cols.clear();
+  P->rowm.clear(); P->colm.clear();
+  P->rbnd.clear(); P->cbnd.clear();
+  P->rstat.clear(); P->cstat.clear();
+  P->rprim.clear(); P->cprim.clear();
   P->status = GLP_UNDEF;
   P->obj_val = 0.0;
   P->it_cnt = 0;
@@ -108,15 +131,17 @@ void glp_copy_prob(glp_prob *dest, glp_prob *src, int names) {
   glp_erase_prob(dest);
   dest->dir = src->dir;
   dest->c0 = src->c0;
-  dest->rows = src->rows;
-  dest->cols = src->cols;
+  dest->rowm = src->rowm; dest->colm = src->colm;
+  dest->rbnd = src->rbnd; dest->cbnd = src->cbnd;
+  dest->rstat = src->rstat; dest->cstat = src->cstat;
+  dest->rprim = src->rprim; dest->cprim = src->cprim;
   dest->status = src->status;
   dest->obj_val = src->obj_val;
   dest->it_cnt = src->it_cnt;
   if (names) dest->name = src->name;
   else {
-    for (auto &r : dest->rows) r.name.clear();
-    for (auto &c : dest->cols) c.name.clear();
+    for (auto &r : dest->rowm.mut()) r.name.clear();
+    for (auto &c : dest->colm.mut()) c.name.clear();
   }
   if ((src->eng || src->ghost) && !src->eng_stale) {
     if (!src->ghost) {
@@ -128,8 +153,6 @@ void glp_copy_prob(glp_prob *dest, glp_prob *src, int names) {
     dest->eng_rows = src->eng_rows;
     dest->eng_stale = false;
     dest->eng_changed = src->eng_changed;
-    dest->eng_lb = src->eng_lb;
-    dest->eng_ub = src->eng_ub;
     dest->dirty = src->dirty;
     dest->head = src->head;
     dest->nb = src->nb;
@@ -177,11 +200,11 @@ int glp_term_out(int flag) {
   return old;
 }
 
-int glp_get_num_rows(glp_prob *P) { return (int)P->rows.size(); }
-int glp_get_num_cols(glp_prob *P) { return (int)P->cols.size(); }
+int glp_get_num_rows(glp_prob *P) { return P->nrows(); }
+int glp_get_num_cols(glp_prob *P) { return P->ncols(); }
 int glp_get_num_int(glp_prob *P) {
   int c = 0;
-  for (auto &col : P->cols) c += col.kind == GLP_IV;
+  for (const MvColM &col : P->colm) c += col.kind == GLP_IV;
   return c;
 }
 
@@ -193,47 +216,49 @@ void glp_set_obj_dir(glp_prob *P, int dir) {
 }
 double glp_get_obj_coef(glp_prob *P, int j) {
   if (j == 0) return P->c0;
-  return col_at(P, j, "glp_get_obj_coef: column out of range").coef;
+  return P->colm[col_at(P, j, "glp_get_obj_coef: column out of range")].coef;
 }
 void glp_set_obj_coef(glp_prob *P, int j, double coef) {
   if (j == 0) {
     // the constant term does not touch the LP: a held solution keeps its point, its value moves
     if (coef != P->c0 && P->status != GLP_UNDEF) {
       double z = coef;
-      for (const MvCol &c : P->cols) z = std::fma(c.coef, c.prim, z);
+      for (int k = 0; k < P->ncols(); k++) z = std::fma(P->colm[k].coef, P->cprim[k], z);
       P->obj_val = z;
     }
     P->c0 = coef;
     return;
   }
-  MvCol &c = col_at(P, j, "glp_set_obj_coef: column out of range");
-  if (c.coef != coef) P->eng_stale = true;
-  c.coef = coef;
+  const size_t k = col_at(P, j, "glp_set_obj_coef: column out of range");
+  if (P->colm[k].coef != coef) {
+    P->eng_stale = true;
+    P->colm.w(k).coef = coef;
+  }
 }
 double glp_get_obj_val(glp_prob *P) { return P->obj_val; }
 
 int glp_add_rows(glp_prob *P, int nrs) {
   if (nrs < 1) shim_abort("glp_add_rows: invalid number of rows");
-  int first = (int)P->rows.size() + 1;
-  P->rows.resize(P->rows.size() + nrs);
+  int first = P->nrows() + 1;
+  mv_add_rows(P, nrs);
   return first;
 }
 
 int glp_add_cols(glp_prob *P, int ncs) {
   if (ncs < 1) shim_abort("glp_add_cols: invalid number of columns");
-  int first = (int)P->cols.size() + 1;
-  P->cols.resize(P->cols.size() + ncs);
+  int first = P->ncols() + 1;
+  mv_add_cols(P, ncs);
   P->eng_stale = true;
   return first;
 }
 
-int glp_get_row_type(glp_prob *P, int i) { return row_at(P, i, "glp_get_row_type").type; }
+int glp_get_row_type(glp_prob *P, int i) { return P->rbnd[row_at(P, i, "glp_get_row_type")].type; }
 double glp_get_row_lb(glp_prob *P, int i) {
-  MvRow &r = row_at(P, i, "glp_get_row_lb");
+  const MvBnd &r = P->rbnd[row_at(P, i, "glp_get_row_lb")];
   return (r.type == GLP_FR || r.type == GLP_UP) ? -DBL_MAX : r.lb;
 }
 double glp_get_row_ub(glp_prob *P, int i) {
-  MvRow &r = row_at(P, i, "glp_get_row_ub");
+  const MvBnd &r = P->rbnd[row_at(P, i, "glp_get_row_ub")];
   return (r.type == GLP_FR || r.type == GLP_LO) ? +DBL_MAX : r.ub;
 }
 
@@ -255,13 +280,17 @@ static void store_bnds(int type, double lb, double ub, int &t, double &l,
 }
 
 void glp_set_row_bnds(glp_prob *P, int i, int type, double lb, double ub) {
-  MvRow &r = row_at(P, i, "glp_set_row_bnds: row out of range");
-  store_bnds(type, lb, ub, r.type, r.lb, r.ub, r.stat);
-  if ((P->eng || P->ghost) && i <= P->eng_rows) P->dirty.push_back((int)P->cols.size() + i - 1);
+  const size_t k = row_at(P, i, "glp_set_row_bnds: row out of range");
+  if ((P->eng || P->ghost) && i <= P->eng_rows) note_dirty(P, P->ncols() + (int)k, P->rbnd[k]);
+  MvBnd b = P->rbnd[k];
+  int stat = P->rstat[k];
+  store_bnds(type, lb, ub, b.type, b.lb, b.ub, stat);
+  P->rbnd.w(k) = b;
+  if (stat != P->rstat[k]) P->rstat.w(k) = stat;
 }
 
 int glp_get_mat_row(glp_prob *P, int i, int ind[], double val[]) {
-  MvRow &r = row_at(P, i, "glp_get_mat_row: row out of range");
+  const MvRowM &r = P->rowm[row_at(P, i, "glp_get_mat_row: row out of range")];
   int len = (int)r.ind.size();
   for (int t = 0; t < len; t++) {
     if (ind) ind[t + 1] = r.ind[t];
@@ -272,8 +301,8 @@ int glp_get_mat_row(glp_prob *P, int i, int ind[], double val[]) {
 
 void glp_set_mat_row(glp_prob *P, int i, int len, const int ind[],
                      const double val[]) {
-  MvRow &r = row_at(P, i, "glp_set_mat_row: row out of range");
-  int n = (int)P->cols.size();
+  const size_t k = row_at(P, i, "glp_set_mat_row: row out of range");
+  int n = P->ncols();
   if (len < 0 || len > n) shim_abort("glp_set_mat_row: invalid row length");
   std::vector<std::pair<int, double>> e;
   e.reserve(len);
@@ -284,46 +313,54 @@ void glp_set_mat_row(glp_prob *P, int i, int len, const int ind[],
   std::sort(e.begin(), e.end(), [](auto &a, auto &b) { return a.first < b.first; });
   for (size_t t = 1; t < e.size(); t++)
     if (e[t].first == e[t - 1].first) shim_abort("glp_set_mat_row: duplicate column indices");
-  r.ind.clear();
-  r.val.clear();
-  for (auto &p : e) { r.ind.push_back(p.first); r.val.push_back(p.second); }
+  MvRowM &r = P->rowm.w(k);
+  std::vector<int> &ri = r.ind.fresh(e.size());
+  std::vector<double> &rv = r.val.fresh(e.size());
+  for (size_t t = 0; t < e.size(); t++) { ri[t] = e[t].first; rv[t] = e[t].second; }
   if (i <= P->eng_rows) P->eng_stale = true;  // a row the tableau already holds
 }
 
-int glp_get_row_stat(glp_prob *P, int i) { return row_at(P, i, "glp_get_row_stat").stat; }
-double glp_get_row_prim(glp_prob *P, int i) { return row_at(P, i, "glp_get_row_prim").prim; }
+int glp_get_row_stat(glp_prob *P, int i) { return P->rstat[row_at(P, i, "glp_get_row_stat")]; }
+double glp_get_row_prim(glp_prob *P, int i) { return P->rprim[row_at(P, i, "glp_get_row_prim")]; }
 
-int glp_get_col_type(glp_prob *P, int j) { return col_at(P, j, "glp_get_col_type").type; }
+int glp_get_col_type(glp_prob *P, int j) { return P->cbnd[col_at(P, j, "glp_get_col_type")].type; }
 double glp_get_col_lb(glp_prob *P, int j) {
-  MvCol &c = col_at(P, j, "glp_get_col_lb");
+  const MvBnd &c = P->cbnd[col_at(P, j, "glp_get_col_lb")];
   return (c.type == GLP_FR || c.type == GLP_UP) ? -DBL_MAX : c.lb;
 }
 double glp_get_col_ub(glp_prob *P, int j) {
-  MvCol &c = col_at(P, j, "glp_get_col_ub");
+  const MvBnd &c = P->cbnd[col_at(P, j, "glp_get_col_ub")];
   return (c.type == GLP_FR || c.type == GLP_LO) ? +DBL_MAX : c.ub;
 }
+static void set_col_bnds(glp_prob *P, size_t k, int type, double lb, double ub) {
+  if (P->eng || P->ghost) note_dirty(P, (int)k, P->cbnd[k]);
+  MvBnd b = P->cbnd[k];
+  int stat = P->cstat[k];
+  store_bnds(type, lb, ub, b.type, b.lb, b.ub, stat);
+  P->cbnd.w(k) = b;
+  if (stat != P->cstat[k]) P->cstat.w(k) = stat;
+}
 void glp_set_col_bnds(glp_prob *P, int j, int type, double lb, double ub) {
-  MvCol &c = col_at(P, j, "glp_set_col_bnds: column out of range");
-  store_bnds(type, lb, ub, c.type, c.lb, c.ub, c.stat);
-  if (P->eng || P->ghost) P->dirty.push_back(j - 1);
+  set_col_bnds(P, col_at(P, j, "glp_set_col_bnds: column out of range"), type, lb, ub);
 }
 int glp_get_col_kind(glp_prob *P, int j) {
-  MvCol &c = col_at(P, j, "glp_get_col_kind");
-  if (c.kind == GLP_IV && c.type == GLP_DB && c.lb == 0.0 && c.ub == 1.0) return GLP_BV;
-  return c.kind;
+  const size_t k = col_at(P, j, "glp_get_col_kind");
+  const MvBnd &c = P->cbnd[k];
+  const int kind = P->colm[k].kind;
+  if (kind == GLP_IV && c.type == GLP_DB && c.lb == 0.0 && c.ub == 1.0) return GLP_BV;
+  return kind;
 }
 void glp_set_col_kind(glp_prob *P, int j, int kind) {
-  MvCol &c = col_at(P, j, "glp_set_col_kind");
+  const size_t k = col_at(P, j, "glp_set_col_kind");
   if (kind == GLP_BV) {
-    c.kind = GLP_IV;
-    store_bnds(GLP_DB, 0.0, 1.0, c.type, c.lb, c.ub, c.stat);
-    if (P->eng || P->ghost) P->dirty.push_back(j - 1);
+    P->colm.w(k).kind = GLP_IV;
+    set_col_bnds(P, k, GLP_DB, 0.0, 1.0);
   } else if (kind == GLP_CV || kind == GLP_IV) {
-    c.kind = kind;
+    if (P->colm[k].kind != kind) P->colm.w(k).kind = kind;
   } else shim_abort("glp_set_col_kind: invalid kind");
 }
-double glp_get_col_prim(glp_prob *P, int j) { return col_at(P, j, "glp_get_col_prim").prim; }
-int glp_get_col_stat(glp_prob *P, int j) { return col_at(P, j, "glp_get_col_stat").stat; }
+double glp_get_col_prim(glp_prob *P, int j) { return P->cprim[col_at(P, j, "glp_get_col_prim")]; }
+int glp_get_col_stat(glp_prob *P, int j) { return P->cstat[col_at(P, j, "glp_get_col_stat")]; }
 int glp_get_status(glp_prob *P) { return P->status; }
 int glp_get_it_cnt(glp_prob *P) { return P->it_cnt; }
 
@@ -342,75 +379,73 @@ static int sync_engine(glp_prob *P, bool *changed) {
 }
 static int sync_engine_delta(glp_prob *P, bool *changed) {
   *changed = false;
-  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  int m = P->nrows(), n = P->ncols();
   const bool ghost = P->ghost;  // mirror only: the owner's rank makes the engine calls
   if ((P->eng || ghost) && !P->eng_stale && P->eng_rows > m) P->eng_stale = true;
   if ((!P->eng && !ghost) || P->eng_stale) {
     *changed = true;
-    std::vector<double> lb(n + m), ub(n + m);
-    for (int j = 0; j < n; j++) {
-      lb[j] = mv_eff_lb(P->cols[j].type, P->cols[j].lb);
-      ub[j] = mv_eff_ub(P->cols[j].type, P->cols[j].ub);
-    }
-    for (int i = 0; i < m; i++) {
-      lb[n + i] = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
-      ub[n + i] = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
-    }
     if (!ghost) {
+      std::vector<double> lb(n + m), ub(n + m);
+      for (int j = 0; j < n; j++) {
+        lb[j] = mv_eff_lb(P->cbnd[j].type, P->cbnd[j].lb);
+        ub[j] = mv_eff_ub(P->cbnd[j].type, P->cbnd[j].ub);
+      }
+      for (int i = 0; i < m; i++) {
+        lb[n + i] = mv_eff_lb(P->rbnd[i].type, P->rbnd[i].lb);
+        ub[n + i] = mv_eff_ub(P->rbnd[i].type, P->rbnd[i].ub);
+      }
       if (P->eng) mvb_lp_free(P->eng);
       P->eng = mvb_lp_create(m, n, m + 32 + m / 8);
       if (!P->eng) return -1;
       std::vector<double> A((size_t)m * n, 0.0), cost(n);
-      for (int i = 0; i < m; i++)
-        for (size_t t = 0; t < P->rows[i].ind.size(); t++)
-          A[(size_t)i * n + P->rows[i].ind[t] - 1] = P->rows[i].val[t];
+      for (int i = 0; i < m; i++) {
+        const MvRowM &r = P->rowm[i];
+        for (size_t t = 0; t < r.ind.size(); t++) A[(size_t)i * n + r.ind[t] - 1] = r.val[t];
+      }
       for (int j = 0; j < n; j++)
-        cost[j] = P->dir == GLP_MAX ? -P->cols[j].coef : P->cols[j].coef;
+        cost[j] = P->dir == GLP_MAX ? -P->colm[j].coef : P->colm[j].coef;
       if (mvb_lp_load(P->eng, A.data(), cost.data(), lb.data(), ub.data())) return -1;
     }
     P->eng_rows = m;
     P->eng_stale = false;
-    P->eng_lb = std::move(lb);
-    P->eng_ub = std::move(ub);
     P->dirty.clear();
     return 0;
   }
   const int old_rows = P->eng_rows;
   if (P->eng_rows < m) {
-    std::vector<double> a(n);
+    std::vector<double> a(ghost ? 0 : n);
     for (int i = P->eng_rows; i < m; i++) {
-      std::fill(a.begin(), a.end(), 0.0);
-      for (size_t t = 0; t < P->rows[i].ind.size(); t++)
-        a[P->rows[i].ind[t] - 1] = P->rows[i].val[t];
-      const double l = mv_eff_lb(P->rows[i].type, P->rows[i].lb);
-      const double u = mv_eff_ub(P->rows[i].type, P->rows[i].ub);
-      if (!ghost && mvb_lp_append_row(P->eng, a.data(), l, u)) return -1;
+      if (!ghost) {
+        std::fill(a.begin(), a.end(), 0.0);
+        const MvRowM &r = P->rowm[i];
+        for (size_t t = 0; t < r.ind.size(); t++) a[r.ind[t] - 1] = r.val[t];
+        const double l = mv_eff_lb(P->rbnd[i].type, P->rbnd[i].lb);
+        const double u = mv_eff_ub(P->rbnd[i].type, P->rbnd[i].ub);
+        if (mvb_lp_append_row(P->eng, a.data(), l, u)) return -1;
+      }
       *changed = true;
-      P->eng_lb.push_back(l);
-      P->eng_ub.push_back(u);
     }
     P->eng_rows = m;
   }
-  /* bounds set since the last sync (the setters log the engine id): forward the ones
-   * that really changed, in ascending id order as a full scan would */
+  /* bounds set since the last sync (the setters log the engine id and what the engine holds):
+   * forward the ones that really changed, in ascending id order as a full scan would */
   if (!P->dirty.empty()) {
-    std::sort(P->dirty.begin(), P->dirty.end());
-    P->dirty.erase(std::unique(P->dirty.begin(), P->dirty.end()), P->dirty.end());
-    for (int k : P->dirty) {
+    if (P->dirty.size() > 1)
+      std::sort(P->dirty.begin(), P->dirty.end(), [](const MvDirty &a, const MvDirty &b) { return a.id < b.id; });
+    for (const MvDirty &d : P->dirty) {
+      const int k = d.id;
       if (k >= n + old_rows) continue;  // a row appended above
       double l, u;
       if (k < n) {
-        l = mv_eff_lb(P->cols[k].type, P->cols[k].lb);
-        u = mv_eff_ub(P->cols[k].type, P->cols[k].ub);
+        l = mv_eff_lb(P->cbnd[k].type, P->cbnd[k].lb);
+        u = mv_eff_ub(P->cbnd[k].type, P->cbnd[k].ub);
       } else {
-        l = mv_eff_lb(P->rows[k - n].type, P->rows[k - n].lb);
-        u = mv_eff_ub(P->rows[k - n].type, P->rows[k - n].ub);
+        l = mv_eff_lb(P->rbnd[k - n].type, P->rbnd[k - n].lb);
+        u = mv_eff_ub(P->rbnd[k - n].type, P->rbnd[k - n].ub);
       }
-      if (l != P->eng_lb[k] || u != P->eng_ub[k]) {
+      if (l != d.lb || u != d.ub) {
         if (!ghost && mvb_lp_set_bounds(P->eng, k, l, u)) return -1;
         *changed = true;
-        P->eng_lb[k] = l;
-        P->eng_ub[k] = u;
       }
     }
     P->dirty.clear();
@@ -429,42 +464,38 @@ static int stat_of(int at) {
 
 /* copy status, primal values and basis back from the engine */
 int mv_pull_solution(glp_prob *P, const mvb_result &res) {
-  int m = (int)P->rows.size(), n = (int)P->cols.size();
-  static thread_local std::vector<double> x;
-  static thread_local std::vector<int> head, nb, at;
-  x.resize(n + m);
-  head.resize(m);
-  nb.resize(n);
-  at.resize(n);
-  if (mvb_lp_get_primal(P->eng, x.data())) return -1;
-  if (mvb_lp_get_basis(P->eng, head.data(), nb.data(), at.data())) return -1;
-  mv_install_solution(P, res, x.data(), head.data(), nb.data(), at.data());
+  const double *x;
+  const int *head, *nb, *at;
+  if (mvb_lp_solution_view(P->eng, &x, &head, &nb, &at)) return -1;
+  mv_install_solution(P, res, x, head, nb, at);
   return 0;
 }
 
 void mv_install_solution(glp_prob *P, const mvb_result &res, const double *x, const int *head,
                          const int *nb, const int *at) {
-  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  int m = P->nrows(), n = P->ncols();
   P->head.assign(head, head + m);
   P->nb.assign(nb, nb + n);
   P->at.assign(at, at + n);
-  MvCol *cols = P->cols.data();
-  MvRow *rows = P->rows.data();
+  // fresh arrays: a copy that still shares its parent's solution does not pay for a copy of it
+  int *cstat = P->cstat.fresh(n).data(), *rstat = P->rstat.fresh(m).data();
+  double *cprim = P->cprim.fresh(n).data(), *rprim = P->rprim.fresh(m).data();
   for (int i = 0; i < m; i++) {
     int k = head[i];
-    if (k < n) cols[k].stat = GLP_BS; else rows[k - n].stat = GLP_BS;
+    if (k < n) cstat[k] = GLP_BS; else rstat[k - n] = GLP_BS;
   }
   for (int j = 0; j < n; j++) {
     int k = nb[j], st = stat_of(at[j]);
-    if (k < n) cols[k].stat = st; else rows[k - n].stat = st;
+    if (k < n) cstat[k] = st; else rstat[k - n] = st;
   }
+  const MvColM *cm = P->colm.data();
   double z = P->c0;
   for (int j = 0; j < n; j++) {
     const double v = mv_snap(x[j]);
-    cols[j].prim = v;
-    z = std::fma(cols[j].coef, v, z);
+    cprim[j] = v;
+    z = std::fma(cm[j].coef, v, z);
   }
-  for (int i = 0; i < m; i++) rows[i].prim = mv_snap(x[n + i]);
+  for (int i = 0; i < m; i++) rprim[i] = mv_snap(x[n + i]);
   P->obj_val = z;
   P->it_cnt = res.iters;
   P->last = res;
@@ -502,7 +533,7 @@ extern "C" {
 
 int glp_simplex(glp_prob *P, const glp_smcp *parm) {
   (void)parm;
-  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  int m = P->nrows(), n = P->ncols();
   if (n == 0) {
     P->status = GLP_UNDEF;
     return GLP_EFAIL;
@@ -512,17 +543,21 @@ int glp_simplex(glp_prob *P, const glp_smcp *parm) {
      * too); nothing to send to the engine.  MVOLPS never gets here. */
     double z = P->c0;
     P->status = GLP_OPT;
-    for (MvCol &c : P->cols) {
-      const double cost = P->dir == GLP_MAX ? -c.coef : c.coef;
+    int *cstat = P->cstat.fresh(n).data();
+    double *cprim = P->cprim.fresh(n).data();
+    for (int j = 0; j < n; j++) {
+      const MvBnd &c = P->cbnd[j];
+      const double coef = P->colm[j].coef;
+      const double cost = P->dir == GLP_MAX ? -coef : coef;
       const double l = mv_eff_lb(c.type, c.lb), u = mv_eff_ub(c.type, c.ub);
       double v;
-      if (c.type == GLP_FX) { v = c.lb; c.stat = GLP_NS; }
-      else if (cost > 0.0 || (cost == 0.0 && l > -HUGE_VAL)) { v = l; c.stat = GLP_NL; }
-      else if (cost < 0.0 || u < HUGE_VAL) { v = u; c.stat = GLP_NU; }
-      else { v = 0.0; c.stat = GLP_NF; }
+      if (c.type == GLP_FX) { v = c.lb; cstat[j] = GLP_NS; }
+      else if (cost > 0.0 || (cost == 0.0 && l > -HUGE_VAL)) { v = l; cstat[j] = GLP_NL; }
+      else if (cost < 0.0 || u < HUGE_VAL) { v = u; cstat[j] = GLP_NU; }
+      else { v = 0.0; cstat[j] = GLP_NF; }
       if (!(v > -HUGE_VAL && v < HUGE_VAL)) { P->status = GLP_UNBND; v = 0.0; }
-      c.prim = v;
-      z = std::fma(c.coef, v, z);
+      cprim[j] = v;
+      z = std::fma(coef, v, z);
     }
     P->obj_val = z;
     P->it_cnt = 0;
@@ -553,7 +588,7 @@ int glp_simplex(glp_prob *P, const glp_smcp *parm) {
 }
 
 int glp_eval_tab_row(glp_prob *P, int k, int ind[], double val[]) {
-  int m = (int)P->rows.size(), n = (int)P->cols.size();
+  int m = P->nrows(), n = P->ncols();
   if (!P->eng || P->eng_stale || P->eng_rows != m || (int)P->head.size() != m)
     shim_abort("glp_eval_tab_row: basis factorization does not exist");
   if (k < 1 || k > m + n) shim_abort("glp_eval_tab_row: variable number out of range");

@@ -6,33 +6,24 @@
 // the product build); this object owns the sparse rows, typed bounds, kinds,
 // basis statuses and the last solution, and remembers what the engine has
 // already seen so that a re-solve ships only bound deltas and new cut rows.
+//
+// Layout: structure of arrays, every array copy-on-write.  A B&B run makes
+// two copies of the problem per branched node (util.cpp:34) that differ from
+// their parent in ONE column bound (bs.cpp:274,282), perhaps one cut row
+// (cut.cpp:23-43), and -- once solved -- the solution.  So glp_copy_prob is a
+// handful of reference counts; the model (coefficients, kinds, objective,
+// names) is shared by every node of the tree; a child detaches the bound array
+// it writes; a solve installs fresh solution arrays without copying the old.
 #pragma once
 
+#include <algorithm>
 #include <memory>
 #include <string>
 #include <vector>
 
 #include "../../include/glpk.h"
 #include "../../include/mvolps_engine.h"
-
-// Copy-on-write vector: every open B&B node holds a copy of the problem
-// (util.cpp:25-42) but only cut rows ever differ, so copies share the
-// coefficient storage and glp_copy_prob costs a reference count per row.
-template <class T>
-class CowVec {
-  std::shared_ptr<std::vector<T>> p_;
-  std::vector<T> &mut() {
-    if (!p_) p_ = std::make_shared<std::vector<T>>();
-    else if (p_.use_count() > 1) p_ = std::make_shared<std::vector<T>>(*p_);
-    return *p_;
-  }
-
- public:
-  size_t size() const { return p_ ? p_->size() : 0; }
-  const T &operator[](size_t i) const { return (*p_)[i]; }
-  void clear() { p_.reset(); }
-  void push_back(const T &v) { mut().push_back(v); }
-};
+#include "cow_vec.hpp"
 
 // Row/column names are never read through the 34-function boundary, only by the
 // readers' messages: shared, so a problem copy does not duplicate the strings.
@@ -49,35 +40,47 @@ struct MvName {
   }
 };
 
-struct MvRow {
-  int type = GLP_FR;
-  double lb = 0.0, ub = 0.0;
+// ---- model part: the same for every node of a B&B tree ----
+struct MvRowM {
   CowVec<int> ind;     // 1-based column numbers, ascending
   CowVec<double> val;
-  int stat = GLP_BS;
-  double prim = 0.0;
   MvName name;
 };
-
-struct MvCol {
-  int type = GLP_FX;
-  double lb = 0.0, ub = 0.0;
+struct MvColM {
   int kind = GLP_CV;
   double coef = 0.0;
-  int stat = GLP_NS;
-  double prim = 0.0;
   MvName name;
+};
+// ---- typed bounds: what branching (columns) and cut rows (rows) change ----
+struct MvBnd {
+  int type;
+  double lb, ub;
+};
+constexpr MvBnd MV_ROW_BND0{GLP_FR, 0.0, 0.0};  // a new row is free, basic
+constexpr MvBnd MV_COL_BND0{GLP_FX, 0.0, 0.0};  // a new column is fixed at zero, non-basic
+
+// a bound the setters changed since the last sync: engine id and the effective bounds the
+// engine holds for it (captured the first time the variable is touched)
+struct MvDirty {
+  int id;
+  double lb, ub;
 };
 
 struct glp_prob {
   int dir = GLP_MIN;
   double c0 = 0.0;
-  std::vector<MvRow> rows;  // rows[i-1]
-  std::vector<MvCol> cols;  // cols[j-1]
+  CowVec<MvRowM> rowm;  // rowm[i-1]
+  CowVec<MvColM> colm;  // colm[j-1]
+  CowVec<MvBnd> rbnd, cbnd;
+  CowVec<int> rstat, cstat;      // GLP_BS / GLP_N*
+  CowVec<double> rprim, cprim;   // last primal values (snapped, see mv_snap)
   int status = GLP_UNDEF;
   double obj_val = 0.0;
   int it_cnt = 0;
   std::string name;
+
+  int nrows() const { return (int)rbnd.size(); }
+  int ncols() const { return (int)cbnd.size(); }
 
   // ---- engine mirror ----
   mvb_lp *eng = nullptr;
@@ -91,9 +94,8 @@ struct glp_prob {
   // `changed`, cached answers and copies behave identically) and solutions arrive by exchange.
   bool ghost = false;
   int owner = 0;
-  std::vector<double> eng_lb, eng_ub;  // bounds last sent, by engine id
-  std::vector<int> dirty;              // engine ids whose bounds were set since the last sync
-  std::vector<int> head, nb, at;       // basis after the last solve
+  std::vector<MvDirty> dirty;          // bounds set since the last sync
+  CowVec<int> head, nb, at;            // basis after the last solve
   mvb_result last{};
 };
 
@@ -123,3 +125,6 @@ void mv_install_solution(glp_prob *P, const mvb_result &res, const double *x, co
                          const int *nb, const int *at);
 // give up the device tableau but keep the mirror: the object becomes a ghost owned by `owner`
 void mv_make_ghost(glp_prob *P, int owner);
+// new rows / columns with the defaults GLPK gives them
+void mv_add_rows(glp_prob *P, int count);
+void mv_add_cols(glp_prob *P, int count);

@@ -21,10 +21,63 @@ std::string lower(std::string s) {
   return s;
 }
 
+// The readers fill an array-of-structs image of the problem (rows and columns are touched again
+// and again while sections are parsed) and commit it to the glp_prob's copy-on-write arrays at the end.
+struct MvRow {
+  int type = GLP_FR;
+  double lb = 0.0, ub = 0.0;
+  std::vector<int> ind;
+  std::vector<double> val;
+  int stat = GLP_BS;
+  MvName name;
+};
+struct MvCol {
+  int type = GLP_FX;
+  double lb = 0.0, ub = 0.0;
+  int kind = GLP_CV;
+  double coef = 0.0;
+  int stat = GLP_NS;
+  MvName name;
+};
+struct BuildProb {
+  int dir = GLP_MIN;
+  double c0 = 0.0;
+  std::string name;
+  std::vector<MvRow> rows;
+  std::vector<MvCol> cols;
+};
+void commit(const BuildProb &b, glp_prob *P) {
+  P->dir = b.dir;
+  P->c0 = b.c0;
+  P->name = b.name;
+  mv_add_cols(P, (int)b.cols.size());
+  mv_add_rows(P, (int)b.rows.size());
+  std::vector<MvColM> &cm = P->colm.mut();
+  std::vector<MvBnd> &cb = P->cbnd.mut();
+  std::vector<int> &cs = P->cstat.mut();
+  for (size_t j = 0; j < b.cols.size(); j++) {
+    const MvCol &c = b.cols[j];
+    cm[j].kind = c.kind; cm[j].coef = c.coef; cm[j].name = c.name;
+    cb[j] = MvBnd{c.type, c.lb, c.ub};
+    cs[j] = c.stat;
+  }
+  std::vector<MvRowM> &rm = P->rowm.mut();
+  std::vector<MvBnd> &rb = P->rbnd.mut();
+  std::vector<int> &rs = P->rstat.mut();
+  for (size_t i = 0; i < b.rows.size(); i++) {
+    const MvRow &r = b.rows[i];
+    rm[i].ind.assign(r.ind.data(), r.ind.data() + r.ind.size());
+    rm[i].val.assign(r.val.data(), r.val.data() + r.val.size());
+    rm[i].name = r.name;
+    rb[i] = MvBnd{r.type, r.lb, r.ub};
+    rs[i] = r.stat;
+  }
+}
+
 struct Builder {
-  glp_prob *P;
+  BuildProb *P;
   std::map<std::string, int> colidx, rowidx;
-  explicit Builder(glp_prob *p) : P(p) {}
+  explicit Builder(BuildProb *p) : P(p) {}
   int col(const std::string &name) {
     auto it = colidx.find(name);
     if (it != colidx.end()) return it->second;
@@ -118,7 +171,7 @@ struct LpParser {
   size_t pos = 0;
   Builder b;
   std::string err;
-  explicit LpParser(glp_prob *P) : b(P) {}
+  explicit LpParser(BuildProb *P) : b(P) {}
 
   const Tok &peek(size_t k = 0) const { return tk[std::min(pos + k, tk.size() - 1)]; }
   bool is_inf_word(const Tok &t) const {
@@ -357,8 +410,10 @@ int mv_read_lp(glp_prob *P, const char *fname, std::string &err) {
   if (!f) { err = "unable to open file"; return 1; }
   std::stringstream ss;
   ss << f.rdbuf();
-  LpParser p(P);
+  BuildProb image;
+  LpParser p(&image);
   if (!p.run(ss.str())) { err = p.err; return 1; }
+  commit(image, P);
   return 0;
 }
 
@@ -368,7 +423,14 @@ int mv_read_lp(glp_prob *P, const char *fname, std::string &err) {
 // INTORG/INTEND), RHS (objective entry = minus the constant term), RANGES,
 // BOUNDS (UP LO FX FR MI PL BV LI UI), ENDATA.  The first N row is the
 // objective; further N rows are dropped.
+static int read_mps_image(BuildProb *P, const char *fname, std::string &err);
 int mv_read_mps(glp_prob *P, const char *fname, std::string &err) {
+  BuildProb image;
+  if (read_mps_image(&image, fname, err)) return 1;
+  commit(image, P);
+  return 0;
+}
+static int read_mps_image(BuildProb *P, const char *fname, std::string &err) {
   std::ifstream f(fname);
   if (!f) { err = "unable to open file"; return 1; }
   Builder b(P);

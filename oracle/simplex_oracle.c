@@ -576,6 +576,22 @@ int mvb_lp_get_basis(mvb_lp *lp, int *head, int *nb, int *at) {
   return 0;
 }
 
+/* pointers valid until the next call on this thread (the shim consumes them at once) */
+int mvb_lp_solution_view(mvb_lp *lp, const double **x, const int **head, const int **nb, const int **at) {
+  static __thread double *vx;
+  static __thread int *vh;
+  static __thread int cap;
+  if (cap < lp->n + lp->m + 1) {
+    cap = 2 * (lp->n + lp->m) + 64;
+    vx = (double *)realloc(vx, (size_t)cap * sizeof(double));
+    vh = (int *)realloc(vh, (size_t)cap * sizeof(int));
+  }
+  mvb_lp_get_primal(lp, vx);
+  for (int i = 0; i < lp->m; i++) vh[i] = lp->head[i + 1];
+  *x = vx; *head = vh; *nb = lp->nb; *at = lp->at;
+  return 0;
+}
+
 int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
   for (int t = 0; t < nrows; t++) {
     if (rows[t] < 0 || rows[t] > lp->m) { set_err("get_tab_rows: row"); return -1; }

@@ -7,7 +7,8 @@ from mvolps_b200 import capi, instances
 from mvolps_b200.lp import EngineLP, solve_batch
 L = capi.load_product()
 L.mvb_device_init(0)
-m, n, nlp = 256, 512, int(sys.argv[1]) if len(sys.argv) > 1 else 592
+nlp = int(sys.argv[1]) if len(sys.argv) > 1 else 592
+m, n = (int(sys.argv[2]), int(sys.argv[3])) if len(sys.argv) > 3 else (256, 512)
 tmpl = [EngineLP.from_instance(L, instances.dense_lp(m, n, sd)) for sd in range(16)]
 work = [tmpl[k % 16].clone() for k in range(nlp)]
 solve_batch(L, work)
