@@ -1,10 +1,15 @@
 // Stand-in for zmqpp (absent from this image).  The reference only touches
 // ZeroMQ when started with --server PORT (message.h:230-255,
-// message.cpp:183-190); the visualiser side channel is out of scope
-// (SURVEY.md section 2.1 row 9), so this stub accepts the calls and drops the
-// events, warning once.  Own code; test/oracle harness only.
+// message.cpp:183-190): every event is one receive() of the client's request
+// followed by one send() of the message text.  This stub answers the receive at
+// once and, when MVOLPS_ZMQ_DUMP names a file, appends every string the
+// reference sends to it -- which turns the reference's own event stream
+// (IPCDispatch::write, message.cpp:32-181) into a golden fixture
+// (tests/golden/make_golden.py -> event_golden.json).  Without the variable the
+// events are dropped.  Own code; test/oracle harness only.
 #pragma once
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 
 namespace zmqpp {
@@ -12,15 +17,25 @@ class context {};
 enum class socket_type { reply, request };
 class message {
  public:
-  message &operator>>(std::string &s) { s.clear(); return *this; }
+  message &operator>>(std::string &s) { s = "stub"; return *this; }
 };
 class socket {
+  std::FILE *dump_ = nullptr;
+
  public:
-  socket(context &, socket_type) {}
+  socket(context &, socket_type) {
+    if (const char *f = std::getenv("MVOLPS_ZMQ_DUMP")) dump_ = std::fopen(f, "w");
+  }
+  ~socket() {
+    if (dump_) std::fclose(dump_);
+  }
   void bind(const std::string &ep) {
-    std::fprintf(stderr, "zmqpp stub: '%s' not served (no ZeroMQ in this build)\n", ep.c_str());
+    if (!dump_) std::fprintf(stderr, "zmqpp stub: '%s' not served (no ZeroMQ in this build)\n", ep.c_str());
   }
   bool receive(message &) { return true; }
-  bool send(const std::string &) { return true; }
+  bool send(const std::string &s) {
+    if (dump_) std::fputs(s.c_str(), dump_);
+    return true;
+  }
 };
 }  // namespace zmqpp

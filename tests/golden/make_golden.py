@@ -83,8 +83,49 @@ def small3_inst():
                 col_ub=np.full(3, 1000.0), integer=np.ones(3, bool))
 
 
+def reference_events(path, flags):
+    """What the reference's IPCDispatch::write (message.cpp:32-181) sends to its visualiser when
+    started with --server: the zmqpp stub (oracle/stubs/zmqpp/zmqpp.hpp) appends every message to
+    $MVOLPS_ZMQ_DUMP.  Returned without the leading timeSpan field and the trailing blank."""
+    with tempfile.NamedTemporaryFile(suffix=".ev", delete=False) as t:
+        dump = t.name
+    env = dict(os.environ, MVOLPS_ZMQ_DUMP=dump)
+    subprocess.run([REF_BIN, "--server", "5555", "-f", path] + flags, capture_output=True, text=True, timeout=600,
+                   env=env, check=True)
+    raw = [ln for ln in open(dump).read().splitlines() if ln.strip()]
+    os.unlink(dump)
+    assert raw and raw[-1] == "END"  # ~IPCDispatch (message.h:232-246) closes the stream with this token
+    return [" ".join(ln.split()[1:]) for ln in raw[:-1]]
+
+
+def event_golden():
+    """event_golden.json: the reference's own event stream per B&B case (message.h:141-226 records)."""
+    out = []
+    for name, gen, args, flags in BNB_CASES:
+        if gen is None:
+            path, tmp = os.path.join(ROOT, "examples", "small3.lp"), None
+        else:
+            tmp = tempfile.NamedTemporaryFile(suffix=".lp", delete=False)
+            tmp.close()
+            path = tmp.name
+            instances.write_lp(getattr(instances, gen)(*args), path)
+        ev = reference_events(path, flags)
+        out.append(dict(name=name, gen=gen, args=args, flags=flags, events=len(ev),
+                        events_sha256=hashlib.sha256("\n".join(ev).encode()).hexdigest(), head=ev[:30]))
+        if tmp:
+            os.unlink(path)
+    with open(os.path.join(HERE, "event_golden.json"), "w") as f:
+        json.dump({"generator": "tests/golden/make_golden.py --events-only",
+                   "source": "reference IPCDispatch::write (message.cpp:32-181) run with --server, messages captured by "
+                             "the zmqpp stub; the timeSpan field is dropped",
+                   "cases": out}, f, indent=1)
+    print(f"wrote {len(out)} event streams")
+
+
 def main():
     subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "all", "ref"], check=True)
+    if "--events-only" in sys.argv:
+        return event_golden()
     orc = capi.load_library(ORACLE)
     orc.glp_term_out(0)
     cases = []
@@ -128,6 +169,7 @@ def main():
                    "source": "reference bs.cpp/util.cpp/gmi.cpp/cut.cpp (unmodified) on the oracle shim",
                    "cases": out}, f, indent=1)
     print(f"wrote {len(cases)} LP cases, {len(out)} B&B cases")
+    event_golden()
 
 
 if __name__ == "__main__":

@@ -137,3 +137,17 @@ def test_reference_objects_on_the_product_library(product, case, tmp_path):
     assert hashlib.sha256("\n".join(tree).encode()).hexdigest() == case["tree_sha256"]
     assert (sol[-1].strip() if sol else "") == case["solution"]
     assert (int(iters[-1].split("after")[1].split()[0]) if iters else None) == case["iterations"]
+
+
+def _event_gold():
+    with open(os.path.join(ROOT, "tests", "golden", "event_golden.json")) as f:
+        return json.load(f)["cases"]
+
+
+@pytest.mark.parametrize("case", _event_gold(), ids=lambda c: c["name"])
+def test_event_stream_on_the_gpu_equals_the_references_own(product, case, tmp_path):
+    """The product's event text == the messages the reference's IPCDispatch::write sends with
+    --server (message.cpp:32-181; fixture captured from the unmodified reference)."""
+    ev = _prob(product, case, tmp_path).bnb(**_kwargs(case["flags"]))["events"].splitlines()
+    assert ev[:30] == case["head"] and len(ev) == case["events"]
+    assert hashlib.sha256("\n".join(ev).encode()).hexdigest() == case["events_sha256"]

@@ -432,3 +432,21 @@ def test_rowless_problem_and_objective_constant(oracle):
     L.glp_set_obj_coef(q.h, 0, 5.0)
     assert abs(q.obj_val() - (z + 5.0)) < 1e-9
     assert q.simplex() == 0 and L.glp_get_it_cnt(q.h) == 0 and abs(q.obj_val() - (z + 5.0)) < 1e-9
+
+
+def _event_gold():
+    with open(os.path.join(GOLDEN, "event_golden.json")) as f:
+        return json.load(f)["cases"]
+
+
+@pytest.mark.parametrize("case", _event_gold(), ids=lambda c: c["name"])
+def test_event_stream_equals_the_references_own(oracle, case, tmp_path):
+    """mvb_bnb_event_text against what the reference's IPCDispatch::write (message.cpp:32-181) sends
+    when it runs with --server: same records (message.h:141-226), same field order and formatting,
+    event by event (the reference's timeSpan field aside).  Fixture: tests/golden/event_golden.json,
+    captured from the unmodified reference by the zmqpp stub."""
+    out = _prob(oracle, case, tmp_path).bnb(**_kwargs(case["flags"]))
+    ev = out["events"].splitlines()
+    assert ev[:30] == case["head"]
+    assert len(ev) == case["events"]
+    assert hashlib.sha256("\n".join(ev).encode()).hexdigest() == case["events_sha256"]
