@@ -1114,7 +1114,10 @@ int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost, const double *l
   lp->patches.clear();
   lp->at_dirty = true;
   if (!lp_push_small(lp)) return -1;
-  std::fill(lp->x.fresh(n + m).begin(), lp->x.mut().end(), 0.0);
+  {
+    std::vector<double> &xv = lp->x.fresh(n + m);
+    std::fill(xv.begin(), xv.end(), 0.0);
+  }
   lp->res = mvb_result{};
   lp->res.status = MVB_UNSOLVED;
   CKI(cudaStreamSynchronize(st));
