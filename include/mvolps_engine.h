@@ -90,11 +90,13 @@ int mvb_flush_l2(void);
  * launch, summed: an LP that needs phase 1 takes a second launch for its phase 2) */
 double mvb_last_kernel_ms(void);
 /* kernel of the last solve launch: 0 general (simplex_kernel), 1 private-state lazy loop
- * (simplex_ps_kernel), 2 resident, tableau in shared memory (simplex_res_kernel) */
+ * (simplex_ps_kernel), 2 resident, tableau in one CTA's shared memory (simplex_res_kernel),
+ * 3 cluster-resident, tableau in the distributed shared memory of a CTA cluster (simplex_cres_kernel) */
 int mvb_last_kernel_mode(void);
 /* A/B switches of the CUDA engine (tests, profiling; each also has an environment variable read at
  * start-up): "no_res" (MVOLPS_NO_RES) never use the resident kernel, "no_ps" (MVOLPS_NO_PS) general
  * kernel only, "no_handover" (MVOLPS_NO_HANDOVER) phase 2 after a phase 1 stays in the general kernel,
+ * "cres" (MVOLPS_CRES) 0 = never use the cluster-resident kernel,
  * "lz_k" (MVOLPS_LZ_K) cap of the pending-update depth, "ps_nt" (MVOLPS_PS_NT) CTA width of wide
  * launches.  value < 0 only queries; returns the previous value, -1 on an unknown name.  oracle: -1 */
 int mvb_engine_option(const char *name, int value);

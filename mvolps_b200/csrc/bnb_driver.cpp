@@ -465,6 +465,7 @@ struct Driver {
   void gen_cuts(glp_prob *a, const double *trows);
   void gen_cut_ref(glp_prob *a, int j, const double *trow);
   void gen_cut_gmi(glp_prob *a, int j, const double *trow);
+  bool gmi_produces(glp_prob *a, int j, const double *trow);
   int add_cut_constraint(glp_prob *a, int cID);
   int deepest_cut(glp_prob *a, size_t first);
 
@@ -662,6 +663,17 @@ void Driver::gen_cut_ref(glp_prob *a, int j, const double *trow) {
   pool.push_back(std::move(c));
 }
 
+// whether gen_cut_gmi(a, j, trow) pools a cut (its two early exits, nothing else)
+bool Driver::gmi_produces(glp_prob *a, int j, const double *trow) {
+  const double f0 = get_fract(glp_get_col_prim(a, j));
+  if (f0 < 1e-6 || f0 > 1.0 - 1e-6) return false;
+  const int n = a->ncols();
+  const int *at = a->at.data();
+  for (int p = 0; p < n; p++)
+    if (trow[p] != 0.0 && at[p] == MVB_AT_FR) return false;  // free non-basic in the row: no cut
+  return true;
+}
+
 // textbook Gomory mixed-integer cut of the row of basic integer column j:
 // with non-basics shifted to their active bounds (y >= 0),
 //   x_j + sum a_k y_k = beta,  f0 = frac(beta),
@@ -756,12 +768,31 @@ void Driver::gen_cuts(glp_prob *a, const double *t) {
   cut_rows_of(a, js, rows);
   pool_trim();
   const size_t pool0 = pool.size();
-  size_t k = 0;
-  for (int j : js) {
-    if (j < 0) { ref_oid_slot = -1; continue; }  // rejected column
-    if (pr.cut_mode == MVB_CUT_GMI) gen_cut_gmi(a, j, t + k * n);
-    else if (ref_oid_slot != -1) gen_cut_ref(a, j, t + k * n);
-    k++;
+  if (pr.cut_select == 0) {
+    // Only the LAST cut the loop of bs.cpp:250-255 pools is ever read (cut.cpp:16-21), so only that
+    // one is built: walk the columns in order to find which generator call is the last to pool a
+    // cut (same accept / reject rules, same ref_oid_slot bookkeeping), count the others.
+    int last_j = 0;
+    size_t last_k = 0, k = 0, pooled = 0;
+    for (int j : js) {
+      if (j < 0) { ref_oid_slot = -1; continue; }
+      const bool pools = pr.cut_mode == MVB_CUT_GMI ? gmi_produces(a, j, t + k * n) : ref_oid_slot != -1;
+      if (pools) { last_j = j; last_k = k; pooled++; }
+      k++;
+    }
+    if (pooled) {
+      pool_base += pooled - 1;
+      if (pr.cut_mode == MVB_CUT_GMI) gen_cut_gmi(a, last_j, t + last_k * n);
+      else gen_cut_ref(a, last_j, t + last_k * n);
+    }
+  } else {
+    size_t k = 0;
+    for (int j : js) {
+      if (j < 0) { ref_oid_slot = -1; continue; }  // rejected column
+      if (pr.cut_mode == MVB_CUT_GMI) gen_cut_gmi(a, j, t + k * n);
+      else if (ref_oid_slot != -1) gen_cut_ref(a, j, t + k * n);
+      k++;
+    }
   }
   if (pr.cut_select == 1) {
     const int pick = deepest_cut(a, pool0);

@@ -26,6 +26,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/mvolps_engine.h"
@@ -409,6 +410,7 @@ __device__ __forceinline__ bool primal_ratio_row(double alpha, int dir, int s, d
 
 #include "engine_lz.cuh"
 #include "engine_res.cuh"
+#include "engine_cres.cuh"
 
 namespace {
 
@@ -737,8 +739,10 @@ struct DeviceCtx {
   // per-launch arenas: bound patches go up and all outboxes come back in ONE copy each
   char *d_out = nullptr, *h_out = nullptr; size_t out_cap = 0;
   BoundPatch *d_patch = nullptr, *h_patch = nullptr; size_t patch_cap = 0;
-  std::vector<std::pair<size_t, char *>> free_slabs;  // recycled LP slabs (size, pointer)
-  size_t free_bytes = 0;
+  // recycled LP slabs by size (node LPs of one problem come and go in equal sizes, util.cpp:25-42;
+  // a second problem in the same process must not have to search through the first one's)
+  std::unordered_map<size_t, std::vector<char *>> free_slabs;
+  size_t free_bytes = 0, free_count = 0;
   // small slabs are carved out of chunks (one driver allocation per chunk instead of one per open
   // B&B node); a carved slab is only ever recycled, its chunk stays reserved until the process ends
   std::vector<std::pair<char *, size_t>> chunks;  // (base, bytes)
@@ -746,7 +750,8 @@ struct DeviceCtx {
   // deferred clones (glp_copy_prob, util.cpp:34 / bs.cpp:116): queued here and carried out
   // by ONE clone_kernel launch in front of the next device operation
   std::vector<CloneJob> clone_jobs;
-  std::vector<std::pair<size_t, char *>> zombies;  // slabs released while a queued clone may read them
+  struct Zombie { size_t bytes; char *slab; bool carved; };
+  std::vector<Zombie> zombies;  // slabs released while a queued clone / cut row may still touch them
   CloneJob *d_jobs = nullptr; size_t jobs_cap = 0;
   unsigned clone_epoch = 1;  // bumped by every flush: marks which handles take part in queued clones
   // deferred cut rows (cut.cpp:23-43 -> mvb_lp_append_row): queued like the clones and formed by ONE
@@ -769,6 +774,8 @@ struct DeviceCtx {
   bool no_ps = false;      // MVOLPS_NO_PS=1: general loop only (debugging / A-B timing)
   bool no_res = false;       // MVOLPS_NO_RES=1: never use the resident (tableau in shared memory) kernel
   size_t max_dyn_res = 0;    // dynamic shared memory simplex_res_kernel may ask for
+  size_t max_dyn_cres = 0;   // dynamic shared memory of one CTA of simplex_cres_kernel
+  int use_cres = 1;          // MVOLPS_CRES=0: never use the cluster-resident kernel
   int last_kind = 0;         // kernel of the last solve launch: 0 general, 1 private-state (lazy), 2 resident
   bool no_handover = false;  // MVOLPS_NO_HANDOVER=1: phase 2 after a phase 1 stays in the general loop (A-B timing)
   int force_k = 0;         // MVOLPS_LZ_K=k: cap the pending-update depth (A-B timing)
@@ -820,6 +827,14 @@ bool ctx_init(int device) {
     g_ctx.max_dyn_res = (size_t)optin > fr.sharedSizeBytes + 1024 ? (size_t)optin - fr.sharedSizeBytes - 1024 : 0;
     CK(cudaFuncSetAttribute(simplex_res_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_ctx.max_dyn_res));
   }
+  {
+    cudaFuncAttributes fc;
+    CK(cudaFuncGetAttributes(&fc, simplex_cres_kernel));
+    g_ctx.max_dyn_cres = (size_t)optin > fc.sharedSizeBytes + 1024 ? (size_t)optin - fc.sharedSizeBytes - 1024 : 0;
+    CK(cudaFuncSetAttribute(simplex_cres_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_ctx.max_dyn_cres));
+    const char *cr = getenv("MVOLPS_CRES");
+    if (cr) g_ctx.use_cres = atoi(cr);
+  }
   const char *noh = getenv("MVOLPS_NO_HANDOVER");
   g_ctx.no_handover = noh && noh[0] == '1';
   const char *fk = getenv("MVOLPS_LZ_K");
@@ -856,6 +871,7 @@ size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 struct mvb_lp {
   int m = 0, n = 0, ld = 0, mcap = 0;
   char *slab = nullptr;
+  bool slab_carved = false;         // the slab is part of a chunk allocation (never freed on its own)
   size_t slab_bytes = 0, t_bytes = 0, small_off = 0, small_bytes = 0, out_off = 0, out_bytes = 0;
   LPDev dev{};
   int curT = 0, curS = 0;
@@ -873,6 +889,7 @@ struct mvb_lp {
   int clone_role = 0;
   unsigned append_epoch = 0;        // == g_ctx.clone_epoch: a cut row of this LP is queued
   bool res_ok = false;              // the last solve request fits the resident kernel
+  int cres_c = 0;                   // ... or a cluster of this many CTAs (cluster-resident kernel); 0: neither
 };
 
 namespace {
@@ -909,14 +926,18 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
   lp->out_bytes = off - lp->out_off;
   lp->slab_bytes = off;
   lp->slab = nullptr;
-  for (size_t k = 0; k < g_ctx.free_slabs.size(); k++)
-    if (g_ctx.free_slabs[k].first == lp->slab_bytes) {  // recycle: no driver call at all
-      lp->slab = g_ctx.free_slabs[k].second;
+  lp->slab_carved = false;
+  {
+    auto it = g_ctx.free_slabs.find(lp->slab_bytes);
+    if (it != g_ctx.free_slabs.end() && !it->second.empty()) {  // recycle: no driver call at all
+      char *s = it->second.back();
+      it->second.pop_back();
+      lp->slab = (char *)((uintptr_t)s & ~(uintptr_t)1);
+      lp->slab_carved = ((uintptr_t)s & 1) != 0;  // (slabs are 256-byte aligned: bit 0 carries the flag)
       g_ctx.free_bytes -= lp->slab_bytes;
-      g_ctx.free_slabs[k] = g_ctx.free_slabs.back();
-      g_ctx.free_slabs.pop_back();
-      break;
+      g_ctx.free_count--;
     }
+  }
   if (!lp->slab && lp->slab_bytes <= ((size_t)4 << 20) && g_ctx.chunk_bytes < ((size_t)16 << 30)) {
     // a growing tree needs one new slab per branched node (util.cpp:25-42): carve them
     const size_t per = std::min<size_t>(256, std::max<size_t>(8, ((size_t)32 << 20) / lp->slab_bytes));
@@ -924,9 +945,12 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
     CK(cudaMallocAsync((void **)&base, per * lp->slab_bytes, g_ctx.stream));
     g_ctx.chunks.emplace_back(base, per * lp->slab_bytes);
     g_ctx.chunk_bytes += per * lp->slab_bytes;
-    for (size_t k = 1; k < per; k++) g_ctx.free_slabs.emplace_back(lp->slab_bytes, base + k * lp->slab_bytes);
+    std::vector<char *> &fl = g_ctx.free_slabs[lp->slab_bytes];
+    for (size_t k = per; k-- > 1;) fl.push_back((char *)((uintptr_t)(base + k * lp->slab_bytes) | 1));
     g_ctx.free_bytes += (per - 1) * lp->slab_bytes;
+    g_ctx.free_count += per - 1;
     lp->slab = base;
+    lp->slab_carved = true;
   }
   if (!lp->slab) CK(cudaMallocAsync((void **)&lp->slab, lp->slab_bytes, g_ctx.stream));
   char *s = lp->slab;
@@ -946,19 +970,12 @@ bool lp_alloc(mvb_lp *lp, int m, int n, int mcap) {
   return true;
 }
 
-bool slab_is_carved(const char *slab) {
-  for (auto &c : g_ctx.chunks)
-    if (slab >= c.first && slab < c.first + c.second) return true;
-  return false;
-}
-
-void slab_recycle(size_t bytes, char *slab) {
-  // node LPs come and go in equal sizes (util.cpp:25-42): keep up to 1 GiB of slabs for reuse
-  // (carved slabs always: they cannot be handed back one by one)
-  if ((bytes <= ((size_t)64 << 20) && g_ctx.free_bytes + bytes <= ((size_t)1 << 30) &&
-       g_ctx.free_slabs.size() < 8192) || slab_is_carved(slab)) {
-    g_ctx.free_slabs.emplace_back(bytes, slab);
+void slab_recycle(size_t bytes, char *slab, bool carved) {
+  // keep up to 1 GiB of slabs for reuse (carved slabs always: they cannot be handed back one by one)
+  if (carved || (bytes <= ((size_t)64 << 20) && g_ctx.free_bytes + bytes <= ((size_t)1 << 30) && g_ctx.free_count < 8192)) {
+    g_ctx.free_slabs[bytes].push_back(carved ? (char *)((uintptr_t)slab | 1) : slab);
     g_ctx.free_bytes += bytes;
+    g_ctx.free_count++;
   } else {
     cudaFreeAsync(slab, g_ctx.stream);
   }
@@ -966,9 +983,10 @@ void slab_recycle(size_t bytes, char *slab) {
 
 void lp_release(mvb_lp *lp) {
   if (lp->slab) {
-    // a queued clone may still have to read (or write) this slab: park it until the flush
-    if (!g_ctx.clone_jobs.empty() || !g_ctx.append_jobs.empty()) g_ctx.zombies.emplace_back(lp->slab_bytes, lp->slab);
-    else slab_recycle(lp->slab_bytes, lp->slab);
+    // a queued clone / cut row may still have to read (or write) this slab: park it until the flush
+    if (!g_ctx.clone_jobs.empty() || !g_ctx.append_jobs.empty())
+      g_ctx.zombies.push_back(DeviceCtx::Zombie{lp->slab_bytes, lp->slab, lp->slab_carved});
+    else slab_recycle(lp->slab_bytes, lp->slab, lp->slab_carved);
   }
   if (lp->pivlog) cudaFreeAsync(lp->pivlog, g_ctx.stream);
   lp->slab = nullptr;
@@ -1004,7 +1022,7 @@ bool flush_clones() {
   }
   std::vector<CloneJob> &jobs = g_ctx.clone_jobs;
   if (jobs.empty()) {
-    for (auto &z : g_ctx.zombies) slab_recycle(z.first, z.second);
+    for (auto &z : g_ctx.zombies) slab_recycle(z.bytes, z.slab, z.carved);
     g_ctx.zombies.clear();
     g_ctx.clone_epoch++;
     return true;
@@ -1026,7 +1044,7 @@ bool flush_clones() {
   g_launches++;
   jobs.clear();
   g_ctx.clone_epoch++;
-  for (auto &z : g_ctx.zombies) slab_recycle(z.first, z.second);
+  for (auto &z : g_ctx.zombies) slab_recycle(z.bytes, z.slab, z.carved);
   g_ctx.zombies.clear();
   return true;
 }
@@ -1237,6 +1255,7 @@ bool lp_grow(mvb_lp *lp, int mcap) {
   CK(cudaMemcpyAsync(d.ub, s.ub, (size_t)(n + m) * sizeof(double), cudaMemcpyDeviceToDevice, st));
   lp_release(lp);
   lp->slab = nl.slab; nl.slab = nullptr;
+  lp->slab_carved = nl.slab_carved;
   lp->slab_bytes = nl.slab_bytes; lp->t_bytes = nl.t_bytes;
   lp->small_off = nl.small_off; lp->small_bytes = nl.small_bytes;
   lp->out_off = nl.out_off; lp->out_bytes = nl.out_bytes;
@@ -1279,8 +1298,8 @@ extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double 
 namespace {
 
 // one cooperative launch over the LPs `idx` (indices into lps), results into the outboxes
-bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opts *opts, int kind) {
-  const bool psk = kind == 1, res = kind == 2;
+bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opts *opts, int kind, int csize = 0) {
+  const bool psk = kind == 1, res = kind == 2 || kind == 3, cres = kind == 3;
   const int count = (int)idx.size();
   if (!count) return true;
   cudaStream_t st = g_ctx.stream;
@@ -1339,14 +1358,34 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
     // one CTA per LP, as many CTAs as are co-resident with the largest tableau of the launch
     // (grid-stride over the LPs: a CTA takes the next LP when it has stored the last one)
     dyn = 0;
-    for (int k = 0; k < count; k++) dyn = std::max(dyn, res_smem_bytes(lps[idx[k]]->m, lps[idx[k]]->ld));
-    int per_sm = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_res_kernel, RES_NT, dyn));
-    if (per_sm < 1) return fail("simplex_res_kernel does not fit an SM");
-    res_grid = std::min(count, per_sm * g_ctx.sms);
-    G = 1;
-    ngroups = res_grid;
-    nt = RES_NT;
+    if (!cres) {
+      for (int k = 0; k < count; k++) dyn = std::max(dyn, res_smem_bytes(lps[idx[k]]->m, lps[idx[k]]->ld));
+      int per_sm = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_res_kernel, RES_NT, dyn));
+      if (per_sm < 1) return fail("simplex_res_kernel does not fit an SM");
+      res_grid = std::min(count, per_sm * g_ctx.sms);
+      G = 1;
+      nt = RES_NT;
+    } else {
+      // clusters of `csize` CTAs, one LP per cluster at a time; as many clusters as are co-resident
+      for (int k = 0; k < count; k++) dyn = std::max(dyn, cres_smem_bytes(lps[idx[k]]->m, lps[idx[k]]->ld, csize));
+      cudaLaunchConfig_t qc{};
+      qc.gridDim = dim3((unsigned)(csize * count));
+      qc.blockDim = dim3(CRES_NT);
+      qc.dynamicSmemBytes = dyn;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = (unsigned)csize; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+      qc.attrs = qa;
+      qc.numAttrs = 1;
+      int nclusters = 0;
+      CK(cudaOccupancyMaxActiveClusters(&nclusters, simplex_cres_kernel, &qc));
+      if (nclusters < 1) return fail("simplex_cres_kernel: no cluster of this size fits the device");
+      res_grid = std::min(count, nclusters) * csize;
+      G = csize;
+      nt = CRES_NT;
+    }
+    ngroups = res_grid / G;
   }
   if (g_ctx.ctrs_cap < ngroups) {
     if (g_ctx.ctrs) CK(cudaFreeAsync(g_ctx.ctrs, st));
@@ -1404,7 +1443,19 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   void *args[] = {(void *)&dl, (void *)&cnt, (void *)&G, (void *)&ctrs, (void *)&tcl};
   if (!g_ctx.kev[0]) { CK(cudaEventCreate(&g_ctx.kev[0])); CK(cudaEventCreate(&g_ctx.kev[1])); }
   CK(cudaEventRecord(g_ctx.kev[0], st));
-  if (res) {
+  if (cres) {
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = dim3((unsigned)res_grid);
+    lc.blockDim = dim3(CRES_NT);
+    lc.dynamicSmemBytes = dyn;
+    lc.stream = st;
+    cudaLaunchAttribute la[1];
+    la[0].id = cudaLaunchAttributeClusterDimension;
+    la[0].val.clusterDim.x = (unsigned)csize; la[0].val.clusterDim.y = 1; la[0].val.clusterDim.z = 1;
+    lc.attrs = la;
+    lc.numAttrs = 1;
+    CK(cudaLaunchKernelEx(&lc, simplex_cres_kernel, dl, cnt, csize));
+  } else if (res) {
     simplex_res_kernel<<<res_grid, RES_NT, dyn, st>>>(dl, cnt);
     CK(cudaGetLastError());
   } else {
@@ -1456,7 +1507,7 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
   cudaStream_t st = g_ctx.stream;
   g_ctx.batch_kernel_ms = 0.0;
   g_ctx.batch_solve_launches = 0;
-  std::vector<int> ps_idx, gen_idx, res_idx;
+  std::vector<int> ps_idx, gen_idx, res_idx, cres_idx[3];
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[k];
     if (!lp_push_small(lp)) return -1;
@@ -1484,21 +1535,32 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     const size_t rb = g_ctx.no_res || lp->m < 1 ? 0 : res_smem_bytes(lp->m, lp->ld);
     lp->res_ok = rb > 0 && rb <= g_ctx.max_dyn_res && !(opts && opts->ctas_per_lp > 0);  // an explicit group size asks for the lazy loop
     if (lp->res_ok) lp->dev.ps_ok = !g_ctx.no_handover;
-    (lp->res_ok ? res_idx : fits ? ps_idx : gen_idx).push_back(k);
+    // cluster-resident kernel: too large for one CTA, but a cluster of 2 / 4 / 8 holds it
+    lp->cres_c = 0;
+    if (!lp->res_ok && g_ctx.use_cres && !g_ctx.no_res && lp->m >= 1 && !(opts && opts->ctas_per_lp > 0))
+      lp->cres_c = cres_pick_c(lp->m, lp->ld, g_ctx.max_dyn_cres);
+    if (lp->cres_c) lp->dev.ps_ok = !g_ctx.no_handover;
+    if (lp->cres_c) cres_idx[lp->cres_c == 2 ? 0 : lp->cres_c == 4 ? 1 : 2].push_back(k);
+    else (lp->res_ok ? res_idx : fits ? ps_idx : gen_idx).push_back(k);
   }
   auto dev_result = [](mvb_lp *lp) { return (const DevResult *)&lp->dres; };
   // resident and private-state kernels first; what needs phase 1 (or fits neither) goes to the general one
   if (!launch_solve(lps, res_idx, opts, 2)) return -1;
+  for (int c = 0; c < 3; c++)
+    if (!launch_solve(lps, cres_idx[c], opts, 3, 2 << c)) return -1;
   if (!launch_solve(lps, ps_idx, opts, 1)) return -1;
   for (int k : res_idx)
     if (dev_result(lps[k])->r.status == MVB_PS_FALLBACK) gen_idx.push_back(k);
+  for (int c = 0; c < 3; c++)
+    for (int k : cres_idx[c])
+      if (dev_result(lps[k])->r.status == MVB_PS_FALLBACK) gen_idx.push_back(k);
   for (int k : ps_idx)
     if (dev_result(lps[k])->r.status == MVB_PS_FALLBACK) gen_idx.push_back(k);
   std::sort(gen_idx.begin(), gen_idx.end());
   if (!launch_solve(lps, gen_idx, opts, 0)) return -1;
   // ... which hands an LP back as soon as its phase 1 has found a primal feasible basis: phase 2
   // (the bulk of the iterations) then runs in the private-state kernel, carrying the tallies on
-  std::vector<int> hand_idx, hand_res;
+  std::vector<int> hand_idx, hand_res, hand_cres[3];
   for (int k : gen_idx) {
     mvb_lp *lp = lps[k];
     const DevResult *dr = dev_result(lp);
@@ -1509,9 +1571,14 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     lp->dev.c_iters = dr->r.iters; lp->dev.c_pivots = dr->r.pivots; lp->dev.c_flips = dr->r.flips;
     lp->dev.c_it1 = dr->r.iters_primal1; lp->dev.c_it2 = dr->r.iters_primal2; lp->dev.c_itd = dr->r.iters_dual;
     lp->dev.c_bland = dr->r.bland_iters; lp->dev.c_hash = dr->r.pivot_hash;
-    (lp->res_ok ? hand_res : hand_idx).push_back(k);
+    if (lp->cres_c) hand_cres[lp->cres_c == 2 ? 0 : lp->cres_c == 4 ? 1 : 2].push_back(k);
+    else (lp->res_ok ? hand_res : hand_idx).push_back(k);
   }
   if (!launch_solve(lps, hand_res, opts, 2)) return -1;
+  for (int c = 0; c < 3; c++) {
+    if (!launch_solve(lps, hand_cres[c], opts, 3, 2 << c)) return -1;
+    for (int k : hand_cres[c]) lps[k]->dev.carry = 0;
+  }
   if (!launch_solve(lps, hand_idx, opts, 1)) return -1;
   for (int k : hand_res) lps[k]->dev.carry = 0;
   for (int k : hand_idx) lps[k]->dev.carry = 0;
@@ -1663,6 +1730,7 @@ int mvb_engine_option(const char *name, int value) {
   if (!strcmp(name, "no_res")) flag(g_ctx.no_res);
   else if (!strcmp(name, "no_ps")) flag(g_ctx.no_ps);
   else if (!strcmp(name, "no_handover")) flag(g_ctx.no_handover);
+  else if (!strcmp(name, "cres")) num(g_ctx.use_cres);
   else if (!strcmp(name, "lz_k")) num(g_ctx.force_k);
   else if (!strcmp(name, "ps_nt")) num(g_ctx.force_nt);
   else { g_err = std::string("mvb_engine_option: unknown option ") + name; return -1; }

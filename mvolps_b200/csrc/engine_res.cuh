@@ -113,61 +113,70 @@ __device__ int res_dual_select(const ResLay &l, int m, bool bland, int par) {
   return best.idx;
 }
 
-// K4 in shared memory: T'[i][j] = fma(col[i], rho[j], j == q ? 0 : T[i][j]), row r <- rho, rows
-// 0..m (row 0 = reduced costs).  Thread (tx, ty) owns the column pairs {ch * CW + 2 tx} and the
-// rows ty, ty + trows, ...  PRICE: the threads that have just written row 0 price their columns
-// for the next iteration and return their best key.
+// K4 in shared memory on a tile of rows 0..nrow (row 0 = reduced costs): T'[i][j] = fma(col[i],
+// rho[j], j == q ? 0 : T[i][j]), row rloc <- rho (rloc < 0: the pivot row is not in this tile).
+// Thread (tx, ty) owns the column pairs {ch * CW + 2 tx} and the rows ty, ty + trows, ...  The
+// main loop is the plain fma on every element (six instructions per row and column pair); the two
+// special cases -- column q reads its old value as 0, row rloc becomes rho -- are rewritten
+// afterwards by the very thread that owns those elements, so the results are the specification's.
+// PRICE: the threads that own row 0 price their columns for the next iteration (position q is
+// taken from registers: kout / atq) and return their best key.
 template <bool PRICE>
-__device__ __forceinline__ Key res_update(const ResLay &l, int m, int n, int ld, int r, int q, bool bland,
-                                          int tcl) {
-  double *T = reinterpret_cast<double *>(dyn_smem + l.oT);
-  const double *col = reinterpret_cast<const double *>(dyn_smem + l.oCol);
-  const double *rhoS = reinterpret_cast<const double *>(dyn_smem + l.oRho);
-  const int *nbv = reinterpret_cast<const int *>(dyn_smem + l.oNb), *atv = reinterpret_cast<const int *>(dyn_smem + l.oAt);
+__device__ __forceinline__ Key smem_tile_update(double *T, unsigned lds, int nrow, int n, int ld, const double *col,
+                                                const double *rhoS, const int *nbv, const int *atv, int rloc,
+                                                int q, bool bland, int tcl, int kout, int atq) {
   const int tcols = 1 << tcl, trows = (int)blockDim.x >> tcl;
   const int tx = threadIdx.x & (tcols - 1), ty = threadIdx.x >> tcl;
   const int CW = 2 * tcols;
-  const unsigned lds = l.lds;
+  const size_t step = (size_t)trows * lds;
   Key best = key_none();
   for (int c0 = 2 * tx; c0 < ld; c0 += CW) {
     const double2 rho = *reinterpret_cast<const double2 *>(rhoS + c0);
-    const bool qx = c0 == q, qy = c0 + 1 == q;
     double *p = T + (size_t)ty * lds + c0;
     int i = ty;
-    for (; i + 3 * trows <= m; i += 4 * trows, p += (size_t)4 * trows * lds) {
+    for (; i + 3 * trows <= nrow; i += 4 * trows, p += 4 * step) {
       double2 t[4];
       double c[4];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
-        t[u] = *reinterpret_cast<const double2 *>(p + (size_t)u * trows * lds);
+        t[u] = *reinterpret_cast<const double2 *>(p + u * step);
         c[u] = col[i + u * trows];
       }
 #pragma unroll
       for (int u = 0; u < 4; u++) {
         double2 o;
-        o.x = fma(c[u], rho.x, qx ? 0.0 : t[u].x);
-        o.y = fma(c[u], rho.y, qy ? 0.0 : t[u].y);
-        if (i + u * trows == r) o = rho;
-        *reinterpret_cast<double2 *>(p + (size_t)u * trows * lds) = o;
+        o.x = fma(c[u], rho.x, t[u].x);
+        o.y = fma(c[u], rho.y, t[u].y);
+        *reinterpret_cast<double2 *>(p + u * step) = o;
       }
     }
-    for (; i <= m; i += trows, p += (size_t)trows * lds) {
+    for (; i <= nrow; i += trows, p += step) {
       const double2 t = *reinterpret_cast<const double2 *>(p);
       const double c = col[i];
       double2 o;
-      o.x = fma(c, rho.x, qx ? 0.0 : t.x);
-      o.y = fma(c, rho.y, qy ? 0.0 : t.y);
-      if (i == r) o = rho;
+      o.x = fma(c, rho.x, t.x);
+      o.y = fma(c, rho.y, t.y);
       *reinterpret_cast<double2 *>(p) = o;
     }
+    // column q of this thread's rows: the old value counts as 0 (exactly fma(c, rho_q, 0))
+    if (c0 == q || c0 + 1 == q) {
+      const double rq = c0 == q ? rho.x : rho.y;
+      double *pq = T + (size_t)ty * lds + q;
+      for (int k = ty; k <= nrow; k += trows, pq += step) *pq = fma(col[k], rq, 0.0);
+    }
+    // the pivot row becomes rho
+    if (rloc >= 0 && (rloc - ty) % trows == 0 && rloc >= ty)
+      *reinterpret_cast<double2 *>(T + (size_t)rloc * lds + c0) = rho;
     if (PRICE && ty == 0) {  // this thread wrote T[0][c0], T[0][c0 + 1]
       const double2 d = *reinterpret_cast<const double2 *>(T + c0);
       if (c0 < n) {
-        const Key k = res_price_key(d.x, atv[c0], nbv[c0], c0, bland);
+        const bool isq = c0 == q;
+        const Key k = res_price_key(d.x, isq ? atq : atv[c0], isq ? kout : nbv[c0], c0, bland);
         if (key_less(k, best)) best = k;
       }
       if (c0 + 1 < n) {
-        const Key k = res_price_key(d.y, atv[c0 + 1], nbv[c0 + 1], c0 + 1, bland);
+        const bool isq = c0 + 1 == q;
+        const Key k = res_price_key(d.y, isq ? atq : atv[c0 + 1], isq ? kout : nbv[c0 + 1], c0 + 1, bland);
         if (key_less(k, best)) best = k;
       }
     }
@@ -175,14 +184,24 @@ __device__ __forceinline__ Key res_update(const ResLay &l, int m, int n, int ld,
   return best;
 }
 
-__device__ __forceinline__ void res_tally(ResCtx *S, const LPDev &L, int mode, int r, int q, bool bland) {
-  Tally &t = S->ty;
+template <bool PRICE>
+__device__ __forceinline__ Key res_update(const ResLay &l, int m, int n, int ld, int r, int q, bool bland,
+                                          int tcl, int kout, int atq) {
+  return smem_tile_update<PRICE>(reinterpret_cast<double *>(dyn_smem + l.oT), l.lds, m, n, ld,
+                                 reinterpret_cast<const double *>(dyn_smem + l.oCol),
+                                 reinterpret_cast<const double *>(dyn_smem + l.oRho),
+                                 reinterpret_cast<const int *>(dyn_smem + l.oNb),
+                                 reinterpret_cast<const int *>(dyn_smem + l.oAt), r, q, bland, tcl, kout, atq);
+}
+
+// bookkeeping of one iteration (as tally_iter); log: this thread also writes the pivot log
+__device__ __forceinline__ void res_tally_to(Tally &t, const LPDev &L, int mode, int r, int q, bool bland, bool log) {
   unsigned long long h = t.hash;
   h = (h ^ (unsigned long long)mode) * MVB_FNV_PRIME;
   h = (h ^ (unsigned long long)r) * MVB_FNV_PRIME;
   h = (h ^ (unsigned long long)q) * MVB_FNV_PRIME;
   t.hash = h;
-  if (L.pivlog && t.iters < L.pivlog_cap) {
+  if (log && L.pivlog && t.iters < L.pivlog_cap) {
     L.pivlog[2 * t.iters] = r;
     L.pivlog[2 * t.iters + 1] = q;
   }
@@ -190,6 +209,9 @@ __device__ __forceinline__ void res_tally(ResCtx *S, const LPDev &L, int mode, i
   if (r) t.pivots++; else t.flips++;
   if (mode == MVB_MODE_PRIMAL2) t.it2++; else t.itd++;
   if (bland) t.bland++;
+}
+__device__ __forceinline__ void res_tally(ResCtx *S, const LPDev &L, int mode, int r, int q, bool bland) {
+  res_tally_to(S->ty, L, mode, r, q, bland, true);
 }
 
 // One whole LP solve by ONE CTA with the tableau in shared memory.
@@ -379,7 +401,7 @@ __device__ void res_solve(const LPDev &L, ResCtx *S) {
         S->degen = degen1;
       }
       __syncthreads();
-      Key bq = res_update<true>(l, m, n, ld, r, q, degen1 >= MVB_BLAND_AFTER, tcl);
+      Key bq = res_update<true>(l, m, n, ld, r, q, degen1 >= MVB_BLAND_AFTER, tcl, kout, atq);
       bq = block_argmin_fast(bq, slot, par);  // barrier: end of the update, next entering column
       par ^= 1;
       q = bq.idx;
@@ -447,7 +469,7 @@ __device__ void res_solve(const LPDev &L, ResCtx *S) {
         S->degen = degen1;
       }
       __syncthreads();
-      res_update<false>(l, m, n, ld, r, q, false, tcl);
+      res_update<false>(l, m, n, ld, r, q, false, tcl, 0, 0);
       // K5a for the next iteration runs on the fresh beta; its barrier also ends the update
       r = res_dual_select(l, m, degen1 >= MVB_BLAND_AFTER, par);
       par ^= 1;

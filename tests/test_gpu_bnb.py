@@ -151,3 +151,17 @@ def test_event_stream_on_the_gpu_equals_the_references_own(product, case, tmp_pa
     ev = _prob(product, case, tmp_path).bnb(**_kwargs(case["flags"]))["events"].splitlines()
     assert ev[:30] == case["head"] and len(ev) == case["events"]
     assert hashlib.sha256("\n".join(ev).encode()).hexdigest() == case["events_sha256"]
+
+
+def test_node_level_vfp_and_round2_options_on_the_gpu(oracle, product):
+    """-vs 3 (most fractional on the node's own LP solution), -cf, the cut selection rule and the root
+    heuristic through the product: identical to the same driver on the oracle engine."""
+    inst = instances.mdkp(30, 8, 11)
+    for kw in (dict(var_strategy=3, max_iters=500), dict(var_strategy=3, node_strategy=1, batch_width=16, max_iters=400),
+               dict(cut_mode=2, cut_freq=0.5, max_iters=300), dict(cut_mode=2, cut_select=1, max_iters=300),
+               dict(root_heuristic=1, max_iters=500)):
+        a = GlpProb.from_instance(oracle, inst).bnb(**kw)
+        b = GlpProb.from_instance(product, inst).bnb(**kw)
+        for k in SAME:
+            assert a[k] == b[k], (kw, k)
+        assert a["launches_aux"] == b["launches_aux"]

@@ -149,3 +149,91 @@ def test_resident_statuses(oracle, product):
     ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)  # resume to optimality
     assert ra["status"] == 0
     _same(a, b, ra, rb)
+
+
+# ---------------------------------------------------------------- cluster-resident kernel
+@pytest.mark.parametrize("m,n,seed,csize", [(128, 256, 5, 2), (100, 400, 31, 2), (257, 300, 7, 4), (200, 520, 8, 8),
+                                             (256, 512, 0, 8), (300, 100, 33, 2)])
+def test_cluster_resident_primal_parity(oracle, product, m, n, seed, csize):
+    """simplex_cres_kernel: the tableau in the distributed shared memory of a cluster of 2 / 4 / 8
+    CTAs (row blocks), candidates exchanged through st.shared::cluster + the cluster barrier, the
+    scaled pivot row sent by cp.async.bulk shared -> shared::cluster: oracle bits."""
+    import ctypes as C
+    inst = instances.dense_lp(m, n, seed)
+    a, b = EngineLP.from_instance(oracle, inst), EngineLP.from_instance(product, inst)
+    ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)
+    assert product.mvb_last_kernel_mode() == 3
+    G, groups, nt = C.c_int(), C.c_int(), C.c_int()
+    product.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
+    assert G.value == csize
+    assert ra["status"] == 0 and ra["pivots"] > 0
+    _same(a, b, ra, rb)
+
+
+@pytest.mark.parametrize("nvars,nrows,seed", [(300, 100, 41), (500, 60, 42), (512, 256, 43)])
+def test_cluster_resident_dual_warm_start_parity(oracle, product, nvars, nrows, seed):
+    """B&B-style on a tableau that needs a cluster: bound change, cut rows, clones."""
+    inst = instances.mdkp(nvars, nrows, seed)
+    a = EngineLP.from_instance(oracle, inst, row_cap=nrows + 2)
+    b = EngineLP.from_instance(product, inst, row_cap=nrows + 2)
+    ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)
+    assert product.mvb_last_kernel_mode() == 3
+    _same(a, b, ra, rb)
+    x = a.primal()[:nvars]
+    frac = [j for j in range(nvars) if x[j] != np.floor(x[j])]
+    j = frac[0]
+    a2, b2 = a.clone(), b.clone()
+    for lp in (a, b):
+        lp.set_bounds(j, -np.inf, np.floor(x[j]))
+    for lp in (a2, b2):
+        lp.set_bounds(j, np.ceil(x[j]), np.inf)
+    ra, ra2 = solve_batch(oracle, [a, a2], log_pivots=1)
+    rb, rb2 = solve_batch(product, [b, b2], log_pivots=1)
+    assert product.mvb_last_kernel_mode() == 3 and ra["iters_dual"] > 0
+    _same(a, b, ra, rb)
+    _same(a2, b2, ra2, rb2)
+    for t in range(3):
+        xa = a.primal()[:nvars]
+        row = np.zeros(nvars)
+        row[t:t + 8] = 1.0
+        rhs = np.floor(row @ xa) - 1.0
+        for lp in (a, b):
+            lp.append_row(row, -np.inf, rhs)
+        ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)
+        _same(a, b, ra, rb)
+
+
+def test_cluster_resident_phase1_handover_batch_and_limits(oracle, product):
+    inst = instances.general_lp(100, 300, 14)
+    a, b = EngineLP.from_instance(oracle, inst), EngineLP.from_instance(product, inst)
+    ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)
+    assert ra["iters_primal1"] > 0 and ra["iters_primal2"] > 0 and product.mvb_last_kernel_mode() == 3
+    _same(a, b, ra, rb)
+    # more LPs than clusters in one launch, two cluster sizes in one batch
+    shapes = [(128, 256, 60 + k % 5) if k % 2 else (200, 520, 70 + k % 3) for k in range(90)]
+    la = [EngineLP.from_instance(oracle, instances.dense_lp(*s)) for s in shapes[:6]]
+    lb = [EngineLP.from_instance(product, instances.dense_lp(*s)) for s in shapes]
+    ra = solve_batch(oracle, la, log_pivots=1)
+    rb = solve_batch(product, lb, log_pivots=1)
+    for k in range(6):
+        _same(la[k], lb[k], ra[k], rb[k])
+    by_shape = {}
+    for s, r in zip(shapes, rb):
+        assert by_shape.setdefault(s, r["pivot_hash"]) == r["pivot_hash"]
+    # iteration limit and resume
+    inst = instances.dense_lp(128, 256, 5)
+    a, b = EngineLP.from_instance(oracle, inst), EngineLP.from_instance(product, inst)
+    ra, rb = a.solve(log_pivots=1, max_iters=9), b.solve(log_pivots=1, max_iters=9)
+    assert ra["status"] == 3
+    _same(a, b, ra, rb)
+    ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)
+    _same(a, b, ra, rb)
+    # the lazy loop on the same LP (cluster-resident switched off) gives the same bits
+    old = product.mvb_engine_option(b"cres", 0)
+    try:
+        c = EngineLP.from_instance(product, inst)
+        rc = c.solve(log_pivots=1)
+        assert product.mvb_last_kernel_mode() == 1
+        _same(a, c, ra, rc)
+    finally:
+        product.mvb_engine_option(b"cres", old)
