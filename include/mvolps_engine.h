@@ -96,7 +96,8 @@ int mvb_last_kernel_mode(void);
 /* A/B switches of the CUDA engine (tests, profiling; each also has an environment variable read at
  * start-up): "no_res" (MVOLPS_NO_RES) never use the resident kernel, "no_ps" (MVOLPS_NO_PS) general
  * kernel only, "no_handover" (MVOLPS_NO_HANDOVER) phase 2 after a phase 1 stays in the general kernel,
- * "cres" (MVOLPS_CRES) 0 = never use the cluster-resident kernel,
+ * "cres" (MVOLPS_CRES) 1 = LPs too large for one CTA's shared memory that fit a cluster of 2/4/8 CTAs use the
+ * cluster-resident kernel (default 0: the lazy loop is faster on full solves),
  * "lz_k" (MVOLPS_LZ_K) cap of the pending-update depth, "ps_nt" (MVOLPS_PS_NT) CTA width of wide
  * launches.  value < 0 only queries; returns the previous value, -1 on an unknown name.  oracle: -1 */
 int mvb_engine_option(const char *name, int value);

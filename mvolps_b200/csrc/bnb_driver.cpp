@@ -747,6 +747,7 @@ void Driver::cut_rows_of(glp_prob *a, std::vector<int> &js, std::vector<int> &ro
   int m = glp_get_num_rows(a), n = glp_get_num_cols(a);
   js.clear();
   rows.clear();
+  mv_need_basis(a);
   row_of.assign(n, 0);
   for (int i = 0; i < m; i++)
     if (a->head[i] < n) row_of[a->head[i]] = i + 1;

@@ -775,7 +775,8 @@ struct DeviceCtx {
   bool no_res = false;       // MVOLPS_NO_RES=1: never use the resident (tableau in shared memory) kernel
   size_t max_dyn_res = 0;    // dynamic shared memory simplex_res_kernel may ask for
   size_t max_dyn_cres = 0;   // dynamic shared memory of one CTA of simplex_cres_kernel
-  int use_cres = 1;          // MVOLPS_CRES=0: never use the cluster-resident kernel
+  int use_cres = 0;          // MVOLPS_CRES=1 / option "cres": LPs that fit no single CTA but a cluster of 2/4/8 go to the
+                             // cluster-resident kernel (measured slower than the lazy loop on full solves: opt-in)
   int last_kind = 0;         // kernel of the last solve launch: 0 general, 1 private-state (lazy), 2 resident
   bool no_handover = false;  // MVOLPS_NO_HANDOVER=1: phase 2 after a phase 1 stays in the general loop (A-B timing)
   int force_k = 0;         // MVOLPS_LZ_K=k: cap the pending-update depth (A-B timing)
@@ -1122,7 +1123,7 @@ int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost, const double *l
   CKI(cudaMemcpyAsync(d.lb, lb, (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, st));
   CKI(cudaMemcpyAsync(d.ub, ub, (size_t)(n + m) * sizeof(double), cudaMemcpyHostToDevice, st));
   {
-    std::vector<int> &hd = lp->head.fresh(m), &nb = lp->nb.fresh(n), &at = lp->at.fresh(n);
+    int *hd = lp->head.fresh(m), *nb = lp->nb.fresh(n), *at = lp->at.fresh(n);
     for (int i = 0; i < m; i++) hd[i] = n + i;
     for (int j = 0; j < n; j++) { nb[j] = j; at[j] = nb_flag_for(lb[j], ub[j], MVB_AT_LB); }
   }
@@ -1133,8 +1134,8 @@ int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost, const double *l
   lp->at_dirty = true;
   if (!lp_push_small(lp)) return -1;
   {
-    std::vector<double> &xv = lp->x.fresh(n + m);
-    std::fill(xv.begin(), xv.end(), 0.0);
+    double *xv = lp->x.fresh(n + m);
+    std::fill(xv, xv + n + m, 0.0);
   }
   lp->res = mvb_result{};
   lp->res.status = MVB_UNSOLVED;

@@ -64,6 +64,7 @@ static void drop_engine(glp_prob *P) {
   P->head.clear();
   P->nb.clear();
   P->at.clear();
+  P->basis_lazy = false;
 }
 
 // 0-based index of row i / column j after the range check GLPK makes
@@ -78,17 +79,17 @@ static size_t col_at(glp_prob *P, int j, const char *fn) {
 
 void mv_add_rows(glp_prob *P, int count) {
   const size_t m = P->rbnd.size() + (size_t)count;
-  P->rowm.mut().resize(m);
-  P->rbnd.mut().resize(m, MV_ROW_BND0);
-  P->rstat.mut().resize(m, GLP_BS);
-  P->rprim.mut().resize(m, 0.0);
+  P->rowm.resize(m);
+  P->rbnd.resize(m, MV_ROW_BND0);
+  P->rstat.resize(m, GLP_BS);
+  P->rprim.resize(m, 0.0);
 }
 void mv_add_cols(glp_prob *P, int count) {
   const size_t n = P->cbnd.size() + (size_t)count;
-  P->colm.mut().resize(n);
-  P->cbnd.mut().resize(n, MV_COL_BND0);
-  P->cstat.mut().resize(n, GLP_NS);
-  P->cprim.mut().resize(n, 0.0);
+  P->colm.resize(n);
+  P->cbnd.resize(n, MV_COL_BND0);
+  P->cstat.resize(n, GLP_NS);
+  P->cprim.resize(n, 0.0);
 }
 
 // the setters note a variable's bounds as the engine holds them the first time they touch it
@@ -157,6 +158,7 @@ void glp_copy_prob(glp_prob *dest, glp_prob *src, int names) {
     dest->head = src->head;
     dest->nb = src->nb;
     dest->at = src->at;
+    dest->basis_lazy = src->basis_lazy;
     dest->last = src->last;
   }
 }
@@ -314,8 +316,8 @@ void glp_set_mat_row(glp_prob *P, int i, int len, const int ind[],
   for (size_t t = 1; t < e.size(); t++)
     if (e[t].first == e[t - 1].first) shim_abort("glp_set_mat_row: duplicate column indices");
   MvRowM &r = P->rowm.w(k);
-  std::vector<int> &ri = r.ind.fresh(e.size());
-  std::vector<double> &rv = r.val.fresh(e.size());
+  int *ri = r.ind.fresh(e.size());
+  double *rv = r.val.fresh(e.size());
   for (size_t t = 0; t < e.size(); t++) { ri[t] = e[t].first; rv[t] = e[t].second; }
   if (i <= P->eng_rows) P->eng_stale = true;  // a row the tableau already holds
 }
@@ -467,19 +469,33 @@ int mv_pull_solution(glp_prob *P, const mvb_result &res) {
   const double *x;
   const int *head, *nb, *at;
   if (mvb_lp_solution_view(P->eng, &x, &head, &nb, &at)) return -1;
-  mv_install_solution(P, res, x, head, nb, at);
+  mv_install_solution(P, res, x, head, nb, at, /*keep_basis=*/false);
+  return 0;
+}
+
+int mv_need_basis(glp_prob *P) {
+  if (!P->basis_lazy) return 0;
+  if (!P->eng) return -1;
+  const int m = P->nrows(), n = P->ncols();
+  if (mvb_lp_get_basis(P->eng, P->head.fresh(m), P->nb.fresh(n), P->at.fresh(n))) return -1;
+  P->basis_lazy = false;
   return 0;
 }
 
 void mv_install_solution(glp_prob *P, const mvb_result &res, const double *x, const int *head,
-                         const int *nb, const int *at) {
+                         const int *nb, const int *at, bool keep_basis) {
   int m = P->nrows(), n = P->ncols();
-  P->head.assign(head, head + m);
-  P->nb.assign(nb, nb + n);
-  P->at.assign(at, at + n);
+  if (keep_basis) {
+    P->head.assign(head, head + m);
+    P->nb.assign(nb, nb + n);
+    P->at.assign(at, at + n);
+    P->basis_lazy = false;
+  } else {
+    P->basis_lazy = true;  // they stay in the engine's mirror until somebody asks (mv_need_basis)
+  }
   // fresh arrays: a copy that still shares its parent's solution does not pay for a copy of it
-  int *cstat = P->cstat.fresh(n).data(), *rstat = P->rstat.fresh(m).data();
-  double *cprim = P->cprim.fresh(n).data(), *rprim = P->rprim.fresh(m).data();
+  int *cstat = P->cstat.fresh(n), *rstat = P->rstat.fresh(m);
+  double *cprim = P->cprim.fresh(n), *rprim = P->rprim.fresh(m);
   for (int i = 0; i < m; i++) {
     int k = head[i];
     if (k < n) cstat[k] = GLP_BS; else rstat[k - n] = GLP_BS;
@@ -509,6 +525,7 @@ void mv_install_solution(glp_prob *P, const mvb_result &res, const double *x, co
 }
 
 void mv_make_ghost(glp_prob *P, int owner) {
+  mv_need_basis(P);  // the mirror must be complete before the engine object goes
   if (P->eng) mvb_lp_free(P->eng);
   P->eng = nullptr;
   P->ghost = true;
@@ -543,8 +560,8 @@ int glp_simplex(glp_prob *P, const glp_smcp *parm) {
      * too); nothing to send to the engine.  MVOLPS never gets here. */
     double z = P->c0;
     P->status = GLP_OPT;
-    int *cstat = P->cstat.fresh(n).data();
-    double *cprim = P->cprim.fresh(n).data();
+    int *cstat = P->cstat.fresh(n);
+    double *cprim = P->cprim.fresh(n);
     for (int j = 0; j < n; j++) {
       const MvBnd &c = P->cbnd[j];
       const double coef = P->colm[j].coef;
@@ -589,7 +606,7 @@ int glp_simplex(glp_prob *P, const glp_smcp *parm) {
 
 int glp_eval_tab_row(glp_prob *P, int k, int ind[], double val[]) {
   int m = P->nrows(), n = P->ncols();
-  if (!P->eng || P->eng_stale || P->eng_rows != m || (int)P->head.size() != m)
+  if (!P->eng || P->eng_stale || P->eng_rows != m || mv_need_basis(P) || (int)P->head.size() != m)
     shim_abort("glp_eval_tab_row: basis factorization does not exist");
   if (k < 1 || k > m + n) shim_abort("glp_eval_tab_row: variable number out of range");
   int id = k <= m ? n + (k - 1) : k - m - 1;

@@ -19,7 +19,7 @@
 #include <algorithm>
 #include <memory>
 #include <string>
-#include <vector>
+#include <vector>  // (the driver and the readers)
 
 #include "../../include/glpk.h"
 #include "../../include/mvolps_engine.h"
@@ -95,7 +95,9 @@ struct glp_prob {
   bool ghost = false;
   int owner = 0;
   std::vector<MvDirty> dirty;          // bounds set since the last sync
-  CowVec<int> head, nb, at;            // basis after the last solve
+  CowVec<int> head, nb, at;            // basis after the last solve (see basis_lazy)
+  bool basis_lazy = false;             // the basis arrays are still in the engine only: mv_need_basis fetches them
+                                       // (only the cut step and glp_eval_tab_row ever read them)
   mvb_result last{};
 };
 
@@ -122,7 +124,9 @@ int mv_pull_solution(glp_prob *P, const mvb_result &res);   // read result back
 // the same from caller-held arrays (x: n+m by engine id; head: m; nb, at: n): how a ghost
 // receives the solution its owner computed
 void mv_install_solution(glp_prob *P, const mvb_result &res, const double *x, const int *head,
-                         const int *nb, const int *at);
+                         const int *nb, const int *at, bool keep_basis = true);
+// make P->head / nb / at valid (fetches them from the engine when the last pull left them there)
+int mv_need_basis(glp_prob *P);
 // give up the device tableau but keep the mirror: the object becomes a ghost owned by `owner`
 void mv_make_ghost(glp_prob *P, int owner);
 // new rows / columns with the defaults GLPK gives them

@@ -52,18 +52,18 @@ void commit(const BuildProb &b, glp_prob *P) {
   P->name = b.name;
   mv_add_cols(P, (int)b.cols.size());
   mv_add_rows(P, (int)b.rows.size());
-  std::vector<MvColM> &cm = P->colm.mut();
-  std::vector<MvBnd> &cb = P->cbnd.mut();
-  std::vector<int> &cs = P->cstat.mut();
+  auto cm = P->colm.mut();
+  auto cb = P->cbnd.mut();
+  auto cs = P->cstat.mut();
   for (size_t j = 0; j < b.cols.size(); j++) {
     const MvCol &c = b.cols[j];
     cm[j].kind = c.kind; cm[j].coef = c.coef; cm[j].name = c.name;
     cb[j] = MvBnd{c.type, c.lb, c.ub};
     cs[j] = c.stat;
   }
-  std::vector<MvRowM> &rm = P->rowm.mut();
-  std::vector<MvBnd> &rb = P->rbnd.mut();
-  std::vector<int> &rs = P->rstat.mut();
+  auto rm = P->rowm.mut();
+  auto rb = P->rbnd.mut();
+  auto rs = P->rstat.mut();
   for (size_t i = 0; i < b.rows.size(); i++) {
     const MvRow &r = b.rows[i];
     rm[i].ind.assign(r.ind.data(), r.ind.data() + r.ind.size());

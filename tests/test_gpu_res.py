@@ -152,9 +152,17 @@ def test_resident_statuses(oracle, product):
 
 
 # ---------------------------------------------------------------- cluster-resident kernel
+@pytest.fixture()
+def cres(product):
+    """The cluster-resident kernel is opt-in (engine option "cres")."""
+    old = product.mvb_engine_option(b"cres", 1)
+    yield product
+    product.mvb_engine_option(b"cres", old)
+
+
 @pytest.mark.parametrize("m,n,seed,csize", [(128, 256, 5, 2), (100, 400, 31, 2), (257, 300, 7, 4), (200, 520, 8, 8),
                                              (256, 512, 0, 8), (300, 100, 33, 2)])
-def test_cluster_resident_primal_parity(oracle, product, m, n, seed, csize):
+def test_cluster_resident_primal_parity(oracle, product, cres, m, n, seed, csize):
     """simplex_cres_kernel: the tableau in the distributed shared memory of a cluster of 2 / 4 / 8
     CTAs (row blocks), candidates exchanged through st.shared::cluster + the cluster barrier, the
     scaled pivot row sent by cp.async.bulk shared -> shared::cluster: oracle bits."""
@@ -171,7 +179,7 @@ def test_cluster_resident_primal_parity(oracle, product, m, n, seed, csize):
 
 
 @pytest.mark.parametrize("nvars,nrows,seed", [(300, 100, 41), (500, 60, 42), (512, 256, 43)])
-def test_cluster_resident_dual_warm_start_parity(oracle, product, nvars, nrows, seed):
+def test_cluster_resident_dual_warm_start_parity(oracle, product, cres, nvars, nrows, seed):
     """B&B-style on a tableau that needs a cluster: bound change, cut rows, clones."""
     inst = instances.mdkp(nvars, nrows, seed)
     a = EngineLP.from_instance(oracle, inst, row_cap=nrows + 2)
@@ -203,7 +211,7 @@ def test_cluster_resident_dual_warm_start_parity(oracle, product, nvars, nrows, 
         _same(a, b, ra, rb)
 
 
-def test_cluster_resident_phase1_handover_batch_and_limits(oracle, product):
+def test_cluster_resident_phase1_handover_batch_and_limits(oracle, product, cres):
     inst = instances.general_lp(100, 300, 14)
     a, b = EngineLP.from_instance(oracle, inst), EngineLP.from_instance(product, inst)
     ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)
@@ -229,11 +237,16 @@ def test_cluster_resident_phase1_handover_batch_and_limits(oracle, product):
     ra, rb = a.solve(log_pivots=1), b.solve(log_pivots=1)
     _same(a, b, ra, rb)
     # the lazy loop on the same LP (cluster-resident switched off) gives the same bits
-    old = product.mvb_engine_option(b"cres", 0)
+    product.mvb_engine_option(b"cres", 0)
     try:
-        c = EngineLP.from_instance(product, inst)
-        rc = c.solve(log_pivots=1)
+        a2, c = EngineLP.from_instance(oracle, inst), EngineLP.from_instance(product, inst)
+        ra2, rc = a2.solve(log_pivots=1), c.solve(log_pivots=1)
         assert product.mvb_last_kernel_mode() == 1
-        _same(a, c, ra, rc)
+        _same(a2, c, ra2, rc)
+        d = EngineLP.from_instance(product, inst)
+        product.mvb_engine_option(b"cres", 1)
+        rd = d.solve(log_pivots=1)
+        assert product.mvb_last_kernel_mode() == 3
+        _same(a2, d, ra2, rd)
     finally:
-        product.mvb_engine_option(b"cres", old)
+        product.mvb_engine_option(b"cres", 1)
