@@ -88,6 +88,9 @@ int mvb_shard_load(mvb_shard *s, const double *A_local, const double *cost_local
 int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_opts *opts, mvb_result *out);
 /* x[n_global + m] by variable id of the last solve (replicated) */
 int mvb_shard_get_primal(mvb_shard *s, double *x);
+/* basis of the last solve (replicated): head[m] = id basic in row i, nb[n_global] / at[n_global] =
+ * id and MVB_AT_* flag at every global non-basic position */
+int mvb_shard_get_basis(mvb_shard *s, int *head, int *nb, int *at);
 /* copies up to cap (row, global position) pairs of the last solve; returns total logged */
 int mvb_shard_get_pivot_log(mvb_shard *s, int *rowcol, int cap);
 /* device time of the last solve's kernels + exchanges (CUDA events), ms */
@@ -96,6 +99,18 @@ double mvb_shard_last_ms(mvb_shard *s);
  * (single-process group), 1 ncclAllGather, 2 pushed into the peers' mailboxes by the price
  * kernel (CUDA IPC over NVLink; default for one process per GPU, MVOLPS_SHARD_EXCHANGE=nccl: 1) */
 int mvb_shard_last_exchange(mvb_shard *s);
+
+/* ---- the sharded path behind glp_simplex (bs.cpp:117) ----
+ * Installs the group glp_simplex may route a large LP to: comm != NULL: the NCCL (or caller-supplied)
+ * communicator of this process, glp_simplex is then COLLECTIVE for such LPs -- every rank calls it on
+ * its own copy of the same problem; comm == NULL && local_world > 1: a single-process group of that
+ * many shards on this GPU (tests); local_world <= 1 and comm == NULL: routing off (default).  An LP
+ * takes the sharded path when it has no engine tableau yet, starts primal feasible from the slack
+ * basis with every non-basic at value 0 (what that path solves), and its tableau has at least
+ * min_bytes bytes (<= 0: 1 GiB).  Afterwards status, objective, primal values and row / column
+ * statuses are those of the single-GPU solve, bit for bit; the tableau stays with the shards (a
+ * later glp_eval_tab_row or warm start rebuilds on one GPU). */
+int mvb_glp_use_shards(const mvb_comm *comm, int local_world, long long min_bytes);
 
 #ifdef __cplusplus
 }

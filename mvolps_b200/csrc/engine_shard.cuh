@@ -618,6 +618,7 @@ struct mvb_shard {
   double *cost = nullptr;          // local costs (device)
   std::vector<double> lb, ub;      // replicated bounds (host)
   std::vector<double> x;           // primal by id after the last solve
+  std::vector<int> bhead, bnb, bat; // basis after the last solve: head[m], nb / at by GLOBAL position (n_global)
   int *pivlog = nullptr; int pivlog_cap = 0, pivlog_n = 0;
   cudaEvent_t ev[2] = {};
   cudaEvent_t ev_dec[2] = {}, ev_upd[2] = {};  // by iteration parity: decide done / update done
@@ -865,6 +866,14 @@ int mvb_shard_get_pivot_log(mvb_shard *s, int *rowcol, int cap) {
   return s->pivlog_n;
 }
 
+int mvb_shard_get_basis(mvb_shard *s, int *head, int *nb, int *at) {
+  if ((int)s->bhead.size() != s->m || (int)s->bnb.size() != s->nglob) { g_err = "mvb_shard_get_basis: no solution"; return -1; }
+  std::memcpy(head, s->bhead.data(), (size_t)s->m * sizeof(int));
+  std::memcpy(nb, s->bnb.data(), (size_t)s->nglob * sizeof(int));
+  std::memcpy(at, s->bat.data(), (size_t)s->nglob * sizeof(int));
+  return 0;
+}
+
 double mvb_shard_last_ms(mvb_shard *s) { return s->last_ms; }
 int mvb_shard_last_exchange(mvb_shard *s) { return s->last_exchange; }
 
@@ -1011,6 +1020,9 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
     CKI(cudaStreamSynchronize(st));
     std::vector<double> cost(ng, 0.0);
     s->x.assign(ng + m, 0.0);
+    s->bhead.assign(head.begin() + 1, head.end());
+    s->bnb.assign(ng, 0);
+    s->bat.assign(ng, 0);
     for (int r = 0; r < W; r++) {
       int c0, nc;
       mvb_shard_partition(ng, W, r, &c0, &nc);
@@ -1019,6 +1031,8 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
       for (int j = 0; j < nc; j++) {
         cost[c0 + j] = co[j];
         const int id = nb[j], f = at[j];
+        s->bnb[c0 + j] = id;
+        s->bat[c0 + j] = f;
         s->x[id] = (f == MVB_AT_LB || f == MVB_AT_FX) ? s->lb[id] : f == MVB_AT_UB ? s->ub[id] : 0.0;
       }
     }

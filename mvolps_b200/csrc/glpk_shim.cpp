@@ -546,6 +546,83 @@ int mv_sync_engine(glp_prob *P, bool *changed) {
   return rc;
 }
 
+#ifdef MVB_WITH_SHARDS
+// ---- the column-sharded path behind glp_simplex (product library only; include/mvolps_dist.h) ----
+#include "../../include/mvolps_dist.h"
+static const mvb_comm *g_shard_comm = nullptr;
+static int g_shard_local = 0;
+static long long g_shard_min_bytes = 1LL << 30;
+
+extern "C" int mvb_glp_use_shards(const mvb_comm *comm, int local_world, long long min_bytes) {
+  g_shard_comm = comm;
+  g_shard_local = comm ? 0 : local_world;
+  g_shard_min_bytes = min_bytes > 0 ? min_bytes : (1LL << 30);
+  return 0;
+}
+
+// 1: solved on the shard group (solution installed), 0: not eligible, -1: error
+static int simplex_on_shards(glp_prob *P) {
+  const int world = g_shard_comm ? g_shard_comm->world : g_shard_local;
+  if (world < 2) return 0;
+  const int m = P->nrows(), n = P->ncols();
+  if ((P->eng && !P->eng_stale) || P->ghost) return 0;                // a tableau exists: warm start on one GPU
+  if ((long long)(m + 1) * n * 8 < g_shard_min_bytes) return 0;
+  std::vector<double> lb(n + m), ub(n + m);
+  for (int j = 0; j < n; j++) {
+    lb[j] = mv_eff_lb(P->cbnd[j].type, P->cbnd[j].lb);
+    ub[j] = mv_eff_ub(P->cbnd[j].type, P->cbnd[j].ub);
+    const bool zero_ok = lb[j] == 0.0 || (!(lb[j] > -HUGE_VAL) && (ub[j] == 0.0 || !(ub[j] < HUGE_VAL)));
+    if (!zero_ok) return 0;  // the sharded path starts with every non-basic at value 0
+  }
+  for (int i = 0; i < m; i++) {
+    lb[n + i] = mv_eff_lb(P->rbnd[i].type, P->rbnd[i].lb);
+    ub[n + i] = mv_eff_ub(P->rbnd[i].type, P->rbnd[i].ub);
+    if (lb[n + i] > 0.0 || ub[n + i] < 0.0) return 0;  // slack basis not primal feasible: phase 1 is not sharded
+  }
+  const bool local = g_shard_comm == nullptr;
+  std::vector<mvb_comm *> own;
+  std::vector<mvb_shard *> shards;
+  auto cleanup = [&] {
+    for (mvb_shard *s : shards) mvb_shard_free(s);
+    for (mvb_comm *c : own) mvb_comm_free(c);
+  };
+  for (int r = local ? 0 : g_shard_comm->rank; r < (local ? world : g_shard_comm->rank + 1); r++) {
+    int c0 = 0, nc = 0;
+    mvb_shard_partition(n, world, r, &c0, &nc);
+    const mvb_comm *cm = g_shard_comm;
+    if (local) { own.push_back(mvb_comm_local(r, world)); cm = own.back(); }
+    mvb_shard *s = mvb_shard_create(m, n, c0, nc, cm);
+    if (!s) { cleanup(); return -1; }
+    shards.push_back(s);
+    std::vector<double> A((size_t)m * std::max(nc, 1), 0.0), cost(std::max(nc, 1));
+    for (int i = 0; i < m; i++) {
+      const MvRowM &row = P->rowm[i];
+      for (size_t t = 0; t < row.ind.size(); t++) {
+        const int j = row.ind[t] - 1;
+        if (j >= c0 && j < c0 + nc) A[(size_t)i * nc + (j - c0)] = row.val[t];
+      }
+    }
+    for (int j = 0; j < nc; j++) cost[j] = P->dir == GLP_MAX ? -P->colm[c0 + j].coef : P->colm[c0 + j].coef;
+    if (mvb_shard_load(s, A.data(), cost.data(), lb.data(), ub.data())) { cleanup(); return -1; }
+  }
+  mvb_result res;
+  mvb_opts opts{};
+  if (mvb_shard_solve(shards.data(), (int)shards.size(), &opts, &res)) { cleanup(); return -1; }
+  std::vector<double> x(n + m);
+  std::vector<int> head(m), nb(n), at(n);
+  if (mvb_shard_get_primal(shards[0], x.data()) || mvb_shard_get_basis(shards[0], head.data(), nb.data(), at.data())) {
+    cleanup();
+    return -1;
+  }
+  mv_install_solution(P, res, x.data(), head.data(), nb.data(), at.data());
+  // the tableau stays with the shards: this object holds the solution, not a factorisation
+  P->eng_stale = true;
+  P->eng_changed = true;
+  cleanup();
+  return 1;
+}
+#endif
+
 extern "C" {
 
 int glp_simplex(glp_prob *P, const glp_smcp *parm) {
@@ -581,6 +658,16 @@ int glp_simplex(glp_prob *P, const glp_smcp *parm) {
     return 0;
   }
   if (P->ghost) shim_abort("glp_simplex: the object is a ghost of a multi-GPU tree (no device tableau on this rank)");
+#ifdef MVB_WITH_SHARDS
+  {
+    const int rc = simplex_on_shards(P);
+    if (rc < 0) {
+      std::fprintf(stderr, "glp_simplex: sharded engine error: %s\n", mvb_last_error());
+      return GLP_EFAIL;
+    }
+    if (rc > 0) return P->last.status == MVB_ITLIM ? GLP_EITLIM : 0;
+  }
+#endif
   bool changed = false;
   if (sync_engine(P, &changed)) {
     std::fprintf(stderr, "glp_simplex: engine error: %s\n", mvb_last_error());

@@ -71,3 +71,38 @@ def test_sharded_rejects_unsupported(product):
     inst = instances.general_lp(20, 30, 12)  # needs phase 1
     with pytest.raises(RuntimeError):
         ShardGroup(product, inst, 2)
+
+
+def test_glp_simplex_routes_to_the_shard_group(oracle, product):
+    """mvb_glp_use_shards: the column-sharded engine behind the reference's own call (bs.cpp:117).
+    A single-process group of 3 shards on this GPU; glp_simplex on a fresh slack-feasible LP is then
+    solved column-sharded: status, objective bits, primal values and statuses of the plain solve."""
+    from mvolps_b200 import capi
+    from mvolps_b200.lp import GlpProb
+    inst = instances.dense_lp(64, 128, 4)
+    a = GlpProb.from_instance(oracle, inst)
+    b = GlpProb.from_instance(product, inst)
+    c = GlpProb.from_instance(product, inst)
+    assert a.simplex() == 0 and b.simplex() == 0
+    l0 = product.mvb_kernel_launches()
+    assert product.mvb_glp_use_shards(None, 3, 1) == 0
+    try:
+        assert c.simplex() == 0
+        launched = product.mvb_kernel_launches() - l0
+        # an LP that does not qualify (needs phase 1) stays on the single-GPU path
+        g = GlpProb.from_instance(product, instances.general_lp(20, 30, 12))
+        go = GlpProb.from_instance(oracle, instances.general_lp(20, 30, 12))
+        assert g.simplex() == 0 and go.simplex() == 0 and g.obj_val() == go.obj_val()
+    finally:
+        product.mvb_glp_use_shards(None, 0, 0)
+    its = product.glp_get_it_cnt(b.h)
+    assert launched >= 3 * 3 * its  # price / decide / update per shard and pivot: the sharded kernels ran
+    assert product.glp_get_it_cnt(c.h) == its == oracle.glp_get_it_cnt(a.h)
+    assert a.status() == b.status() == c.status() == capi.GLP_OPT
+    assert a.obj_val() == b.obj_val() == c.obj_val()
+    assert np.array_equal(a.col_prim(), c.col_prim())
+    for j in range(1, 129):
+        assert product.glp_get_col_stat(c.h, j) == oracle.glp_get_col_stat(a.h, j)
+    for i in range(1, 65):
+        assert product.glp_get_row_stat(c.h, i) == oracle.glp_get_row_stat(a.h, i)
+        assert product.glp_get_row_prim(c.h, i) == oracle.glp_get_row_prim(a.h, i)
