@@ -373,8 +373,12 @@ __device__ void cres_solve(const LPDev &L, CresCtx *S, int C, unsigned rank) {
       const int owner = (r - 1) / RB;
       const int rloc = owner == (int)rank ? r - g0 + 1 : -1;
       const int degen1 = tmin == 0.0 ? degen0 + 1 : 0;
-      for (int i = 1 + tid; i <= nloc; i += NT) beta[i] = i == rloc ? newbr : fma(col[i], delta, beta[i]);
+      for (int i = 1 + tid; i <= nloc; i += NT) {
+        beta[i] = i == rloc ? newbr : fma(col[i], delta, beta[i]);
+        if (i != rloc) T[(size_t)i * lds + q] = 0.0;  // column q enters the update as 0 (smem_tile_update)
+      }
       if (tid == 0) {
+        T[q] = 0.0;
         // arm the rho barrier for this iteration's arrival
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(barR)), "r"(rho_bytes) : "memory");
         res_tally_to(S->ty, L, mode, r, q, bland, rank == 0);
@@ -490,11 +494,12 @@ __device__ void cres_solve(const LPDev &L, CresCtx *S, int C, unsigned rank) {
       const int kout = win.var;
       const int atq = lr == ur ? MVB_AT_FX : (rs < 0 ? MVB_AT_LB : MVB_AT_UB);
       // pivot column from this CTA's rows (not yet updated), beta
-      if (tid == 0) col[0] = T[q];
+      if (tid == 0) { col[0] = T[q]; T[q] = 0.0; }
       for (int i = 1 + tid; i <= nloc; i += NT) {
         const double v = T[(size_t)i * lds + q];
         col[i] = v;
         beta[i] = i == rloc ? newbr : fma(v, delta, beta[i]);
+        if (i != rloc) T[(size_t)i * lds + q] = 0.0;  // column q enters the update as 0 (smem_tile_update)
       }
       if (tid == 32) {
         nbv[q] = kout;

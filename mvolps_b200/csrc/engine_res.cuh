@@ -116,9 +116,11 @@ __device__ int res_dual_select(const ResLay &l, int m, bool bland, int par) {
 // K4 in shared memory on a tile of rows 0..nrow (row 0 = reduced costs): T'[i][j] = fma(col[i],
 // rho[j], j == q ? 0 : T[i][j]), row rloc <- rho (rloc < 0: the pivot row is not in this tile).
 // Thread (tx, ty) owns the column pairs {ch * CW + 2 tx} and the rows ty, ty + trows, ...  The
-// main loop is the plain fma on every element (six instructions per row and column pair); the two
-// special cases -- column q reads its old value as 0, row rloc becomes rho -- are rewritten
-// afterwards by the very thread that owns those elements, so the results are the specification's.
+// main loop is the plain fma on every element (six instructions per row and column pair).  The two
+// special cases of the specification are taken out of it: column q reads its old value as 0 --
+// the CALLER has stored 0.0 into T[i][q] of every row but the pivot row after copying the column
+// out (each row by the thread that copied it), so the plain fma yields exactly fma(c, rho_q, 0);
+// the pivot row becomes rho -- rewritten after the loop by the thread that owns that element.
 // PRICE: the threads that own row 0 price their columns for the next iteration (position q is
 // taken from registers: kout / atq) and return their best key.
 template <bool PRICE>
@@ -157,12 +159,6 @@ __device__ __forceinline__ Key smem_tile_update(double *T, unsigned lds, int nro
       o.x = fma(c, rho.x, t.x);
       o.y = fma(c, rho.y, t.y);
       *reinterpret_cast<double2 *>(p) = o;
-    }
-    // column q of this thread's rows: the old value counts as 0 (exactly fma(c, rho_q, 0))
-    if (c0 == q || c0 + 1 == q) {
-      const double rq = c0 == q ? rho.x : rho.y;
-      double *pq = T + (size_t)ty * lds + q;
-      for (int k = ty; k <= nrow; k += trows, pq += step) *pq = fma(col[k], rq, 0.0);
     }
     // the pivot row becomes rho
     if (rloc >= 0 && (rloc - ty) % trows == 0 && rloc >= ty)
@@ -383,7 +379,11 @@ __device__ void res_solve(const LPDev &L, ResCtx *S) {
       const double inv = 1.0 / colr;
       const double delta = dir > 0 ? tmin : -tmin;
       const double newbr = nb_value(fq, lq, uq) + delta;
-      for (int i = 1 + tid; i <= m; i += NT) beta[i] = i == r ? newbr : fma(col[i], delta, beta[i]);
+      for (int i = 1 + tid; i <= m; i += NT) {
+        beta[i] = i == r ? newbr : fma(col[i], delta, beta[i]);
+        if (i != r) T[(size_t)i * lds + q] = 0.0;  // column q enters the update as 0 (smem_tile_update)
+      }
+      if (tid == 0) T[q] = 0.0;
       {  // K3: scaled pivot row
         const double *row = T + (size_t)r * lds;
         for (int j = tid; j < ld; j += NT) rho[j] = j == q ? inv : -(row[j] * inv);
@@ -448,11 +448,12 @@ __device__ void res_solve(const LPDev &L, ResCtx *S) {
       const double delta = (target - br) / alpha;
       const double newbr = nb_value(fq, lq, uq) + delta;
       // pivot column copy + beta + K3; nothing of the tableau is written before the barrier
-      if (tid == 0) col[0] = T[q];
+      if (tid == 0) { col[0] = T[q]; T[q] = 0.0; }
       for (int i = 1 + tid; i <= m; i += NT) {
         const double v = T[(size_t)i * lds + q];
         col[i] = v;
         beta[i] = i == r ? newbr : fma(v, delta, beta[i]);
+        if (i != r) T[(size_t)i * lds + q] = 0.0;  // column q enters the update as 0 (smem_tile_update)
       }
       for (int j = tid; j < ld; j += NT) rho[j] = j == q ? inv : -(row[j] * inv);
       const int degen1 = degenerate ? degen0 + 1 : 0;
