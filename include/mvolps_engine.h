@@ -24,6 +24,8 @@
 #ifndef MVOLPS_ENGINE_H
 #define MVOLPS_ENGINE_H
 
+#include <stddef.h>
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -112,6 +114,9 @@ void mvb_lp_free(mvb_lp *lp);
  * A: m*n row-major; cost: n (internal min form); lb/ub: n+m by variable id */
 int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost,
                 const double *lb, const double *ub);
+/* a host buffer of at least `bytes` bytes the caller may build A in before mvb_lp_load (CUDA: pinned
+ * memory, so the upload is one DMA; reused by the next call, valid until then).  NULL: use your own */
+void *mvb_host_staging(size_t bytes);
 /* deep copy incl. tableau, basis and bounds (device-to-device on CUDA) */
 mvb_lp *mvb_lp_clone(const mvb_lp *src);
 /* same, into an existing object of equal (n, row capacity >= src m) */

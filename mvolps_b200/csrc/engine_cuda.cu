@@ -736,6 +736,7 @@ struct DeviceCtx {
   unsigned *ctrs = nullptr; int ctrs_cap = 0;
   LPDev *dlps = nullptr; int dlps_cap = 0;
   char *stage = nullptr; size_t stage_cap = 0;   // device staging (row gathers, new rows)
+  void *h_stage = nullptr; size_t h_stage_cap = 0;  // pinned host staging handed out by mvb_host_staging
   // per-launch arenas: bound patches go up and all outboxes come back in ONE copy each
   char *d_out = nullptr, *h_out = nullptr; size_t out_cap = 0;
   BoundPatch *d_patch = nullptr, *h_patch = nullptr; size_t patch_cap = 0;
@@ -1099,6 +1100,18 @@ void mvb_lp_free(mvb_lp *lp) {
   if (!lp) return;
   lp_release(lp);
   delete lp;
+}
+
+void *mvb_host_staging(size_t bytes) {
+  if (!ctx_init(-1)) return nullptr;
+  if (g_ctx.h_stage_cap < bytes) {
+    if (g_ctx.h_stage) cudaFreeHost(g_ctx.h_stage);
+    g_ctx.h_stage = nullptr;
+    g_ctx.h_stage_cap = 0;
+    if (cudaMallocHost(&g_ctx.h_stage, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    g_ctx.h_stage_cap = bytes;
+  }
+  return g_ctx.h_stage;
 }
 
 int mvb_lp_dims(const mvb_lp *lp, int *m, int *n) {

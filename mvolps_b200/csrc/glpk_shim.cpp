@@ -399,14 +399,26 @@ static int sync_engine_delta(glp_prob *P, bool *changed) {
       if (P->eng) mvb_lp_free(P->eng);
       P->eng = mvb_lp_create(m, n, m + 32 + m / 8);
       if (!P->eng) return -1;
-      std::vector<double> A((size_t)m * n, 0.0), cost(n);
+      // dense A built straight into the engine's (pinned) staging buffer: the upload is one DMA
+      std::vector<double> own, cost(n);
+      double *A = (double *)mvb_host_staging((size_t)m * n * sizeof(double));
+      if (!A) { own.resize((size_t)m * n); A = own.data(); }
       for (int i = 0; i < m; i++) {
         const MvRowM &r = P->rowm[i];
-        for (size_t t = 0; t < r.ind.size(); t++) A[(size_t)i * n + r.ind[t] - 1] = r.val[t];
+        double *row = A + (size_t)i * n;
+        const int len = (int)r.ind.size();
+        const int *ind = r.ind.data();
+        const double *val = r.val.data();
+        if (len == n) {  // a dense row lists every column, ascending: a straight copy
+          std::memcpy(row, val, (size_t)n * sizeof(double));
+        } else {
+          std::memset(row, 0, (size_t)n * sizeof(double));
+          for (int t = 0; t < len; t++) row[ind[t] - 1] = val[t];
+        }
       }
       for (int j = 0; j < n; j++)
         cost[j] = P->dir == GLP_MAX ? -P->colm[j].coef : P->colm[j].coef;
-      if (mvb_lp_load(P->eng, A.data(), cost.data(), lb.data(), ub.data())) return -1;
+      if (mvb_lp_load(P->eng, A, cost.data(), lb.data(), ub.data())) return -1;
     }
     P->eng_rows = m;
     P->eng_stale = false;

@@ -128,6 +128,7 @@ int main(int argc, char **argv) {
     std::FILE *f = std::fopen(in.get("-ev").c_str(), "w");
     if (!f) { std::fprintf(stderr, "cannot write %s\n", in.get("-ev").c_str()); return -1; }
     std::fputs(mvb_bnb_event_text(h), f);
+    std::fputs("END", f);  // ~IPCDispatch closes its stream with this token (message.h:230-236)
     std::fclose(f);
   }
   if (!in.has("-s") && !in.has("--silent")) {

@@ -114,6 +114,17 @@ void mvb_lp_free(mvb_lp *lp) {
   free(lp);
 }
 
+void *mvb_host_staging(size_t bytes) {
+  static __thread void *buf;
+  static __thread size_t cap;
+  if (cap < bytes) {
+    free(buf);
+    buf = malloc(bytes);
+    cap = buf ? bytes : 0;
+  }
+  return buf;
+}
+
 int mvb_lp_dims(const mvb_lp *lp, int *m, int *n) {
   if (m) *m = lp->m;
   if (n) *n = lp->n;
