@@ -357,6 +357,10 @@ def main():
         hargs.root_heuristic = True
         bh = X.run_bnb(hargs, L, rank, world, local, dist, ClockSampler, peaks, steps=1, warmup=1, comm=comm,
                        cpu_baseline=False)
+        c3 = argparse.Namespace(**vars(args))  # configs[3] node-LP shape: frontier batches of 4096 LPs of 256 x 512
+        c3.m, c3.n, c3.batch_width, c3.nodes = 256, 512, 4096, 8192
+        b3 = X.run_bnb(c3, L, rank, world, local, dist, ClockSampler, peaks, steps=1, warmup=1, comm=comm,
+                       cpu_baseline=False)
         close = X.run_bnb_close(args, L, rank, world, local, dist, comm=comm)
         if comm is not None:
             L.mvb_comm_free(comm)
@@ -369,9 +373,10 @@ def main():
             line["bnb"] = bn
             line["bnb"]["with_gmi_cuts"] = {k: bc[k] for k in ("value", "unit", "ms_per_step", "config", "gpu_launches")}
             line["bnb"]["with_root_heuristic"] = {k: bh[k] for k in ("value", "unit", "ms_per_step", "config")}
+            line["bnb"]["configs3_shape"] = {k: b3[k] for k in ("value", "unit", "ms_per_step", "config", "gpu_launches")}
             line["bnb"]["time_to_optimum"] = close
             line["legs_wall_s"] = time.perf_counter() - t_legs
-            line["gpu_launches_legs"] = sh["gpu_launches"] + bn["gpu_launches"] + bc["gpu_launches"]
+            line["gpu_launches_legs"] = sh["gpu_launches"] + bn["gpu_launches"] + bc["gpu_launches"] + b3["gpu_launches"]
     if rank != 0:
         return
     if not args.no_cpu_baseline and world == 1:

@@ -233,7 +233,8 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks, steps=None, 
                                + (f" at frequency {args.cut_freq}" if args.cut_freq != 1.0 else "")
                                + f", batch width {args.batch_width}"
                                + (", root rounding heuristic" if args.root_heuristic else "")
-                               + " (BASELINE configs[2]); host wall clock around mvb_bnb_run[_dist] (host logic + "
+                               + (" (BASELINE configs[3] node-LP shape)" if (args.n, args.m) == (512, 256) else
+                                  " (BASELINE configs[2])") + "; host wall clock around mvb_bnb_run[_dist] (host logic + "
                                "H2D/D2H included)"
                                + ("" if world == 1 else
                                   ("; one tree, round-synchronous sequence-identical mode" if args.dist_mode == 1 else

@@ -40,12 +40,16 @@ def main():
     old = json.load(open(OUT)) if os.path.exists(OUT) else {}
     g = {"generator": "tests/golden/make_bench_golden.py (CPU oracle)"}
 
-    lp = EngineLP.from_instance(orc, instances.dense_lp(1024, 2048, 1234))
-    r = lp.solve(threads=8)
-    g["dense"] = {"1024x2048_s1234": {"pivot_hash": str(r["pivot_hash"]), "pivots": r["pivots"], "obj_hex": float(r["obj"]).hex()}}
+    only_c3 = "--only-c3" in sys.argv
+    if only_c3:
+        g["dense"] = old["dense"]
+    else:
+        lp = EngineLP.from_instance(orc, instances.dense_lp(1024, 2048, 1234))
+        r = lp.solve(threads=8)
+        g["dense"] = {"1024x2048_s1234": {"pivot_hash": str(r["pivot_hash"]), "pivots": r["pivots"], "obj_hex": float(r["obj"]).hex()}}
     print("dense", g["dense"], flush=True)
 
-    if "--skip-shard" in sys.argv and "shard" in old:
+    if (only_c3 or "--skip-shard" in sys.argv) and "shard" in old:
         g["shard"] = old["shard"]
     else:
         lp = EngineLP.from_instance(orc, instances.dense_lp(16384, 32768, 5))
@@ -58,18 +62,26 @@ def main():
     print("shard", g["shard"], flush=True)
 
     g["bnb"] = {}
-    inst = instances.mdkp(200, 50, 2024)
-    for cm, rh, nodes in ((0, 0, 80000), (2, 0, 20000), (0, 1, 80000), (0, 0, 10000), (2, 0, 10000)):
-        out = GlpProb.from_instance(orc, inst).bnb(cut_mode=cm, root_heuristic=rh, max_iters=nodes, batch_width=256,
+    # (vars, rows, batch width, cut mode, root heuristic, node budget); the 512 x 256 line is the
+    # BASELINE configs[3] node-LP shape (frontier batches of 4096 node LPs)
+    runs = ((200, 50, 256, 0, 0, 80000), (200, 50, 256, 2, 0, 20000), (200, 50, 256, 0, 1, 80000),
+            (200, 50, 256, 0, 0, 10000), (200, 50, 256, 2, 0, 10000), (512, 256, 4096, 0, 0, 8192))
+    if "--only-c3" in sys.argv:
+        g = old
+        runs = runs[-1:]
+    for nv, nr, bw, cm, rh, nodes in runs:
+        inst = instances.mdkp(nv, nr, 2024)
+        out = GlpProb.from_instance(orc, inst).bnb(cut_mode=cm, root_heuristic=rh, max_iters=nodes, batch_width=bw,
                                                    total_budget=1)
-        key = f"mdkp_200x50_s2024_bs0_cm{cm}_rh{rh}_n{nodes}"
+        key = f"mdkp_{nv}x{nr}_s2024_bs0_cm{cm}_rh{rh}_n{nodes}"
         g["bnb"][key] = {"event_hash": str(out["event_hash"]), "iterations": out["iterations"],
                          "incumbent": out["incumbent"], "has_incumbent": out["has_incumbent"], "oids": out["oids"]}
         print(key, g["bnb"][key], flush=True)
 
-    out = GlpProb.from_instance(orc, instances.mdkp(30, 8, 4)).bnb()
-    g["bnb_close"] = {"mdkp_30x8_s4": {"incumbent": out["incumbent"], "iterations": out["iterations"],
-                                      "event_hash": str(out["event_hash"])}}
+    if not only_c3:
+        out = GlpProb.from_instance(orc, instances.mdkp(30, 8, 4)).bnb()
+        g["bnb_close"] = {"mdkp_30x8_s4": {"incumbent": out["incumbent"], "iterations": out["iterations"],
+                                          "event_hash": str(out["event_hash"])}}
     print(g["bnb_close"], flush=True)
     with open(OUT, "w") as f:
         json.dump(g, f, indent=1, sort_keys=True)
