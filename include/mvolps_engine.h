@@ -149,6 +149,19 @@ int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out);
  * those of LP k-1 in `rows`, its rows (n_k doubles each) follow those of LP k-1 in `out` */
 int mvb_lp_get_tab_rows_batch(mvb_lp *const *lps, int count, const int *rows, const int *nrows,
                               double *out);
+/* mvb_lp_get_tab_rows for callers that may not allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+ * reference.  Same arguments and result as
+ * mvb_lp_get_tab_rows; the row numbers and the gathered rows are staged in ONE static device array
+ * of MVB_NOALLOC_SCRATCH_BYTES bytes (held by every GPU that loads the library until the process
+ * ends), so the call makes no cudaMalloc / cudaFree / allocating library call.  It fails with a
+ * message in mvb_last_error() when align256(4*nrows) + 8*nrows*n exceeds that size (e.g. more
+ * than 255 rows of a 512-column LP), or while clones / cut rows are still queued on the engine
+ * (carrying them out may allocate: mvb_solve_batch or mvb_lp_get_tab_rows does it).  All calls
+ * share the array and it keeps the last call's contents: calls that overlap on the GPU (several
+ * host threads) race -- serialise them. */
+#define MVB_NOALLOC_SCRATCH_BYTES (1 << 20)
+int mvb_lp_get_tab_rows_noalloc(mvb_lp *lp, const int *rows, int nrows, double *out);
 /* whole current tableau ((m+1)*n) and beta (m+1, [0] unused); parity tests */
 int mvb_lp_get_tableau(mvb_lp *lp, double *T, double *beta);
 /* copies up to cap (row,col) pairs of the last solve; returns total logged */

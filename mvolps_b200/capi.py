@@ -41,7 +41,7 @@ ENGINE_SYMBOLS = [
     "mvb_timer_record", "mvb_timer_elapsed_ms", "mvb_flush_l2", "mvb_last_launch", "mvb_last_kernel_ms", "mvb_last_kernel_mode", "mvb_engine_option",
     "mvb_host_staging", "mvb_lp_create", "mvb_lp_free", "mvb_lp_load", "mvb_lp_clone", "mvb_lp_assign",
     "mvb_lp_dims", "mvb_lp_set_bounds", "mvb_lp_append_row", "mvb_solve_batch",
-    "mvb_lp_get_primal", "mvb_lp_get_basis", "mvb_lp_get_tab_rows", "mvb_lp_get_tab_rows_batch",
+    "mvb_lp_get_primal", "mvb_lp_get_basis", "mvb_lp_get_tab_rows", "mvb_lp_get_tab_rows_batch", "mvb_lp_get_tab_rows_noalloc",
     "mvb_lp_get_tableau", "mvb_lp_get_pivot_log",
 ]
 BNB_SYMBOLS = [
@@ -163,6 +163,7 @@ def _bind(lib):
         "mvb_lp_get_basis": (C.c_int, [_P, _ip, _ip, _ip]),
         "mvb_lp_get_tab_rows": (C.c_int, [_P, _ip, C.c_int, _dp]),
         "mvb_lp_get_tab_rows_batch": (C.c_int, [C.POINTER(_P), C.c_int, _ip, _ip, _dp]),
+        "mvb_lp_get_tab_rows_noalloc": (C.c_int, [_P, _ip, C.c_int, _dp]),
         "mvb_lp_get_tableau": (C.c_int, [_P, _dp, _dp]),
         "mvb_lp_get_pivot_log": (C.c_int, [_P, _ip, C.c_int]),
         "mvb_bnb_run": (_P, [_P, C.POINTER(BnbParams)]),

@@ -1675,6 +1675,83 @@ int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
   return mvb_lp_get_tab_rows_batch(&lp, 1, rows, &nrows, out);
 }
 
+}  // extern "C"
+
+// ---- mvb_lp_get_tab_rows_noalloc: K7 with its staging in a static device array --------------------
+// For callers that may not allocate (CUDA graph capture around them, tight serving loops, harnesses
+// that forbid cudaMalloc).  gather_rows_kernel stages its job list and the gathered rows in a
+// device buffer the engine grows on demand (ensure_stage -> cudaMallocAsync) and in pinned host
+// memory (cudaMallocHost); this variant keeps both in ONE file-scope device array of a fixed size:
+// no cudaMalloc*, cudaFree* or allocating library routine on its path.  Every GPU that loads the
+// library holds the array until the process ends.  All calls share it and it keeps the previous
+// call's contents (nothing in it has to start at zero: the row numbers and every gathered double
+// of a call are written before they are read), so calls that overlap on the GPU race.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[MVB_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int MVB_NOALLOC_MAX_DEVICES = 64;
+// device addresses of g_noalloc_scratch, one per device ordinal.  In host code the array's NAME is
+// a host-side stand-in, not a device address: the kernel gets what cudaGetSymbolAddress returns
+// with that device current.
+unsigned char *g_noalloc_ptr[MVB_NOALLOC_MAX_DEVICES] = {};
+
+// row job blockIdx.x: row rows[blockIdx.x] of the tableau T (row stride ld) -> dst[blockIdx.x * n ...]
+__global__ void gather_rows_noalloc_kernel(const double *T, int ld, int n, const int *rows, double *dst) {
+  const double *src = T + (size_t)rows[blockIdx.x] * ld;
+  double *d = dst + (size_t)blockIdx.x * n;
+  for (int c = threadIdx.x; c < n; c += blockDim.x) d[c] = src[c];
+}
+
+}  // namespace
+
+extern "C" int mvb_lp_get_tab_rows_noalloc(mvb_lp *lp, const int *rows, int nrows, double *out) {
+  if (!lp || !g_ctx.ready) { g_err = "mvb_lp_get_tab_rows_noalloc: engine not initialised"; return -1; }
+  if (nrows < 0) { g_err = "mvb_lp_get_tab_rows_noalloc: negative row count"; return -1; }
+  if (nrows == 0) return 0;
+  if (!rows || !out) { g_err = "mvb_lp_get_tab_rows_noalloc: null rows / out"; return -1; }
+  if (!g_ctx.append_jobs.empty() || !g_ctx.clone_jobs.empty()) {
+    // carrying out queued cut rows / clones may grow the engine's job buffers (an allocation)
+    g_err = "mvb_lp_get_tab_rows_noalloc: queued clones or cut rows are pending; run mvb_solve_batch or "
+            "mvb_lp_get_tab_rows first";
+    return -1;
+  }
+  const size_t rb = align_up((size_t)nrows * sizeof(int), 256), ob = (size_t)nrows * lp->n * sizeof(double);
+  if (rb + ob > (size_t)MVB_NOALLOC_SCRATCH_BYTES) {
+    g_err = "mvb_lp_get_tab_rows_noalloc: " + std::to_string(nrows) + " rows of " + std::to_string(lp->n) +
+            " columns need " + std::to_string(rb + ob) + " bytes of staging, the static scratch holds " +
+            std::to_string((size_t)MVB_NOALLOC_SCRATCH_BYTES) + " (MVB_NOALLOC_SCRATCH_BYTES); use mvb_lp_get_tab_rows";
+    return -1;
+  }
+  for (int r = 0; r < nrows; r++)
+    if (rows[r] < 0 || rows[r] > lp->m) { g_err = "mvb_lp_get_tab_rows_noalloc: row out of range"; return -1; }
+  const int dev = g_ctx.device;
+  if (dev < 0 || dev >= MVB_NOALLOC_MAX_DEVICES) { g_err = "mvb_lp_get_tab_rows_noalloc: device ordinal out of range"; return -1; }
+  if (!g_noalloc_ptr[dev]) {  // set-up, once per device, with that device current
+    int cur = -1;
+    CKI(cudaGetDevice(&cur));
+    if (cur != dev) CKI(cudaSetDevice(dev));
+    unsigned char *ptr = nullptr;
+    CKI(cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch));
+    if (!ptr) { g_err = "mvb_lp_get_tab_rows_noalloc: cudaGetSymbolAddress returned null"; return -1; }
+    g_noalloc_ptr[dev] = ptr;
+  }
+  unsigned char *scratch = g_noalloc_ptr[dev];
+  cudaStream_t st = g_ctx.stream;
+  int *drows = (int *)scratch;
+  double *dout = (double *)(scratch + rb);
+  // pageable source and destination: the driver stages them itself, nothing is allocated here
+  CKI(cudaMemcpyAsync(drows, rows, (size_t)nrows * sizeof(int), cudaMemcpyHostToDevice, st));
+  gather_rows_noalloc_kernel<<<(unsigned)nrows, 128, 0, st>>>(lp->dev.T[lp->curT], lp->ld, lp->n, drows, dout);
+  CKI(cudaGetLastError());
+  g_launches++;
+  CKI(cudaMemcpyAsync(out, dout, ob, cudaMemcpyDeviceToHost, st));
+  CKI(cudaStreamSynchronize(st));
+  return 0;
+}
+
+extern "C" {
+
 int mvb_lp_get_tableau(mvb_lp *lp, double *T, double *beta) {
   if (!flush_clones()) return -1;
   cudaStream_t st = g_ctx.stream;

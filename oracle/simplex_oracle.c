@@ -612,6 +612,13 @@ int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
   return 0;
 }
 
+/* CUDA-only entry point (static device scratch); the CPU oracle has none: always fails */
+int mvb_lp_get_tab_rows_noalloc(mvb_lp *lp, const int *rows, int nrows, double *out) {
+  (void)lp; (void)rows; (void)nrows; (void)out;
+  set_err("mvb_lp_get_tab_rows_noalloc: CUDA engine only");
+  return -1;
+}
+
 int mvb_lp_get_tab_rows_batch(mvb_lp *const *lps, int count, const int *rows, const int *nrows,
                               double *out) {
   for (int k = 0; k < count; k++) {
