@@ -17,9 +17,15 @@
  *     single-GPU engine (mvolps_engine.h) and therefore to the oracle.
  *     It stands behind the same reference call as the single-GPU path:
  *     glp_simplex (bs.cpp:117,279,287).
- *     Restrictions of this path: primal phase 2 from the slack basis (every
- *     non-basic variable at value 0 and the slack basis primal feasible, as in
- *     configs[1]/[4]); anything else is rejected with an error.
+ *     Restrictions of this path: it starts from the slack basis with every
+ *     non-basic variable at value 0 and runs primal phase 2 when that basis is
+ *     primal feasible (configs[1]/[4]) or the dual simplex when it is dual
+ *     feasible instead (covering rows: K5a on the replicated basic values, K5b
+ *     over the local columns of the leaving row, the same record exchange),
+ *     or the composite phase 1 followed by phase 2 when it is neither (the
+ *     infeasibility costs of a rank's columns need no exchange: all rows of
+ *     a column live on its rank).  Non-zero non-basic start values are
+ *     rejected with an error (mvb_shard_start_mode tells in advance).
  *
  * (2) Open B&B nodes SHARDED across GPUs: node LPs are independent, so each
  *     rank solves its own nodes with mvb_solve_batch; the only exchange is
@@ -77,6 +83,13 @@ typedef struct mvb_shard mvb_shard;
  * columns [col0, col0+ncols) = mvb_shard_partition(n_global, comm->world, comm->rank) */
 mvb_shard *mvb_shard_create(int m, int n_global, int col0, int ncols, const mvb_comm *comm);
 void mvb_shard_free(mvb_shard *s);
+/* which simplex the column-sharded path would run from the slack basis of this LP (cost: n, internal
+ * min form; lb/ub: n + m by variable id): MVB_MODE_PRIMAL2 (slack basis primal feasible), MVB_MODE_DUAL
+ * (not primal but dual feasible: covering rows, B&B-style right-hand sides), MVB_MODE_PRIMAL1 (neither:
+ * composite phase 1, then phase 2), 0 = not eligible (non-zero non-basic values: one GPU), by the rule of
+ * the single-GPU engine's mode selection.  What glp_simplex asks before it routes an
+ * LP to the shard group (bs.cpp:117). */
+int mvb_shard_start_mode(int m, int n, const double *cost, const double *lb, const double *ub);
 /* A_local: m x ncols row-major (the shard's columns of A); cost_local: ncols
  * (internal min form); lb/ub: n_global + m by variable id (replicated) */
 int mvb_shard_load(mvb_shard *s, const double *A_local, const double *cost_local,

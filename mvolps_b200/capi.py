@@ -53,7 +53,7 @@ DIST_SYMBOLS = [  # include/mvolps_dist.h: exported by the product only
     "mvb_incumbent_exchange",
     "mvb_shard_create", "mvb_shard_free", "mvb_shard_load", "mvb_shard_solve",
     "mvb_shard_get_primal", "mvb_shard_get_basis", "mvb_shard_get_pivot_log", "mvb_shard_last_ms", "mvb_shard_last_exchange",
-    "mvb_glp_use_shards",
+    "mvb_glp_use_shards", "mvb_shard_start_mode",
 ]
 ALL_SYMBOLS = GLPK_SYMBOLS + GLPK_EXTRA_SYMBOLS + ENGINE_SYMBOLS + BNB_SYMBOLS
 
@@ -197,6 +197,7 @@ def _bind(lib):
         "mvb_shard_last_exchange": (C.c_int, [_P]),
         "mvb_shard_get_basis": (C.c_int, [_P, _ip, _ip, _ip]),
         "mvb_glp_use_shards": (C.c_int, [_P, C.c_int, C.c_longlong]),
+        "mvb_shard_start_mode": (C.c_int, [C.c_int, C.c_int, _dp, _dp, _dp]),
     }
     if hasattr(lib, "mvb_shard_create"):  # the oracle build has no multi-GPU layer
         for name, (res, args) in dist.items():

@@ -31,7 +31,14 @@
 namespace {
 
 constexpr int PS_CREG = 8;            // pivot-column values a thread can hold in flight
-constexpr int LZ_KMAX = 8;            // most pending pivots between two flush passes (12 measured: no gain)
+#ifndef MVB_LZ_KMAX
+#define MVB_LZ_KMAX 8
+#endif
+#ifndef MVB_LZ_UN_DEEP
+#define MVB_LZ_UN_DEEP 2
+#endif
+constexpr int LZ_KMAX = MVB_LZ_KMAX;  // most pending pivots between two flush passes (<= 16: two qmask bits each)
+static_assert(LZ_KMAX >= 1 && LZ_KMAX <= 16, "LZ_KMAX");
 constexpr int MVB_PS_FALLBACK = 100;  // DevResult status: needs the general kernel
 constexpr int MVB_PS_HANDOVER = 101;  // DevResult status of the general kernel: phase 1 has reached a primal
                                       // feasible basis, phase 2 goes to the private-state kernel
@@ -285,7 +292,7 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
   // path 4 % (register pressure), so it is not here; staging the reads through a 32-48 KB TMA ring
   // (twice the bytes in flight, depth 6 to make room) measured 6-9 % SLOWER than this register path
   // at depth 8: during the flush the batch already runs HBM at ~70 % of its copy peak
-  constexpr int UN = KC <= 4 ? 8 : 4;
+  constexpr int UN = KC <= 4 ? 8 : KC <= 8 ? 4 : MVB_LZ_UN_DEEP;
   while (u0 < u1) {
     const int ch = (int)(u0 / (unsigned)R);
     const int ia = (int)(u0 - (unsigned)ch * (unsigned)R);
@@ -348,7 +355,23 @@ __device__ __forceinline__ void lz_flush(LZS *S) {
     case 5: lz_flush_k<5>(S); break;
     case 6: lz_flush_k<6>(S); break;
     case 7: lz_flush_k<7>(S); break;
+#if MVB_LZ_KMAX > 8
+    case 8: lz_flush_k<8>(S); break;
+    case 9: lz_flush_k<9>(S); break;
+    case 10: lz_flush_k<10>(S); break;
+    case 11: lz_flush_k<11>(S); break;
+    case 12: lz_flush_k<12>(S); break;
+#if MVB_LZ_KMAX > 12
+    case 13: lz_flush_k<13>(S); break;
+    case 14: lz_flush_k<14>(S); break;
+    case 15: lz_flush_k<15>(S); break;
+    default: lz_flush_k<16>(S); break;
+#else
+    default: lz_flush_k<12>(S); break;
+#endif
+#else
     default: lz_flush_k<8>(S); break;
+#endif
   }
   __syncthreads();  // all stores of this CTA issued
   if (threadIdx.x == 0) {

@@ -39,6 +39,9 @@ struct ShardCtl {
   int cur, cS;  // tableau buffer that holds the current tableau once the pending update landed; small-state parity
   int pend;     // 1: the update of the previous iteration (step[par ^ 1]) may still be running on the
                 // update stream, readers take the other buffer and apply that step on the fly
+  int mode;     // MVB_MODE_PRIMAL2 / MVB_MODE_DUAL (neither changes mode) or MVB_MODE_PRIMAL1, which becomes
+                // PRIMAL2 when the decide kernel finds the NEXT basis primal feasible
+  int it1;      // iterations spent in phase 1
   unsigned long long hash;
 };
 
@@ -46,6 +49,7 @@ struct Cand {  // header of one exchange record; the column (m+1 doubles) follow
   unsigned long long key;  // ~bits(|d_q|), 0 under Bland's rule, ~0: no eligible column
   int var, pos, flag, pad;
   double lq, uq;
+  double dq;  // the cost the column was priced on (phase 1: the infeasibility cost d1_q; else T[0][q])
 };
 constexpr size_t SHARD_HDR = 64;
 
@@ -73,6 +77,8 @@ struct ShardDev {
   ShardCtl *ctl;    // [2] by iteration parity
   ShardStep *step;  // [2] by iteration parity
   double *rho[2];   // scaled pivot row over the local columns, by iteration parity
+  double *p1part;   // phase 1: partial column sums, ceil(m / MVB_P1_CHUNK) x ld (as LPDev::p1part)
+  double *d1;       // phase 1: infeasibility costs of the local columns (ld)
   unsigned char *send, *recv[SHARD_SLOTS];  // recv[slot]: world records, by sender rank
   size_t rec_bytes;
   // peer exchange (nullptr / 0 when the host copies or NCCL moves the records)
@@ -122,6 +128,9 @@ __device__ __forceinline__ ShardView shard_view(const ShardDev &D, const ShardCt
   return v;
 }
 
+__device__ void shard_emit_record(const ShardDev &D, const ShardView &V, int slot, const Key best, const int *at,
+                                  double dq);
+
 // K1 over the local columns + gather of the winning column into the send
 // record.  Every CTA of the (small) grid repeats the cheap argmin over the
 // local reduced costs and then gathers its own slice of the column rows, so the
@@ -132,19 +141,67 @@ __global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int pa
   if (c.status != -1) return;  // finished on every rank alike: nobody waits for a record
   const ShardView V = shard_view(D, c, par);
   const bool bland = c.degen >= MVB_BLAND_AFTER;
+  const bool phase1 = c.mode == MVB_MODE_PRIMAL1;  // costs = D.d1 (shard_p1_* kernels of this iteration)
   const int *at = D.at[c.cS], *nb = D.nb[c.cS];
   Key best = key_none();
   for (int j = threadIdx.x; j < D.nloc; j += blockDim.x) {
     const int f = at[j];
     if (f == MVB_AT_FX) continue;
-    const double dj = V.at(0, j);
+    const double dj = phase1 ? ldcg(D.d1 + j) : V.at(0, j);
     if (!dj_eligible(f, dj)) continue;
     const Key k{bland ? 0ULL : ~dbits(fabs(dj)), nb[j], j};
     if (key_less(k, best)) best = k;
   }
   best = block_argmin(best, red);  // result on every thread, identical in every CTA
+  shard_emit_record(D, V, slot, best, at, best.idx >= 0 ? (phase1 ? ldcg(D.d1 + best.idx) : V.at(0, best.idx)) : 0.0);
+}
+
+// ---- composite phase 1 on the shards: the infeasibility costs d1_j = sum_i sign_i * T_ij of the
+// LOCAL columns (all rows of a column live on its rank: no exchange), summed in the order of the
+// specification: 32-row chunks in row order, then the chunk sums in order (p1_partials / p1_cost
+// of the general loop).  Two small-state-free kernels in front of the price kernel, no-ops once
+// the solve has left phase 1.
+__global__ void __launch_bounds__(256) shard_p1_partials_kernel(ShardDev D, int par) {
+  const ShardCtl c = D.ctl[par];
+  if (c.status != -1 || c.mode != MVB_MODE_PRIMAL1) return;
+  const ShardView V = shard_view(D, c, par);
+  const double *b = D.beta[c.cS];
+  const int *h = D.head[c.cS];
+  const int m = D.m, n = D.nloc, ld = D.ld;
+  const int nchunks = (m + MVB_P1_CHUNK - 1) / MVB_P1_CHUNK;
+  const long long items = (long long)nchunks * n;
+  for (long long it = (long long)blockIdx.x * blockDim.x + threadIdx.x; it < items;
+       it += (long long)gridDim.x * blockDim.x) {
+    const int ch = (int)(it / n), j = (int)(it - (long long)ch * n);
+    const int i0 = 1 + ch * MVB_P1_CHUNK;
+    const int i1 = i0 + MVB_P1_CHUNK - 1 < m ? i0 + MVB_P1_CHUNK - 1 : m;
+    double acc = 0.0;
+    for (int i = i0; i <= i1; i++) {
+      const int k = h[i];
+      const int sg = row_infeas(b[i], D.lb[k], D.ub[k]);
+      if (sg > 0) acc = acc + V.at(i, j);
+      else if (sg < 0) acc = acc - V.at(i, j);
+    }
+    D.p1part[(size_t)ch * ld + j] = acc;
+  }
+}
+__global__ void __launch_bounds__(256) shard_p1_reduce_kernel(ShardDev D, int par) {
+  const ShardCtl c = D.ctl[par];
+  if (c.status != -1 || c.mode != MVB_MODE_PRIMAL1) return;
+  const int nchunks = (D.m + MVB_P1_CHUNK - 1) / MVB_P1_CHUNK;
+  for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < D.nloc; j += gridDim.x * blockDim.x) {
+    double d = 0.0;
+    for (int ch = 0; ch < nchunks; ch++) d = d + ldcg(D.p1part + (size_t)ch * D.ld + j);
+    D.d1[j] = d;
+  }
+}
+
+// The candidate `best` (idx = local position or -1, k, var) of this rank goes out as one record:
+// header + its column through the view, into the send buffer (host copy / NCCL) or straight into
+// this rank's place in every peer's mailbox, followed by the arrival counters (push mode).
+__device__ void shard_emit_record(const ShardDev &D, const ShardView &V, int slot, const Key best, const int *at,
+                                  double dq) {
   const int q = best.idx;
-  // where the record goes: the send buffer (host copy / NCCL) or this rank's place in every mailbox
   const int ndst = D.push ? D.world : 1;
   const size_t place = (size_t)slot * D.world * D.rec_bytes + (size_t)D.rank * D.rec_bytes;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -155,6 +212,7 @@ __global__ void __launch_bounds__(1024, 1) shard_price_kernel(ShardDev D, int pa
     h.flag = q >= 0 ? at[q] : 0;
     h.lq = q >= 0 ? D.lb[best.var] : 0.0;
     h.uq = q >= 0 ? D.ub[best.var] : 0.0;
+    h.dq = dq;
     for (int k = 0; k < ndst; k++) *reinterpret_cast<Cand *>(D.push ? D.peer[k] + place : D.send) = h;
   }
   if (q >= 0)
@@ -295,8 +353,9 @@ __global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int pa
     if (h->pos < 0) continue;
     if (h->key < bk || (h->key == bk && h->var < bvar)) { bk = h->key; bvar = h->var; wk = k; }
   }
+  const bool phase1 = c.mode == MVB_MODE_PRIMAL1;
   if (wk < 0) {
-    n.status = MVB_OPT;
+    n.status = phase1 ? MVB_NOFEAS : MVB_OPT;
     if (lead) { *next = n; D.step[par] = stp; }
     return;
   }
@@ -310,14 +369,16 @@ __global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int pa
   const bool bland = c.degen >= MVB_BLAND_AFTER;
   const double *beta = D.beta[c.cS];
   const int *head = D.head[c.cS];
-  const int dir = col[0] < 0.0 ? 1 : -1;
-  // K2 ratio test over the gathered pivot column, lowest variable id on ties
+  const int dir = (phase1 ? cand.dq : col[0]) < 0.0 ? 1 : -1;
+  // K2 ratio test over the gathered pivot column, lowest variable id on ties (phase 1: an
+  // infeasible basic variable blocks only where it reaches its violated bound)
   Key bi = key_none();
   for (int i = 1 + tid; i <= m; i += NT) {
     const int var = head[i];
+    const double b = beta[i], l = D.lb[var], u = D.ub[var];
     double t;
     int fl;
-    if (!primal_ratio_row(col[i], dir, 0, beta[i], D.lb[var], D.ub[var], t, fl)) continue;
+    if (!primal_ratio_row(col[i], dir, phase1 ? row_infeas(b, l, u) : 0, b, l, u, t, fl)) continue;
     const Key k{dbits(t), var, i};
     if (key_less(k, bi)) bi = k;
   }
@@ -330,7 +391,7 @@ __global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int pa
   double delta, newbr = 0.0;
   if (tflip <= tmin) {
     if (!(tflip < HUGE_VAL)) {
-      n.status = MVB_UNBND;
+      n.status = phase1 ? MVB_NOFEAS : MVB_UNBND;
       if (lead) { *next = n; D.step[par] = stp; }
       return;
     }
@@ -340,7 +401,8 @@ __global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int pa
   } else {
     r = bi.idx;
     double t;
-    primal_ratio_row(col[r], dir, 0, beta[r], D.lb[bi.var], D.ub[bi.var], t, newat);
+    const double b = beta[r], l = D.lb[bi.var], u = D.ub[bi.var];
+    primal_ratio_row(col[r], dir, phase1 ? row_infeas(b, l, u) : 0, b, l, u, t, newat);
     delta = dir > 0 ? tmin : -tmin;
     newbr = nb_value(fq, lq, uq) + delta;
     n.degen = tmin == 0.0 ? c.degen + 1 : 0;
@@ -381,9 +443,24 @@ __global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int pa
     n.pend = 1;
   }
   n.cS = c.cS ^ 1;
+  if (phase1) {
+    // leave phase 1 as soon as the NEXT basis is primal feasible (the loop head of solve_lp: mode =
+    // PRIMAL2, degen = 0): every CTA counts the infeasible rows of the state it has just derived
+    int cnt = 0;
+    for (int i = 1 + tid; i <= m; i += NT) {
+      const double bn = i == r ? newbr : fma(col[i], delta, beta[i]);
+      const int hv = i == r ? kin : head[i];
+      cnt += row_infeas(bn, D.lb[hv], D.ub[hv]) != 0;
+    }
+    cnt = block_sum(cnt, sm.redI);
+    if (cnt == 0) {
+      n.mode = MVB_MODE_PRIMAL2;
+      n.degen = 0;
+    }
+  }
   if (lead) {
     unsigned long long h = c.hash;
-    h = (h ^ (unsigned long long)MVB_MODE_PRIMAL2) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)c.mode) * MVB_FNV_PRIME;
     h = (h ^ (unsigned long long)r) * MVB_FNV_PRIME;
     h = (h ^ (unsigned long long)cand.pos) * MVB_FNV_PRIME;
     n.hash = h;
@@ -392,6 +469,7 @@ __global__ void __launch_bounds__(512, 1) shard_decide_kernel(ShardDev D, int pa
       D.pivlog[2 * c.iters + 1] = cand.pos;
     }
     n.iters = c.iters + 1;
+    if (phase1) n.it1++;
     if (r) n.pivots++; else n.flips++;
     if (bland) n.bland_iters++;
     *next = n;
@@ -407,6 +485,168 @@ __global__ void __launch_bounds__(512, 1) shard_update_kernel(ShardDev D, int pa
   if (!st.valid) return;
   const double *col = reinterpret_cast<const double *>(D.recv[st.slot] + (size_t)st.wk * D.rec_bytes + SHARD_HDR);
   shard_tile_update(D, D.T[st.src], D.T[st.src ^ 1], st.r, st.qloc, D.rho[par], col, sm);
+}
+
+// ---- dual simplex on the column shards (B&B children / covering rows: the slack basis is dual
+// feasible but not primal feasible).  Same pipeline and the same records as the primal pair:
+//   shard_price_dual_kernel : K5a leaving row on the replicated beta (every rank finds the same r),
+//                             K5b ratio test |d_j| / |T_rj| over the LOCAL columns of row r (through
+//                             the view), record = (ratio bits, id, position, flag, bounds) + column
+//   shard_decide_dual_kernel: same global winner everywhere by (ratio bits, variable id), step
+//                             delta = (target - beta_r) / T_rq, next small state, K3 scaled row.
+// Arithmetic and tie-breaks are those of the general loop (solve_lp, MVB_MODE_DUAL) and the oracle.
+
+// K5a: largest bound violation, lowest variable id on ties (Bland: lowest id); idx = r or -1
+__device__ Key shard_dual_leaving(const ShardDev &D, const ShardCtl &c, Key *red) {
+  const bool bland = c.degen >= MVB_BLAND_AFTER;
+  const double *beta = D.beta[c.cS];
+  const int *head = D.head[c.cS];
+  Key best = key_none();
+  for (int i = 1 + threadIdx.x; i <= D.m; i += blockDim.x) {
+    const int var = head[i];
+    const double b = beta[i], lo = D.lb[var], up = D.ub[var];
+    const int sg = row_infeas(b, lo, up);
+    if (!sg) continue;
+    const double viol = sg < 0 ? lo - b : b - up;
+    const Key k{bland ? 0ULL : ~dbits(viol), var, i};
+    if (key_less(k, best)) best = k;
+  }
+  return block_argmin(best, red);
+}
+
+__global__ void __launch_bounds__(1024, 1) shard_price_dual_kernel(ShardDev D, int par, int slot) {
+  __shared__ Key red[32];
+  const ShardCtl c = D.ctl[par];
+  if (c.status != -1) return;
+  const ShardView V = shard_view(D, c, par);
+  const int *at = D.at[c.cS], *nb = D.nb[c.cS];
+  const Key lv = shard_dual_leaving(D, c, red);
+  Key best = key_none();
+  if (lv.idx >= 0) {
+    const int r = lv.idx;
+    const int rs = row_infeas(D.beta[c.cS][r], D.lb[lv.var], D.ub[lv.var]);
+    for (int j = threadIdx.x; j < D.nloc; j += blockDim.x) {
+      const int f = at[j];
+      if (f == MVB_AT_FX) continue;
+      const double alpha = V.at(r, j);
+      const double a = rs < 0 ? alpha : -alpha;
+      const bool ok = (f == MVB_AT_LB && a > MVB_TOL_PIV) || (f == MVB_AT_UB && a < -MVB_TOL_PIV) ||
+                      (f == MVB_AT_FR && (a > MVB_TOL_PIV || a < -MVB_TOL_PIV));
+      if (!ok) continue;
+      const double ratio = fabs(V.at(0, j)) / fabs(alpha);
+      const Key k{dbits(ratio), nb[j], j};
+      if (key_less(k, best)) best = k;
+    }
+  }
+  best = block_argmin(best, red);  // primal feasible basis (no r): an empty record from every rank
+  shard_emit_record(D, V, slot, best, at, best.idx >= 0 ? V.at(0, best.idx) : 0.0);
+}
+
+__global__ void __launch_bounds__(512, 1) shard_decide_dual_kernel(ShardDev D, int par, int slot,
+                                                                   unsigned long long expect) {
+  __shared__ Smem sm;
+  __shared__ int arrived;
+  const ShardCtl c = D.ctl[par];
+  ShardCtl *next = &D.ctl[par ^ 1];
+  const bool lead = blockIdx.x == 0 && threadIdx.x == 0;
+  ShardCtl n = c;
+  n.pend = 0;
+  ShardStep stp{};
+  stp.slot = slot;
+  if (c.status != -1) {
+    if (lead) { *next = n; D.step[par] = stp; }
+    return;
+  }
+  if (D.push && !shard_wait_records(D, slot, expect, &arrived)) {
+    n.status = SHARD_ST_TIMEOUT;
+    if (lead) { *next = n; D.step[par] = stp; }
+    return;
+  }
+  const int m = D.m, tid = threadIdx.x, NT = blockDim.x;
+  const Key lv = shard_dual_leaving(D, c, sm.redK);
+  if (lv.idx < 0) {
+    n.status = MVB_OPT;
+    if (lead) { *next = n; D.step[par] = stp; }
+    return;
+  }
+  if (c.iters >= D.max_iters) {
+    n.status = MVB_ITLIM;
+    if (lead) { *next = n; D.step[par] = stp; }
+    return;
+  }
+  // same winner everywhere: minimum (ratio bits, variable id) over the ranks' candidates
+  int wk = -1;
+  unsigned long long bk = ~0ULL;
+  int bvar = 0x7fffffff;
+  for (int k = 0; k < D.world; k++) {
+    const Cand *h = reinterpret_cast<const Cand *>(D.recv[slot] + (size_t)k * D.rec_bytes);
+    if (h->pos < 0) continue;
+    if (wk < 0 || h->key < bk || (h->key == bk && h->var < bvar)) { bk = h->key; bvar = h->var; wk = k; }
+  }
+  if (wk < 0) {
+    n.status = MVB_NOFEAS;
+    if (lead) { *next = n; D.step[par] = stp; }
+    return;
+  }
+  const Cand cand = *reinterpret_cast<const Cand *>(D.recv[slot] + (size_t)wk * D.rec_bytes);
+  const double *col = reinterpret_cast<const double *>(D.recv[slot] + (size_t)wk * D.rec_bytes + SHARD_HDR);
+  const bool bland = c.degen >= MVB_BLAND_AFTER;
+  const double *beta = D.beta[c.cS];
+  const int *head = D.head[c.cS];
+  const int r = lv.idx, kout = lv.var, kin = cand.var;
+  const double br = beta[r], lr = D.lb[kout], ur = D.ub[kout];
+  const int rs = row_infeas(br, lr, ur);
+  const double qratio = __longlong_as_double((long long)cand.key);
+  const double target = rs < 0 ? lr : ur;
+  const double delta = (target - br) / col[r];
+  const double newbr = nb_value(cand.flag, cand.lq, cand.uq) + delta;
+  const int newat = lr == ur ? MVB_AT_FX : (rs < 0 ? MVB_AT_LB : MVB_AT_UB);
+  n.degen = qratio == 0.0 ? c.degen + 1 : 0;
+  const int qloc = cand.pos - D.col0;
+  const int gt = blockIdx.x * NT + tid, stride = gridDim.x * NT;
+  {
+    double *bd = D.beta[c.cS ^ 1];
+    int *hd = D.head[c.cS ^ 1], *nd = D.nb[c.cS ^ 1], *ad = D.at[c.cS ^ 1];
+    const int *ns = D.nb[c.cS], *as = D.at[c.cS];
+    for (int i = 1 + gt; i <= m; i += stride) {
+      bd[i] = i == r ? newbr : fma(col[i], delta, beta[i]);
+      hd[i] = i == r ? kin : head[i];
+    }
+    for (int j = gt; j < D.nloc; j += stride) {
+      nd[j] = j == qloc ? kout : ns[j];
+      ad[j] = j == qloc ? newat : as[j];
+    }
+  }
+  {  // K3 on the current row r (through the view)
+    const ShardView V = shard_view(D, c, par);
+    const double inv = 1.0 / col[r];
+    double *rho = D.rho[par];
+    for (int j = gt; j < D.ld; j += stride) rho[j] = j == qloc ? inv : -(V.at(r, j) * inv);
+    stp.valid = 1;
+    stp.r = r;
+    stp.qloc = qloc;
+    stp.wk = wk;
+    stp.src = c.cur;
+    n.cur = c.cur ^ 1;
+    n.pend = 1;
+  }
+  n.cS = c.cS ^ 1;
+  if (lead) {
+    unsigned long long h = c.hash;
+    h = (h ^ (unsigned long long)MVB_MODE_DUAL) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)r) * MVB_FNV_PRIME;
+    h = (h ^ (unsigned long long)cand.pos) * MVB_FNV_PRIME;
+    n.hash = h;
+    if (D.pivlog && c.iters < D.pivlog_cap) {
+      D.pivlog[2 * c.iters] = r;
+      D.pivlog[2 * c.iters + 1] = cand.pos;
+    }
+    n.iters = c.iters + 1;
+    n.pivots++;
+    if (bland) n.bland_iters++;
+    *next = n;
+    D.step[par] = stp;
+  }
 }
 
 }  // namespace
@@ -626,6 +866,8 @@ struct mvb_shard {
   int last_exchange = 0;
   unsigned char *mail = nullptr;   // in-slab mailbox
   size_t mail_flag_off = 0;
+  int start_mode = MVB_MODE_PRIMAL2;  // from the slack basis: primal phase 2, or the dual simplex
+  bool dual_ok_local = true;          // dual start: no local column prices (the ranks agree at solve time)
 };
 
 namespace {
@@ -660,6 +902,8 @@ bool shard_alloc(mvb_shard *s) {
   size_t oc = take((size_t)s->ld * sizeof(double));
   size_t octl = take(2 * sizeof(ShardCtl)), ostep = take(2 * sizeof(ShardStep));
   size_t orho0 = take((size_t)s->ld * sizeof(double)), orho1 = take((size_t)s->ld * sizeof(double));
+  const size_t p1chunks = ((size_t)m + MVB_P1_CHUNK - 1) / MVB_P1_CHUNK;
+  size_t op1 = take(p1chunks * s->ld * sizeof(double)), od1 = take((size_t)s->ld * sizeof(double));
   // in-slab mailbox, same layout as the IPC one (PeerMail): SHARD_SLOTS x world records, then the counters
   const size_t mail_flag_off = align_up((size_t)SHARD_SLOTS * s->world * rec, 256);
   size_t osend = take(rec), omail = take(mail_flag_off + (size_t)SHARD_SLOTS * s->world * sizeof(unsigned long long));
@@ -679,6 +923,7 @@ bool shard_alloc(mvb_shard *s) {
   d.ctl = (ShardCtl *)(b + octl);
   d.step = (ShardStep *)(b + ostep);
   d.rho[0] = (double *)(b + orho0); d.rho[1] = (double *)(b + orho1);
+  d.p1part = (double *)(b + op1); d.d1 = (double *)(b + od1);
   d.send = (unsigned char *)(b + osend);
   s->mail = (unsigned char *)(b + omail);
   s->mail_flag_off = mail_flag_off;
@@ -806,21 +1051,55 @@ void mvb_shard_free(mvb_shard *s) {
   delete s;
 }
 
+// rows of the slack basis with every non-basic at value 0 (beta = 0), by the rule of the general
+// loop (row_infeas): 1 = primal feasible (primal phase 2), 2 = some row violates its bound beyond
+// the tolerance (the dual simplex if no column prices, else the composite phase 1)
+static int shard_row_start(int m, const double *rlb, const double *rub) {
+  for (int i = 0; i < m; i++) {
+    const double l = rlb[i], u = rub[i];
+    if (l - 0.0 > MVB_TOL_BND * (1.0 + std::fabs(l)) || 0.0 - u > MVB_TOL_BND * (1.0 + std::fabs(u))) return 2;
+  }
+  return 1;
+}
+// no column [0, n) prices at its slack-basis flag: the slack basis is dual feasible
+static bool shard_cols_dual_ok(int n, const double *cost, const double *clb, const double *cub) {
+  for (int j = 0; j < n; j++) {
+    const int f = nb_flag_for(clb[j], cub[j], MVB_AT_LB);
+    const double dj = cost[j];
+    const bool elig = f == MVB_AT_LB ? dj < -MVB_TOL_DJ : f == MVB_AT_UB ? dj > MVB_TOL_DJ
+                      : f == MVB_AT_FR ? (dj < -MVB_TOL_DJ || dj > MVB_TOL_DJ) : false;
+    if (elig) return false;
+  }
+  return true;
+}
+
+int mvb_shard_start_mode(int m, int n, const double *cost, const double *lb, const double *ub) {
+  for (int j = 0; j < n; j++) {
+    const double l = lb[j], u = ub[j];
+    const bool zero_ok = (l == 0.0) || (!(l > -HUGE_VAL) && (u == 0.0 || !(u < HUGE_VAL)));
+    if (!zero_ok) return 0;
+  }
+  if (shard_row_start(m, lb + n, ub + n) == 1) return MVB_MODE_PRIMAL2;
+  return shard_cols_dual_ok(n, cost, lb, ub) ? MVB_MODE_DUAL : MVB_MODE_PRIMAL1;
+}
+
 int mvb_shard_load(mvb_shard *s, const double *A_local, const double *cost_local, const double *lb,
                    const double *ub) {
   const int m = s->m, nloc = s->nloc, ng = s->nglob;
   cudaStream_t st = g_ctx.stream;
-  // this path starts primal phase 2 from the slack basis with every non-basic at value 0
+  // this path starts from the slack basis with every non-basic at value 0: primal phase 2 when
+  // that basis is primal feasible, the dual simplex when it is dual feasible instead, the
+  // composite phase 1 (then phase 2) when it is neither
   for (int j = 0; j < nloc; j++) {
     const double l = lb[s->col0 + j], u = ub[s->col0 + j];
     const bool zero_ok = (l == 0.0) || (!(l > -HUGE_VAL) && (u == 0.0 || !(u < HUGE_VAL)));
     if (!zero_ok) { g_err = "mvb_shard_load: sharded path needs non-basic values 0 (lb = 0 or free)"; return -1; }
   }
-  for (int i = 0; i < m; i++)
-    if (lb[ng + i] > 0.0 || ub[ng + i] < 0.0) {
-      g_err = "mvb_shard_load: slack basis is not primal feasible (phase 1 is not sharded)";
-      return -1;
-    }
+  const int rstart = shard_row_start(m, lb + ng, ub + ng);
+  s->start_mode = rstart == 1 ? MVB_MODE_PRIMAL2 : MVB_MODE_DUAL;
+  // (not primal feasible: the dual simplex if no column of ANY rank prices, else the composite
+  // phase 1 -- agreed in mvb_shard_solve, where all ranks meet)
+  s->dual_ok_local = rstart == 1 || shard_cols_dual_ok(nloc, cost_local, lb + s->col0, ub + s->col0);
   if (s->slab) { CKI(cudaFreeAsync(s->slab, st)); s->slab = nullptr; }
   if (!shard_alloc(s)) return -1;
   ShardDev &d = s->dev;
@@ -890,12 +1169,26 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
   if (!local && nlocal != 1) { g_err = "mvb_shard_solve: one shard per process over NCCL"; return -1; }
   const int m = s0->m, ng = s0->nglob;
   const int mi = (opts && opts->max_iters > 0) ? opts->max_iters : 50 * (m + ng) + 10000;
+  for (int k = 0; k < nlocal; k++)
+    if (!shards[k]->slab) { g_err = "mvb_shard_solve: shard not loaded"; return -1; }
+  int mode = s0->start_mode;
+  if (mode == MVB_MODE_DUAL) {  // a column prices somewhere: neither primal nor dual feasible = composite phase 1
+    double bad = 0.0;
+    for (int k = 0; k < nlocal; k++) if (!shards[k]->dual_ok_local) bad = 1.0;
+    if (!local) {
+      if (!s0->comm->allreduce_max) { g_err = "mvb_shard_solve: the communicator has no reduction"; return -1; }
+      if (s0->comm->allreduce_max(s0->comm->ctx, &bad, 1)) { g_err = "mvb_shard_solve: reduction failed"; return -1; }
+    }
+    if (bad != 0.0) mode = MVB_MODE_PRIMAL1;
+  }
+  const bool dual = mode == MVB_MODE_DUAL;
+  bool phase1 = mode == MVB_MODE_PRIMAL1;  // the host stops launching the phase-1 kernels once it sees PRIMAL2
   ShardCtl init{};
   init.status = -1;
+  init.mode = mode;
   init.hash = MVB_FNV_OFFSET;
   for (int k = 0; k < nlocal; k++) {
     mvb_shard *s = shards[k];
-    if (!s->slab) { g_err = "mvb_shard_solve: shard not loaded"; return -1; }
     if (opts && opts->log_pivots) {
       const int want = std::min(mi, 1 << 22);
       if (s->pivlog_cap < want) {
@@ -976,10 +1269,20 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
         for (int k = 0; k < nlocal; k++) CKI(cudaStreamWaitEvent(st, shards[k]->ev_upd[par], 0));
       const int slot = (int)(t_it % SHARD_SLOTS);
       const unsigned long long expect = (unsigned long long)price_grid * (unsigned long long)(t_it / SHARD_SLOTS + 1);
-      for (int k = 0; k < nlocal; k++) shard_price_kernel<<<price_grid, 1024, 0, st>>>(shards[k]->dev, par, slot);
+      if (phase1)
+        for (int k = 0; k < nlocal; k++) {
+          shard_p1_partials_kernel<<<grid, 256, 0, st>>>(shards[k]->dev, par);
+          shard_p1_reduce_kernel<<<std::max(1, (shards[k]->nloc + 255) / 256), 256, 0, st>>>(shards[k]->dev, par);
+          g_launches += 2;
+        }
+      for (int k = 0; k < nlocal; k++) {
+        if (dual) shard_price_dual_kernel<<<price_grid, 1024, 0, st>>>(shards[k]->dev, par, slot);
+        else shard_price_kernel<<<price_grid, 1024, 0, st>>>(shards[k]->dev, par, slot);
+      }
       if (!exchange(false, slot)) return -1;
       for (int k = 0; k < nlocal; k++) {
-        shard_decide_kernel<<<small_grid, 512, 0, st>>>(shards[k]->dev, par, slot, expect);
+        if (dual) shard_decide_dual_kernel<<<small_grid, 512, 0, st>>>(shards[k]->dev, par, slot, expect);
+        else shard_decide_kernel<<<small_grid, 512, 0, st>>>(shards[k]->dev, par, slot, expect);
         CKI(cudaEventRecord(shards[k]->ev_dec[par], st));
       }
       for (int k = 0; k < nlocal; k++) {
@@ -994,6 +1297,7 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
     CKI(cudaMemcpyAsync(&h, &s0->dev.ctl[par], sizeof(h), cudaMemcpyDeviceToHost, st));
     CKI(cudaStreamSynchronize(st));
     if (h.status != -1) break;
+    if (h.mode != MVB_MODE_PRIMAL1) phase1 = false;
   }
   if (h.status == SHARD_ST_TIMEOUT) { g_err = "mvb_shard_solve: a peer's record did not arrive (peer exchange timed out)"; return -1; }
   // the last updates, then back to one stream
@@ -1059,7 +1363,8 @@ extern "C" int mvb_shard_solve(mvb_shard *const *shards, int nlocal, const mvb_o
       r.iters = h.iters;
       r.pivots = h.pivots;
       r.flips = h.flips;
-      r.iters_primal2 = h.iters;
+      if (dual) r.iters_dual = h.iters;
+      else { r.iters_primal1 = h.it1; r.iters_primal2 = h.iters - h.it1; }
       r.bland_iters = h.bland_iters;
       r.pivot_hash = h.hash;
       r.obj = lane[0];

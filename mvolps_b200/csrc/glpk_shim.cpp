@@ -589,7 +589,12 @@ static int simplex_on_shards(glp_prob *P) {
   for (int i = 0; i < m; i++) {
     lb[n + i] = mv_eff_lb(P->rbnd[i].type, P->rbnd[i].lb);
     ub[n + i] = mv_eff_ub(P->rbnd[i].type, P->rbnd[i].ub);
-    if (lb[n + i] > 0.0 || ub[n + i] < 0.0) return 0;  // slack basis not primal feasible: phase 1 is not sharded
+  }
+  {
+    // primal phase 2 or the dual simplex from the slack basis; the composite phase 1 is not sharded
+    std::vector<double> c(n);
+    for (int j = 0; j < n; j++) c[j] = P->dir == GLP_MAX ? -P->colm[j].coef : P->colm[j].coef;
+    if (!mvb_shard_start_mode(m, n, c.data(), lb.data(), ub.data())) return 0;
   }
   const bool local = g_shard_comm == nullptr;
   std::vector<mvb_comm *> own;

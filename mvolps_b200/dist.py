@@ -53,12 +53,14 @@ def nccl_comm(lib, rank, world, dist):
 class ShardGroup:
     """The shards this process holds: all of them (local group) or one (NCCL)."""
 
-    def __init__(self, lib, inst, world, comm=None, rank=0):
+    def __init__(self, lib, inst, world, comm=None, rank=0, slices=None):
+        """`slices`: {rank: slice_instance(inst, world, rank)} prepared by the caller (bench.py times the
+        load without the host-side column slicing of the harness)."""
         self.lib, self.world = lib, world
         self.shards, self.comms = [], []
         ranks = range(world) if comm is None else [rank]
         for r in ranks:
-            sl = slice_instance(inst, world, r)
+            sl = slices[r] if slices is not None else slice_instance(inst, world, r)
             c = lib.mvb_comm_local(r, world) if comm is None else comm
             if comm is None:
                 self.comms.append(c)

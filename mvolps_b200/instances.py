@@ -26,6 +26,29 @@ def mdkp(n, m, seed, U=3):
                 col_lb=np.zeros(n), col_ub=np.full(n, float(U)), integer=np.ones(n, bool))
 
 
+def covering_lp(m, n, seed, frac_le=0.25, boxed=0.3):
+    """min c.x, covering rows a.x >= b mixed with some packing rows a.x <= b', 0 <= x (<= u), c > 0:
+    the slack basis is dual feasible but not primal feasible, so the solve is the dual simplex from
+    the first iteration (the start a B&B child has after a bound change).  Feasible by construction
+    around a known point x0."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    A = np.round(rng.random((m, n)) * 8) / 8
+    x0 = rng.integers(0, 3, size=n).astype(np.float64)
+    act = A @ x0
+    row_lb = np.full(m, -INF)
+    row_ub = np.full(m, INF)
+    kind = rng.random(m)
+    for i in range(m):
+        if kind[i] < frac_le:
+            row_ub[i] = act[i] + float(rng.integers(0, 4))
+        else:
+            row_lb[i] = max(act[i] - float(rng.integers(0, 3)), 0.125)
+    col_ub = np.where(rng.random(n) < boxed, x0 + rng.integers(1, 3, size=n), INF)
+    c = 0.5 + rng.random(n)
+    return dict(A=A, c=c, sense="min", row_lb=row_lb, row_ub=row_ub,
+                col_lb=np.zeros(n), col_ub=col_ub, integer=np.zeros(n, bool))
+
+
 def general_lp(m, n, seed, frac_ge=0.3, frac_eq=0.1, boxed=0.5):
     """Mixed-sense feasible LP exercising phase 1 / dual / bound flips: rows of
     type <=, >=, = built around a known interior point so the LP is feasible."""

@@ -26,8 +26,9 @@ ms = L.mvb_last_kernel_ms()
 iters = sum(r["iters"] for r in res)
 G, groups, nt = C.c_int(), C.c_int(), C.c_int()
 L.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
+hsum = sum(r["pivot_hash"] for r in res) & ((1 << 64) - 1)  # same LPs, same pivots: equal at every depth / build
 print(f"{nlp} LPs m={m} n={n}: kernel {ms:.2f} ms, {iters} iterations -> {iters / ms / 1e3:.2f} M LP-pivots/s; "
-      f"G={G.value} groups={groups.value} threads={nt.value}")
+      f"G={G.value} groups={groups.value} threads={nt.value} hash_sum={hsum}")
 if not have_prof:
     sys.exit(0)
 p = buf.reshape(256, 16)

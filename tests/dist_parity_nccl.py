@@ -7,7 +7,8 @@ process per GPU).  Run on a box with N >= 2 GPUs:
 Checks, bit for bit against the CPU oracle (test infrastructure) on every rank:
   * column-sharded tableau, one process per GPU: the pushed exchange (price kernel writes into the
     peers' cudaIpc mailboxes, atomicAdd_system / ld.acquire.sys hand-shake) AND ncclAllGather
-    (MVOLPS_SHARD_EXCHANGE=nccl): pivot log, hash, objective bits, primal vector
+    (MVOLPS_SHARD_EXCHANGE=nccl): pivot log, hash, objective bits, primal vector; primal
+    phase 2 and the dual simplex
   * node-sharded B&B (NCCL incumbent max-reduction, ncclSend/Recv work stealing): serial optimum and x
   * round-synchronous B&B (MVB_DIST_SYNC, results by ncclAllGather): tree text, event stream, counters
     of the serial run, without and with GMI cut rows
@@ -40,25 +41,31 @@ def main():
     comm = nccl_comm(L, rank, world, dist)
     report = {"world": world, "shard": [], "bnb_steal": [], "bnb_sync": []}
 
-    for m, n, seed in ((33, 70, 3), (64, 128, 4), (128, 256, 5), (200, 520, 8), (256, 512, 0)):
-        a = EngineLP.from_instance(orc, instances.dense_lp(m, n, seed))
+    # primal phase 2 (dense_lp) and the dual simplex (covering_lp: dual feasible slack basis)
+    for gen, m, n, seed in (("dense_lp", 33, 70, 3), ("dense_lp", 64, 128, 4), ("dense_lp", 128, 256, 5),
+                            ("dense_lp", 200, 520, 8), ("dense_lp", 256, 512, 0),
+                            ("covering_lp", 33, 70, 3), ("covering_lp", 128, 256, 5), ("covering_lp", 200, 520, 8)):
+        make = getattr(instances, gen)
+        a = EngineLP.from_instance(orc, make(m, n, seed))
         ra = a.solve(log_pivots=1)
         la, _ = a.pivot_log()
+        assert (ra["iters_dual"] == ra["iters"]) == (gen == "covering_lp")
         for mode in ("push", "nccl"):
             if mode == "nccl":
                 os.environ["MVOLPS_SHARD_EXCHANGE"] = "nccl"
             else:
                 os.environ.pop("MVOLPS_SHARD_EXCHANGE", None)
-            g = ShardGroup(L, instances.dense_lp(m, n, seed), world, comm=comm, rank=rank)
+            g = ShardGroup(L, make(m, n, seed), world, comm=comm, rank=rank)
             rg = g.solve(log_pivots=1)
             how = g.last_exchange()
-            for k in ("status", "iters", "pivots", "flips", "pivot_hash", "bland_iters", "primal_feasible"):
-                assert ra[k] == rg[k], (m, n, seed, mode, k, ra[k], rg[k])
+            for k in ("status", "iters", "pivots", "flips", "pivot_hash", "bland_iters", "primal_feasible", "iters_dual"):
+                assert ra[k] == rg[k], (gen, m, n, seed, mode, k, ra[k], rg[k])
             assert ra["obj"] == rg["obj"]
             lg, _ = g.pivot_log()
             assert np.array_equal(la, lg) and np.array_equal(a.primal(), g.primal())
             assert ("ncclAllGather" in how) == (mode == "nccl"), how
-            report["shard"].append({"m": m, "n": n, "iters": rg["iters"], "exchange": how.split(" (")[0]})
+            report["shard"].append({"lp": gen, "m": m, "n": n, "iters": rg["iters"], "dual": rg["iters_dual"],
+                                    "exchange": how.split(" (")[0]})
             g.free()
     os.environ.pop("MVOLPS_SHARD_EXCHANGE", None)
 

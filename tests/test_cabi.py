@@ -87,3 +87,31 @@ def test_product_sources_do_not_reference_oracle():
                 assert "libglpk_oracle" not in txt and "oracle/_" not in txt, f
                 assert not re.search(r'#include\s*[<"][^>"]*oracle', txt), f
                 assert not re.search(r"^\s*(from|import)\s+\S*oracle", txt, flags=re.M), f
+
+
+def test_shard_start_mode_is_host_logic(product_nogpu):
+    """mvb_shard_start_mode (include/mvolps_dist.h): which simplex the column-sharded path would start
+    with from the slack basis -- pure host logic, so it is checked here against the mode the oracle's
+    own solve takes (iters_primal2 / iters_dual / iters_primal1 of solve_one)."""
+    import numpy as np
+    from mvolps_b200 import instances
+    from mvolps_b200.dist import slice_instance
+    from mvolps_b200.lp import EngineLP
+    from conftest import ORACLE_LIB
+    if not os.path.exists(ORACLE_LIB):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "all"], check=True, capture_output=True)
+    orc = capi.load_library(ORACLE_LIB)
+    L = product_nogpu
+    cases = [(instances.dense_lp(8, 12, 2), 1), (instances.covering_lp(33, 70, 3), 2),
+             (instances.general_lp(20, 30, 12), 3), (instances.mdkp(12, 4, 1), 1)]
+    for inst, want in cases:
+        sl = slice_instance(inst, 1, 0)
+        got = L.mvb_shard_start_mode(sl["m"], sl["n"], capi.dptr(sl["cost"]), capi.dptr(sl["lb"]), capi.dptr(sl["ub"]))
+        assert got == want
+        r = EngineLP.from_instance(orc, inst).solve()
+        took = 3 if r["iters_primal1"] > 0 else 1 if r["iters_primal2"] == r["iters"] else 2
+        assert took == want, (r, want)
+    inst = instances.dense_lp(8, 12, 2)
+    inst["col_lb"] = np.full(12, 1.0)   # non-basic values would not be 0: one GPU
+    sl = slice_instance(inst, 1, 0)
+    assert L.mvb_shard_start_mode(sl["m"], sl["n"], capi.dptr(sl["cost"]), capi.dptr(sl["lb"]), capi.dptr(sl["ub"])) == 0
