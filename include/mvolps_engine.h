@@ -101,7 +101,10 @@ int mvb_last_kernel_mode(void);
  * "cres" (MVOLPS_CRES) 1 = LPs too large for one CTA's shared memory that fit a cluster of 2/4/8 CTAs use the
  * cluster-resident kernel (default 0: the lazy loop is faster on full solves),
  * "lz_k" (MVOLPS_LZ_K) cap of the pending-update depth, "ps_nt" (MVOLPS_PS_NT) CTA width of wide
- * launches.  value < 0 only queries; returns the previous value, -1 on an unknown name.  oracle: -1 */
+ * launches, "lz_ring" (MVOLPS_LZ_RING) 0 = the flush of HBM-streaming batches reads through registers
+ * instead of the cp.async ring, "last_ring" / "last_lz_k" / "last_stream" (query only) ring slots per
+ * thread, pending depth and kernel (1 = simplex_ps_stream_kernel) of the last lazy launch.
+ * value < 0 only queries; returns the previous value, -1 on an unknown name.  oracle: -1 */
 int mvb_engine_option(const char *name, int value);
 /* shape of the last launch: CTAs per LP, groups, threads per CTA */
 int mvb_last_launch(int *ctas_per_lp, int *groups, int *threads);

@@ -71,6 +71,7 @@ struct LPDev {
   int curT, curS;   // parities at entry
   int max_iters;
   int lzK;          // pending-update depth of the lazy loop for this launch
+  int lzRing;       // slots of the flush's cp.async ring per thread (0: flush reads through registers)
   int npatch;       // bound patches to apply before the solve
   const BoundPatch *patch;
   // hand-over from the general kernel to the private-state kernel once phase 1 has reached a
@@ -417,7 +418,9 @@ namespace {
 // One whole LP solve by a group of G CTAs (this CTA is number g of it).
 // dyn != nullptr: the launch carries enough dynamic shared memory for the
 // private-state loop (engine_ps.cuh), used unless the LP needs phase 1.
-template <bool PSK>
+// PSK: 0 = the general loop below; 1 = the lazy private-state loop (simplex_ps_kernel); 2 = the same
+// loop with the streaming flush (simplex_ps_stream_kernel)
+template <int PSK>
 __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &gen, int tcl,
                          Smem &sm, unsigned char *dyn) {
   const int m = L.m, n = L.n, ld = L.ld, tid = threadIdx.x, NT = blockDim.x;
@@ -451,7 +454,7 @@ __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &
       if (g == 0 && tid == 0) L.res->r.status = MVB_PS_FALLBACK;
       return;
     }
-    status = lz_loop(L, g, G, ctr, gen, tcl, L.lzK, mode, cT, cS, ty);
+    status = lz_loop<PSK == 2>(L, g, G, ctr, gen, tcl, L.lzK, L.lzRing, mode, cT, cS, ty);
   }
 
   while (!PSK) {
@@ -636,7 +639,7 @@ __device__ void solve_lp(const LPDev &L, int g, int G, unsigned *ctr, unsigned &
 
 // grid = ngroups * G CTAs (all co-resident: cooperative launch); group k owns
 // LPs k, k + ngroups, ...
-template <bool PSK>
+template <int PSK>
 __device__ __forceinline__ void kernel_body(const LPDev *lps, int nlp, int G, unsigned *ctrs,
                                             int tcl, unsigned char *dyn) {
   __shared__ Smem sm;
@@ -670,7 +673,7 @@ __device__ __forceinline__ void kernel_body(const LPDev *lps, int nlp, int G, un
 // LPs k, k + ngroups, ...
 __global__ void __launch_bounds__(512, 1)
 simplex_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
-  kernel_body<false>(lps, nlp, G, ctrs, tcl, nullptr);
+  kernel_body<0>(lps, nlp, G, ctrs, tcl, nullptr);
 }
 
 // private-state variant (engine_ps.cuh): every LP of the launch fits the
@@ -678,7 +681,16 @@ simplex_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
 // status MVB_PS_FALLBACK and are re-run by simplex_kernel.
 __global__ void __launch_bounds__(MVB_PS_NT, 1)
 simplex_ps_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
-  kernel_body<true>(lps, nlp, G, ctrs, tcl, dyn_smem);
+  kernel_body<1>(lps, nlp, G, ctrs, tcl, dyn_smem);
+}
+
+// streaming variant: launches of one CTA per LP whose tableaux do not stay in L2 (configs[3]-shape
+// batches, B&B rounds of large node LPs).  A kernel of its own so that the code of the
+// L2-resident path above stays exactly what it was (its per-pivot time moved by 2-8 % with the
+// placement of unrelated functions in the same kernel, profiles/r2_runs/r2q_ab*.txt).
+__global__ void __launch_bounds__(MVB_PS_NT, 1)
+simplex_ps_stream_kernel(const LPDev *lps, int nlp, int G, unsigned *ctrs, int tcl) {
+  kernel_body<2>(lps, nlp, G, ctrs, tcl, dyn_smem);
 }
 
 }  // namespace
@@ -781,6 +793,9 @@ struct DeviceCtx {
   int last_kind = 0;         // kernel of the last solve launch: 0 general, 1 private-state (lazy), 2 resident
   bool no_handover = false;  // MVOLPS_NO_HANDOVER=1: phase 2 after a phase 1 stays in the general loop (A-B timing)
   int force_k = 0;         // MVOLPS_LZ_K=k: cap the pending-update depth (A-B timing)
+  int ring_slots = LZ_RING_SLOTS;  // option "lz_ring" / MVOLPS_LZ_RING=0: no cp.async ring in the streaming flush (A-B timing)
+  int last_ring = 0, last_lz_k = 0;
+  bool last_stream = false;  // the last lazy launch ran simplex_ps_stream_kernel
   int force_nt = 0;        // MVOLPS_PS_NT=t: CTA width for launches with more LPs than SMs (A-B timing)
   int last_nt = 0;
 };
@@ -819,6 +834,14 @@ bool ctx_init(int device) {
   CK(cudaFuncGetAttributes(&fa, simplex_ps_kernel));
   g_ctx.max_dyn = (size_t)optin > fa.sharedSizeBytes + 1024 ? (size_t)optin - fa.sharedSizeBytes - 1024 : 0;
   CK(cudaFuncSetAttribute(simplex_ps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_ctx.max_dyn));
+  {
+    // (the streaming variant takes the same dynamic shared memory; its static part may differ by a few bytes)
+    cudaFuncAttributes fs;
+    CK(cudaFuncGetAttributes(&fs, simplex_ps_stream_kernel));
+    if ((size_t)optin < fs.sharedSizeBytes + 1024 + g_ctx.max_dyn)
+      g_ctx.max_dyn = (size_t)optin > fs.sharedSizeBytes + 1024 ? (size_t)optin - fs.sharedSizeBytes - 1024 : 0;
+    CK(cudaFuncSetAttribute(simplex_ps_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g_ctx.max_dyn));
+  }
   const char *nops = getenv("MVOLPS_NO_PS");
   g_ctx.no_ps = nops && nops[0] == '1';
   const char *nores = getenv("MVOLPS_NO_RES");
@@ -841,6 +864,8 @@ bool ctx_init(int device) {
   g_ctx.no_handover = noh && noh[0] == '1';
   const char *fk = getenv("MVOLPS_LZ_K");
   g_ctx.force_k = fk ? atoi(fk) : 0;
+  const char *frg = getenv("MVOLPS_LZ_RING");
+  if (frg) g_ctx.ring_slots = atoi(frg) > 0 ? LZ_RING_SLOTS : 0;
   const char *fnt = getenv("MVOLPS_PS_NT");
   g_ctx.force_nt = fnt ? atoi(fnt) : 0;
   int per_sm = 0;
@@ -1327,6 +1352,10 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   }
   int max_ctas = psk ? g_ctx.max_ctas_ps : g_ctx.max_ctas;
   int nt = psk ? g_ctx.nt_ps : g_ctx.nt;
+  // the launch's tableaux do not stay in L2: flush passes stream from HBM (deeper pending chains,
+  // reads staged through the cp.async ring when one CTA owns an LP)
+  const bool streams = tot_bytes > ((size_t)96 << 20);
+  int ring = psk && streams ? g_ctx.ring_slots : 0;
   if (psk && count > g_ctx.sms && !(opts && opts->ctas_per_lp > 0)) {
     // more small LPs than SMs (a B&B round): narrower CTAs, several resident per SM, so more
     // LPs are in flight; the vectors of one LP do not fill 512 threads anyway
@@ -1334,12 +1363,20 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
     for (int k = 0; k < count; k++) span = std::max(span, std::max(lps[idx[k]]->ld, lps[idx[k]]->m + 1));
     const int want = g_ctx.force_nt > 0 ? g_ctx.force_nt : span <= 256 ? 128 : span <= 512 ? 256 : nt;
     if (want < nt) {
+      // (more LPs than SMs: one CTA per LP, so a streaming launch runs the streaming kernel)
+      const int kcap = g_ctx.force_k > 0 ? g_ctx.force_k : streams ? LZ_KMAX_STREAM : LZ_KMAX;
+      const void *kern = streams ? (const void *)simplex_ps_stream_kernel : (const void *)simplex_ps_kernel;
       size_t dyn_max = 0;
       for (int k = 0; k < count; k++)
         dyn_max = std::max(dyn_max, lz_smem_bytes(lps[idx[k]]->m, lps[idx[k]]->ld,
-                                                  std::min(lz_pick_k(lps[idx[k]]->m, lps[idx[k]]->ld, g_ctx.max_dyn), LZ_KMAX)));
+                                                  lz_pick_k(lps[idx[k]]->m, lps[idx[k]]->ld, g_ctx.max_dyn, std::min(kcap, LZ_KCAP))));
       int per_sm = 0;
-      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, simplex_ps_kernel, want, dyn_max));
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, want, dyn_max));
+      if (ring) {  // the ring must not cost a resident CTA
+        int per_sm_ring = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_ring, kern, want, dyn_max + 16 + lz_ring_bytes(ring, want)));
+        if (per_sm_ring < per_sm) ring = 0;
+      }
       if (per_sm > 1) {
         nt = want;
         max_ctas = per_sm * g_ctx.sms;
@@ -1353,19 +1390,33 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   if (!(opts && opts->ctas_per_lp > 0) && count > 1) G = std::max(1, std::min(G, max_ctas / count));
   G = std::max(1, std::min(G, max_ctas));
   int ngroups = std::max(1, std::min(count, max_ctas / G));
+  const bool stream_kernel = psk && streams && G == 1;
   if (psk) {
     // pending-update depth: 5 is the measured sweet spot while the tableaux stay in L2
     // (flush passes are cheap, deeper chains cost decisions); a wide batch of one-CTA LPs
-    // streams its tableaux from HBM, where halving the flush traffic wins (depth 8)
-    const bool streams = tot_bytes > ((size_t)96 << 20);  // the launch's tableaux do not stay in L2
-    const int cap = g_ctx.force_k > 0 ? g_ctx.force_k : (G == 1 && streams) ? LZ_KMAX : 5;
-    for (int k = 0; k < count; k++) {
-      mvb_lp *lp = lps[idx[k]];
-      const int K = std::min(lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn), cap);
-      h[k].lzK = K;
-
-      dyn = std::max(dyn, lz_smem_bytes(lp->m, lp->ld, K));
+    // streams its tableaux from HBM, where every pending pivot more divides the flush traffic
+    // (depth 12 in the streaming kernel: 13.8 against 12.5 M LP-pivots/s at depth 8 with the ring)
+    const int kmax = stream_kernel ? LZ_KMAX_STREAM : LZ_KMAX;
+    const int cap = std::min(kmax, g_ctx.force_k > 0 ? g_ctx.force_k : stream_kernel ? LZ_KMAX_STREAM : 5);
+    if (!stream_kernel) ring = 0;
+    for (int pass = 0; pass < 2; pass++) {  // (second pass: without the ring, when it does not fit every LP)
+      dyn = 0;
+      bool fits = true;
+      for (int k = 0; k < count; k++) {
+        mvb_lp *lp = lps[idx[k]];
+        const int K = std::min(lz_pick_k(lp->m, lp->ld, g_ctx.max_dyn, kmax), cap);
+        h[k].lzK = K;
+        h[k].lzRing = ring;
+        g_ctx.last_lz_k = K;
+        const size_t need = ring ? lz_ring_off(lp->m, lp->ld, K) + lz_ring_bytes(ring, nt) : lz_smem_bytes(lp->m, lp->ld, K);
+        if (need > g_ctx.max_dyn) fits = false;
+        dyn = std::max(dyn, need);
+      }
+      if (fits || !ring) break;
+      ring = 0;
     }
+    g_ctx.last_ring = ring;
+    g_ctx.last_stream = stream_kernel;
   }
   int res_grid = 0;
   if (res) {
@@ -1473,7 +1524,9 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
     simplex_res_kernel<<<res_grid, RES_NT, dyn, st>>>(dl, cnt);
     CK(cudaGetLastError());
   } else {
-    CK(cudaLaunchCooperativeKernel(psk ? (const void *)simplex_ps_kernel : (const void *)simplex_kernel,
+    CK(cudaLaunchCooperativeKernel(stream_kernel ? (const void *)simplex_ps_stream_kernel
+                                   : psk         ? (const void *)simplex_ps_kernel
+                                                 : (const void *)simplex_kernel,
                                    dim3(ngroups * G), dim3(nt), args, dyn, st));
   }
   CK(cudaEventRecord(g_ctx.kev[1], st));
@@ -1824,6 +1877,10 @@ int mvb_engine_option(const char *name, int value) {
   else if (!strcmp(name, "cres")) num(g_ctx.use_cres);
   else if (!strcmp(name, "lz_k")) num(g_ctx.force_k);
   else if (!strcmp(name, "ps_nt")) num(g_ctx.force_nt);
+  else if (!strcmp(name, "lz_ring")) { old = g_ctx.ring_slots; if (value >= 0) g_ctx.ring_slots = value ? LZ_RING_SLOTS : 0; }
+  else if (!strcmp(name, "last_ring")) old = g_ctx.last_ring;  // read-only: ring slots of the last lazy launch
+  else if (!strcmp(name, "last_lz_k")) old = g_ctx.last_lz_k;  // read-only: pending depth of the last lazy launch
+  else if (!strcmp(name, "last_stream")) old = g_ctx.last_stream;  // read-only: it ran the streaming kernel
   else { g_err = std::string("mvb_engine_option: unknown option ") + name; return -1; }
   return old;
 }

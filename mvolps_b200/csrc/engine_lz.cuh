@@ -34,11 +34,19 @@ constexpr int PS_CREG = 8;            // pivot-column values a thread can hold i
 #ifndef MVB_LZ_KMAX
 #define MVB_LZ_KMAX 8
 #endif
-#ifndef MVB_LZ_UN_DEEP
-#define MVB_LZ_UN_DEEP 2
+#ifndef MVB_LZ_KMAX_STREAM
+#define MVB_LZ_KMAX_STREAM 12
 #endif
-constexpr int LZ_KMAX = MVB_LZ_KMAX;  // most pending pivots between two flush passes (<= 16: two qmask bits each)
-static_assert(LZ_KMAX >= 1 && LZ_KMAX <= 16, "LZ_KMAX");
+#ifndef MVB_LZ_UN_DEEP
+#define MVB_LZ_UN_DEEP 4
+#endif
+// most pending pivots between two flush passes: simplex_ps_kernel (12 measured there: no gain), and
+// the streaming variant simplex_ps_stream_kernel (HBM-bound batches: every pending pivot more divides
+// the flush traffic; two qmask bits per pivot limit both to 16)
+constexpr int LZ_KMAX = MVB_LZ_KMAX;
+constexpr int LZ_KMAX_STREAM = MVB_LZ_KMAX_STREAM;
+constexpr int LZ_KCAP = LZ_KMAX > LZ_KMAX_STREAM ? LZ_KMAX : LZ_KMAX_STREAM;
+static_assert(LZ_KMAX >= 1 && LZ_KMAX <= 8 && LZ_KMAX_STREAM >= LZ_KMAX && LZ_KMAX_STREAM <= 16, "LZ_KMAX");
 constexpr int MVB_PS_FALLBACK = 100;  // DevResult status: needs the general kernel
 constexpr int MVB_PS_HANDOVER = 101;  // DevResult status of the general kernel: phase 1 has reached a primal
                                       // feasible basis, phase 2 goes to the private-state kernel
@@ -164,16 +172,22 @@ namespace {
 struct Lay {
   unsigned nv, mv;
   int K;
+  int ring;  // flush reads staged through a per-thread cp.async ring of this many 16-byte slots (0: registers)
 };
 __host__ __device__ inline unsigned lz_nv(int ld) { return (unsigned)ld * 8u; }
 __host__ __device__ inline unsigned lz_mv(int m) { return ((unsigned)(m + 2) * 8u + 15u) & ~15u; }
 __host__ __device__ inline size_t lz_smem_bytes(int m, int ld, int K) {
   return (size_t)lz_nv(ld) * (K + 2) + (size_t)lz_mv(m) * (K + 4) + (size_t)(m + 2) * 4 + 16 +
-         sizeof(Key) * 64 + 16 /* mbarrier */ + 8 * LZ_KMAX /* (row, column) of the pending pivots */;
+         sizeof(Key) * 64 + 16 /* mbarrier */ + 8 * LZ_KCAP /* (row, column) of the pending pivots */;
 }
-// largest K <= LZ_KMAX that fits `avail` bytes (0: does not fit at all)
-__host__ __device__ inline int lz_pick_k(int m, int ld, size_t avail) {
-  for (int K = LZ_KMAX; K >= 1; K--)
+// the cp.async ring of the streaming flush follows the layout above (16-byte aligned)
+constexpr int LZ_RING_UN = 4;               // rows per block of the ring
+constexpr int LZ_RING_SLOTS = 2 * LZ_RING_UN;  // two blocks per thread: one being consumed, one in flight
+__host__ __device__ inline size_t lz_ring_off(int m, int ld, int K) { return (lz_smem_bytes(m, ld, K) + 15) & ~(size_t)15; }
+__host__ __device__ inline size_t lz_ring_bytes(int slots, int nt) { return (size_t)slots * nt * 16; }
+// largest K <= kmax that fits `avail` bytes (0: does not fit at all)
+__host__ __device__ inline int lz_pick_k(int m, int ld, size_t avail, int kmax = LZ_KMAX) {
+  for (int K = kmax; K >= 1; K--)
     if (lz_smem_bytes(m, ld, K) <= avail) return K;
   return 0;
 }
@@ -205,6 +219,8 @@ __device__ __forceinline__ Key (*zSlot(const Lay &l, int m))[32] {
 __device__ __forceinline__ unsigned long long *zMbar(const Lay &l, int m) {
   return reinterpret_cast<unsigned long long *>(zTail(l, m) + sizeof(Key) * 64);
 }
+
+__device__ __forceinline__ unsigned char *zRing(const Lay &l, int m, int ld) { return dyn_smem + lz_ring_off(m, ld, l.K); }
 
 // rows pr[p] = zPend[2p], columns pq[p] = zPend[2p+1] of the pending pivots
 __device__ __forceinline__ int *zPend(const Lay &l, int m) {
@@ -267,7 +283,56 @@ __device__ __forceinline__ double2 lz_chain(double2 o, const unsigned char *cb, 
   return o;
 }
 
+// The column pairs that hold a pending entering column q_p need the special cases of lz_step in
+// EVERY row.  Left to the threads that own them, they would drag their whole warp through the slow
+// chain next to the fast one (divergence: with 8 pending columns two warps in three, measured as
+// 3.3x the instructions of the pass), so the owners sit the streaming loop out and the CTA
+// re-derives those few pairs afterwards, rows spread over all threads: rows [ia, ib) of the
+// column chunk [c0, c1).
 template <int KC>
+__device__ __noinline__ void lz_flush_qpairs(const LZS *S, const Lay &l, const double *__restrict__ Ts,
+                                                double *__restrict__ Td, int ia, int ib, int c0, int c1) {
+  const int m = S->m, ld = S->ld;
+  const int *pend = zPend(l, m);
+  int pair[KC], npair = 0;  // distinct q pairs inside this chunk (the same list in every thread)
+#pragma unroll
+  for (int p = 0; p < KC; p++) {
+    const int cq = pend[2 * p + 1] & ~1;
+    bool take = cq >= c0 && cq < c1;
+#pragma unroll
+    for (int e = 0; e < p; e++) take &= (pend[2 * e + 1] & ~1) != cq;
+#pragma unroll
+    for (int e = 0; e < KC; e++)
+      if (e == npair && take) pair[e] = cq;  // (static indexing: the list stays in registers)
+    npair += take;
+  }
+  // (rows of one pair after the other, one element per thread and trip: a version that issued four
+  // loads per thread first measured slower on the batch AND cost the unrelated configs[1] path 8 %
+  // through code placement / register allocation of the whole kernel, profiles/r2_runs/r2q_ab.txt)
+  for (int p = 0; p < npair; p++) {
+    int cq = 0;
+#pragma unroll
+    for (int e = 0; e < KC; e++)
+      if (e == p) cq = pair[e];
+    for (int i = ia + (int)threadIdx.x; i < ib; i += (int)blockDim.x) {
+      double2 o = ldcg2(Ts + (size_t)i * ld + cq);
+      for (int e = 0; e < KC; e++) {
+        const double c = zCol(l, e)[i];
+        const double2 rh = *reinterpret_cast<const double2 *>(zRho(l, e) + cq);
+        const int qe = pend[2 * e + 1];
+        const bool isr = i == pend[2 * e];
+        o.x = lz_step(o.x, isr, cq == qe, c, rh.x);
+        o.y = lz_step(o.y, isr, cq + 1 == qe, c, rh.y);
+      }
+      stcg2(Td + (size_t)i * ld + cq, o);
+    }
+  }
+}
+
+// PEEL (one CTA per LP): the owners of a q pair sit the loop out, lz_flush_qpairs re-derives those
+// pairs afterwards (see there).  A group of CTAs keeps them in the loop: with a dozen rows per CTA
+// and chunk the extra pass would cost a dependent L2 round trip per flush.
+template <int KC, bool PEEL>
 __device__ __noinline__ void lz_flush_k(const LZS *S) {
   const Lay l = S->lay;
   const int m = S->m, ld = S->ld, tcl = S->tcl, g = S->g, G = S->G;
@@ -300,14 +365,21 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
     const unsigned segend = u1 < chend ? u1 : chend;
     const int ib = ia + (int)(segend - u0);
     const int col = ch * CW + 2 * tx;
-    if (col < ld) {
+    bool mine = col < ld;
+    if (PEEL) {
+#pragma unroll
+      for (int p = 0; p < KC; p++) mine &= (pend[2 * p + 1] & ~1) != col;
+    }
+    if (mine) {
       double2 rh[KC];
-      unsigned qmask = 0;  // bit 2p: col == q_p, bit 2p+1: col + 1 == q_p
+      unsigned qmask = 0;  // bit 2p: col == q_p, bit 2p+1: col + 1 == q_p (PEEL: never set)
 #pragma unroll
       for (int p = 0; p < KC; p++) {
         rh[p] = *reinterpret_cast<const double2 *>(zRho(l, p) + col);
-        const int qp = pend[2 * p + 1];
-        qmask |= (col == qp ? 1u : 0u) << (2 * p) | (col + 1 == qp ? 1u : 0u) << (2 * p + 1);
+        if (!PEEL) {
+          const int qp = pend[2 * p + 1];
+          qmask |= (col == qp ? 1u : 0u) << (2 * p) | (col + 1 == qp ? 1u : 0u) << (2 * p + 1);
+        }
       }
       const size_t rs = (size_t)trows * ld;  // row step of this thread, in doubles
       const double *src = Ts + (size_t)(ia + ty) * ld + col;
@@ -338,40 +410,169 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
       for (; i < ib; i += trows, src += rs, dst += rs)
         stcg2(dst, lz_chain<KC, true>(ldcg2(src), colbase + (size_t)i * 8, mv, rh, pr, qmask, i));
     }
+    if (PEEL) lz_flush_qpairs<KC>(S, l, Ts, Td, ia, ib, ch * CW, min(ch * CW + CW, ld));
     u0 = segend;
+  }
+}
+
+// ---- the same pass with the reads staged through shared memory by cp.async (LDGSTS) ----
+// HBM-streaming batches (one CTA per LP, tableaux far larger than L2): the register path above has
+// 4 rows x 16 B per thread in flight and issues the next loads only after the fma chains of the
+// current rows, so a CTA sustains ~15 GB/s against a loaded DRAM latency of ~1 us (phase clocks,
+// profiles/r2_runs/r2m_prof_batch.txt).  Here every thread keeps a private ring of two 4-row
+// blocks in shared memory: the block after next is requested the moment a block has been read out
+// of the ring, so 8 x 16 B per thread stay in flight THROUGH the arithmetic and cost no registers.
+// A thread reads only what it requested itself (cp.async.wait_group): no barrier, no mbarrier.
+__device__ __forceinline__ void cp_async16(unsigned dst, const void *src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ double2 lds2(unsigned addr) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr) : "memory");
+  return v;
+}
+
+template <int KC>
+__device__ __noinline__ void lz_flush_ring_k(const LZS *S) {
+  const Lay l = S->lay;
+  const int m = S->m, ld = S->ld, tcl = S->tcl, g = S->g, G = S->G;
+  const double *__restrict__ Ts = S->T[S->cT];
+  double *__restrict__ Td = S->T[S->cT ^ 1];
+  const int R = m + 1;
+  const int tcols = 1 << tcl, trows = blockDim.x >> tcl;
+  const int tx = threadIdx.x & (tcols - 1), ty = threadIdx.x >> tcl;
+  const int CW = 2 * tcols, nch = (ld + CW - 1) / CW;
+  const int *pend = zPend(l, m);
+  const unsigned mv = l.mv;
+  const unsigned char *colbase = zM(l);
+  int pr[KC];
+#pragma unroll
+  for (int p = 0; p < KC; p++) pr[p] = pend[2 * p];
+  const unsigned nunits = (unsigned)nch * (unsigned)R;
+  unsigned u0 = (unsigned)((unsigned long long)nunits * (unsigned)g / (unsigned)G);
+  const unsigned u1 = (unsigned)((unsigned long long)nunits * (unsigned)(g + 1) / (unsigned)G);
+  constexpr int UN = LZ_RING_UN;
+  // slot s of this thread: ring0 + s * sstep (consecutive threads, consecutive 16-byte units)
+  const unsigned sstep = blockDim.x * 16u;
+  const unsigned ring0 = smem_u32(zRing(l, m, ld)) + threadIdx.x * 16u;
+  while (u0 < u1) {
+    const int ch = (int)(u0 / (unsigned)R);
+    const int ia = (int)(u0 - (unsigned)ch * (unsigned)R);
+    const unsigned chend = (unsigned)(ch + 1) * (unsigned)R;
+    const unsigned segend = u1 < chend ? u1 : chend;
+    const int ib = ia + (int)(segend - u0);
+    const int col = ch * CW + 2 * tx;
+    bool mine = col < ld;
+#pragma unroll
+    for (int p = 0; p < KC; p++) mine &= (pend[2 * p + 1] & ~1) != col;  // q pairs: lz_flush_qpairs below
+    if (mine) {
+      double2 rh[KC];
+      constexpr unsigned qmask = 0;
+#pragma unroll
+      for (int p = 0; p < KC; p++) rh[p] = *reinterpret_cast<const double2 *>(zRho(l, p) + col);
+      const size_t rs = (size_t)trows * ld;
+      const double *src = Ts + (size_t)(ia + ty) * ld + col;
+      double *dst = Td + (size_t)(ia + ty) * ld + col;
+      const unsigned span = (unsigned)(trows * UN);
+      // prologue: the first two blocks (a commit per block even when it is empty: the group count
+      // the waits rely on stays the same for every thread and every tail)
+      int iload = ia + ty;
+      const double *lsrc = src;
+#pragma unroll
+      for (int b = 0; b < 2; b++) {
+#pragma unroll
+        for (int u = 0; u < UN; u++)
+          if (iload + u * trows < ib) cp_async16(ring0 + (unsigned)(b * UN + u) * sstep, lsrc + rs * u);
+        cp_async_commit();
+        iload += trows * UN;
+        lsrc += rs * UN;
+      }
+      unsigned blk = 0;  // which half of the ring holds the block being consumed
+      for (int i = ia + ty; i < ib; i += trows * UN, src += rs * UN, dst += rs * UN, blk ^= (unsigned)UN) {
+        cp_async_wait<1>();  // all but the newest block have landed: the block of row i is in the ring
+        double2 t[UN];
+#pragma unroll
+        for (int u = 0; u < UN; u++) t[u] = lds2(ring0 + (blk + (unsigned)u) * sstep);
+        // its slots are free again: request the block after next (same thread, program order)
+#pragma unroll
+        for (int u = 0; u < UN; u++)
+          if (iload + u * trows < ib) cp_async16(ring0 + (blk + (unsigned)u) * sstep, lsrc + rs * u);
+        cp_async_commit();
+        iload += trows * UN;
+        lsrc += rs * UN;
+        bool special = qmask != 0 || i + (UN - 1) * trows >= ib;  // (a tail block takes the guarded path)
+#pragma unroll
+        for (int p = 0; p < KC; p++) special |= (unsigned)(pr[p] - i) < span;
+        const unsigned char *cb = colbase + (size_t)i * 8;
+        if (!special) {
+#pragma unroll
+          for (int u = 0; u < UN; u++)
+            stcg2(dst + rs * u, lz_chain<KC, false>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, 0));
+        } else {
+#pragma unroll
+          for (int u = 0; u < UN; u++)
+            if (i + u * trows < ib)
+              stcg2(dst + rs * u,
+                    lz_chain<KC, true>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, i + u * trows));
+        }
+      }
+      cp_async_wait<0>();  // (only empty groups are left)
+    }
+    lz_flush_qpairs<KC>(S, l, Ts, Td, ia, ib, ch * CW, min(ch * CW + CW, ld));
+    u0 = segend;
+  }
+}
+
+// STREAM (simplex_ps_stream_kernel, one CTA per LP, tableaux streamed from HBM): peeled passes, reads
+// through the cp.async ring when the launch has room for it, up to LZ_KMAX_STREAM pending pivots.
+// Otherwise exactly the pass simplex_ps_kernel has always run.
+template <bool STREAM, int KC>
+__device__ __forceinline__ void lz_flush_pick(LZS *S) {
+  if (STREAM) {
+    if (S->lay.ring) lz_flush_ring_k<KC>(S);
+    else lz_flush_k<KC, true>(S);
+  } else {
+    lz_flush_k < KC <= LZ_KMAX ? KC : LZ_KMAX, false > (S);
   }
 }
 
 // flush + arrive at the group barrier; the wait is deferred to the next read
 // of the tableau (lz_need_tableau)
+template <bool STREAM>
 __device__ __forceinline__ void lz_flush(LZS *S) {
   const int np = S->np;
   if (np == 0) return;
-  switch (np) {
-    case 1: lz_flush_k<1>(S); break;
-    case 2: lz_flush_k<2>(S); break;
-    case 3: lz_flush_k<3>(S); break;
-    case 4: lz_flush_k<4>(S); break;
-    case 5: lz_flush_k<5>(S); break;
-    case 6: lz_flush_k<6>(S); break;
-    case 7: lz_flush_k<7>(S); break;
-#if MVB_LZ_KMAX > 8
-    case 8: lz_flush_k<8>(S); break;
-    case 9: lz_flush_k<9>(S); break;
-    case 10: lz_flush_k<10>(S); break;
-    case 11: lz_flush_k<11>(S); break;
-    case 12: lz_flush_k<12>(S); break;
-#if MVB_LZ_KMAX > 12
-    case 13: lz_flush_k<13>(S); break;
-    case 14: lz_flush_k<14>(S); break;
-    case 15: lz_flush_k<15>(S); break;
-    default: lz_flush_k<16>(S); break;
+  if (!STREAM || np <= 8) {
+    switch (np) {
+      case 1: lz_flush_pick<STREAM, 1>(S); break;
+      case 2: lz_flush_pick<STREAM, 2>(S); break;
+      case 3: lz_flush_pick<STREAM, 3>(S); break;
+      case 4: lz_flush_pick<STREAM, 4>(S); break;
+      case 5: lz_flush_pick<STREAM, 5>(S); break;
+      case 6: lz_flush_pick<STREAM, 6>(S); break;
+      case 7: lz_flush_pick<STREAM, 7>(S); break;
+      default: lz_flush_pick<STREAM, 8>(S); break;
+    }
+  } else {
+    switch (np) {
+      case 9: lz_flush_pick<STREAM, 9>(S); break;
+      case 10: lz_flush_pick<STREAM, 10>(S); break;
+      case 11: lz_flush_pick<STREAM, 11>(S); break;
+#if MVB_LZ_KMAX_STREAM > 12
+      case 12: lz_flush_pick<STREAM, 12>(S); break;
+      case 13: lz_flush_pick<STREAM, 13>(S); break;
+      case 14: lz_flush_pick<STREAM, 14>(S); break;
+      case 15: lz_flush_pick<STREAM, 15>(S); break;
+      default: lz_flush_pick<STREAM, 16>(S); break;
 #else
-    default: lz_flush_k<12>(S); break;
+      default: lz_flush_pick<STREAM, 12>(S); break;
 #endif
-#else
-    default: lz_flush_k<8>(S); break;
-#endif
+    }
   }
   __syncthreads();  // all stores of this CTA issued
   if (threadIdx.x == 0) {
@@ -931,12 +1132,13 @@ namespace {
 // neither changes mode).  Entered after the common prologue (beta[cS] valid in
 // global memory); leaves the final small state in the global arrays of parity
 // cS and the final tableau in buffer cT, as the general loop does.
+template <bool STREAM>
 __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &gen, int tcl,
-                       int K, int mode, int &cT, int cS, Tally &ty) {
+                       int K, int ring, int mode, int &cT, int cS, Tally &ty) {
   const int m = L.m, n = L.n, ld = L.ld, tid = threadIdx.x, NT = blockDim.x;
   __shared__ LZS ctx;
   LZS *S = &ctx;
-  const Lay l{lz_nv(ld), lz_mv(m), K};
+  const Lay l{lz_nv(ld), lz_mv(m), K, ring};
   if (tid == 0) {
     S->lb = L.lb; S->ub = L.ub; S->T[0] = L.T[0]; S->T[1] = L.T[1];
     S->pivlog = L.pivlog; S->pivlog_cap = L.pivlog_cap; S->ctr = ctr; S->lay = l;
@@ -989,7 +1191,7 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
       q = (int)(unsigned)qr;
       if (q < 0) { status = MVB_NOFEAS; break; }
       rnext = (int)(qr >> 32);
-      if (S->np == K) lz_flush(S);
+      if (S->np == K) lz_flush<STREAM>(S);
       continue;
     } else {
       q = qnext != -2 ? qnext : lz_price(S);
@@ -1002,7 +1204,7 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
       if (r < 0) { status = MVB_UNBND; break; }
       if (r > 0) {  // pivot: the private state is updated and the next column priced
         qnext = (int)(rq >> 32);
-        if (S->np == K) lz_flush(S);
+        if (S->np == K) lz_flush<STREAM>(S);
         continue;
       }
     }
@@ -1010,7 +1212,7 @@ __device__ int lz_loop(const LPDev &L, int g, int G, unsigned *ctr, unsigned &ge
     PROF(5);
   }
   __syncthreads();
-  lz_flush(S);
+  lz_flush<STREAM>(S);
   lz_need_tableau(S);
   __syncthreads();
   // the next LP of this CTA lays its shared memory out afresh: the barrier object must not stay

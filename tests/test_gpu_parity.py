@@ -249,11 +249,61 @@ def test_hbm_streaming_batch_matches_oracle(oracle, product):
     G, groups, nt = C.c_int(), C.c_int(), C.c_int()
     product.mvb_last_launch(C.byref(G), C.byref(groups), C.byref(nt))
     assert G.value == 1 and nt.value == 256 and groups.value == 160
+    # a streaming batch runs simplex_ps_stream_kernel: 12 pending pivots per flush pass here (the
+    # cp.async ring does not fit next to them with two CTAs per SM)
+    opt = product.mvb_engine_option
+    assert opt(b"last_stream", -1) == 1 and opt(b"last_lz_k", -1) == 12 and opt(b"last_ring", -1) == 0
     for k, (w, r) in enumerate(zip(work, res)):
         ra, xa = ref[k % 16]
         for key in ("status", "iters", "pivots", "pivot_hash", "obj"):
             assert r[key] == ra[key], (k, key)
         assert np.array_equal(w.primal(), xa)
+    # A/B: depth 8 with the flush reads staged through the per-thread cp.async ring, then the same
+    # depth through registers: the same bits every time (tableau bytes included)
+    T12 = work[3].tableau()
+    try:
+        opt(b"lz_k", 8)
+        work2 = [tmpl[k % 16].clone() for k in range(160)]
+        res2 = solve_batch(product, work2)
+        assert opt(b"last_stream", -1) == 1 and opt(b"last_lz_k", -1) == 8 and opt(b"last_ring", -1) == 8
+        assert opt(b"lz_ring", 0) == 8
+        work3 = [tmpl[k % 16].clone() for k in range(160)]
+        res3 = solve_batch(product, work3)
+        assert opt(b"last_ring", -1) == 0 and opt(b"last_lz_k", -1) == 8
+    finally:
+        opt(b"lz_ring", 1)
+        opt(b"lz_k", 0)
+    for r, r2, r3 in zip(res, res2, res3):
+        assert r == r2 == r3
+    for w in (work2[3], work3[3]):
+        Tw = w.tableau()
+        assert np.array_equal(T12[0], Tw[0]) and np.array_equal(T12[1], Tw[1])
+
+
+@pytest.mark.parametrize("m,n,nlp", [(100, 300, 900), (256, 130, 700), (64, 1000, 600)])
+def test_hbm_streaming_batch_ragged_shapes(oracle, product, m, n, nlp):
+    """Streaming launches whose rows do not divide into ring blocks of 4 and whose CTAs hold several
+    rows per pass (narrow tableaux): tails of the cp.async ring flush."""
+    insts = [instances.dense_lp(m, n, 700 + k) for k in range(4)]
+    ref = []
+    for inst in insts:
+        a = EngineLP.from_instance(oracle, inst)
+        ref.append((a.solve(), a.primal(), a.tableau()))
+    tmpl = [EngineLP.from_instance(product, inst) for inst in insts]
+    work = [tmpl[k % 4].clone() for k in range(nlp)]
+    product.mvb_engine_option(b"no_res", 1)   # these fit the resident kernel: keep them on the lazy loop
+    try:
+        res = solve_batch(product, work)
+    finally:
+        product.mvb_engine_option(b"no_res", 0)
+    assert product.mvb_last_kernel_mode() == 1
+    for k in (0, 1, 2, 3, nlp - 1):
+        ra, xa, (Ta, ba) = ref[k % 4]
+        for key in ("status", "iters", "pivots", "pivot_hash", "obj"):
+            assert res[k][key] == ra[key], (k, key)
+        assert np.array_equal(work[k].primal(), xa)
+        Tb, bb = work[k].tableau()
+        assert np.array_equal(Ta, Tb) and np.array_equal(ba, bb)
 
 
 def _kat_instances():
