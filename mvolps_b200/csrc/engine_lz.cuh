@@ -40,6 +40,9 @@ constexpr int PS_CREG = 8;            // pivot-column values a thread can hold i
 #ifndef MVB_LZ_UN_DEEP
 #define MVB_LZ_UN_DEEP 4
 #endif
+#ifndef MVB_LZ_PF
+#define MVB_LZ_PF 4  // streaming register-path flush: L2 prefetch distance in 4-row blocks (0: none); 2: 14.7, 4: 14.9, 8: 13.8 M LP-pivots/s
+#endif
 // most pending pivots between two flush passes: simplex_ps_kernel (12 measured there: no gain), and
 // the streaming variant simplex_ps_stream_kernel (HBM-bound batches: every pending pivot more divides
 // the flush traffic; two qmask bits per pivot limit both to 16)
@@ -306,9 +309,10 @@ __device__ __noinline__ void lz_flush_qpairs(const LZS *S, const Lay &l, const d
       if (e == npair && take) pair[e] = cq;  // (static indexing: the list stays in registers)
     npair += take;
   }
-  // (rows of one pair after the other, one element per thread and trip: a version that issued four
-  // loads per thread first measured slower on the batch AND cost the unrelated configs[1] path 8 %
-  // through code placement / register allocation of the whole kernel, profiles/r2_runs/r2q_ab.txt)
+  // rows of one pair after the other, one element per thread and trip.  Each element is a DRAM sector
+  // of its own (8 % of the kernel's stall samples sit on these loads, profiles/r2_stream_kernel_summary.txt),
+  // but flattening the (pair, row) items over the threads and requesting them into L2 first measured
+  // no faster (14.85 against 14.91 M LP-pivots/s): the other CTA of the SM fills the gaps.
   for (int p = 0; p < npair; p++) {
     int cq = 0;
 #pragma unroll
@@ -388,6 +392,14 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
       int i = ia + ty;
       for (; i + (UN - 1) * trows < ib; i += trows * UN, src += rs * UN, dst += rs * UN) {
         double2 t[UN];
+#if MVB_LZ_PF > 0
+        if (PEEL) {  // streaming kernel: the rows MVB_LZ_PF blocks ahead on their way into L2 (costs no registers)
+#pragma unroll
+          for (int u = 0; u < UN; u++)
+            if (i + (UN * MVB_LZ_PF + u) * trows < ib)
+              asm volatile("prefetch.global.L2 [%0];" ::"l"(src + rs * (UN * MVB_LZ_PF + u)));
+        }
+#endif
 #pragma unroll
         for (int u = 0; u < UN; u++) t[u] = ldcg2(src + rs * u);
         // pivot rows / columns of the pending updates need the special cases
