@@ -213,7 +213,7 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks, steps=None, 
     kw = dict(cut_mode=args.cut_mode, batch_width=args.batch_width, max_iters=args.nodes,
               no_steal=int(args.no_steal), node_strategy=args.node_strategy,
               no_speculation=int(args.no_speculation), total_budget=1, root_heuristic=int(args.root_heuristic),
-              dist_mode=args.dist_mode, cut_freq=args.cut_freq)
+              dist_mode=args.dist_mode, cut_freq=args.cut_freq, no_event_text=1)
     key = f"mdkp_{args.n or 200}x{args.m or 50}_s{args.inst_seed}_bs{args.node_strategy}_cm{args.cut_mode}_rh{int(args.root_heuristic)}_n{args.nodes}"
     gold = golden()["bnb"].get(key) if args.cut_freq == 1.0 else None
     for _ in range(warmup):
@@ -252,7 +252,8 @@ def run_bnb(args, L, rank, world, local, dist, ClockSampler, peaks, steps=None, 
                                + (", root rounding heuristic" if args.root_heuristic else "")
                                + (" (BASELINE configs[3] node-LP shape)" if (args.n, args.m) == (512, 256) else
                                   " (BASELINE configs[2])") + "; host wall clock around mvb_bnb_run[_dist] (host logic + "
-                               "H2D/D2H included)"
+                               "H2D/D2H included); event lines not formatted (the reference formats them only with "
+                               "--server), event hash computed and asserted"
                                + ("" if world == 1 else
                                   ("; one tree, round-synchronous sequence-identical mode" if args.dist_mode == 1 else
                                    "; one tree node-sharded over the ranks, NCCL incumbent max-reduction per round, "
@@ -293,7 +294,7 @@ def run_bnb_close(args, L, rank, world, local, dist, comm=None):
     own_comm = comm is None and dist is not None
     if own_comm:
         comm = nccl_comm(L, rank, world, dist)
-    kw = dict(batch_width=args.batch_width, no_steal=int(args.no_steal), dist_mode=args.dist_mode)
+    kw = dict(batch_width=args.batch_width, no_steal=int(args.no_steal), dist_mode=args.dist_mode, no_event_text=1)
     _bnb_once(L, prob, comm, **kw)
     if dist is not None:
         dist.barrier()

@@ -70,6 +70,9 @@ typedef struct mvb_bnb_params {
                          reference never reads): cuts are generated at a branched node with probability
                          1 - cut_skip, decided by a fixed hash of the node's oid (reproducible); 0 = at
                          every branched node, as the reference does */
+  int no_event_text;  /* !=0: the event lines are not formatted and mvb_bnb_event_text is empty (the reference
+                         formats and sends them only with --server, message.cpp:32-168); the event hash,
+                         which covers (event, oid, pid, prune tag), is computed all the same */
 } mvb_bnb_params;
 
 typedef struct mvb_bnb_stats {

@@ -77,7 +77,7 @@ class BnbParams(C.Structure):
                 ("batch_width", C.c_int), ("max_iters", C.c_int), ("quiet", C.c_int), ("no_steal", C.c_int),
                 ("no_speculation", C.c_int), ("timed_events", C.c_int), ("total_budget", C.c_int),
                 ("cut_select", C.c_int), ("root_heuristic", C.c_int), ("dist_mode", C.c_int),
-                ("cut_skip", C.c_double)]
+                ("cut_skip", C.c_double), ("no_event_text", C.c_int)]
 
 
 class BnbStats(C.Structure):

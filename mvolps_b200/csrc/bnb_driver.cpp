@@ -817,11 +817,26 @@ bool Driver::run() {
   std::deque<std::unique_ptr<Node>> open;  // leafContainer, bs.cpp:79
   std::vector<std::string> evs;            // event lines (candidates filled late)
   std::vector<double> ev_ms;               // timed_events: BaseMessagePOD::timeSpan (message.h:142-146)
+  // no_event_text: nothing is formatted or kept; the hash takes what it would have taken from the
+  // line -- the characters of "type oid pid", up to the third blank -- as the event happens
+  const bool keep_text = !pr.no_event_text;
+  size_t nev = 0;
   auto ev_line = [&](const char *type, int oid, const std::string &fields) {
+    if (!keep_text) {
+      char buf[32];
+      for (const char *c = type; *c; c++) hash_mix((unsigned char)*c);
+      hash_mix((unsigned char)' ');
+      for (const char *c = buf, *e = std::to_chars(buf, buf + sizeof buf, oid).ptr; c < e; c++) hash_mix((unsigned char)*c);
+      hash_mix((unsigned char)' ');
+      for (const char *c = buf, *e = std::to_chars(buf, buf + sizeof buf, pid_of(oid)).ptr; c < e; c++) hash_mix((unsigned char)*c);
+      return nev++;
+    }
     if (pr.timed_events) ev_ms.push_back(1e3 * (now() - t_run0));
     evs.push_back(sstr(type, " ", oid, " ", pid_of(oid), " ", dir_of(oid), fields));
     return evs.size() - 1;
   };
+  // the fields of an event line (formatted only when the text is kept)
+  auto fld = [&](auto &&...a) { return keep_text ? sstr(a...) : std::string(); };
 
   {  // S1, bs.cpp:80-87
     glp_prob *c = glp_create_prob();
@@ -885,7 +900,7 @@ bool Driver::run() {
             const double *p = buf.data() + 1;
             for (int k = 0; k < sp.k; k++) {
               auto nd = unpack_node(p);
-              ev_line("candidate", nd->oid, sstr(" ", nd->upperBound));
+              ev_line("candidate", nd->oid, fld(" ", nd->upperBound));
               open.push_back(std::move(nd));
             }
             out->st.nodes_received += sp.k;
@@ -934,7 +949,7 @@ bool Driver::run() {
       Node *node = nd.get();
       glp_prob *a = node->prob;
       TreeRec &rec = tree[node->oid];
-      ev_line("pregnant", node->oid, sstr(" ", glp_get_obj_val(a), " 1 2"));
+      ev_line("pregnant", node->oid, fld(" ", glp_get_obj_val(a), " 1 2"));
       std::vector<int> vars;
       int status = classify(a, vars);
       if (node->initial) {  // bs.cpp:134-149
@@ -946,7 +961,7 @@ bool Driver::run() {
         double hobj;
         if (floor_point(a, hx, hobj) && hobj > bestLower) {
           bestLower = hobj;
-          ev_line("heuristic", node->oid, sstr(" ", hobj));
+          ev_line("heuristic", node->oid, fld(" ", hobj));
           solution = sstr("[", node->oid, "] Heuristic solution (root LP rounded down) = ", hobj, "\n");
           out->incumbent = hx;
           out->st.has_incumbent = 1;
@@ -957,7 +972,7 @@ bool Driver::run() {
       node->upperBound = glp_get_obj_val(a);
       if (status == 1) {  // bs.cpp:158-193
         rec.prune = P_INTG;
-        ev_line("integer", node->oid, sstr(" ", node->upperBound));
+        ev_line("integer", node->oid, fld(" ", node->upperBound));
         if (node->upperBound > bestLower) {
           bestLower = node->upperBound;
           solution = sstr("[", node->oid, "] Solution is: ");
@@ -982,7 +997,7 @@ bool Driver::run() {
       } else {  // branch, bs.cpp:224-324
         double acc = 0;
         for (int i : vars) acc += get_fract(glp_get_col_prim(a, i));
-        ev_line("branched", node->oid, sstr(" ", node->upperBound, " ", acc, " ", vars.size(), " 1 2"));
+        ev_line("branched", node->oid, fld(" ", node->upperBound, " ", acc, " ", vars.size(), " 1 2"));
         if (pr.cut_mode != MVB_CUT_NONE && cuts_wanted(node->oid)) {
           const size_t bk = consumed - 1;
           std::vector<double> one;
@@ -1052,7 +1067,7 @@ bool Driver::run() {
       if (!solve_many(ps)) return false;
       for (auto &k : kids) {
         k.node->upperBound = glp_get_obj_val(k.node->prob);
-        evs[k.ev_slot] += sstr(" ", k.node->upperBound);
+        if (keep_text) evs[k.ev_slot] += sstr(" ", k.node->upperBound);
         if (pr.node_strategy == MVB_NODE_BEST) {
           open_ub.push_back(k.node->upperBound);
           open_tried.push_back(0);

@@ -83,6 +83,7 @@ int main(int argc, char **argv) {
     p.cut_skip = 1.0 - chance;
   }
   p.root_heuristic = in.has("-rh");
+  p.no_event_text = !in.has("-ev");  // the event lines are formatted only when they are written somewhere
   p.timed_events = in.has("-ev");
   int np = 1;
   if (!ival("-np", 1, 16, np) || !ival("-dm", 0, 1, p.dist_mode)) return -1;

@@ -213,11 +213,12 @@ class GlpProb:
 
     def bnb(self, node_strategy=0, var_strategy=0, cut_mode=0, batch_width=0, max_iters=0, comm=None,
             no_steal=0, no_speculation=0, timed_events=0, total_budget=0, cut_select=0, root_heuristic=0,
-            dist_mode=0, cut_freq=1.0):
+            dist_mode=0, cut_freq=1.0, no_event_text=0):
         """comm: None (serial driver) or a communicator (capi.Comm / pointer) for the node-sharded run."""
         L = self.lib
         p = capi.BnbParams(node_strategy, var_strategy, cut_mode, batch_width, max_iters, 1, no_steal, no_speculation,
-                           timed_events, total_budget, cut_select, root_heuristic, dist_mode, 1.0 - cut_freq)
+                           timed_events, total_budget, cut_select, root_heuristic, dist_mode, 1.0 - cut_freq,
+                           no_event_text)
         if comm is None:
             hb = L.mvb_bnb_run(self.h, C.byref(p))
         else:

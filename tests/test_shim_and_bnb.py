@@ -246,6 +246,20 @@ def test_timed_event_stream(oracle, tmp_path):
     assert [l.split(" ", 1)[1] for l in b] == a and ts == sorted(ts) and ts[0] >= 0.0
 
 
+@pytest.mark.parametrize("kw", [dict(), dict(cut_mode=2, max_iters=400), dict(node_strategy=1, var_strategy=2, batch_width=8),
+                                dict(root_heuristic=1, max_iters=300)])
+def test_event_hash_without_the_event_text(oracle, tmp_path, kw):
+    """no_event_text (what the CLI does without -ev and bench.py inside its timed region): no line is
+    formatted or kept, the event hash -- (event, oid, pid) of every event in order, then (oid, prune
+    tag) of every node -- and everything else are those of the run that keeps the text."""
+    case = [c for c in _gold() if c["name"] == "mdkp_15x5_s2"][0]
+    full = _prob(oracle, case, tmp_path).bnb(**kw)
+    bare = _prob(oracle, case, tmp_path).bnb(no_event_text=1, **kw)
+    assert full["events"] and bare["events"] == ""
+    for key in ("event_hash", "tree", "solution", "iterations", "oids", "incumbent", "lp_solves", "simplex_iters"):
+        assert full[key] == bare[key], key
+
+
 def test_bnb_live_reference_driver(oracle, ref_bin, tmp_path):
     """Where /root/reference was compiled (oracle/_ref): run it now and compare stdout."""
     inst = instances.mdkp(11, 4, 9)
