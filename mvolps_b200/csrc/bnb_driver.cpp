@@ -461,6 +461,12 @@ struct Driver {
 
   bool cuts_wanted(int oid) const;
   std::vector<int> row_of;  // scratch of cut_rows_of
+  // what cut_rows_of found out when only ONE row has to cross PCIe (textbook GMI, the last pooled cut
+  // becomes the row, no free non-basic variable in the node: whether a column produces a cut is then
+  // decided by the fraction of its value alone): lean_k = position among the accepted columns of the
+  // last one that produces (-1: none), lean_pooled = how many produce; lean = false: every row
+  bool lean = false;
+  int lean_k = -1, lean_j = 0, lean_pooled = 0;
   void cut_rows_of(glp_prob *a, std::vector<int> &js, std::vector<int> &rows);
   void gen_cuts(glp_prob *a, const double *trows);
   void gen_cut_ref(glp_prob *a, int j, const double *trow);
@@ -758,6 +764,26 @@ void Driver::cut_rows_of(glp_prob *a, std::vector<int> &js, std::vector<int> &ro
     js.push_back(j);
     rows.push_back(row_of[j - 1]);
   }
+  lean = false;
+  if (pr.cut_mode == MVB_CUT_GMI && pr.cut_select == 0) {
+    bool any_free = false;
+    for (int p = 0; p < n; p++) any_free |= a->at[p] == MVB_AT_FR;
+    if (!any_free) {
+      // gmi_produces without the row: with no free non-basic variable it is the fraction test alone
+      lean = true;
+      lean_k = -1;
+      lean_pooled = 0;
+      int k = 0, last_row = 0;
+      for (int j : js) {
+        if (j < 0) continue;
+        const double f0 = get_fract(glp_get_col_prim(a, j));
+        if (!(f0 < 1e-6 || f0 > 1.0 - 1e-6)) { lean_k = k; lean_j = j; lean_pooled++; last_row = rows[k]; }
+        k++;
+      }
+      rows.clear();
+      if (lean_k >= 0) rows.push_back(last_row);
+    }
+  }
 }
 
 // bs.cpp:249-258: every basic GLP_IV column generates; the rows were gathered from the engine
@@ -769,7 +795,14 @@ void Driver::gen_cuts(glp_prob *a, const double *t) {
   cut_rows_of(a, js, rows);
   pool_trim();
   const size_t pool0 = pool.size();
-  if (pr.cut_select == 0) {
+  if (lean) {
+    // (cut_rows_of has walked the columns already: `t` holds the one row of the last column that
+    // produces a cut; the others are counted, as below)
+    if (lean_pooled) {
+      pool_base += lean_pooled - 1;
+      gen_cut_gmi(a, lean_j, t);
+    }
+  } else if (pr.cut_select == 0) {
     // Only the LAST cut the loop of bs.cpp:250-255 pools is ever read (cut.cpp:16-21), so only that
     // one is built: walk the columns in order to find which generator call is the last to pool a
     // cut (same accept / reject rules, same ref_oid_slot bookkeeping), count the others.
