@@ -184,7 +184,10 @@ __host__ __device__ inline size_t lz_smem_bytes(int m, int ld, int K) {
          sizeof(Key) * 64 + 16 /* mbarrier */ + 8 * LZ_KCAP /* (row, column) of the pending pivots */;
 }
 // the cp.async ring of the streaming flush follows the layout above (16-byte aligned)
-constexpr int LZ_RING_UN = 4;               // rows per block of the ring
+#ifndef MVB_LZ_RING_UN
+#define MVB_LZ_RING_UN 4
+#endif
+constexpr int LZ_RING_UN = MVB_LZ_RING_UN;  // rows per block of the ring
 constexpr int LZ_RING_SLOTS = 2 * LZ_RING_UN;  // two blocks per thread: one being consumed, one in flight
 __host__ __device__ inline size_t lz_ring_off(int m, int ld, int K) { return (lz_smem_bytes(m, ld, K) + 15) & ~(size_t)15; }
 __host__ __device__ inline size_t lz_ring_bytes(int slots, int nt) { return (size_t)slots * nt * 16; }
@@ -356,11 +359,11 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
   const unsigned nunits = (unsigned)nch * (unsigned)R;  // < 2^31 (checked on the host)
   unsigned u0 = (unsigned)((unsigned long long)nunits * (unsigned)g / (unsigned)G);
   const unsigned u1 = (unsigned)((unsigned long long)nunits * (unsigned)(g + 1) / (unsigned)G);
-  // rows in flight per thread: measured flat between 2 and 4 at K = 5, 6 and 8 spill (tools/ab.sh);
-  // an L2 prefetch of the rows ahead gained 5 % on HBM-streaming batches but cost the L2-resident
-  // path 4 % (register pressure), so it is not here; staging the reads through a 32-48 KB TMA ring
-  // (twice the bytes in flight, depth 6 to make room) measured 6-9 % SLOWER than this register path
-  // at depth 8: during the flush the batch already runs HBM at ~70 % of its copy peak
+  // rows in flight per thread: measured flat between 2 and 4 at K = 5, 6 and 8 spill (tools/ab.sh).
+  // The L2 prefetch of the rows ahead below is compiled into the PEEL instances only (the streaming
+  // kernel, +8.5 % there): in r1, inside the one kernel of that time, it cost the L2-resident path 4 %.
+  // A 32-48 KB TMA (bulk) ring measured 6-9 % slower than this register path in r1; the per-thread
+  // cp.async ring of lz_flush_ring_k needs no barrier and gains 12 % at depth 8.
   constexpr int UN = KC <= 4 ? 8 : KC <= 8 ? 4 : MVB_LZ_UN_DEEP;
   while (u0 < u1) {
     const int ch = (int)(u0 / (unsigned)R);
@@ -549,7 +552,11 @@ __device__ __forceinline__ void lz_flush_pick(LZS *S) {
     if (S->lay.ring) lz_flush_ring_k<KC>(S);
     else lz_flush_k<KC, true>(S);
   } else {
+#ifdef MVB_PEEL_GROUPS  // A/B: peeled passes for groups of CTAs as well (configs[1])
+    lz_flush_k < KC <= LZ_KMAX ? KC : LZ_KMAX, true > (S);
+#else
     lz_flush_k < KC <= LZ_KMAX ? KC : LZ_KMAX, false > (S);
+#endif
   }
 }
 

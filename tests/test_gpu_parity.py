@@ -235,7 +235,7 @@ def test_many_small_lps_use_narrow_ctas_and_match(oracle, product):
 
 def test_hbm_streaming_batch_matches_oracle(oracle, product):
     """configs[3] shape: more 256x512 LPs than SMs in one launch, tableaux (340 MB) far beyond L2:
-    256-thread CTAs, two per SM, pending depth 8.  Every copy must reproduce the oracle's pivot
+    256-thread CTAs, two per SM, pending depth 12 (simplex_ps_stream_kernel).  Every copy must reproduce the oracle's pivot
     sequence of its template (this regime once exposed a race on the TMA slot index)."""
     import ctypes as C
     insts = [instances.dense_lp(256, 512, 900 + k) for k in range(16)]
