@@ -741,6 +741,8 @@ void Driver::gen_cut_gmi(glp_prob *a, int j, const double *trow) {
     }
   }
   Cut c;
+  c.inds.reserve(n + 1);
+  c.vals.reserve(n + 1);
   c.inds.push_back(0);
   c.vals.push_back(rhs);
   for (int i = 1; i <= n; i++) { c.inds.push_back(i); c.vals.push_back(g[i]); }
@@ -769,12 +771,20 @@ void Driver::cut_rows_of(glp_prob *a, std::vector<int> &js, std::vector<int> &ro
   row_of.assign(n, 0);
   for (int i = 0; i < m; i++)
     if (a->head[i] < n) row_of[a->head[i]] = i + 1;
-  for (int j = 1; j <= n; j++) {
-    int kind = glp_get_col_kind(a, j);
-    bool ok = pr.cut_mode == MVB_CUT_REF ? kind == GLP_IV : kind != GLP_CV;
-    if (!ok || glp_get_col_stat(a, j) != GLP_BS || !row_of[j - 1]) { js.push_back(-j); continue; }
-    js.push_back(j);
-    rows.push_back(row_of[j - 1]);
+  js.reserve(n);
+  {
+    // (glp_get_col_kind / glp_get_col_stat of every column, read from the arrays they read)
+    const MvColM *cm = a->colm.data();
+    const MvBnd *cb = a->cbnd.data();
+    const int *cs = a->cstat.data();
+    for (int j = 1; j <= n; j++) {
+      int kind = cm[j - 1].kind;
+      if (kind == GLP_IV && cb[j - 1].type == GLP_DB && cb[j - 1].lb == 0.0 && cb[j - 1].ub == 1.0) kind = GLP_BV;
+      bool ok = pr.cut_mode == MVB_CUT_REF ? kind == GLP_IV : kind != GLP_CV;
+      if (!ok || cs[j - 1] != GLP_BS || !row_of[j - 1]) { js.push_back(-j); continue; }
+      js.push_back(j);
+      rows.push_back(row_of[j - 1]);
+    }
   }
   lean = false;
   if (pr.cut_mode == MVB_CUT_GMI && pr.cut_select == 0) {

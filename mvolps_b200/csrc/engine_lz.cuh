@@ -187,7 +187,8 @@ __host__ __device__ inline size_t lz_smem_bytes(int m, int ld, int K) {
 #ifndef MVB_LZ_RING_UN
 #define MVB_LZ_RING_UN 4
 #endif
-constexpr int LZ_RING_UN = MVB_LZ_RING_UN;  // rows per block of the ring
+constexpr int LZ_RING_UN = MVB_LZ_RING_UN;  // rows per block of the ring (3, which fits next to depth 11: 14.5 against 14.9 M
+                                            // LP-pivots/s of depth 12 without the ring, same file)
 constexpr int LZ_RING_SLOTS = 2 * LZ_RING_UN;  // two blocks per thread: one being consumed, one in flight
 __host__ __device__ inline size_t lz_ring_off(int m, int ld, int K) { return (lz_smem_bytes(m, ld, K) + 15) & ~(size_t)15; }
 __host__ __device__ inline size_t lz_ring_bytes(int slots, int nt) { return (size_t)slots * nt * 16; }
@@ -552,7 +553,8 @@ __device__ __forceinline__ void lz_flush_pick(LZS *S) {
     if (S->lay.ring) lz_flush_ring_k<KC>(S);
     else lz_flush_k<KC, true>(S);
   } else {
-#ifdef MVB_PEEL_GROUPS  // A/B: peeled passes for groups of CTAs as well (configs[1])
+#ifdef MVB_PEEL_GROUPS  // A/B: peeled passes for groups of CTAs as well: configs[1] 5.33 against 5.17 us per pivot
+                        // (profiles/r2_runs/r2y_peel_groups_ring6_ab.txt), so groups keep the in-loop handling
     lz_flush_k < KC <= LZ_KMAX ? KC : LZ_KMAX, true > (S);
 #else
     lz_flush_k < KC <= LZ_KMAX ? KC : LZ_KMAX, false > (S);

@@ -308,11 +308,15 @@ void glp_set_mat_row(glp_prob *P, int i, int len, const int ind[],
   if (len < 0 || len > n) shim_abort("glp_set_mat_row: invalid row length");
   std::vector<std::pair<int, double>> e;
   e.reserve(len);
+  bool ascending = true;
   for (int t = 1; t <= len; t++) {
     if (ind[t] < 1 || ind[t] > n) shim_abort("glp_set_mat_row: column index out of range");
-    if (val[t] != 0.0) e.emplace_back(ind[t], val[t]);
+    if (val[t] != 0.0) {
+      if (!e.empty() && ind[t] < e.back().first) ascending = false;
+      e.emplace_back(ind[t], val[t]);
+    }
   }
-  std::sort(e.begin(), e.end(), [](auto &a, auto &b) { return a.first < b.first; });
+  if (!ascending) std::sort(e.begin(), e.end(), [](auto &a, auto &b) { return a.first < b.first; });
   for (size_t t = 1; t < e.size(); t++)
     if (e[t].first == e[t - 1].first) shim_abort("glp_set_mat_row: duplicate column indices");
   MvRowM &r = P->rowm.w(k);
