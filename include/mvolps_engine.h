@@ -136,6 +136,15 @@ int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double ub);
 int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *opts,
                     mvb_result *out);
 
+/* the same solve in two halves, so that the host can work while the device does: begin enqueues the
+ * launch (bounds patches up, kernel, results down) and returns; end waits, runs what the first launch
+ * hands on (phase 1 / phase 2 hand-overs) and delivers out[count] in the order of begin's lps.  One
+ * batch at a time; between the two calls its LPs must not be touched, other LPs may be created,
+ * cloned, changed and freed (the batched B&B driver prepares the next round meanwhile, DESIGN.md
+ * section 3).  A batch that needs more than one first launch is solved inside begin. */
+int mvb_solve_batch_begin(mvb_lp *const *lps, int count, const mvb_opts *opts);
+int mvb_solve_batch_end(mvb_result *out);
+
 /* ---- read-back (only small vectors cross PCIe) ---- */
 /* x[n+m] by variable id (raw, no rounding) */
 int mvb_lp_get_primal(mvb_lp *lp, double *x);

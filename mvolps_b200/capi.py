@@ -40,7 +40,7 @@ ENGINE_SYMBOLS = [
     "mvb_backend", "mvb_last_error", "mvb_device_init", "mvb_kernel_launches",
     "mvb_timer_record", "mvb_timer_elapsed_ms", "mvb_flush_l2", "mvb_last_launch", "mvb_last_kernel_ms", "mvb_last_kernel_mode", "mvb_engine_option",
     "mvb_host_staging", "mvb_lp_create", "mvb_lp_free", "mvb_lp_load", "mvb_lp_clone", "mvb_lp_assign",
-    "mvb_lp_dims", "mvb_lp_set_bounds", "mvb_lp_append_row", "mvb_solve_batch",
+    "mvb_lp_dims", "mvb_lp_set_bounds", "mvb_lp_append_row", "mvb_solve_batch", "mvb_solve_batch_begin", "mvb_solve_batch_end",
     "mvb_lp_get_primal", "mvb_lp_get_basis", "mvb_lp_get_tab_rows", "mvb_lp_get_tab_rows_batch", "mvb_lp_get_tab_rows_noalloc",
     "mvb_lp_get_tableau", "mvb_lp_get_pivot_log",
 ]
@@ -159,6 +159,8 @@ def _bind(lib):
         "mvb_lp_set_bounds": (C.c_int, [_P, C.c_int, C.c_double, C.c_double]),
         "mvb_lp_append_row": (C.c_int, [_P, _dp, C.c_double, C.c_double]),
         "mvb_solve_batch": (C.c_int, [C.POINTER(_P), C.c_int, C.POINTER(Opts), C.POINTER(Result)]),
+        "mvb_solve_batch_begin": (C.c_int, [C.POINTER(_P), C.c_int, C.POINTER(Opts)]),
+        "mvb_solve_batch_end": (C.c_int, [C.POINTER(Result)]),
         "mvb_lp_get_primal": (C.c_int, [_P, _dp]),
         "mvb_lp_get_basis": (C.c_int, [_P, _ip, _ip, _ip]),
         "mvb_lp_get_tab_rows": (C.c_int, [_P, _ip, C.c_int, _dp]),

@@ -328,6 +328,51 @@ struct Driver {
     return true;
   }
 
+  // solve_many in two halves (mvb_solve_batch_begin / _end): the launch of one round's children
+  // stays in flight while the host consumes the next round's nodes (FIFO without cuts: those were
+  // created -- and solved -- rounds ago; Driver::run keeps one batch in flight)
+  std::vector<glp_prob *> fly_ps;
+  bool fly_counted = true;
+  bool solve_many_begin(const std::vector<glp_prob *> &all, bool counted = true) {
+    fly_ps.clear();
+    fly_counted = counted;
+    if (all.empty()) return true;
+    std::vector<mvb_lp *> engs;
+    const double t0 = now();
+    for (auto *p : all) {
+      bool changed = false;
+      if (mv_sync_engine(p, &changed)) return false;
+      if (mv_answer_cached(p, changed)) { if (counted) out->st.cached_solves++; continue; }
+      fly_ps.push_back(p);
+      engs.push_back(p->eng);
+    }
+    if (counted) out->st.lp_solves += (int)all.size();
+    const double t1 = now();
+    t_sync += t1 - t0;
+    if (fly_ps.empty()) return true;
+    mvb_opts o{};
+    if (mvb_solve_batch_begin(engs.data(), (int)engs.size(), &o)) return false;
+    out->st.solved_here += (int)engs.size();
+    t_solve += now() - t1;
+    return true;
+  }
+  bool solve_many_end() {
+    if (fly_ps.empty()) return true;
+    std::vector<mvb_result> res(fly_ps.size());
+    const double t0 = now();
+    if (mvb_solve_batch_end(res.data())) return false;
+    const double t1 = now();
+    for (size_t k = 0; k < fly_ps.size(); k++) {
+      if (mv_pull_solution(fly_ps[k], res[k])) return false;
+      if (fly_counted) out->st.simplex_iters += res[k].iters;
+    }
+    t_solve += t1 - t0;
+    t_pull += now() - t1;
+    out->st.launches++;
+    fly_ps.clear();
+    return true;
+  }
+
   // sync mode, end of the ramp-up: owners are dealt round-robin over the open nodes; a rank gives
   // up the device tableau of every node it does not own
   void deal_owners(std::deque<std::unique_ptr<Node>> &open) {
@@ -892,6 +937,31 @@ bool Driver::run() {
   };
   // the fields of an event line (formatted only when the text is kept)
   auto fld = [&](auto &&...a) { return keep_text ? sstr(a...) : std::string(); };
+  // One launch in flight (FIFO without cuts, not the round-synchronous mode): the children of round t
+  // are solved while the host consumes round t + 1, whose nodes were created -- and solved -- long
+  // before; the children's bounds (and the tail of their "candidate" events) are filled in when the
+  // launch is read back, which happens before any of them is popped, handed to another rank, or the
+  // next launch begins.  Decisions, ids, events and statistics are those of the unpipelined loop.
+  struct {
+    std::vector<Node *> nodes;
+    std::vector<size_t> slots;
+    int min_oid = std::numeric_limits<int>::max();
+    bool active = false;
+  } fly;
+  auto finish_fly = [&]() -> bool {
+    if (!fly.active) return true;
+    fly.active = false;
+    if (!solve_many_end()) return false;
+    for (size_t i = 0; i < fly.nodes.size(); i++) {
+      Node *k = fly.nodes[i];
+      k->upperBound = glp_get_obj_val(k->prob);
+      if (keep_text) evs[fly.slots[i]] += sstr(" ", k->upperBound);
+    }
+    fly.nodes.clear();
+    fly.slots.clear();
+    fly.min_oid = std::numeric_limits<int>::max();
+    return true;
+  };
 
   {  // S1, bs.cpp:80-87
     glp_prob *c = glp_create_prob();
@@ -920,6 +990,8 @@ bool Driver::run() {
 
   sync_mode = comm != nullptr && comm->world > 1 && pr.dist_mode == MVB_DIST_SYNC;
   const bool dist = comm != nullptr && comm->world > 1 && !sync_mode;
+  const bool pipe = pr.node_strategy != MVB_NODE_BEST && pr.cut_mode == MVB_CUT_NONE && !sync_mode &&
+                    !getenv("MVOLPS_BNB_NO_PIPELINE");
   const bool steal = dist && !pr.no_steal && comm->sendrecv_host != nullptr;
   bool split = false;        // dist: the queue has been dealt out, ranks now work on their own share
   bool retired = false;      // dist: this rank hit its budget and only takes part in the exchanges
@@ -936,6 +1008,7 @@ bool Driver::run() {
         if (!pairs.empty()) out->st.steal_rounds++;
         for (const StealPair &sp : pairs) {
           if (sp.donor == comm->rank) {
+            if (!finish_fly()) return false;  // the newest nodes go: they may be the ones in flight
             std::vector<double> buf(1, 0.0);
             for (int k = 0; k < sp.k; k++) {  // newest first
               pack_node(*open.back(), buf);
@@ -986,6 +1059,8 @@ bool Driver::run() {
       size_t w = std::min<size_t>(width, open.size());
       if (limit > 0) w = std::min<size_t>(w, (size_t)std::max(1, limit - count));
       for (size_t k = 0; k < w; k++) { batch.push_back(std::move(open.front())); open.pop_front(); }
+      for (auto &nd : batch)
+        if (nd->oid >= fly.min_oid) { if (!finish_fly()) return false; break; }  // (short queue: ramp-up, the end)
     }
     // ---- LP solve #1 of every popped node (bs.cpp:114-117), one launch ----
     {
@@ -1117,7 +1192,19 @@ bool Driver::run() {
     for (size_t k = batch.size(); k-- > consumed;)
       if (batch[k] && batch[k]->prob) open.push_front(std::move(batch[k]));
     // ---- LP solves #2/#3 of the new children (bs.cpp:279,287), one launch ----
-    {
+    if (pipe) {
+      if (!finish_fly()) return false;  // one launch in flight at a time: the previous round's comes home now
+      std::vector<glp_prob *> ps;
+      for (auto &k : kids) ps.push_back(k.node->prob);
+      if (!solve_many_begin(ps)) return false;
+      fly.active = true;
+      for (auto &k : kids) {
+        fly.nodes.push_back(k.node.get());
+        fly.slots.push_back(k.ev_slot);
+        fly.min_oid = std::min(fly.min_oid, k.node->oid);
+        open.push_back(std::move(k.node));
+      }
+    } else {
       std::vector<glp_prob *> ps;
       for (auto &k : kids)
         if (!k.solved) ps.push_back(k.node->prob);
@@ -1139,6 +1226,7 @@ bool Driver::run() {
     if (dist) {
       if (!split && !stop && pr.node_strategy != MVB_NODE_BEST && open.size() >= (size_t)4 * comm->world) {
         // deal the FIFO queue round-robin; from here on every rank owns its share
+        if (!finish_fly()) return false;  // (the nodes that go to other ranks are dropped here)
         std::deque<std::unique_ptr<Node>> mine;
         for (size_t k = 0; k < open.size(); k++)
           if ((int)(k % comm->world) == comm->rank) mine.push_back(std::move(open[k]));
@@ -1149,7 +1237,10 @@ bool Driver::run() {
           limit = count + std::max(1, (limit - count + comm->world - 1) / comm->world);
       }
       if (split) {
-        if (stop) { retired = true; stop = false; open.clear(); }
+        if (stop) {
+          if (!finish_fly()) return false;
+          retired = true; stop = false; open.clear();
+        }
         // incumbent broadcast: the bound test (bs.cpp:210) sees the best incumbent of all ranks
         double best = bestLower;
         if (!reduce_max(&best, 1)) return false;
@@ -1157,6 +1248,7 @@ bool Driver::run() {
       }
     }
   }
+  if (!finish_fly()) return false;
   if (dist) {
     // final exchange: who holds the optimum (lowest rank on ties), its x, and the node counts
     double best = out->st.has_incumbent ? bestLower : -inf;

@@ -794,6 +794,13 @@ struct DeviceCtx {
   bool no_handover = false;  // MVOLPS_NO_HANDOVER=1: phase 2 after a phase 1 stays in the general loop (A-B timing)
   int force_k = 0;         // MVOLPS_LZ_K=k: cap the pending-update depth (A-B timing)
   int ring_slots = LZ_RING_SLOTS;  // option "lz_ring" / MVOLPS_LZ_RING=0: no cp.async ring in the streaming flush (A-B timing)
+  // a launch whose results have not been read back yet (mvb_solve_batch_begin): the D2H of its outbox is
+  // enqueued; launch_finish() waits for it and fills the host mirrors.  At most one at a time.
+  struct InFlight {
+    bool active = false;
+    std::vector<mvb_lp *> lps;
+    std::vector<size_t> ooff;
+  } inflight;
   int last_ring = 0, last_lz_k = 0;
   bool last_stream = false;  // the last lazy launch ran simplex_ps_stream_kernel
   int force_nt = 0;        // MVOLPS_PS_NT=t: CTA width for launches with more LPs than SMs (A-B timing)
@@ -802,6 +809,7 @@ struct DeviceCtx {
 DeviceCtx g_ctx;
 
 bool fail(const std::string &m) { g_err = m; return false; }
+bool launch_finish();  // read back a deferred solve launch (below)
 #define CK(call)                                                                     \
   do {                                                                               \
     cudaError_t e_ = (call);                                                         \
@@ -912,6 +920,7 @@ struct mvb_lp {
   mvb_result res{};
   int *pivlog = nullptr; int pivlog_cap = 0, pivlog_n = 0;
   DevResult dres{};                 // result block of the last launch this LP took part in
+  bool in_flight = false;           // part of a launch whose results have not been read back (mvb_solve_batch_begin)
   unsigned clone_epoch = 0;         // == g_ctx.clone_epoch: source (1) / destination (2) of a queued clone
   int clone_role = 0;
   unsigned append_epoch = 0;        // == g_ctx.clone_epoch: a cut row of this LP is queued
@@ -1123,6 +1132,7 @@ mvb_lp *mvb_lp_create(int m, int n, int row_cap) {
 
 void mvb_lp_free(mvb_lp *lp) {
   if (!lp) return;
+  if (lp->in_flight) launch_finish();  // (the read-back of a deferred launch writes into this object)
   lp_release(lp);
   delete lp;
 }
@@ -1182,6 +1192,7 @@ int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost, const double *l
 }
 
 int mvb_lp_assign(mvb_lp *dst, const mvb_lp *src) {
+  if ((dst->in_flight || src->in_flight) && !launch_finish()) return -1;
   if (dst->n != src->n || dst->mcap != src->mcap) { g_err = "mvb_lp_assign: shape mismatch"; return -1; }
   dst->m = src->m;
   dst->dev.m = src->m;
@@ -1222,6 +1233,7 @@ mvb_lp *mvb_lp_clone(const mvb_lp *src) {
 }
 
 int mvb_lp_set_bounds(mvb_lp *lp, int k, double lb, double ub) {
+  if (lp->in_flight && !launch_finish()) return -1;
   if (k < 0 || k >= lp->n + lp->m) { g_err = "mvb_lp_set_bounds: variable id"; return -1; }
   // the change travels as a patch the next solve kernel applies (bounds have no host mirror)
   int pos = -1, flag = 0;
@@ -1307,6 +1319,7 @@ bool lp_grow(mvb_lp *lp, int mcap) {
 }  // namespace
 
 extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double ub) {
+  if (lp->in_flight && !launch_finish()) return -1;
   // queued: the rows of a B&B round are formed by one kernel (flush_clones).  An LP that takes
   // part in a queued clone, already has a queued row, or must grow is brought up to date first.
   const bool in_clone = lp->clone_epoch == g_ctx.clone_epoch && lp->clone_role != 0;
@@ -1337,10 +1350,47 @@ extern "C" int mvb_lp_append_row(mvb_lp *lp, const double *a, double lb, double 
 namespace {
 
 // one cooperative launch over the LPs `idx` (indices into lps), results into the outboxes
-bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opts *opts, int kind, int csize = 0) {
+// read back a deferred launch: wait for its D2H, fill the host mirrors of its LPs
+bool launch_finish() {
+  if (!g_ctx.inflight.active) return true;
+  g_ctx.inflight.active = false;
+  CK(cudaStreamSynchronize(g_ctx.stream));
+  {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, g_ctx.kev[0], g_ctx.kev[1]) == cudaSuccess) g_ctx.batch_kernel_ms += ms;
+    g_ctx.batch_solve_launches++;
+  }
+  // results of this launch into the host mirrors (an LP that reports MVB_PS_FALLBACK /
+  // MVB_PS_HANDOVER is launched again and overwritten)
+  const std::vector<mvb_lp *> &lps = g_ctx.inflight.lps;
+  for (size_t k = 0; k < lps.size(); k++) {
+    mvb_lp *lp = lps[k];
+    lp->in_flight = false;
+    const char *ob = g_ctx.h_out + g_ctx.inflight.ooff[k];
+    const char *base = lp->slab + lp->out_off;
+    const DevResult *dr = (const DevResult *)(ob + ((const char *)lp->dev.res - base));
+    lp->dres = *dr;
+    if (dr->r.status == MVB_PS_FALLBACK) continue;
+    const double *x = (const double *)(ob + ((const char *)lp->dev.xval - base));
+    const int *oh = (const int *)(ob + ((const char *)lp->dev.ohead - base));
+    const int *on = (const int *)(ob + ((const char *)lp->dev.onb - base));
+    const int *oa = (const int *)(ob + ((const char *)lp->dev.oat - base));
+    lp->x.assign(x, x + lp->n + lp->m);
+    lp->head.assign(oh, oh + lp->m);
+    lp->nb.assign(on, on + lp->n);
+    lp->at.assign(oa, oa + lp->n);
+  }
+  g_ctx.inflight.lps.clear();
+  return true;
+}
+
+// defer: return as soon as the launch and the D2H of its results are enqueued (launch_finish reads them)
+bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opts *opts, int kind, int csize = 0,
+                  bool defer = false) {
   const bool psk = kind == 1, res = kind == 2 || kind == 3, cres = kind == 3;
   const int count = (int)idx.size();
   if (!count) return true;
+  if (!launch_finish()) return false;  // (its staging buffers are about to be reused)
   cudaStream_t st = g_ctx.stream;
   std::vector<LPDev> h(count);
   size_t max_bytes = 0, dyn = 0, tot_bytes = 0;
@@ -1537,44 +1587,41 @@ bool launch_solve(mvb_lp *const *lps, const std::vector<int> &idx, const mvb_opt
   g_ctx.last_ps = psk;
   g_ctx.last_kind = kind;
   CK(cudaMemcpyAsync(g_ctx.h_out, g_ctx.d_out, otot, cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
-  {
-    float ms = 0.f;
-    if (cudaEventElapsedTime(&ms, g_ctx.kev[0], g_ctx.kev[1]) == cudaSuccess) g_ctx.batch_kernel_ms += ms;
-    g_ctx.batch_solve_launches++;
-  }
-  // results of this launch into the host mirrors (an LP that reports MVB_PS_FALLBACK /
-  // MVB_PS_HANDOVER is launched again and overwritten)
+  g_ctx.inflight.active = true;
+  g_ctx.inflight.lps.resize(count);
   for (int k = 0; k < count; k++) {
-    mvb_lp *lp = lps[idx[k]];
-    const char *ob = g_ctx.h_out + ooff[k];
-    const char *base = lp->slab + lp->out_off;
-    const DevResult *dr = (const DevResult *)(ob + ((const char *)lp->dev.res - base));
-    lp->dres = *dr;
-    if (dr->r.status == MVB_PS_FALLBACK) continue;
-    const double *x = (const double *)(ob + ((const char *)lp->dev.xval - base));
-    const int *oh = (const int *)(ob + ((const char *)lp->dev.ohead - base));
-    const int *on = (const int *)(ob + ((const char *)lp->dev.onb - base));
-    const int *oa = (const int *)(ob + ((const char *)lp->dev.oat - base));
-    lp->x.assign(x, x + lp->n + lp->m);
-    lp->head.assign(oh, oh + lp->m);
-    lp->nb.assign(on, on + lp->n);
-    lp->at.assign(oa, oa + lp->n);
+    g_ctx.inflight.lps[k] = lps[idx[k]];
+    lps[idx[k]]->in_flight = true;
   }
-  return true;
+  g_ctx.inflight.ooff = ooff;
+  return defer ? true : launch_finish();
 }
 
 }  // namespace
 
-extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *opts,
-                               mvb_result *out) {
-  if (count <= 0) return 0;
-  if (!ctx_init(-1)) return -1;
-  if (!flush_clones()) return -1;
-  cudaStream_t st = g_ctx.stream;
-  g_ctx.batch_kernel_ms = 0.0;
-  g_ctx.batch_solve_launches = 0;
+namespace {
+
+// One mvb_solve_batch call: which kernel every LP goes to first (plan), the first launches, then
+// what they hand on (phase 1 to the general kernel, phase 2 back to the fast ones) and the results.
+struct BatchPlan {
+  std::vector<mvb_lp *> lps;
+  mvb_opts opts{};
+  bool have_opts = false;
   std::vector<int> ps_idx, gen_idx, res_idx, cres_idx[3];
+  bool deferred = false;  // the one first launch is in flight (mvb_solve_batch_begin)
+  bool active = false;
+  bool done = false;                // brought home early (another solve came in between): results held here
+  std::vector<mvb_result> results;
+};
+BatchPlan g_plan;  // the batch between mvb_solve_batch_begin and mvb_solve_batch_end
+
+int batch_plan(BatchPlan &P) {
+  cudaStream_t st = g_ctx.stream;
+  mvb_lp *const *lps = P.lps.data();
+  const int count = (int)P.lps.size();
+  const mvb_opts *opts = P.have_opts ? &P.opts : nullptr;
+  std::vector<int> &ps_idx = P.ps_idx, &gen_idx = P.gen_idx, &res_idx = P.res_idx;
+  std::vector<int> *cres_idx = P.cres_idx;
   for (int k = 0; k < count; k++) {
     mvb_lp *lp = lps[k];
     if (!lp_push_small(lp)) return -1;
@@ -1610,12 +1657,34 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     if (lp->cres_c) cres_idx[lp->cres_c == 2 ? 0 : lp->cres_c == 4 ? 1 : 2].push_back(k);
     else (lp->res_ok ? res_idx : fits ? ps_idx : gen_idx).push_back(k);
   }
-  auto dev_result = [](mvb_lp *lp) { return (const DevResult *)&lp->dres; };
-  // resident and private-state kernels first; what needs phase 1 (or fits neither) goes to the general one
-  if (!launch_solve(lps, res_idx, opts, 2)) return -1;
+  return 0;
+}
+
+// resident and private-state kernels first; what needs phase 1 (or fits neither) goes to the general one
+int batch_first(BatchPlan &P, bool defer) {
+  mvb_lp *const *lps = P.lps.data();
+  const mvb_opts *opts = P.have_opts ? &P.opts : nullptr;
+  // a single first launch can stay in flight while the host goes on (its results are read by batch_rest)
+  const int kinds = !P.res_idx.empty() + !P.ps_idx.empty() + !P.cres_idx[0].empty() + !P.cres_idx[1].empty() +
+                    !P.cres_idx[2].empty();
+  const bool d = defer && kinds == 1 && P.gen_idx.empty() && (!P.res_idx.empty() || !P.ps_idx.empty());
+  if (!launch_solve(lps, P.res_idx, opts, 2, 0, d)) return -1;
   for (int c = 0; c < 3; c++)
-    if (!launch_solve(lps, cres_idx[c], opts, 3, 2 << c)) return -1;
-  if (!launch_solve(lps, ps_idx, opts, 1)) return -1;
+    if (!launch_solve(lps, P.cres_idx[c], opts, 3, 2 << c)) return -1;
+  if (!launch_solve(lps, P.ps_idx, opts, 1, 0, d)) return -1;
+  P.deferred = d;
+  return 0;
+}
+
+int batch_rest(BatchPlan &P, mvb_result *out) {
+  if (!launch_finish()) return -1;
+  P.deferred = false;
+  mvb_lp *const *lps = P.lps.data();
+  const int count = (int)P.lps.size();
+  const mvb_opts *opts = P.have_opts ? &P.opts : nullptr;
+  std::vector<int> &ps_idx = P.ps_idx, &gen_idx = P.gen_idx, &res_idx = P.res_idx;
+  std::vector<int> *cres_idx = P.cres_idx;
+  auto dev_result = [](mvb_lp *lp) { return (const DevResult *)&lp->dres; };
   for (int k : res_idx)
     if (dev_result(lps[k])->r.status == MVB_PS_FALLBACK) gen_idx.push_back(k);
   for (int c = 0; c < 3; c++)
@@ -1659,6 +1728,58 @@ extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *op
     out[k] = dr->r;
   }
   return 0;
+}
+
+int batch_setup(BatchPlan &P, mvb_lp *const *lps, int count, const mvb_opts *opts) {
+  if (!ctx_init(-1)) return -1;
+  if (!launch_finish()) return -1;
+  if (!flush_clones()) return -1;
+  g_ctx.batch_kernel_ms = 0.0;
+  g_ctx.batch_solve_launches = 0;
+  P = BatchPlan{};
+  P.lps.assign(lps, lps + count);
+  if (opts) { P.opts = *opts; P.have_opts = true; }
+  return batch_plan(P);
+}
+
+}  // namespace
+
+extern "C" int mvb_solve_batch(mvb_lp *const *lps, int count, const mvb_opts *opts,
+                               mvb_result *out) {
+  if (count <= 0) return 0;
+  if (g_plan.active && !g_plan.done && !g_plan.lps.empty()) {
+    // a batch is in flight: it comes home now (mvb_solve_batch_end will hand its results out)
+    g_plan.results.resize(g_plan.lps.size());
+    if (batch_rest(g_plan, g_plan.results.data())) return -1;
+    g_plan.done = true;
+  }
+  BatchPlan P;
+  if (batch_setup(P, lps, count, opts)) return -1;
+  if (batch_first(P, false)) return -1;
+  return batch_rest(P, out);
+}
+
+// The same solve in two halves: begin enqueues the (first) launch and returns while the device works,
+// end waits, runs whatever the first launch hands on, and delivers the results.  One batch at a
+// time; its LPs must not be touched in between (other LPs may be created, cloned, changed, freed).
+extern "C" int mvb_solve_batch_begin(mvb_lp *const *lps, int count, const mvb_opts *opts) {
+  if (g_plan.active) { g_err = "mvb_solve_batch_begin: a batch is already in flight"; return -1; }
+  if (count <= 0) { g_plan = BatchPlan{}; g_plan.active = true; return 0; }
+  if (batch_setup(g_plan, lps, count, opts)) return -1;
+  if (batch_first(g_plan, true)) return -1;
+  g_plan.active = true;
+  return 0;
+}
+
+extern "C" int mvb_solve_batch_end(mvb_result *out) {
+  if (!g_plan.active) { g_err = "mvb_solve_batch_end: no batch in flight"; return -1; }
+  g_plan.active = false;
+  if (g_plan.lps.empty()) return 0;
+  if (g_plan.done) {
+    std::copy(g_plan.results.begin(), g_plan.results.end(), out);
+    return 0;
+  }
+  return batch_rest(g_plan, out);
 }
 
 extern "C" {

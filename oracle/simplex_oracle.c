@@ -612,6 +612,23 @@ int mvb_lp_get_tab_rows(mvb_lp *lp, const int *rows, int nrows, double *out) {
   return 0;
 }
 
+/* the two-halves form of mvb_solve_batch: the CPU oracle solves inside begin */
+static mvb_result *g_pending = NULL;
+static int g_pending_n = -1;
+int mvb_solve_batch_begin(mvb_lp *const *lps, int count, const mvb_opts *opts) {
+  if (g_pending_n >= 0) { set_err("mvb_solve_batch_begin: a batch is already in flight"); return -1; }
+  free(g_pending);
+  g_pending = (mvb_result *)malloc(sizeof(mvb_result) * (size_t)(count > 0 ? count : 1));
+  g_pending_n = count > 0 ? count : 0;
+  return count > 0 ? mvb_solve_batch(lps, count, opts, g_pending) : 0;
+}
+int mvb_solve_batch_end(mvb_result *out) {
+  if (g_pending_n < 0) { set_err("mvb_solve_batch_end: no batch in flight"); return -1; }
+  if (g_pending_n > 0) memcpy(out, g_pending, sizeof(mvb_result) * (size_t)g_pending_n);
+  g_pending_n = -1;
+  return 0;
+}
+
 /* CUDA-only entry point (static device scratch); the CPU oracle has none: always fails */
 int mvb_lp_get_tab_rows_noalloc(mvb_lp *lp, const int *rows, int nrows, double *out) {
   (void)lp; (void)rows; (void)nrows; (void)out;

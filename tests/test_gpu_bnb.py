@@ -165,3 +165,67 @@ def test_node_level_vfp_and_round2_options_on_the_gpu(oracle, product):
         for k in SAME:
             assert a[k] == b[k], (kw, k)
         assert a["launches_aux"] == b["launches_aux"]
+
+
+@pytest.mark.parametrize("kw", [dict(batch_width=64, max_iters=6000), dict(batch_width=7, max_iters=900),
+                                dict(batch_width=256, root_heuristic=1, max_iters=4000), dict(batch_width=32)])
+def test_pipelined_rounds_equal_the_unpipelined_loop(product, monkeypatch, kw):
+    """FIFO without cuts keeps one launch in flight (mvb_solve_batch_begin / _end): the children of a
+    round are solved while the host consumes the next round.  Everything the run reports -- tree, ids,
+    events, counters, incumbent -- equals the loop that waits for every launch (MVOLPS_BNB_NO_PIPELINE)."""
+    inst = instances.mdkp(30, 8, 4) if "max_iters" not in kw else instances.mdkp(200, 50, 2024)
+    a = GlpProb.from_instance(product, inst).bnb(**kw)
+    monkeypatch.setenv("MVOLPS_BNB_NO_PIPELINE", "1")
+    b = GlpProb.from_instance(product, inst).bnb(**kw)
+    monkeypatch.delenv("MVOLPS_BNB_NO_PIPELINE")
+    for k in SAME:
+        assert a[k] == b[k], k
+    if a["x"] is not None:
+        assert np.array_equal(a["x"], b["x"])
+
+
+def test_solve_batch_in_two_halves(oracle, product):
+    """mvb_solve_batch_begin / _end through the C ABI: other LPs are created, cloned, changed and
+    freed while the launch is in flight; results equal the one-call solve and the oracle."""
+    import ctypes as C
+    from mvolps_b200 import capi
+    from mvolps_b200.lp import EngineLP, solve_batch
+    # (a batch of resident-kernel LPs: one launch, left in flight; with an LP that needs phase 1 the
+    # batch takes several launches and is solved inside begin)
+    mixed = [instances.mdkp(40, 10, 30 + k) for k in range(24)]
+    for extra in ([], [instances.general_lp(20, 30, 12)]):
+        _two_halves(oracle, product, mixed + extra)
+
+
+def _two_halves(oracle, product, insts):
+    import ctypes as C
+    from mvolps_b200.lp import EngineLP, solve_batch
+    ref = [EngineLP.from_instance(oracle, i).solve() for i in insts]
+    lps = [EngineLP.from_instance(product, i) for i in insts]
+    n = len(lps)
+    arr = (C.c_void_p * n)(*[lp.h for lp in lps])
+    opts = capi.Opts(0, 0, 0, 0)
+    assert product.mvb_solve_batch_begin(arr, n, C.byref(opts)) == 0
+    assert product.mvb_solve_batch_begin(arr, n, C.byref(opts)) != 0  # one batch at a time
+    other = EngineLP.from_instance(product, instances.mdkp(40, 10, 77))
+    twin = other.clone()
+    twin.set_bounds(3, 0.0, 1.0)
+    other.free()
+    if len(insts) % 2 == 0:   # a one-call solve in between: the batch in flight comes home first, end hands it out
+        rt = twin.solve()
+    res = (capi.Result * n)()
+    assert product.mvb_solve_batch_end(res) == 0
+    assert product.mvb_solve_batch_end(res) != 0
+    if len(insts) % 2:
+        rt = twin.solve()
+    for r, want, lp in zip(res, ref, lps):
+        for f in ("status", "iters", "pivots", "pivot_hash", "obj", "iters_primal1", "iters_dual"):
+            assert getattr(r, f) == want[f], f
+    o = EngineLP.from_instance(oracle, instances.mdkp(40, 10, 77))
+    o.set_bounds(3, 0.0, 1.0)
+    ro = o.solve()
+    assert rt["pivot_hash"] == ro["pivot_hash"] and rt["obj"] == ro["obj"]
+    # and the batch again in one call: the same results
+    again = [EngineLP.from_instance(product, i) for i in insts]
+    for r, r2 in zip(res, solve_batch(product, again)):
+        assert r.pivot_hash == r2["pivot_hash"] and r.obj == r2["obj"]
