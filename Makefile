@@ -20,7 +20,7 @@ $(OBJ)/engine_cuda.o: $(CSRC)/engine_cuda.cu $(wildcard $(CSRC)/*.cuh) $(ROOT)/i
 
 # (MVB_WITH_SHARDS: the product's glp_simplex can route a large LP to the column-sharded engine; the
 # oracle build of the same host sources has no multi-GPU layer)
-$(OBJ)/%.o: $(CSRC)/%.cpp $(CSRC)/lp_model.hpp $(CSRC)/cow_vec.hpp $(ROOT)/include/glpk.h $(ROOT)/include/mvolps_engine.h $(ROOT)/include/mvolps_bnb.h $(ROOT)/include/mvolps_dist.h
+$(OBJ)/%.o: $(CSRC)/%.cpp $(CSRC)/lp_model.hpp $(CSRC)/cow_vec.hpp $(CSRC)/par_for.hpp $(ROOT)/include/glpk.h $(ROOT)/include/mvolps_engine.h $(ROOT)/include/mvolps_bnb.h $(ROOT)/include/mvolps_dist.h
 	@mkdir -p $(OBJ)
 	g++ $(CXXFLAGS) -DMVB_WITH_SHARDS -c $< -o $@
 

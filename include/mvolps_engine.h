@@ -113,6 +113,8 @@ int mvb_last_launch(int *ctas_per_lp, int *groups, int *threads);
 /* new empty LP with room for row_cap rows (grown on demand) */
 mvb_lp *mvb_lp_create(int m, int n, int row_cap);
 void mvb_lp_free(mvb_lp *lp);
+/* the same for count LPs at once (the open queue of a finished B&B run: 10^5 handles) */
+void mvb_lp_free_many(mvb_lp *const *lps, int count);
 /* load host data and reset to the slack basis (all auxiliaries basic).
  * A: m*n row-major; cost: n (internal min form); lb/ub: n+m by variable id */
 int mvb_lp_load(mvb_lp *lp, const double *A, const double *cost,

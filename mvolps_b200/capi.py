@@ -39,7 +39,7 @@ GLPK_EXTRA_SYMBOLS = ["glp_add_cols", "glp_set_col_kind", "glp_get_row_prim", "g
 ENGINE_SYMBOLS = [
     "mvb_backend", "mvb_last_error", "mvb_device_init", "mvb_kernel_launches",
     "mvb_timer_record", "mvb_timer_elapsed_ms", "mvb_flush_l2", "mvb_last_launch", "mvb_last_kernel_ms", "mvb_last_kernel_mode", "mvb_engine_option",
-    "mvb_host_staging", "mvb_lp_create", "mvb_lp_free", "mvb_lp_load", "mvb_lp_clone", "mvb_lp_assign",
+    "mvb_host_staging", "mvb_lp_create", "mvb_lp_free", "mvb_lp_free_many", "mvb_lp_load", "mvb_lp_clone", "mvb_lp_assign",
     "mvb_lp_dims", "mvb_lp_set_bounds", "mvb_lp_append_row", "mvb_solve_batch", "mvb_solve_batch_begin", "mvb_solve_batch_end",
     "mvb_lp_get_primal", "mvb_lp_get_basis", "mvb_lp_get_tab_rows", "mvb_lp_get_tab_rows_batch", "mvb_lp_get_tab_rows_noalloc",
     "mvb_lp_get_tableau", "mvb_lp_get_pivot_log",
@@ -150,6 +150,7 @@ def _bind(lib):
         "mvb_engine_option": (C.c_int, [C.c_char_p, C.c_int]),
         "mvb_last_launch": (C.c_int, [_ip, _ip, _ip]),
         "mvb_host_staging": (_P, [C.c_size_t]),
+        "mvb_lp_free_many": (None, [C.POINTER(_P), C.c_int]),
         "mvb_lp_create": (_P, [C.c_int, C.c_int, C.c_int]),
         "mvb_lp_free": (None, [_P]),
         "mvb_lp_load": (C.c_int, [_P, _dp, _dp, _dp, _dp]),

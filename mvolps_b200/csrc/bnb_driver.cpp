@@ -19,6 +19,7 @@
 #include <map>
 #include <memory>
 #include <charconv>
+#include <atomic>
 #include <sstream>
 #include <type_traits>
 #include <string>
@@ -27,6 +28,7 @@
 #include "../../include/mvolps_bnb.h"
 #include "../../include/mvolps_spec.h"
 #include "lp_model.hpp"
+#include "par_for.hpp"
 
 namespace {
 
@@ -265,6 +267,20 @@ struct Driver {
     return comm->allgather_host(comm->ctx, send.data(), all.data(), stride) == 0;
   }
 
+  // the solutions of one launch into their problem objects: every LP on its own (statuses, primal
+  // values with the integer snap, objective), so the loop runs on the host worker threads
+  bool pull_many(const std::vector<glp_prob *> &ps, const std::vector<mvb_result> &res, bool counted) {
+    std::atomic<bool> bad{false};
+    par_for(ps.size(), [&](size_t a, size_t b) {
+      for (size_t k = a; k < b; k++)
+        if (mv_pull_solution(ps[k], res[k])) bad = true;
+    });
+    if (bad) return false;
+    if (counted)
+      for (size_t k = 0; k < ps.size(); k++) out->st.simplex_iters += res[k].iters;
+    return true;
+  }
+
   // counted = false: speculative solves; they enter lp_solves / simplex_iters when (and if) the
   // serial order adopts them, so the statistics are those of the unspeculated run
   bool solve_many(const std::vector<glp_prob *> &all, bool counted = true) {
@@ -288,10 +304,7 @@ struct Driver {
     out->st.solved_here += (int)engs.size();
     double t2 = now();
     if (!(sync_mode && dealt)) {
-      for (size_t k = 0; k < ps.size(); k++) {
-        if (mv_pull_solution(ps[k], res[k])) return false;
-        if (counted) out->st.simplex_iters += res[k].iters;
-      }
+      if (!pull_many(ps, res, counted)) return false;
     } else {
       // records of my LPs, in batch order: result | x | head | nb | at
       std::vector<size_t> seg(comm->world, 0);
@@ -362,10 +375,7 @@ struct Driver {
     const double t0 = now();
     if (mvb_solve_batch_end(res.data())) return false;
     const double t1 = now();
-    for (size_t k = 0; k < fly_ps.size(); k++) {
-      if (mv_pull_solution(fly_ps[k], res[k])) return false;
-      if (fly_counted) out->st.simplex_iters += res[k].iters;
-    }
+    if (!pull_many(fly_ps, res, fly_counted)) return false;
     t_solve += t1 - t0;
     t_pull += now() - t1;
     out->st.launches++;
@@ -617,14 +627,16 @@ struct Driver {
     return true;
   }
 
-  void print_tree(int oid, std::ostringstream &os) {  // tree_print.h:12-22
+  void print_tree(int oid, std::string &os) {  // tree_print.h:12-22
     TreeRec &t = tree[oid];
-    for (int i = 0; i < t.depth; i++) os << " ";
-    os << "-" << oid;
-    if (t.prune == P_INTG) os << " I";
-    else if (t.prune == P_FEAS) os << " F";
-    else if (t.prune == P_BNDS) os << " B";
-    os << "\n";
+    char buf[16];
+    os.append((size_t)t.depth, ' ');
+    os += '-';
+    os.append(buf, std::to_chars(buf, buf + sizeof buf, oid).ptr);
+    if (t.prune == P_INTG) os += " I";
+    else if (t.prune == P_FEAS) os += " F";
+    else if (t.prune == P_BNDS) os += " B";
+    os += '\n';
     for (int k : t.kids) print_tree(k, os);
   }
 
@@ -913,6 +925,11 @@ namespace {
 
 bool Driver::run() {
   const double t_run0 = now();
+  {
+    // host worker threads of the per-LP loops: the ranks of a multi-GPU run share the cores
+    const int hw = (int)std::thread::hardware_concurrency(), w = comm ? std::max(1, comm->world) : 1;
+    ParPool::get().set_threads(std::max(1, std::min(4, hw / (2 * w))));
+  }
   const double inf = std::numeric_limits<double>::infinity();
   std::deque<std::unique_ptr<Node>> open;  // leafContainer, bs.cpp:79
   std::vector<std::string> evs;            // event lines (candidates filled late)
@@ -1285,9 +1302,8 @@ bool Driver::run() {
   out->st.incumbent_rank = inc_rank;
 
   const double tfin0 = now();
-  std::ostringstream ts;
-  print_tree(1, ts);
-  out->tree = ts.str();
+  out->tree.clear();
+  print_tree(1, out->tree);
   out->solution = solution;
   for (size_t e = 0; e < evs.size(); e++) {
     const std::string &l = evs[e];
@@ -1314,6 +1330,9 @@ bool Driver::run() {
   out->st.iterations = count;
   out->st.oids = next_id - 1;
   out->st.event_hash = ehash;
+  // (the open queue is destroyed by the caller's thread: freeing its 10^5 problem objects on the
+  // worker threads measured SLOWER -- 106 k against 124 k nodes/s -- every block goes back to the
+  // allocating thread's arena, under its lock)
   return true;
 }
 

@@ -32,6 +32,7 @@
 #include "../../include/mvolps_engine.h"
 #include "../../include/mvolps_spec.h"
 #include "cow_vec.hpp"
+#include "par_for.hpp"
 
 #ifndef MVB_PS_NT
 #define MVB_PS_NT 512  // threads per CTA of the private-state kernel
@@ -1137,6 +1138,14 @@ void mvb_lp_free(mvb_lp *lp) {
   delete lp;
 }
 
+void mvb_lp_free_many(mvb_lp *const *lps, int count) {
+  if (count <= 0) return;
+  for (int k = 0; k < count; k++)
+    if (lps[k] && lps[k]->in_flight) { launch_finish(); break; }
+  for (int k = 0; k < count; k++)
+    if (lps[k]) { lp_release(lps[k]); delete lps[k]; }
+}
+
 void *mvb_host_staging(size_t bytes) {
   if (!ctx_init(-1)) return nullptr;
   if (g_ctx.h_stage_cap < bytes) {
@@ -1363,23 +1372,25 @@ bool launch_finish() {
   // results of this launch into the host mirrors (an LP that reports MVB_PS_FALLBACK /
   // MVB_PS_HANDOVER is launched again and overwritten)
   const std::vector<mvb_lp *> &lps = g_ctx.inflight.lps;
-  for (size_t k = 0; k < lps.size(); k++) {
-    mvb_lp *lp = lps[k];
-    lp->in_flight = false;
-    const char *ob = g_ctx.h_out + g_ctx.inflight.ooff[k];
-    const char *base = lp->slab + lp->out_off;
-    const DevResult *dr = (const DevResult *)(ob + ((const char *)lp->dev.res - base));
-    lp->dres = *dr;
-    if (dr->r.status == MVB_PS_FALLBACK) continue;
-    const double *x = (const double *)(ob + ((const char *)lp->dev.xval - base));
-    const int *oh = (const int *)(ob + ((const char *)lp->dev.ohead - base));
-    const int *on = (const int *)(ob + ((const char *)lp->dev.onb - base));
-    const int *oa = (const int *)(ob + ((const char *)lp->dev.oat - base));
-    lp->x.assign(x, x + lp->n + lp->m);
-    lp->head.assign(oh, oh + lp->m);
-    lp->nb.assign(on, on + lp->n);
-    lp->at.assign(oa, oa + lp->n);
-  }
+  par_for(lps.size(), [&](size_t k0, size_t k1) {  // (every LP on its own: host worker threads)
+    for (size_t k = k0; k < k1; k++) {
+      mvb_lp *lp = lps[k];
+      lp->in_flight = false;
+      const char *ob = g_ctx.h_out + g_ctx.inflight.ooff[k];
+      const char *base = lp->slab + lp->out_off;
+      const DevResult *dr = (const DevResult *)(ob + ((const char *)lp->dev.res - base));
+      lp->dres = *dr;
+      if (dr->r.status == MVB_PS_FALLBACK) continue;
+      const double *x = (const double *)(ob + ((const char *)lp->dev.xval - base));
+      const int *oh = (const int *)(ob + ((const char *)lp->dev.ohead - base));
+      const int *on = (const int *)(ob + ((const char *)lp->dev.onb - base));
+      const int *oa = (const int *)(ob + ((const char *)lp->dev.oat - base));
+      lp->x.assign(x, x + lp->n + lp->m);
+      lp->head.assign(oh, oh + lp->m);
+      lp->nb.assign(on, on + lp->n);
+      lp->at.assign(oa, oa + lp->n);
+    }
+  });
   g_ctx.inflight.lps.clear();
   return true;
 }

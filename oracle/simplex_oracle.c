@@ -114,6 +114,10 @@ void mvb_lp_free(mvb_lp *lp) {
   free(lp);
 }
 
+void mvb_lp_free_many(mvb_lp *const *lps, int count) {
+  for (int k = 0; k < count; k++) mvb_lp_free(lps[k]);
+}
+
 void *mvb_host_staging(size_t bytes) {
   static __thread void *buf;
   static __thread size_t cap;
