@@ -523,9 +523,17 @@ struct Driver {
   bool lean = false;
   int lean_k = -1, lean_j = 0, lean_pooled = 0;
   void cut_rows_of(glp_prob *a, std::vector<int> &js, std::vector<int> &rows);
-  void gen_cuts(glp_prob *a, const double *trows);
+  // what the lean path knows about a node of the batch before the serial loop reaches it
+  struct PreCut {
+    bool lean = false, have = false;
+    int j = 0, pooled = 0;
+    Cut cut;
+  };
+  std::vector<PreCut> pre_cuts;  // by position in the batch (prefetch_cut_rows)
+  void gen_cuts(glp_prob *a, const double *trows, PreCut *pre = nullptr);
   void gen_cut_ref(glp_prob *a, int j, const double *trow);
   void gen_cut_gmi(glp_prob *a, int j, const double *trow);
+  static bool build_cut_gmi(glp_prob *a, int j, const double *trow, Cut &c);
   bool gmi_produces(glp_prob *a, int j, const double *trow);
   int add_cut_constraint(glp_prob *a, int cID);
   int deepest_cut(glp_prob *a, size_t first);
@@ -538,6 +546,7 @@ struct Driver {
   bool prefetch_cut_rows(const std::vector<std::unique_ptr<Node>> &batch, double bestLower,
                          std::vector<double> &buf, std::vector<size_t> &off) {
     off.assign(batch.size(), npos);
+    pre_cuts.assign(batch.size(), PreCut{});
     std::vector<mvb_lp *> lps;
     std::vector<int> rows, nrows, js, r1, vars;
     size_t tot = 0;
@@ -547,6 +556,9 @@ struct Driver {
       if (!cuts_wanted(nd->oid) || classify(a, vars) != 0) continue;
       if (glp_get_obj_val(a) <= bestLower) continue;  // fathomed whatever happens (bs.cpp:210)
       cut_rows_of(a, js, r1);
+      pre_cuts[k].lean = lean;
+      pre_cuts[k].j = lean_j;
+      pre_cuts[k].pooled = lean ? lean_pooled : 0;
       off[k] = tot;
       tot += r1.size() * (size_t)a->ncols();
       if (r1.empty()) continue;
@@ -561,6 +573,7 @@ struct Driver {
       const int rc = mvb_lp_get_tab_rows_batch(lps.data(), (int)lps.size(), rows.data(), nrows.data(), buf.data());
       t_rows += now() - t0;
       out->st.launches_aux++;
+      if (rc == 0) precompute_cuts(batch, buf, off);
       return rc == 0;
     }
     // sync mode: every rank gathers the rows of the nodes it owns, one all-gather shares them
@@ -600,7 +613,23 @@ struct Driver {
       std::memcpy(buf.data() + off[k], allrows.data() + (size_t)a->owner * stride + cur[a->owner], bytes);
       cur[a->owner] += bytes;
     }
+    precompute_cuts(batch, buf, off);
     return true;
+  }
+
+  // lean path: the one cut a node can contribute depends on that node alone, so the cuts of the whole
+  // batch are built on the host worker threads before the serial loop consumes the nodes in order
+  void precompute_cuts(const std::vector<std::unique_ptr<Node>> &batch, const std::vector<double> &buf,
+                       const std::vector<size_t> &off) {
+    const double t0 = now();
+    par_for(batch.size(), [&](size_t k0, size_t k1) {
+      for (size_t k = k0; k < k1; k++) {
+        PreCut &pc = pre_cuts[k];
+        if (off[k] == npos || !pc.lean || pc.pooled == 0) continue;
+        pc.have = build_cut_gmi(batch[k]->prob, pc.j, buf.data() + off[k], pc.cut);
+      }
+    }, 4);
+    t_gen += now() - t0;
   }
 
   // root_heuristic: the root LP solution with its integer columns rounded down; feasible -> objective
@@ -744,10 +773,17 @@ bool Driver::gmi_produces(glp_prob *a, int j, const double *trow) {
 //   continuous y_k: g = a_k/f0 if a_k >= 0 else -a_k/(1-f0)
 //   sum g_k y_k >= 1, then y_k substituted back to structurals.
 void Driver::gen_cut_gmi(glp_prob *a, int j, const double *trow) {
+  Cut c;
+  if (build_cut_gmi(a, j, trow, c)) pool.push_back(std::move(c));
+}
+
+// the cut itself: reads the node, touches nothing else (the batch's cuts are built on the host
+// worker threads ahead of the serial loop, precompute_cuts)
+bool Driver::build_cut_gmi(glp_prob *a, int j, const double *trow, Cut &c) {
   int n = glp_get_num_cols(a);
   double beta = glp_get_col_prim(a, j);
   double f0 = get_fract(beta);
-  if (f0 < 1e-6 || f0 > 1.0 - 1e-6) return;
+  if (f0 < 1e-6 || f0 > 1.0 - 1e-6) return false;
   std::vector<double> g(n + 1, 0.0);  // cut over structurals, 1-based
   double rhs = 1.0;
   for (int p = 0; p < n; p++) {
@@ -755,7 +791,7 @@ void Driver::gen_cut_gmi(glp_prob *a, int j, const double *trow) {
     if (alpha == 0.0) continue;
     int v = a->nb[p], at = a->at[p];
     if (at == MVB_AT_FX) continue;
-    if (at == MVB_AT_FR) return;  // free non-basic in the row: no cut
+    if (at == MVB_AT_FR) return false;  // free non-basic in the row: no cut
     bool is_int = false;
     double bound;
     if (v < n) {
@@ -797,14 +833,15 @@ void Driver::gen_cut_gmi(glp_prob *a, int j, const double *trow) {
       }
     }
   }
-  Cut c;
+  c.inds.clear();
+  c.vals.clear();
   c.inds.reserve(n + 1);
   c.vals.reserve(n + 1);
   c.inds.push_back(0);
   c.vals.push_back(rhs);
   for (int i = 1; i <= n; i++) { c.inds.push_back(i); c.vals.push_back(g[i]); }
   c.lb = rhs;
-  pool.push_back(std::move(c));
+  return true;
 }
 
 // "-cf" (2test.cpp:135-149): whether the cut step of bs.cpp:249-258 runs at the node with this
@@ -868,7 +905,17 @@ void Driver::cut_rows_of(glp_prob *a, std::vector<int> &js, std::vector<int> &ro
 // bs.cpp:249-258: every basic GLP_IV column generates; the rows were gathered from the engine
 // tableaus of all branching candidates of the round in one call (prefetch_cut_rows), so only
 // those rows cross PCIe, once per round
-void Driver::gen_cuts(glp_prob *a, const double *t) {
+void Driver::gen_cuts(glp_prob *a, const double *t, PreCut *pre) {
+  if (pre && pre->lean) {  // everything was worked out ahead of the loop (prefetch_cut_rows / precompute_cuts)
+    pool_trim();
+    const size_t pool0 = pool.size();
+    if (pre->pooled) {
+      pool_base += pre->pooled - 1;
+      if (pre->have) pool.push_back(std::move(pre->cut));
+    }
+    if (pool.size() > pool0) add_cut_constraint(a, -1);
+    return;
+  }
   int n = glp_get_num_cols(a);
   std::vector<int> js, rows;
   cut_rows_of(a, js, rows);
@@ -1158,7 +1205,7 @@ bool Driver::run() {
           }
           const size_t rows0 = (size_t)a->nrows();
           const double tg0 = now();
-          gen_cuts(a, trows);
+          gen_cuts(a, trows, cut_off[bk] != npos && bk < pre_cuts.size() ? &pre_cuts[bk] : nullptr);
           t_gen += now() - tg0;
           // the new row goes to a's engine now (queued; all rows of the round are formed by one
           // kernel), so the children clone a tableau that already holds it
