@@ -975,6 +975,8 @@ bool Driver::run() {
   {
     // host worker threads of the per-LP loops: the ranks of a multi-GPU run share the cores
     const int hw = (int)std::thread::hardware_concurrency(), w = comm ? std::max(1, comm->world) : 1;
+    // (half the cores of a rank's share: at 8 ranks on 32 cores 2 threads per rank measured 720 k nodes/s,
+    // 4 threads 678 k -- profiles/r2_runs/r2z_n8_bench.json against r3f_n8_bench.json)
     ParPool::get().set_threads(std::max(1, std::min(4, hw / (2 * w))));
   }
   const double inf = std::numeric_limits<double>::infinity();

@@ -3,7 +3,7 @@
 // workers spin, and with one process per GPU eight ranks share the host cores.  The workers here
 // wait on a condition variable and cost nothing between two calls.  One pool per process, shared by
 // the engine and the driver (both are in the same library); created on first use (after the CLI's
-// fork), sized by par_set_threads() or MVOLPS_HOST_THREADS, default min(4, cores / 2).
+// fork), sized by set_threads() (the B&B driver: min(4, cores / (2 x ranks))) or MVOLPS_HOST_THREADS, default min(4, cores / 2).
 #pragma once
 
 #include <algorithm>
