@@ -83,6 +83,12 @@ def run_batch(args, L, rank, world, local, dist, ClockSampler, peaks):
     # the streaming kernel moves ~16*R*ld/K per pivot (K pending updates per flush pass)
     R, ld = m + 1, (n + 15) // 16 * 16
     per_lp_once = 16.0 * R * ld
+    opt = getattr(L, "mvb_engine_option", None)
+    lz_k = opt(b"last_lz_k", -1) if opt and mode == 1 else 0
+    stream = bool(opt(b"last_stream", -1)) if opt and mode == 1 else False
+    # streaming kernel: a flush pass (read + write of the tableau) every lz_k pivots, plus the pivot
+    # column (one 32-byte sector per row) and the pivot row of every pivot
+    est = piv * (per_lp_once / lz_k + 32.0 * R + 8.0 * ld) if lz_k > 0 else None
     return {
         "metric": "lp_pivots_per_sec", "value": tot_piv / (max_ms * 1e-3), "unit": "pivots/s", "n_gpus": world,
         "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": max_ms / args.steps,
@@ -94,6 +100,11 @@ def run_batch(args, L, rank, world, local, dist, ClockSampler, peaks):
         "roofline": {"bound": "hbm" if mode != 2 else "shared-memory / issue (tableau resident on chip)",
                      "algorithmic_GBs_rank0": alg / (kms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                      "min_dram_bytes_per_step_rank0": per_lp_once * len(mine),
+                     "pending_depth": lz_k, "streaming_kernel": stream,
+                     "dram_bytes_estimate_rank0": est,
+                     "dram_frac_estimate": None if est is None else est / (kms * 1e-3) / 1e9 / peak,
+                     "dram_frac_ncu": "0.57 (3.70 TB/s) on 592 LPs of 256x512, profiles/r2_stream_kernel_summary.txt"
+                                      if stream else None,
                      "note": "frac is reported from DRAM bytes (ncu capture under profiles/), never from the "
                              "algorithmic 16*R*C*pivots: lazy / on-chip updates move far fewer bytes",
                      "peak_source": src, "kernel_ms_per_launch_rank0": kms / args.steps},
