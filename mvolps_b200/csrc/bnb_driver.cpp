@@ -1065,9 +1065,14 @@ bool Driver::run() {
   out->st.split_at = -1;
   while (true) {
     if (dist && split) {     // termination is global: somebody still has open nodes
-      std::vector<double> cnt(comm->world, -inf);
+      // ONE reduction per round: the open-node counts and, in the last slot, the incumbent -- the bound
+      // test (bs.cpp:210) sees the best incumbent of all ranks
+      std::vector<double> cnt(comm->world + 1, -inf);
       cnt[comm->rank] = retired ? -1.0 : (double)open.size();
-      if (!reduce_max(cnt.data(), comm->world)) return false;
+      cnt[comm->world] = bestLower;
+      if (!reduce_max(cnt.data(), comm->world + 1)) return false;
+      if (cnt[comm->world] > bestLower) { bestLower = cnt[comm->world]; solution.clear(); out->st.has_incumbent = 0; }
+      cnt.pop_back();
       if (*std::max_element(cnt.begin(), cnt.end()) <= 0.0) break;
       if (steal) {           // work stealing: poor ranks take over open nodes of rich ones
         const auto pairs = steal_matching(cnt);
@@ -1307,10 +1312,7 @@ bool Driver::run() {
           if (!finish_fly()) return false;
           retired = true; stop = false; open.clear();
         }
-        // incumbent broadcast: the bound test (bs.cpp:210) sees the best incumbent of all ranks
-        double best = bestLower;
-        if (!reduce_max(&best, 1)) return false;
-        if (best > bestLower) { bestLower = best; solution.clear(); out->st.has_incumbent = 0; }
+        // (the incumbent travels with the open-node counts at the top of the next round)
       }
     }
   }
