@@ -26,6 +26,14 @@
 // phase needs travel in registers or in the argmin payload, never through a
 // shared location another thread may already be overwriting.
 // Phase 1 is not implemented here: such LPs are handed to simplex_kernel.
+//
+// Two instances of the loop (lz_loop<STREAM>): simplex_ps_kernel (a group of CTAs per LP or small
+// L2-resident batches: the flush pass above, up to LZ_KMAX pending pivots) and
+// simplex_ps_stream_kernel (one CTA per LP, tableaux streamed from HBM: up to LZ_KMAX_STREAM pending
+// pivots, PEELED flush passes -- the threads that own the column pair of a pending entering column
+// stay out of the streaming loop and lz_flush_qpairs re-derives those pairs afterwards, so no warp runs
+// the slow chain next to the fast one -- with the rows ahead prefetched into L2, or staged through a
+// per-thread cp.async ring where the launch has the shared memory: lz_flush_ring_k).
 #pragma once
 
 namespace {
