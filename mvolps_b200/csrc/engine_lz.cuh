@@ -527,6 +527,13 @@ __device__ __noinline__ void lz_flush_ring_k(const LZS *S) {
         for (int u = 0; u < UN; u++)
           if (iload + u * trows < ib) cp_async16(ring0 + (blk + (unsigned)u) * sstep, lsrc + rs * u);
         cp_async_commit();
+#ifdef MVB_LZ_RING_PF  // A/B: the rows MVB_LZ_RING_PF blocks beyond the ring on their way into L2: no gain
+                       // (13.8 M LP-pivots/s with and without, profiles/r2_runs/r3l_ring_prefetch_ab.txt)
+#pragma unroll
+        for (int u = 0; u < UN; u++)
+          if (iload + (UN * MVB_LZ_RING_PF + u) * trows < ib)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(lsrc + rs * (UN * MVB_LZ_RING_PF + u)));
+#endif
         iload += trows * UN;
         lsrc += rs * UN;
         bool special = qmask != 0 || i + (UN - 1) * trows >= ib;  // (a tail block takes the guarded path)
