@@ -345,6 +345,24 @@ __device__ __noinline__ void lz_flush_qpairs(const LZS *S, const Lay &l, const d
   }
 }
 
+// flush stores / loads of the streaming kernel.  A/B switch MVB_STREAM_CS: 1 = evict-first stores (the written
+// tableau is not read again before 300 MB of other tableaux have passed through L2): no change, 14.90 against
+// 14.91 M LP-pivots/s; 2 = evict-first loads as well: 14.28 M (profiles/r2_runs/r3n_evict_first_ab.txt).  Off.
+template <bool STREAMING>
+__device__ __forceinline__ void st_flush(double *p, double2 v) {
+#ifdef MVB_STREAM_CS
+  if (STREAMING) { __stcs(reinterpret_cast<double2 *>(p), v); return; }
+#endif
+  stcg2(p, v);
+}
+template <bool STREAMING>
+__device__ __forceinline__ double2 ld_flush(const double *p) {
+#if defined(MVB_STREAM_CS) && MVB_STREAM_CS > 1
+  if (STREAMING) return __ldcs(reinterpret_cast<const double2 *>(p));
+#endif
+  return ldcg2(p);
+}
+
 // PEEL (one CTA per LP): the owners of a q pair sit the loop out, lz_flush_qpairs re-derives those
 // pairs afterwards (see there).  A group of CTAs keeps them in the loop: with a dozen rows per CTA
 // and chunk the extra pass would cost a dependent L2 round trip per flush.
@@ -413,7 +431,7 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
         }
 #endif
 #pragma unroll
-        for (int u = 0; u < UN; u++) t[u] = ldcg2(src + rs * u);
+        for (int u = 0; u < UN; u++) t[u] = ld_flush<PEEL>(src + rs * u);
         // pivot rows / columns of the pending updates need the special cases
         // of lz_step; everything else is a plain fma chain
         bool special = qmask != 0;
@@ -423,16 +441,16 @@ __device__ __noinline__ void lz_flush_k(const LZS *S) {
         if (!special) {
 #pragma unroll
           for (int u = 0; u < UN; u++)
-            stcg2(dst + rs * u, lz_chain<KC, false>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, 0));
+            st_flush<PEEL>(dst + rs * u, lz_chain<KC, false>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, 0));
         } else {
 #pragma unroll
           for (int u = 0; u < UN; u++)
-            stcg2(dst + rs * u,
+            st_flush<PEEL>(dst + rs * u,
                   lz_chain<KC, true>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, i + u * trows));
         }
       }
       for (; i < ib; i += trows, src += rs, dst += rs)
-        stcg2(dst, lz_chain<KC, true>(ldcg2(src), colbase + (size_t)i * 8, mv, rh, pr, qmask, i));
+        st_flush<PEEL>(dst, lz_chain<KC, true>(ldcg2(src), colbase + (size_t)i * 8, mv, rh, pr, qmask, i));
     }
     if (PEEL) lz_flush_qpairs<KC>(S, l, Ts, Td, ia, ib, ch * CW, min(ch * CW + CW, ld));
     u0 = segend;
@@ -543,12 +561,12 @@ __device__ __noinline__ void lz_flush_ring_k(const LZS *S) {
         if (!special) {
 #pragma unroll
           for (int u = 0; u < UN; u++)
-            stcg2(dst + rs * u, lz_chain<KC, false>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, 0));
+            st_flush<true>(dst + rs * u, lz_chain<KC, false>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, 0));
         } else {
 #pragma unroll
           for (int u = 0; u < UN; u++)
             if (i + u * trows < ib)
-              stcg2(dst + rs * u,
+              st_flush<true>(dst + rs * u,
                     lz_chain<KC, true>(t[u], cb + (size_t)u * trows * 8, mv, rh, pr, qmask, i + u * trows));
         }
       }
