@@ -250,3 +250,19 @@ def test_cluster_resident_phase1_handover_batch_and_limits(oracle, product, cres
         _same(a2, d, ra2, rd)
     finally:
         product.mvb_engine_option(b"cres", 1)
+
+
+def test_free_many_on_the_device(product):
+    """mvb_lp_free_many: the slabs go back to the engine's free lists, new LPs reuse them and solve as before."""
+    import ctypes as C
+    inst = instances.mdkp(40, 10, 21)
+    ref = EngineLP.from_instance(product, inst).solve()
+    lps = [EngineLP.from_instance(product, inst) for _ in range(40)]
+    kids = [lp.clone() for lp in lps[:10]]          # queued clones keep their sources' slabs alive until the flush
+    arr = (C.c_void_p * len(lps))(*[lp.h for lp in lps])
+    product.mvb_lp_free_many(arr, len(lps))
+    for lp in lps:
+        lp.h = None
+    again = [EngineLP.from_instance(product, inst) for _ in range(40)]
+    for r in solve_batch(product, again + kids):
+        assert r["pivot_hash"] == ref["pivot_hash"] and r["obj"] == ref["obj"]
