@@ -20,6 +20,7 @@
 #include <memory>
 #include <charconv>
 #include <atomic>
+#include <future>
 #include <sstream>
 #include <type_traits>
 #include <string>
@@ -300,6 +301,7 @@ struct Driver {
     if (ps.empty()) { t_sync += t1 - t0; return true; }
     std::vector<mvb_result> res(std::max<size_t>(engs.size(), 1));
     mvb_opts o{};
+    if (!fly_wait()) return false;  // (the engine solves one batch at a time)
     if (!engs.empty() && mvb_solve_batch(engs.data(), (int)engs.size(), &o, res.data())) return false;
     out->st.solved_here += (int)engs.size();
     double t2 = now();
@@ -381,6 +383,36 @@ struct Driver {
     out->st.launches++;
     fly_ps.clear();
     return true;
+  }
+
+  // The read-back of the launch in flight (wait for the device, host mirrors, solutions into the problem
+  // objects) runs on a thread of its own while this one consumes the next round: it touches the
+  // launch's LPs and problem objects only, which nobody else looks at before fly_wait().  Whoever
+  // needs the engine for another solve, or the children themselves, calls fly_wait() first.
+  std::future<bool> fly_done;
+  bool fly_async = false, fly_ok = true;
+  std::string fly_err;
+  void fly_start() {
+    fly_ok = true;
+    if (fly_ps.empty() || getenv("MVOLPS_BNB_NO_ASYNC_PULL")) return;
+    // (a thread per launch: worth it from a few tens of thousands of solution values on -- on the closing
+    // instance, 38 values per LP, it cost 5-10 %)
+    const glp_prob *p0 = fly_ps[0];
+    if (fly_ps.size() * (size_t)(p0->nrows() + p0->ncols()) < 24576) return;
+    fly_async = true;
+    fly_done = std::async(std::launch::async, [this] {
+      const bool ok = solve_many_end();
+      if (!ok) fly_err = mvb_last_error();
+      return ok;
+    });
+  }
+  bool fly_wait() {  // idempotent; false: the read-back failed
+    if (fly_async) {
+      fly_async = false;
+      fly_ok = fly_done.get();
+      if (!fly_ok) std::fprintf(stderr, "mvb_bnb_run: read-back of a launch failed: %s\n", fly_err.c_str());
+    }
+    return fly_ok;
   }
 
   // sync mode, end of the ramp-up: owners are dealt round-robin over the open nodes; a rank gives
@@ -1017,7 +1049,8 @@ bool Driver::run() {
   auto finish_fly = [&]() -> bool {
     if (!fly.active) return true;
     fly.active = false;
-    if (!solve_many_end()) return false;
+    if (fly_async || !fly_ok) { if (!fly_wait()) return false; }
+    else if (!solve_many_end()) return false;  // (also a no-op after fly_wait: its list is empty then)
     for (size_t i = 0; i < fly.nodes.size(); i++) {
       Node *k = fly.nodes[i];
       k->upperBound = glp_get_obj_val(k->prob);
@@ -1269,6 +1302,7 @@ bool Driver::run() {
       for (auto &k : kids) ps.push_back(k.node->prob);
       if (!solve_many_begin(ps)) return false;
       fly.active = true;
+      fly_start();
       for (auto &k : kids) {
         fly.nodes.push_back(k.node.get());
         fly.slots.push_back(k.ev_slot);

@@ -1784,6 +1784,12 @@ extern "C" int mvb_solve_batch_begin(mvb_lp *const *lps, int count, const mvb_op
 
 extern "C" int mvb_solve_batch_end(mvb_result *out) {
   if (!g_plan.active) { g_err = "mvb_solve_batch_end: no batch in flight"; return -1; }
+  // (may be called from another host thread than begin -- the B&B driver reads a launch back on a
+  // thread of its own -- and the current device is per thread)
+  if (g_ctx.device >= 0) {
+    int cur = -1;
+    if (cudaGetDevice(&cur) != cudaSuccess || cur != g_ctx.device) CKI(cudaSetDevice(g_ctx.device));
+  }
   g_plan.active = false;
   if (g_plan.lps.empty()) return 0;
   if (g_plan.done) {
